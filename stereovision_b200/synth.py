@@ -1,0 +1,64 @@
+"""Deterministic synthetic stereo pairs: no webcams on the box.
+
+NumPy only.  The scene is a textured background plane plus a few fronto-parallel
+rectangles painted far-to-near, so occlusions are physically consistent; the right
+view is the left texture shifted by the per-layer disparity, plus integer noise.
+"""
+import numpy as np
+
+
+def _gauss_blur(a, sigma):
+    r = max(1, int(3 * sigma + 0.5))
+    k = np.exp(-0.5 * (np.arange(-r, r + 1) / sigma) ** 2)
+    k /= k.sum()
+    a = np.pad(a, ((r, r), (r, r)), mode="reflect")
+    a = np.apply_along_axis(lambda v: np.convolve(v, k, mode="valid"), 0, a)
+    a = np.apply_along_axis(lambda v: np.convolve(v, k, mode="valid"), 1, a)
+    return a
+
+
+def make_pair(H, W, D, seed=0, noise=6):
+    """Returns (left u8 [H,W], right u8 [H,W], true_disparity int32 [H,W])."""
+    rng = np.random.default_rng(seed)
+    pad = 2 * D
+    tex = _gauss_blur(rng.uniform(0, 255, (H, W + pad)), 1.2)
+    tex = ((tex - tex.min()) / (tex.max() - tex.min()) * 255).astype(np.uint8)
+    dB = int(rng.integers(2, max(3, D // 8) + 1))
+    layers = [(0, H, 0, W, dB, tex)]
+    for _ in range(int(rng.integers(3, 7))):
+        d = int(rng.integers(max(dB + 1, D // 8), max(dB + 2, int(0.8 * D))))
+        h, w = int(rng.integers(H // 6, H // 2)), int(rng.integers(W // 8, W // 2))
+        y0, x0 = int(rng.integers(0, H - h)), int(rng.integers(0, W - w))
+        t = _gauss_blur(rng.uniform(0, 255, (H, W + pad)), 1.2)
+        t = ((t - t.min()) / (t.max() - t.min()) * 255).astype(np.uint8)
+        layers.append((y0, y0 + h, x0, x0 + w, d, t))
+    layers.sort(key=lambda l: l[4])
+    left = np.zeros((H, W), np.uint8)
+    right = np.zeros((H, W), np.uint8)
+    disp = np.zeros((H, W), np.int32)
+    for (y0, y1, x0, x1, d, t) in layers:
+        left[y0:y1, x0:x1] = t[y0:y1, pad // 2 + x0: pad // 2 + x1]
+        disp[y0:y1, x0:x1] = d
+        xr0, xr1 = max(0, x0 - d), max(0, x1 - d)
+        if xr1 > xr0:
+            right[y0:y1, xr0:xr1] = t[y0:y1, pad // 2 + xr0 + d: pad // 2 + xr1 + d]
+    if W > dB:
+        right[:, W - dB:] = tex[:, pad // 2 + W: pad // 2 + W + dB]
+    if noise:
+        n = rng.integers(-noise, noise + 1, (H, W))
+        right = np.clip(right.astype(np.int32) + n, 0, 255).astype(np.uint8)
+    return left, right, disp
+
+
+def make_batch(B, H, W, D, seed0=0):
+    L = np.empty((B, H, W), np.uint8)
+    R = np.empty((B, H, W), np.uint8)
+    for i in range(B):
+        L[i], R[i], _ = make_pair(H, W, D, seed0 + i)
+    return L, R
+
+
+def to_bgr(gray):
+    """gray replicated x3 with per-channel gain 0.9/1.0/1.1."""
+    g = gray.astype(np.float32)
+    return np.clip(np.stack([g * 0.9, g, g * 1.1], -1), 0, 255).astype(np.uint8)

@@ -1,0 +1,122 @@
+/*
+ * svb.h -- C ABI of libsvb.so, the B200-native (sm_100a) stereo depth engine.
+ *
+ * This is the drop-in boundary for the per-frame hot path of the reference
+ * (AlexGr5/StereoVision: depth_map.py, fused_depth_map.py).  The reference has no
+ * FFI of its own: it calls the OpenCV Python bindings (cv2.*).  Each entry point
+ * below therefore names the cv2 call / reference call site it replaces; the
+ * ctypes binding a maintainer would add is shown in INTEGRATION.md and lives in
+ * stereovision_b200/_lib.py.
+ *
+ * Conventions
+ *   - plain C types only; every function returns 0 on success or a negative
+ *     svb_status; svb_last_error() gives the thread-local message.
+ *   - "*_dev" pointers are DEVICE pointers (cudaMalloc'ed / torch CUDA tensors);
+ *     work is enqueued on `stream` (a cudaStream_t passed as void*, NULL = legacy
+ *     default stream) and the call does not synchronise.
+ *   - "*_host" entry points take HOST buffers, copy in, compute, copy out and
+ *     synchronise: this is what a cv2-shaped caller (NumPy in / NumPy out) binds.
+ *   - images are dense row-major; a leading batch dimension B is always present
+ *     (B = 1 for a single pair).
+ *   - there is NO CPU fallback: without a CUDA device every call fails with
+ *     SVB_ERR_CUDA.
+ */
+#ifndef SVB_H
+#define SVB_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    SVB_OK = 0,
+    SVB_ERR_PARAM = -1,       /* what cv2 would reject with cv2.error (bad sizes, D<=0 ...) */
+    SVB_ERR_UNSUPPORTED = -2, /* valid for cv2 but outside this engine (stated in the message) */
+    SVB_ERR_CUDA = -3,        /* CUDA runtime error, no device */
+    SVB_ERR_NOMEM = -4
+} svb_status;
+
+/* cv2.STEREO_SGBM_MODE_* */
+enum { SVB_MODE_SGBM = 0, SVB_MODE_HH = 1, SVB_MODE_SGBM_3WAY = 2, SVB_MODE_HH4 = 3 };
+
+const char* svb_last_error(void);
+int svb_version(void);
+/* Select + initialise the CUDA device for the calling thread (cudaSetDevice). */
+int svb_init(int device);
+int svb_device_count(void);
+
+/* ---- cv2.StereoSGBM_create(...)  (depth_map.py:894-906, fused_depth_map.py:988-1000) */
+typedef struct {
+    int minDisparity, numDisparities, blockSize, P1, P2, disp12MaxDiff;
+    int preFilterCap, uniquenessRatio, speckleWindowSize, speckleRange, mode;
+} svb_sgbm_params;
+typedef struct svb_sgbm svb_sgbm_t;
+
+int svb_sgbm_create(const svb_sgbm_params* p, svb_sgbm_t** out);
+void svb_sgbm_destroy(svb_sgbm_t* h);
+/* Bytes of device workspace the handle will hold for this shape (grow-only, owned by the handle). */
+size_t svb_sgbm_workspace_bytes(const svb_sgbm_t* h, int B, int H, int W);
+/* Cap on the workspace; batches are processed in chunks that fit (0 = default 24 GiB). */
+int svb_sgbm_set_workspace_limit(svb_sgbm_t* h, size_t bytes);
+/* stereo.compute(left, right) -> int16 disparity x16 (depth_map.py:909, fused_depth_map.py:1004).
+ * left/right: u8 [B,H,W]; disp: s16 [B,H,W]. */
+int svb_sgbm_compute_dev(svb_sgbm_t* h, const uint8_t* left_dev, const uint8_t* right_dev,
+                         int B, int H, int W, int16_t* disp_dev, void* stream);
+int svb_sgbm_compute_host(svb_sgbm_t* h, const uint8_t* left_host, const uint8_t* right_host,
+                          int B, int H, int W, int16_t* disp_host);
+/* Test hook: copy internal stages of the LAST compute (chunk 0, image 0) to host buffers
+ * (any may be NULL).  C,S: u16 [rows,width1,D] (3WAY: kept rows only are meaningful),
+ * raw: s16 [H,W] disparity before median/speckle. */
+int svb_sgbm_debug_stages(svb_sgbm_t* h, uint16_t* C_host, uint16_t* S_host, int16_t* raw_host);
+/* Number of kernel launches issued by the last compute call (bench.py's gpu_launches). */
+int svb_sgbm_last_launches(const svb_sgbm_t* h);
+
+/* ---- cv2.StereoBM_create(numDisparities, blockSize) + setters (BASELINE config 2) */
+typedef struct {
+    int minDisparity, numDisparities, blockSize, preFilterCap, textureThreshold;
+    int uniquenessRatio, speckleWindowSize, speckleRange, disp12MaxDiff;
+} svb_bm_params;
+typedef struct svb_bm svb_bm_t;
+int svb_bm_create(const svb_bm_params* p, svb_bm_t** out);
+void svb_bm_destroy(svb_bm_t* h);
+int svb_bm_compute_dev(svb_bm_t* h, const uint8_t* left_dev, const uint8_t* right_dev,
+                       int B, int H, int W, int16_t* disp_dev, void* stream);
+int svb_bm_compute_host(svb_bm_t* h, const uint8_t* left_host, const uint8_t* right_host,
+                        int B, int H, int W, int16_t* disp_host);
+int svb_bm_last_launches(const svb_bm_t* h);
+
+/* ---- cv2.remap(src, map1 CV_16SC2, map2 CV_16UC1, INTER_LINEAR), BORDER_CONSTANT 0
+ *      (depth_map.py:815-826, fused_depth_map.py:480-491); to_gray!=0 fuses
+ *      cv2.cvtColor(BGR2GRAY) (depth_map.py:871-879) into the epilogue (C must be 3).
+ *      src u8 [B,Hs,Ws,C]; map1 s16 [Ho,Wo,2]; map2 u16 [Ho,Wo]; dst u8 [B,Ho,Wo,C] or [B,Ho,Wo]. */
+int svb_remap_u8_dev(const uint8_t* src_dev, int B, int Hs, int Ws, int C,
+                     const int16_t* map1_dev, const uint16_t* map2_dev, int Ho, int Wo,
+                     uint8_t* dst_dev, int to_gray, void* stream);
+/* cv2.cvtColor(img, COLOR_BGR2GRAY): u8 [n,3] -> u8 [n] */
+int svb_bgr2gray_dev(const uint8_t* bgr_dev, size_t npix, uint8_t* gray_dev, void* stream);
+
+/* ---- cv2.medianBlur: 3x3 on s16 (inside StereoSGBM), 5x5 on f32 (depth_map.py:912) */
+int svb_median3_s16_dev(const int16_t* src_dev, int B, int H, int W, int16_t* dst_dev, void* stream);
+int svb_median5_f32_dev(const float* src_dev, int B, int H, int W, float* dst_dev, void* stream);
+
+/* ---- cv2.filterSpeckles(img, newVal, maxSpeckleSize, maxDiff) in place on s16 [B,H,W].
+ *      labels_dev: caller scratch of B*H*W int32 (2 arrays: 2*B*H*W*4 bytes). */
+int svb_filter_speckles_s16_dev(int16_t* img_dev, int B, int H, int W, int newVal,
+                                int maxSpeckleSize, int maxDiff, int32_t* scratch_dev, void* stream);
+
+/* ---- depth_map.py:909-933 fused: disparity = s16/16 -> medianBlur 5 -> depth = fx*B/(d+1e-6),
+ *      clip [min_depth,max_depth], zero where invalid.  disp16 s16 [B,H,W] -> disparity f32, depth f32. */
+int svb_disp_to_depth_dev(const int16_t* disp16_dev, int B, int H, int W, double fx, double baseline,
+                          double min_disp, double min_depth, double max_depth,
+                          float* disparity_dev, float* depth_dev, void* stream);
+/* ---- cv2.reprojectImageTo3D(disp, Q, handleMissingValues): disp f32 or s16 [B,H,W] -> f32 [B,H,W,3].
+ *      Q_host16: 4x4 row-major doubles on the HOST; minscratch_dev: B floats (only read when
+ *      handleMissingValues != 0, may be NULL otherwise). */
+int svb_reproject3d_dev(const void* disp_dev, int is_s16, int B, int H, int W, const double* Q_host16,
+                        int handleMissingValues, float* minscratch_dev, float* out_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVB_H */

@@ -1,0 +1,16 @@
+"""stereovision_b200 -- B200-native (sm_100a) engine for the per-frame hot path of
+AlexGr5/StereoVision (depth_map.py / fused_depth_map.py), behind cv2's call surface.
+
+Hand-written CUDA behind a C ABI (include/svb.h, libsvb.so); Python + torch are plumbing.
+No CPU fallback: without the built library or a CUDA device, calls raise.
+"""
+from .cv_api import (  # noqa: F401
+    STEREO_SGBM_MODE_SGBM, STEREO_SGBM_MODE_HH, STEREO_SGBM_MODE_SGBM_3WAY, STEREO_SGBM_MODE_HH4,
+    StereoSGBM_MODE_SGBM, StereoSGBM_MODE_HH, StereoSGBM_MODE_SGBM_3WAY, StereoSGBM_MODE_HH4,
+    INTER_LINEAR, COLOR_BGR2GRAY,
+    StereoSGBM, StereoBM, StereoSGBM_create, StereoBM_create,
+    remap, cvtColor, medianBlur, filterSpeckles, reprojectImageTo3D, disparity_to_depth,
+    release_workspaces,
+)
+
+__version__ = "0.1.0"

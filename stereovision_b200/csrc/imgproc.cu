@@ -1,0 +1,383 @@
+// imgproc.cu -- the OpenCV imgproc/calib3d helpers on the reference's per-frame path,
+// as sm_100a kernels (bit-exact for integer outputs):
+//   remap (+ fused BGR2GRAY)   depth_map.py:815-826, 871-879; fused_depth_map.py:480-491, 979-984
+//   medianBlur 3 (s16) / 5 (f32)            inside StereoSGBM; depth_map.py:912
+//   filterSpeckles (connected components)   inside StereoSGBM
+//   disparity -> depth                      depth_map.py:909-933
+//   reprojectImageTo3D                      BASELINE.json (Q from depth_map.py:625)
+#include "svb_common.cuh"
+#include <float.h>
+#include <algorithm>
+
+// ---------------------------------------------------------------------------------------
+// Exact medians by forgetful selection: keep ceil(N/2)+1 candidates, repeatedly drop the
+// min and the max and take in the next sample.  Everything is unrolled so the candidates
+// stay in registers.
+// ---------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ void cex(T& a, T& b)
+{
+    T lo = a < b ? a : b, hi = a < b ? b : a;
+    a = lo; b = hi;
+}
+template <> __device__ __forceinline__ void cex<float>(float& a, float& b)
+{
+    float lo = fminf(a, b), hi = fmaxf(a, b);
+    a = lo; b = hi;
+}
+// min of v[0..N) -> v[0], max -> v[N-1]
+template <int N, typename T> __device__ __forceinline__ void minmax(T (&v)[14])
+{
+#pragma unroll
+    for (int i = 0; i < N / 2; ++i) cex(v[i], v[N - 1 - i]);
+#pragma unroll
+    for (int i = 1; i < (N + 1) / 2; ++i) cex(v[0], v[i]);
+#pragma unroll
+    for (int i = N / 2; i < N - 1; ++i) cex(v[i], v[N - 1]);
+}
+__global__ void __launch_bounds__(256) k_median3_s16(const int16_t* __restrict__ src, int H, int W,
+                                                     int16_t* __restrict__ dst)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= W) return;
+    const size_t img = (size_t)blockIdx.z * H * W;
+    int s[9];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        const int16_t* r = src + img + (size_t)min(max(y + j - 1, 0), H - 1) * W;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) s[j * 3 + i] = r[min(max(x + i - 1, 0), W - 1)];
+    }
+    int v[14];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) v[i] = s[i];
+    // 9 samples: keep 6, then 5, 4, 3
+    minmax<6>(v); v[0] = s[6];
+    minmax<5>(v); v[0] = s[7];
+    minmax<4>(v); v[0] = s[8];
+    minmax<3>(v);
+    dst[img + (size_t)y * W + x] = (int16_t)v[1];
+}
+
+// 5x5 median on f32.  FROM_S16: the source is the s16 x16 disparity and is scaled by 1/16
+// on load (exact), fusing depth_map.py:909 with :912.  DEPTH: also emit
+// depth_map.py:926-933 (depth = fxB / (d + 1e-6), clip, validity mask) in the epilogue.
+template <bool FROM_S16, bool DEPTH>
+__global__ void __launch_bounds__(256) k_median5_f32(const void* __restrict__ src_, int H, int W,
+                                                     float* __restrict__ dst, float* __restrict__ depth,
+                                                     float fxB, float min_disp, float min_depth, float max_depth)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= W) return;
+    const size_t img = (size_t)blockIdx.z * H * W;
+    float s[25];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const size_t ro = img + (size_t)min(max(y + j - 2, 0), H - 1) * W;
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            const int xx = min(max(x + i - 2, 0), W - 1);
+            if (FROM_S16) s[j * 5 + i] = (float)((const int16_t*)src_)[ro + xx] * 0.0625f;
+            else s[j * 5 + i] = ((const float*)src_)[ro + xx];
+        }
+    }
+    float v[14];
+#pragma unroll
+    for (int i = 0; i < 14; ++i) v[i] = s[i];
+    minmax<14>(v); v[0] = s[14];
+    minmax<13>(v); v[0] = s[15];
+    minmax<12>(v); v[0] = s[16];
+    minmax<11>(v); v[0] = s[17];
+    minmax<10>(v); v[0] = s[18];
+    minmax<9>(v); v[0] = s[19];
+    minmax<8>(v); v[0] = s[20];
+    minmax<7>(v); v[0] = s[21];
+    minmax<6>(v); v[0] = s[22];
+    minmax<5>(v); v[0] = s[23];
+    minmax<4>(v); v[0] = s[24];
+    minmax<3>(v);
+    const float d = v[1];
+    const size_t o = img + (size_t)y * W + x;
+    dst[o] = d;
+    if (DEPTH) {
+        // NumPy float32 semantics of depth_map.py:926-933
+        const float z = __fdiv_rn(fxB, __fadd_rn(d, 1e-6f));
+        const float zc = fminf(fmaxf(z, min_depth), max_depth);
+        const bool valid = (d > min_disp) && (zc >= min_depth) && (zc <= max_depth);
+        depth[o] = valid ? zc : 0.f;
+    }
+}
+
+extern "C" int svb_median3_s16_dev(const int16_t* src, int B, int H, int W, int16_t* dst, void* stream)
+{
+    if (!src || !dst || B <= 0 || H <= 0 || W <= 0) { svb_set_error("median3: bad argument"); return SVB_ERR_PARAM; }
+    k_median3_s16<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(src, H, W, dst);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+extern "C" int svb_median5_f32_dev(const float* src, int B, int H, int W, float* dst, void* stream)
+{
+    if (!src || !dst || B <= 0 || H <= 0 || W <= 0) { svb_set_error("median5: bad argument"); return SVB_ERR_PARAM; }
+    k_median5_f32<false, false><<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(
+        src, H, W, dst, nullptr, 0.f, 0.f, 0.f, 0.f);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+extern "C" int svb_disp_to_depth_dev(const int16_t* disp16, int B, int H, int W, double fx, double baseline,
+                                     double min_disp, double min_depth, double max_depth,
+                                     float* disparity, float* depth, void* stream)
+{
+    if (!disp16 || !disparity || !depth || B <= 0 || H <= 0 || W <= 0) {
+        svb_set_error("disp_to_depth: bad argument"); return SVB_ERR_PARAM;
+    }
+    // Python computes fx*BASELINE in double, NumPy then casts the scalar to float32
+    k_median5_f32<true, true><<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(
+        disp16, H, W, disparity, depth, (float)(fx * baseline), (float)min_disp, (float)min_depth, (float)max_depth);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// filterSpeckles = connected-component labelling (4-neighbourhood, |a-b| <= maxDiff, both
+// != newVal) + size threshold.  Union-find with atomicMin hooking (roots are the smallest
+// linear index of their component), so the outcome is deterministic.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ int ccl_find(const int32_t* label, int a)
+{
+    int p = label[a];
+    while (p != a) { a = p; p = label[a]; }
+    return a;
+}
+__device__ __forceinline__ void ccl_union(int32_t* label, int a, int b)
+{
+    while (true) {
+        a = ccl_find(label, a);
+        b = ccl_find(label, b);
+        if (a == b) return;
+        if (a < b) { int t = a; a = b; b = t; }      // a > b: hook a under b
+        const int old = atomicMin(&label[a], b);
+        if (old == a) return;
+        a = old;
+    }
+}
+__global__ void __launch_bounds__(256) k_ccl_init(const int16_t* __restrict__ img, size_t n, int newVal,
+                                                  int32_t* __restrict__ label, int32_t* __restrict__ count)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    label[i] = img[i] != newVal ? (int32_t)i : -1;
+    count[i] = 0;
+}
+__global__ void __launch_bounds__(256) k_ccl_merge(const int16_t* __restrict__ img, int H, int W, int newVal,
+                                                   int maxDiff, int32_t* __restrict__ label)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= W) return;
+    const int p = (int)(((size_t)blockIdx.z * H + y) * W + x);
+    const int v = img[p];
+    if (v == newVal) return;
+    if (x > 0) {
+        const int q = img[p - 1];
+        if (q != newVal && abs(v - q) <= maxDiff) ccl_union(label, p, p - 1);
+    }
+    if (y > 0) {
+        const int q = img[p - W];
+        if (q != newVal && abs(v - q) <= maxDiff) ccl_union(label, p, p - W);
+    }
+}
+__global__ void __launch_bounds__(256) k_ccl_count(size_t n, int32_t* __restrict__ label, int32_t* __restrict__ count)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int root = -1;
+    if (i < n && label[i] >= 0) { root = ccl_find(label, (int)i); label[i] = root; }
+    // warp-aggregated increment: one atomic per distinct root per warp
+    const unsigned peers = __match_any_sync(0xffffffffu, root);
+    if (root >= 0 && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&count[root], __popc(peers));
+}
+__global__ void __launch_bounds__(256) k_ccl_apply(int16_t* __restrict__ img, size_t n, int newVal, int maxSize,
+                                                   const int32_t* __restrict__ label, const int32_t* __restrict__ count)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int l = label[i];
+    // label[i] may still point at a non-root written before flattening finished elsewhere: chase it
+    if (l >= 0) {
+        const int root = ccl_find(label, l);
+        if (count[root] <= maxSize) img[i] = (int16_t)newVal;
+    }
+}
+
+extern "C" int svb_filter_speckles_s16_dev(int16_t* img, int B, int H, int W, int newVal, int maxSpeckleSize,
+                                           int maxDiff, int32_t* scratch, void* stream)
+{
+    if (!img || !scratch || B <= 0 || H <= 0 || W <= 0) { svb_set_error("filterSpeckles: bad argument"); return SVB_ERR_PARAM; }
+    const size_t n = (size_t)B * H * W;
+    if (n >= ((size_t)1 << 31)) { svb_set_error("filterSpeckles: batch too large for 32-bit labels"); return SVB_ERR_UNSUPPORTED; }
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t* label = scratch;
+    int32_t* count = scratch + n;
+    const int nb = svb_ceil_div(n, 256);
+    k_ccl_init<<<nb, 256, 0, st>>>(img, n, newVal, label, count);
+    SVB_LAUNCH_CHECK();
+    k_ccl_merge<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(img, H, W, newVal, maxDiff, label);
+    SVB_LAUNCH_CHECK();
+    k_ccl_count<<<nb, 256, 0, st>>>(n, label, count);
+    SVB_LAUNCH_CHECK();
+    k_ccl_apply<<<nb, 256, 0, st>>>(img, n, newVal, maxSpeckleSize, label, count);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// remap, INTER_LINEAR with fixed-point maps (A.7): src tap (sx,sy) = map1, 5+5-bit fraction
+// in map2; weights (32-fy)(32-fx)*32 ... sum to 32768; (acc + 16384) >> 15; taps outside the
+// source contribute 0.  One thread per output pixel; C = 1 or 3 interleaved channels; the
+// maps are shared by the whole batch (blockIdx.z) and stay L2-resident.
+// ---------------------------------------------------------------------------------------
+template <int C, bool GRAY>
+__global__ void __launch_bounds__(256) k_remap_u8(const uint8_t* __restrict__ src, int Hs, int Ws,
+                                                  const int16_t* __restrict__ map1, const uint16_t* __restrict__ map2,
+                                                  int Ho, int Wo, uint8_t* __restrict__ dst)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= Wo) return;
+    const size_t mo = (size_t)y * Wo + x;
+    const short2 m1 = reinterpret_cast<const short2*>(map1)[mo];
+    const int f = map2[mo] & 1023, fx = f & 31, fy = f >> 5;
+    const int sx = m1.x, sy = m1.y;
+    const int w00 = (32 - fy) * (32 - fx) * 32, w01 = (32 - fy) * fx * 32;
+    const int w10 = fy * (32 - fx) * 32, w11 = fy * fx * 32;
+    const uint8_t* img = src + (size_t)blockIdx.z * Hs * Ws * C;
+    const bool x0 = sx >= 0 && sx < Ws, x1 = sx + 1 >= 0 && sx + 1 < Ws;
+    const bool y0 = sy >= 0 && sy < Hs, y1 = sy + 1 >= 0 && sy + 1 < Hs;
+    int out[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        int acc = 16384;
+        if (y0) {
+            const uint8_t* r = img + ((size_t)sy * Ws + sx) * C + c;
+            if (x0) acc += w00 * r[0];
+            if (x1) acc += w01 * r[C];
+        }
+        if (y1) {
+            const uint8_t* r = img + ((size_t)(sy + 1) * Ws + sx) * C + c;
+            if (x0) acc += w10 * r[0];
+            if (x1) acc += w11 * r[C];
+        }
+        out[c] = min(max(acc >> 15, 0), 255);
+    }
+    const size_t o = ((size_t)blockIdx.z * Ho + y) * Wo + x;
+    if (GRAY) {
+        dst[o] = (uint8_t)((3735 * out[0] + 19235 * out[1] + 9798 * out[C - 1] + 16384) >> 15);
+    } else {
+#pragma unroll
+        for (int c = 0; c < C; ++c) dst[o * C + c] = (uint8_t)out[c];
+    }
+}
+
+extern "C" int svb_remap_u8_dev(const uint8_t* src, int B, int Hs, int Ws, int C, const int16_t* map1,
+                                const uint16_t* map2, int Ho, int Wo, uint8_t* dst, int to_gray, void* stream)
+{
+    if (!src || !map1 || !map2 || !dst || B <= 0 || Hs <= 0 || Ws <= 0 || Ho <= 0 || Wo <= 0) {
+        svb_set_error("remap: bad argument"); return SVB_ERR_PARAM;
+    }
+    if (C != 1 && C != 3) { svb_set_error("remap: channels must be 1 or 3 (got %d)", C); return SVB_ERR_UNSUPPORTED; }
+    if (to_gray && C != 3) { svb_set_error("remap: to_gray needs 3 channels"); return SVB_ERR_PARAM; }
+    dim3 grid(svb_ceil_div(Wo, 256), Ho, B);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (C == 1) k_remap_u8<1, false><<<grid, 256, 0, st>>>(src, Hs, Ws, map1, map2, Ho, Wo, dst);
+    else if (to_gray) k_remap_u8<3, true><<<grid, 256, 0, st>>>(src, Hs, Ws, map1, map2, Ho, Wo, dst);
+    else k_remap_u8<3, false><<<grid, 256, 0, st>>>(src, Hs, Ws, map1, map2, Ho, Wo, dst);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// BGR -> gray (A.8), 4 pixels per thread where possible
+__global__ void __launch_bounds__(256) k_bgr2gray(const uint8_t* __restrict__ bgr, size_t n, uint8_t* __restrict__ gray)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint8_t* p = bgr + 3 * i;
+    gray[i] = (uint8_t)((3735 * p[0] + 19235 * p[1] + 9798 * p[2] + 16384) >> 15);
+}
+extern "C" int svb_bgr2gray_dev(const uint8_t* bgr, size_t npix, uint8_t* gray, void* stream)
+{
+    if (!bgr || !gray || npix == 0) { svb_set_error("bgr2gray: bad argument"); return SVB_ERR_PARAM; }
+    k_bgr2gray<<<svb_ceil_div(npix, 256), 256, 0, (cudaStream_t)stream>>>(bgr, npix, gray);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// reprojectImageTo3D: [X Y Z W]^T = Q [x y d 1]^T, out = (X,Y,Z)/W, double accumulate.
+// handleMissingValues: Z = 10000 where d equals the image's minimum disparity.
+// ---------------------------------------------------------------------------------------
+struct QMat { double q[16]; };
+template <bool S16> __device__ __forceinline__ float load_disp(const void* p, size_t i)
+{
+    return S16 ? (float)((const int16_t*)p)[i] : ((const float*)p)[i];
+}
+template <bool S16>
+__global__ void __launch_bounds__(256) k_min_per_image(const void* __restrict__ disp, size_t npix, float* __restrict__ minv)
+{
+    // minv[b] pre-set to +inf bit pattern; non-negative-float trick does not hold for negative
+    // disparities, so reduce in a block and finish with an integer CAS-free ordered-int atomic.
+    const size_t base = (size_t)blockIdx.y * npix;
+    float m = FLT_MAX;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (size_t)gridDim.x * blockDim.x)
+        m = fminf(m, load_disp<S16>(disp, base + i));
+    for (int o = 16; o; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) {
+        // order-preserving map float -> int for atomicMin
+        int bits = __float_as_int(m);
+        bits = bits >= 0 ? bits : bits ^ 0x7fffffff;
+        atomicMin(reinterpret_cast<int*>(minv) + blockIdx.y, bits);
+    }
+}
+template <bool S16>
+__global__ void __launch_bounds__(256) k_reproject(const void* __restrict__ disp, int H, int W, QMat Q, int handle,
+                                                   const float* __restrict__ minv, float* __restrict__ out)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= W) return;
+    const size_t i = ((size_t)blockIdx.z * H + y) * W + x;
+    const double d = load_disp<S16>(disp, i);
+    const double X = Q.q[0] * x + Q.q[1] * y + Q.q[2] * d + Q.q[3];
+    const double Y = Q.q[4] * x + Q.q[5] * y + Q.q[6] * d + Q.q[7];
+    double Z = Q.q[8] * x + Q.q[9] * y + Q.q[10] * d + Q.q[11];
+    const double Wd = Q.q[12] * x + Q.q[13] * y + Q.q[14] * d + Q.q[15];
+    const double iw = 1.0 / Wd;
+    float zf = (float)(Z * iw);
+    if (handle) {
+        int bits = reinterpret_cast<const int*>(minv)[blockIdx.z];
+        bits = bits >= 0 ? bits : bits ^ 0x7fffffff;
+        if (fabs(d - (double)__int_as_float(bits)) <= FLT_EPSILON) zf = 10000.f;
+    }
+    out[3 * i] = (float)(X * iw);
+    out[3 * i + 1] = (float)(Y * iw);
+    out[3 * i + 2] = zf;
+}
+__global__ void k_fill_i32(int* p, int n, int v) { int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) p[i] = v; }
+
+extern "C" int svb_reproject3d_dev(const void* disp, int is_s16, int B, int H, int W, const double* Q16,
+                                   int handleMissingValues, float* minscratch_dev, float* out, void* stream)
+{
+    if (!disp || !Q16 || !out || B <= 0 || H <= 0 || W <= 0) { svb_set_error("reproject3d: bad argument"); return SVB_ERR_PARAM; }
+    if (handleMissingValues && !minscratch_dev) { svb_set_error("reproject3d: handleMissingValues needs B floats of scratch"); return SVB_ERR_PARAM; }
+    QMat Q;
+    for (int i = 0; i < 16; ++i) Q.q[i] = Q16[i];
+    cudaStream_t st = (cudaStream_t)stream;
+    if (handleMissingValues) {
+        k_fill_i32<<<svb_ceil_div(B, 256), 256, 0, st>>>((int*)minscratch_dev, B, 0x7f7fffff);
+        dim3 g(std::min(svb_ceil_div((size_t)H * W, 1024), 512), B);
+        if (is_s16) k_min_per_image<true><<<g, 256, 0, st>>>(disp, (size_t)H * W, minscratch_dev);
+        else k_min_per_image<false><<<g, 256, 0, st>>>(disp, (size_t)H * W, minscratch_dev);
+        SVB_LAUNCH_CHECK();
+    }
+    dim3 grid(svb_ceil_div(W, 256), H, B);
+    if (is_s16) k_reproject<true><<<grid, 256, 0, st>>>(disp, H, W, Q, handleMissingValues, minscratch_dev, out);
+    else k_reproject<false><<<grid, 256, 0, st>>>(disp, H, W, Q, handleMissingValues, minscratch_dev, out);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}

@@ -1,0 +1,370 @@
+"""OpenCV-shaped surface of the engine: the calls the reference makes on its per-frame
+path, with cv2's names, argument order and error behaviour, running on libsvb.so.
+
+    cv2.StereoSGBM_create(...).compute   depth_map.py:894-909, fused_depth_map.py:988-1004
+    cv2.StereoBM_create(...).compute     BASELINE.json config 2
+    cv2.remap / cv2.cvtColor             depth_map.py:815-826, 871-879
+    cv2.medianBlur / cv2.filterSpeckles  depth_map.py:912; inside StereoSGBM
+    cv2.reprojectImageTo3D               BASELINE.json (Q from depth_map.py:625)
+
+Inputs may be NumPy arrays (host: copied in and out, exactly what the reference passes)
+or torch CUDA tensors (zero-copy, results stay on the device, work is enqueued on the
+current torch stream).  Every function also accepts a leading batch dimension.
+"""
+import ctypes
+import threading
+
+import numpy as np
+
+from . import _lib
+
+STEREO_SGBM_MODE_SGBM = 0
+STEREO_SGBM_MODE_HH = 1
+STEREO_SGBM_MODE_SGBM_3WAY = 2
+STEREO_SGBM_MODE_HH4 = 3
+StereoSGBM_MODE_SGBM, StereoSGBM_MODE_HH = 0, 1
+StereoSGBM_MODE_SGBM_3WAY, StereoSGBM_MODE_HH4 = 2, 3
+INTER_LINEAR = 1
+COLOR_BGR2GRAY = 6
+
+_tls = threading.local()
+_pool_lock = threading.Lock()
+_pool = {}  # (thread, device, kind, params) -> handle
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def _is_tensor(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _ensure_device(device=None):
+    """cudaSetDevice for the calling thread (the reference calls from a pool thread,
+    fused_depth_map.py:2591)."""
+    torch = _torch()
+    if device is None:
+        device = torch.cuda.current_device() if torch.cuda.is_available() else 0
+    if getattr(_tls, "device", None) != device:
+        _lib.check(_lib.lib().svb_init(int(device)))
+        _tls.device = device
+    return device
+
+
+def _stream_ptr():
+    torch = _torch()
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _handle(kind, params, device):
+    key = (threading.get_ident(), device, kind, params)
+    with _pool_lock:
+        h = _pool.get(key)
+    if h is None:
+        L = _lib.lib()
+        out = ctypes.c_void_p()
+        if kind == "sgbm":
+            prm = _lib.SgbmParams(*params)
+            _lib.check(L.svb_sgbm_create(ctypes.byref(prm), ctypes.byref(out)))
+        else:
+            prm = _lib.BmParams(*params)
+            _lib.check(L.svb_bm_create(ctypes.byref(prm), ctypes.byref(out)))
+        h = out
+        with _pool_lock:
+            _pool[key] = h
+    return h
+
+
+def release_workspaces():
+    """Free every cached matcher handle (device workspaces)."""
+    L = _lib.lib()
+    with _pool_lock:
+        for (_, _, kind, _), h in _pool.items():
+            (L.svb_sgbm_destroy if kind == "sgbm" else L.svb_bm_destroy)(h)
+        _pool.clear()
+
+
+def _check_pair(left, right):
+    if _is_tensor(left) != _is_tensor(right):
+        raise ValueError("left and right must both be NumPy arrays or both torch tensors")
+    if tuple(left.shape) != tuple(right.shape):
+        raise ValueError(f"left and right must have the same size: {tuple(left.shape)} vs {tuple(right.shape)}")
+    if left.ndim not in (2, 3):
+        raise ValueError("expected [H,W] or [B,H,W] single-channel 8-bit images")
+    if _is_tensor(left):
+        torch = _torch()
+        if left.dtype != torch.uint8 or right.dtype != torch.uint8:
+            raise ValueError("images must be 8-bit (CV_8U)")
+        if not left.is_cuda:
+            raise ValueError("torch inputs must be CUDA tensors (use NumPy for host data)")
+    else:
+        if left.dtype != np.uint8 or right.dtype != np.uint8:
+            raise ValueError("images must be 8-bit (CV_8U)")
+
+
+class _Matcher:
+    _kind = None
+
+    def _params(self):
+        raise NotImplementedError
+
+    def compute(self, left, right):
+        """disparity = matcher.compute(left, right) -> int16 (x16 fixed point), same shape."""
+        _check_pair(left, right)
+        L = _lib.lib()
+        batched = left.ndim == 3
+        B = left.shape[0] if batched else 1
+        H, W = left.shape[-2], left.shape[-1]
+        host_fn = L.svb_sgbm_compute_host if self._kind == "sgbm" else L.svb_bm_compute_host
+        dev_fn = L.svb_sgbm_compute_dev if self._kind == "sgbm" else L.svb_bm_compute_dev
+        if _is_tensor(left):
+            torch = _torch()
+            dev = _ensure_device(left.device.index)
+            h = _handle(self._kind, self._params(), dev)
+            l, r = left.contiguous(), right.contiguous()
+            out = torch.empty(left.shape, dtype=torch.int16, device=left.device)
+            _lib.check(dev_fn(h, l.data_ptr(), r.data_ptr(), B, H, W, out.data_ptr(), _stream_ptr()))
+            self._last = h
+            return out
+        dev = _ensure_device()
+        h = _handle(self._kind, self._params(), dev)
+        l = np.ascontiguousarray(left)
+        r = np.ascontiguousarray(right)
+        out = np.empty(left.shape, np.int16)
+        _lib.check(host_fn(h, l.ctypes.data, r.ctypes.data, B, H, W, out.ctypes.data))
+        self._last = h
+        return out
+
+    def last_launches(self):
+        L = _lib.lib()
+        h = getattr(self, "_last", None)
+        if h is None:
+            return 0
+        return (L.svb_sgbm_last_launches if self._kind == "sgbm" else L.svb_bm_last_launches)(h)
+
+
+class StereoSGBM(_Matcher):
+    """Parameter holder, cheap to construct every frame as the reference does
+    (depth_map.py:894); device workspaces live in a module-level pool."""
+    _kind = "sgbm"
+    _names = ("minDisparity", "numDisparities", "blockSize", "P1", "P2", "disp12MaxDiff",
+              "preFilterCap", "uniquenessRatio", "speckleWindowSize", "speckleRange", "mode")
+
+    def __init__(self, minDisparity=0, numDisparities=16, blockSize=3, P1=0, P2=0, disp12MaxDiff=0,
+                 preFilterCap=0, uniquenessRatio=0, speckleWindowSize=0, speckleRange=0,
+                 mode=STEREO_SGBM_MODE_SGBM):
+        for n in self._names:
+            setattr(self, "_" + n, int(locals()[n]))
+
+    def _params(self):
+        return tuple(getattr(self, "_" + n) for n in self._names)
+
+    def debug_stages(self, H, W):
+        """Test hook: (C, S, raw) of image 0 of the last compute as NumPy arrays."""
+        L = _lib.lib()
+        D, minD = self._numDisparities, self._minDisparity
+        w1 = W + min(minD, 0) - max(minD + D, 0)
+        C = np.zeros((H, w1, D), np.uint16)
+        S = np.zeros((H, w1, D), np.uint16)
+        raw = np.zeros((H, W), np.int16)
+        _lib.check(L.svb_sgbm_debug_stages(self._last, C.ctypes.data, S.ctypes.data, raw.ctypes.data))
+        return C, S, raw
+
+
+def _add_accessors(cls, names):
+    for n in names:
+        cap = n[0].upper() + n[1:]
+        setattr(cls, "get" + cap, (lambda n: lambda self: getattr(self, "_" + n))(n))
+        setattr(cls, "set" + cap, (lambda n: lambda self, v: setattr(self, "_" + n, int(v)))(n))
+
+
+_add_accessors(StereoSGBM, StereoSGBM._names)
+
+
+def StereoSGBM_create(minDisparity=0, numDisparities=16, blockSize=3, P1=0, P2=0, disp12MaxDiff=0,
+                      preFilterCap=0, uniquenessRatio=0, speckleWindowSize=0, speckleRange=0,
+                      mode=STEREO_SGBM_MODE_SGBM):
+    """cv2.StereoSGBM_create with cv2's positional order and defaults."""
+    return StereoSGBM(minDisparity, numDisparities, blockSize, P1, P2, disp12MaxDiff, preFilterCap,
+                      uniquenessRatio, speckleWindowSize, speckleRange, mode)
+
+
+class StereoBM(_Matcher):
+    """cv2.StereoBM_create(numDisparities=0 -> 64, blockSize=21) with cv2's defaults
+    (preFilterCap 31, textureThreshold 10, uniquenessRatio 15, X-Sobel prefilter)."""
+    _kind = "bm"
+    _names = ("minDisparity", "numDisparities", "blockSize", "preFilterCap", "textureThreshold",
+              "uniquenessRatio", "speckleWindowSize", "speckleRange", "disp12MaxDiff")
+
+    def __init__(self, numDisparities=0, blockSize=21):
+        self._minDisparity = 0
+        self._numDisparities = int(numDisparities) if numDisparities > 0 else 64
+        self._blockSize = int(blockSize)
+        self._preFilterCap = 31
+        self._textureThreshold = 10
+        self._uniquenessRatio = 15
+        self._speckleWindowSize = 0
+        self._speckleRange = 0
+        self._disp12MaxDiff = -1
+
+    def _params(self):
+        return tuple(getattr(self, "_" + n) for n in self._names)
+
+
+_add_accessors(StereoBM, StereoBM._names)
+
+
+def StereoBM_create(numDisparities=0, blockSize=21):
+    return StereoBM(numDisparities, blockSize)
+
+
+# --------------------------------------------------------------------------------------
+# imgproc / calib3d helpers
+# --------------------------------------------------------------------------------------
+def _to_dev(a, dtype=None):
+    """NumPy -> CUDA tensor (plumbing only); tensors pass through."""
+    torch = _torch()
+    if _is_tensor(a):
+        if not a.is_cuda:
+            raise ValueError("torch inputs must be CUDA tensors")
+        return a.contiguous(), True
+    if not torch.cuda.is_available():
+        raise _lib.SvbError("no CUDA device available; stereovision_b200 has no CPU fallback")
+    t = torch.from_numpy(np.ascontiguousarray(a if dtype is None else a.astype(dtype, copy=False)))
+    return t.cuda(non_blocking=False), False
+
+
+def _ret(t, was_tensor):
+    return t if was_tensor else t.cpu().numpy()
+
+
+def remap(src, map1, map2, interpolation=INTER_LINEAR, to_gray=False):
+    """cv2.remap(src, map1, map2, cv2.INTER_LINEAR) for the fixed-point maps the reference
+    builds with initUndistortRectifyMap(..., CV_16SC2) (depth_map.py:633-638, 815-826).
+    src: u8 [H,W], [H,W,3], or batched [B,H,W(,3)].  to_gray=True additionally applies
+    cv2.cvtColor(BGR2GRAY) to the remapped image (depth_map.py:871-879) in the same kernel."""
+    if interpolation != INTER_LINEAR:
+        raise NotImplementedError("only INTER_LINEAR is on the reference's path")
+    torch = _torch()
+    m1, _ = _to_dev(map1)
+    m2, _ = _to_dev(map2)
+    if m1.dtype != torch.int16 or m1.ndim != 3 or m1.shape[2] != 2 or m2.dtype not in (torch.uint16, torch.int16):
+        raise ValueError("maps must be CV_16SC2 [H,W,2] int16 + CV_16UC1 [H,W] uint16")
+    s, was = _to_dev(src)
+    if s.dtype != torch.uint8:
+        raise ValueError("src must be 8-bit")
+    Ho, Wo = int(m2.shape[0]), int(m2.shape[1])
+    # layouts: [H,W] [H,W,3] [B,H,W] [B,H,W,3]; a trailing dim of 3 means channels
+    if s.ndim == 2:
+        B, C, batched = 1, 1, False
+    elif s.ndim == 3 and s.shape[-1] == 3:
+        B, C, batched = 1, 3, False
+    elif s.ndim == 3:
+        B, C, batched = int(s.shape[0]), 1, True
+    elif s.ndim == 4 and s.shape[-1] == 3:
+        B, C, batched = int(s.shape[0]), 3, True
+    else:
+        raise ValueError(f"unsupported src shape {tuple(s.shape)}")
+    Hs, Ws = (int(s.shape[1]), int(s.shape[2])) if batched else (int(s.shape[0]), int(s.shape[1]))
+    dev = _ensure_device(s.device.index)
+    oshape = ([B] if batched else []) + [Ho, Wo] + ([3] if (C == 3 and not to_gray) else [])
+    out = torch.empty(oshape, dtype=torch.uint8, device=s.device)
+    _lib.check(_lib.lib().svb_remap_u8_dev(s.data_ptr(), B, Hs, Ws, C, m1.data_ptr(), m2.data_ptr(), Ho, Wo,
+                                           out.data_ptr(), int(bool(to_gray)), _stream_ptr()))
+    return _ret(out, was)
+
+
+def cvtColor(src, code=COLOR_BGR2GRAY):
+    """cv2.cvtColor(img, cv2.COLOR_BGR2GRAY) (depth_map.py:871-879)."""
+    if code != COLOR_BGR2GRAY:
+        raise NotImplementedError("only COLOR_BGR2GRAY is on the reference's path")
+    torch = _torch()
+    s, was = _to_dev(src)
+    if s.dtype != torch.uint8 or s.shape[-1] != 3:
+        raise ValueError("expected 8-bit BGR [...,3]")
+    _ensure_device(s.device.index)
+    out = torch.empty(s.shape[:-1], dtype=torch.uint8, device=s.device)
+    _lib.check(_lib.lib().svb_bgr2gray_dev(s.data_ptr(), out.numel(), out.data_ptr(), _stream_ptr()))
+    return _ret(out, was)
+
+
+def medianBlur(src, ksize):
+    """cv2.medianBlur: ksize 3 on int16 (as inside StereoSGBM) or 5 on float32 (depth_map.py:912)."""
+    torch = _torch()
+    s, was = _to_dev(src)
+    if s.ndim not in (2, 3):
+        raise ValueError("expected [H,W] or [B,H,W]")
+    B = 1 if s.ndim == 2 else int(s.shape[0])
+    H, W = int(s.shape[-2]), int(s.shape[-1])
+    _ensure_device(s.device.index)
+    out = torch.empty_like(s)
+    L = _lib.lib()
+    if ksize == 3 and s.dtype == torch.int16:
+        _lib.check(L.svb_median3_s16_dev(s.data_ptr(), B, H, W, out.data_ptr(), _stream_ptr()))
+    elif ksize == 5 and s.dtype == torch.float32:
+        _lib.check(L.svb_median5_f32_dev(s.data_ptr(), B, H, W, out.data_ptr(), _stream_ptr()))
+    else:
+        raise NotImplementedError("medianBlur: only (ksize=3, int16) and (ksize=5, float32) are on the path")
+    return _ret(out, was)
+
+
+def filterSpeckles(img, newVal, maxSpeckleSize, maxDiff):
+    """cv2.filterSpeckles(img, newVal, maxSpeckleSize, maxDiff) on int16; returns the filtered
+    image (tensors are modified in place like cv2 does, NumPy inputs get a filtered copy back
+    AND are updated in place to keep cv2's in-place contract)."""
+    torch = _torch()
+    s, was = _to_dev(img)
+    if s.dtype != torch.int16 or s.ndim not in (2, 3):
+        raise ValueError("expected int16 [H,W] or [B,H,W]")
+    B = 1 if s.ndim == 2 else int(s.shape[0])
+    H, W = int(s.shape[-2]), int(s.shape[-1])
+    _ensure_device(s.device.index)
+    scratch = torch.empty(2 * s.numel(), dtype=torch.int32, device=s.device)
+    _lib.check(_lib.lib().svb_filter_speckles_s16_dev(s.data_ptr(), B, H, W, int(newVal), int(maxSpeckleSize),
+                                                      int(maxDiff), scratch.data_ptr(), _stream_ptr()))
+    if was:
+        return s
+    out = s.cpu().numpy()
+    img[...] = out
+    return img
+
+
+def reprojectImageTo3D(disparity, Q, handleMissingValues=False):
+    """cv2.reprojectImageTo3D(disparity, Q): int16 input is NOT divided by 16."""
+    torch = _torch()
+    d, was = _to_dev(disparity)
+    if d.dtype not in (torch.int16, torch.float32) or d.ndim not in (2, 3):
+        raise ValueError("disparity must be int16 or float32, [H,W] or [B,H,W]")
+    Qh = np.ascontiguousarray(Q.detach().cpu().numpy() if _is_tensor(Q) else Q, dtype=np.float64)
+    if Qh.shape != (4, 4):
+        raise ValueError("Q must be 4x4")
+    B = 1 if d.ndim == 2 else int(d.shape[0])
+    H, W = int(d.shape[-2]), int(d.shape[-1])
+    _ensure_device(d.device.index)
+    out = torch.empty(tuple(d.shape) + (3,), dtype=torch.float32, device=d.device)
+    scratch = torch.empty(B, dtype=torch.float32, device=d.device)
+    _lib.check(_lib.lib().svb_reproject3d_dev(
+        d.data_ptr(), int(d.dtype == torch.int16), B, H, W, Qh.ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
+        int(bool(handleMissingValues)), scratch.data_ptr(), out.data_ptr(), _stream_ptr()))
+    return _ret(out, was)
+
+
+def disparity_to_depth(disp16, fx=700.0, baseline=0.08, min_disp=0.0, min_depth=0.3, max_depth=2.0):
+    """The tail of depth_map.create_depth_map (depth_map.py:909-933) in one kernel:
+    disparity = disp16/16 -> medianBlur 5 -> depth = fx*B/(d+1e-6), clip, validity mask.
+    Returns (depth_final f32, disparity f32)."""
+    torch = _torch()
+    d, was = _to_dev(disp16)
+    if d.dtype != torch.int16 or d.ndim not in (2, 3):
+        raise ValueError("disp16 must be int16 [H,W] or [B,H,W]")
+    B = 1 if d.ndim == 2 else int(d.shape[0])
+    H, W = int(d.shape[-2]), int(d.shape[-1])
+    _ensure_device(d.device.index)
+    disparity = torch.empty(d.shape, dtype=torch.float32, device=d.device)
+    depth = torch.empty(d.shape, dtype=torch.float32, device=d.device)
+    _lib.check(_lib.lib().svb_disp_to_depth_dev(d.data_ptr(), B, H, W, float(fx), float(baseline), float(min_disp),
+                                                float(min_depth), float(max_depth), disparity.data_ptr(),
+                                                depth.data_ptr(), _stream_ptr()))
+    return _ret(depth, was), _ret(disparity, was)

@@ -1,0 +1,62 @@
+"""Generates tests/golden/*.npz with the reference's own arithmetic: live OpenCV
+(opencv-python-headless 4.13.0.92), the third-party dependency the reference calls on its
+per-frame path (depth_map.py:815-826, 871-912; BASELINE.json's StereoBM / reprojectImageTo3D).
+Inputs are re-created in the tests from seeds (stereovision_b200.synth); only parameters and
+cv2's outputs are stored.  Run from the repo root:  python tests/golden/make_golden.py
+"""
+import os
+import sys
+
+import cv2
+import numpy as np
+
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", ".."))
+from stereovision_b200.synth import make_pair, to_bgr  # noqa: E402
+from tests.golden_cases import SGBM_CASES, BM_CASES, synth_calibration  # noqa: E402
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def main():
+    out = {"cv2_version": np.array(cv2.__version__)}
+    for i, c in enumerate(SGBM_CASES):
+        l, r, _ = make_pair(c["H"], c["W"], max(c["prm"]["numDisparities"], 16), seed=c["seed"])
+        out[f"sgbm_{i}"] = cv2.StereoSGBM_create(**c["prm"]).compute(l, r)
+    for i, c in enumerate(BM_CASES):
+        l, r, _ = make_pair(c["H"], c["W"], max(c["numDisparities"], 16), seed=c["seed"])
+        bm = cv2.StereoBM_create(c["numDisparities"], c["blockSize"])
+        for k, v in c.get("set", {}).items():
+            getattr(bm, "set" + k)(v)
+        out[f"bm_{i}"] = bm.compute(l, r)
+    # remap + gray with maps from the reference's own recipe (depth_map.py:625-638)
+    H, W = 120, 160
+    calib = synth_calibration(W, H)
+    l, r, _ = make_pair(H, W, 16, seed=7)
+    bgr = to_bgr(l)
+    out["remap_map1"], out["remap_map2"] = calib["left_map1"], calib["left_map2"]
+    out["remap_bgr"] = cv2.remap(bgr, calib["left_map1"], calib["left_map2"], cv2.INTER_LINEAR)
+    out["remap_gray"] = cv2.remap(l, calib["left_map1"], calib["left_map2"], cv2.INTER_LINEAR)
+    out["gray"] = cv2.cvtColor(bgr, cv2.COLOR_BGR2GRAY)
+    out["Q"] = calib["Q"]
+    # median / speckle / reproject on a cv2 disparity
+    prm = SGBM_CASES[0]["prm"]
+    l0, r0, _ = make_pair(SGBM_CASES[0]["H"], SGBM_CASES[0]["W"], 16, seed=SGBM_CASES[0]["seed"])
+    d16 = cv2.StereoSGBM_create(**{**prm, "speckleWindowSize": 0}).compute(l0, r0)
+    out["med3_in"] = d16
+    out["med3"] = cv2.medianBlur(d16, 3)
+    f = d16.astype(np.float32) / 16.0
+    out["med5"] = cv2.medianBlur(f, 5)
+    sp = d16.copy()
+    cv2.filterSpeckles(sp, (prm["minDisparity"] - 1) * 16, 40, 16)
+    out["speckle"] = sp
+    Hh, Ww = d16.shape
+    Q = synth_calibration(Ww, Hh)["Q"]
+    out["Q2"] = Q
+    out["reproj_s16"] = cv2.reprojectImageTo3D(d16, Q)
+    out["reproj_f32"] = cv2.reprojectImageTo3D(f, Q, handleMissingValues=True)
+    np.savez_compressed(os.path.join(HERE, "golden.npz"), **out)
+    print("wrote", os.path.join(HERE, "golden.npz"), os.path.getsize(os.path.join(HERE, "golden.npz")), "bytes")
+
+
+if __name__ == "__main__":
+    main()

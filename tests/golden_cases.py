@@ -1,0 +1,53 @@
+"""Case tables shared by tests/golden/make_golden.py (which runs cv2) and the tests (which
+must not need cv2 or /root/reference)."""
+import numpy as np
+
+MODE_SGBM, MODE_HH, MODE_3WAY = 0, 1, 2
+
+
+def _p(minD, D, bs, mode, uniq=10, spw=100, spr=32, d12=1, cap=63, p1=None, p2=None):
+    return dict(minDisparity=minD, numDisparities=D, blockSize=bs,
+                P1=8 * bs * bs if p1 is None else p1, P2=32 * bs * bs if p2 is None else p2,
+                disp12MaxDiff=d12, preFilterCap=cap, uniquenessRatio=uniq,
+                speckleWindowSize=spw, speckleRange=spr, mode=mode)
+
+
+SGBM_CASES = [
+    dict(H=60, W=96, seed=11, prm=_p(0, 16, 3, MODE_SGBM)),
+    dict(H=72, W=130, seed=12, prm=_p(0, 32, 5, MODE_SGBM, spw=50, spr=2)),
+    dict(H=64, W=141, seed=13, prm=_p(0, 64, 5, MODE_HH)),
+    dict(H=81, W=131, seed=14, prm=_p(0, 48, 7, MODE_3WAY)),
+    dict(H=66, W=110, seed=15, prm=_p(-8, 32, 3, MODE_SGBM, uniq=5, spw=0)),
+    dict(H=70, W=120, seed=16, prm=_p(4, 32, 5, MODE_HH, uniq=15, d12=2, cap=31)),
+    dict(H=57, W=200, seed=17, prm=_p(0, 128, 5, MODE_SGBM)),
+    dict(H=48, W=120, seed=18, prm=_p(0, 80, 7, MODE_3WAY, uniq=0, spw=0)),     # D not a power of two
+    dict(H=64, W=100, seed=19, prm=_p(0, 32, 9, MODE_SGBM, p1=1944, p2=7776)),   # S saturates at 32767
+    dict(H=40, W=400, seed=20, prm=_p(0, 320, 7, MODE_3WAY)),                    # the reference's own D / bs
+]
+
+BM_CASES = [
+    dict(H=60, W=120, seed=31, numDisparities=16, blockSize=9),
+    dict(H=72, W=150, seed=32, numDisparities=64, blockSize=15),
+    dict(H=65, W=131, seed=33, numDisparities=32, blockSize=21),
+    dict(H=64, W=128, seed=34, numDisparities=32, blockSize=7, set={"MinDisparity": -4, "UniquenessRatio": 0}),
+    dict(H=64, W=140, seed=35, numDisparities=48, blockSize=11,
+         set={"TextureThreshold": 50, "SpeckleWindowSize": 30, "SpeckleRange": 4}),
+]
+
+
+def synth_calibration(W, H):
+    """Synthetic stereo calibration turned into rectification maps with the
+    reference's own recipe (depth_map.py:613-638).  Needs cv2: only the golden generator and
+    cv2-gated tests call this."""
+    import cv2
+    fx = 0.78 * W
+    K = np.array([[fx, 0, W / 2 + 3], [0, fx, H / 2 - 2], [0, 0, 1]], np.float64)
+    dl = np.array([-0.10, 0.02, 1e-3, -1e-3, 0], np.float64)
+    dr = np.array([-0.09, 0.015, -1e-3, 1e-3, 0], np.float64)
+    R, _ = cv2.Rodrigues(np.array([0.01, -0.02, 0.005]))
+    T = np.array([[-6.0], [0.05], [0.02]])
+    R1, R2, P1, P2, Q, _, _ = cv2.stereoRectify(K, dl, K, dr, (W, H), R, T, alpha=0)
+    m1l, m2l = cv2.initUndistortRectifyMap(K, dl, R1, P1, (W, H), cv2.CV_16SC2)
+    m1r, m2r = cv2.initUndistortRectifyMap(K, dr, R2, P2, (W, H), cv2.CV_16SC2)
+    return dict(mtx_left=K, dist_left=dl, mtx_right=K, dist_right=dr, R=R, T=T, img_size=(W, H),
+                left_map1=m1l, left_map2=m2l, right_map1=m1r, right_map2=m2r, Q=Q)

@@ -1,0 +1,80 @@
+"""GPU: remap / gray / median / speckle / depth / reproject kernels against the oracle and
+the cv2-made golden vectors."""
+import numpy as np
+import pytest
+
+import oracle
+import stereovision_b200 as svb
+from stereovision_b200.synth import make_pair, to_bgr
+from tests.golden_cases import SGBM_CASES
+
+pytestmark = pytest.mark.gpu
+
+
+def test_remap_and_gray_bit_exact(golden):
+    l, _, _ = make_pair(120, 160, 16, seed=7)
+    bgr = to_bgr(l)
+    m1, m2 = golden["remap_map1"], golden["remap_map2"]
+    assert np.array_equal(svb.remap(bgr, m1, m2, svb.INTER_LINEAR), golden["remap_bgr"])
+    assert np.array_equal(svb.remap(l, m1, m2, svb.INTER_LINEAR), golden["remap_gray"])
+    assert np.array_equal(svb.cvtColor(bgr, svb.COLOR_BGR2GRAY), golden["gray"])
+    fused = svb.remap(bgr, m1, m2, svb.INTER_LINEAR, to_gray=True)
+    assert np.array_equal(fused, oracle.bgr2gray(golden["remap_bgr"]))
+    # batched, and maps that point outside the source (BORDER_CONSTANT 0)
+    rng = np.random.default_rng(3)
+    src = rng.integers(0, 256, (3, 50, 70, 3), dtype=np.uint8)
+    mm1 = rng.integers(-5, 75, (40, 60, 2)).astype(np.int16)
+    mm2 = rng.integers(0, 1024, (40, 60)).astype(np.uint16)
+    out = svb.remap(src, mm1, mm2, svb.INTER_LINEAR)
+    for b in range(3):
+        assert np.array_equal(out[b], oracle.remap(src[b], mm1, mm2))
+
+
+def test_median_and_speckle_bit_exact(golden):
+    d16 = golden["med3_in"]
+    assert np.array_equal(svb.medianBlur(d16, 3), golden["med3"])
+    f = d16.astype(np.float32) / 16.0
+    assert np.array_equal(svb.medianBlur(f, 5), golden["med5"])
+    prm = SGBM_CASES[0]["prm"]
+    sp = d16.copy()
+    svb.filterSpeckles(sp, (prm["minDisparity"] - 1) * 16, 40, 16)
+    assert np.array_equal(sp, golden["speckle"])
+    rng = np.random.default_rng(9)
+    for it in range(6):
+        H, W = int(rng.integers(5, 90)), int(rng.integers(5, 130))
+        img = (rng.integers(0, 6, (2, H, W)) * int(rng.choice([8, 40])) - 16).astype(np.int16)
+        maxsz, maxdiff = int(rng.choice([3, 20, 200])), int(rng.choice([0, 8, 40]))
+        got = svb.filterSpeckles(img.copy(), -16, maxsz, maxdiff)
+        for b in range(2):
+            assert np.array_equal(got[b], oracle.filter_speckles(img[b], -16, maxsz, maxdiff)), (H, W, maxsz, maxdiff)
+        fm = rng.normal(0, 30, (2, H, W)).astype(np.float32)
+        got5 = svb.medianBlur(fm, 5)
+        got3 = svb.medianBlur(img, 3)
+        for b in range(2):
+            assert np.array_equal(got5[b], oracle.median5_f32(fm[b]))
+            assert np.array_equal(got3[b], oracle.median3_s16(img[b]))
+
+
+def test_reproject_within_1e4(golden):
+    d16 = golden["med3_in"]
+    Q = golden["Q2"]
+    for got, ref in ((svb.reprojectImageTo3D(d16, Q), golden["reproj_s16"]),
+                     (svb.reprojectImageTo3D(d16.astype(np.float32) / 16.0, Q, True), golden["reproj_f32"])):
+        fin = np.isfinite(ref)
+        assert np.array_equal(fin, np.isfinite(got))
+        np.testing.assert_allclose(got[fin], ref[fin], rtol=1e-4, atol=1e-6)
+
+
+def test_depth_tail_matches_numpy_restatement(golden):
+    """depth_map.py:909-933 restated in NumPy float32 (the reference's own arithmetic)."""
+    d16 = golden["med3_in"]
+    depth, disparity = svb.disparity_to_depth(d16, fx=700, baseline=0.08, min_disp=0, min_depth=0.3, max_depth=2.0)
+    disp_ref = oracle.median5_f32(d16.astype(np.float32) / 16.0)
+    assert np.array_equal(disparity, disp_ref)
+    with np.errstate(divide="ignore"):
+        z = (700 * 0.08) / (disp_ref + 1e-6)
+    zc = np.clip(z, 0.3, 2.0)
+    valid = (disp_ref > 0) & (zc >= 0.3) & (zc <= 2.0)
+    ref = np.where(valid, zc, 0)
+    assert ref.dtype == np.float32
+    np.testing.assert_allclose(depth, ref, rtol=1e-6, atol=0)

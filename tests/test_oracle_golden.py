@@ -1,0 +1,64 @@
+"""CPU: the oracle (oracle/*.c) against the cv2-made golden vectors, and against live cv2
+where it is importable.  This is what pins the oracle (prompt section 3)."""
+import numpy as np
+import pytest
+
+import oracle
+from stereovision_b200.synth import make_pair, to_bgr
+from tests.golden_cases import SGBM_CASES
+
+
+@pytest.mark.parametrize("i", range(len(SGBM_CASES)))
+def test_sgbm_oracle_matches_golden(golden, i):
+    c = SGBM_CASES[i]
+    l, r, _ = make_pair(c["H"], c["W"], max(c["prm"]["numDisparities"], 16), seed=c["seed"])
+    got = oracle.sgbm_compute(l, r, **c["prm"])
+    ref = golden[f"sgbm_{i}"]
+    assert got.dtype == np.int16 and got.shape == ref.shape
+    assert int((got != ref).sum()) == 0          # bit-exact
+
+
+def test_remap_gray_oracle_matches_golden(golden):
+    l, _, _ = make_pair(120, 160, 16, seed=7)
+    bgr = to_bgr(l)
+    m1, m2 = golden["remap_map1"], golden["remap_map2"]
+    assert np.array_equal(oracle.remap(bgr, m1, m2), golden["remap_bgr"])
+    assert np.array_equal(oracle.remap(l, m1, m2), golden["remap_gray"])
+    assert np.array_equal(oracle.bgr2gray(bgr), golden["gray"])
+
+
+def test_median_speckle_oracle_matches_golden(golden):
+    d16 = golden["med3_in"]
+    assert np.array_equal(oracle.median3_s16(d16), golden["med3"])
+    assert np.array_equal(oracle.median5_f32(d16.astype(np.float32) / 16.0), golden["med5"])
+    prm = SGBM_CASES[0]["prm"]
+    assert np.array_equal(oracle.filter_speckles(d16, (prm["minDisparity"] - 1) * 16, 40, 16), golden["speckle"])
+
+
+def test_reproject_oracle_matches_golden(golden):
+    d16 = golden["med3_in"]
+    Q = golden["Q2"]
+    for got, ref in ((oracle.reproject_image_to_3d(d16, Q), golden["reproj_s16"]),
+                     (oracle.reproject_image_to_3d(d16.astype(np.float32) / 16.0, Q, True), golden["reproj_f32"])):
+        fin = np.isfinite(ref)
+        assert np.array_equal(fin, np.isfinite(got))
+        np.testing.assert_allclose(got[fin], ref[fin], rtol=1e-4, atol=1e-6)   # north_star: 1e-4 relative
+
+
+def test_sgbm_oracle_vs_live_cv2_random(have_cv2):
+    if not have_cv2:
+        pytest.skip("cv2 not importable here")
+    import cv2
+    rng = np.random.default_rng(5)
+    for it in range(12):
+        D = int(rng.choice([16, 32, 48]))
+        bs = int(rng.choice([3, 5, 7]))
+        mode = int(rng.choice([0, 1, 2]))
+        minD = 0 if mode == 2 else int(rng.choice([0, -8, 4]))
+        H, W = int(rng.integers(40, 80)), int(rng.integers(D + 40, D + 120))
+        prm = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=8 * bs * bs, P2=32 * bs * bs,
+                   disp12MaxDiff=int(rng.choice([1, 2])), preFilterCap=int(rng.choice([31, 63])),
+                   uniquenessRatio=int(rng.choice([0, 10, 15])), speckleWindowSize=int(rng.choice([0, 60])),
+                   speckleRange=2, mode=mode)
+        l, r, _ = make_pair(H, W, D, seed=500 + it)
+        assert np.array_equal(cv2.StereoSGBM_create(**prm).compute(l, r), oracle.sgbm_compute(l, r, **prm)), prm

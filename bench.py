@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the stereo hot path (BASELINE.json).
+
+Workload (config.workload): BASELINE.json configs[3] -- StereoSGBM 1920x1080, numDisparities
+256, 8-path MODE_HH, LR check + speckle filter, a batch of pairs per GPU (weak scaling:
+per-GPU batch fixed as N grows).  One "step" = one pass of the SGBM hot path over one batch.
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (libsvb.so, sm_100a)
+    python bench.py --impl reference --gpus N ...            # the reference's CPU path (cv2)
+
+Prints ONE JSON line on rank 0 (see README/DESIGN.md for the keys).
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: H, W, D, mode, default batch per GPU
+    "sgbm_1080p_d256_hh": dict(H=1080, W=1920, D=256, mode=1, batch=32),
+    "sgbm_720p_d128_sgbm": dict(H=720, W=1280, D=128, mode=0, batch=64),
+    "sgbm_480p_d64_sgbm": dict(H=480, W=640, D=64, mode=0, batch=128),
+    "sgbm_480p_d320_3way": dict(H=480, W=640, D=320, mode=2, batch=64),
+}
+
+
+def sgbm_params(wl):
+    bs = 5
+    return dict(minDisparity=0, numDisparities=wl["D"], blockSize=bs, P1=8 * bs * bs, P2=32 * bs * bs,
+                disp12MaxDiff=1, preFilterCap=63, uniquenessRatio=10, speckleWindowSize=100, speckleRange=32,
+                mode=wl["mode"])
+
+
+def b_alg_bytes(wl):
+    """algorithmic bytes per pair = 2 u8 images in + s16 out + one write and one
+    read of an int16 W*H*D volume = 4*W*H + 4*W*H*D."""
+    return 4 * wl["W"] * wl["H"] + 4 * wl["W"] * wl["H"] * wl["D"]
+
+
+def make_inputs(wl, B, seed0):
+    """Synthetic pairs: a few distinct seeded scenes, tiled to the batch (generation is slow)."""
+    from stereovision_b200.synth import make_pair
+    nuniq = min(B, 4)
+    Ls, Rs = [], []
+    for i in range(nuniq):
+        l, r, _ = make_pair(wl["H"], wl["W"], wl["D"], seed=seed0 + i)
+        Ls.append(l); Rs.append(r)
+    idx = [i % nuniq for i in range(B)]
+    return np.stack([Ls[i] for i in idx]), np.stack([Rs[i] for i in idx])
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        super().__init__(daemon=True)
+        self.gpu, self.samples, self.stop_flag = gpu, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [s.strip() for s in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def cpu_reference_run(wl, npairs, threads):
+    """The reference's own CPU implementation of the path: cv2.StereoSGBM.compute
+    (depth_map.py:894-909) over `npairs` distinct pairs, one pair per worker thread (cv2
+    releases the GIL; MODE_SGBM/HH/3WAY are serial per image -- SURVEY 2.1).  Falls back to
+    the oracle port when cv2 is not importable.  Returns (seconds, kind, cores)."""
+    from concurrent.futures import ThreadPoolExecutor
+    L, R = make_inputs(wl, npairs, seed0=100)
+    prm = sgbm_params(wl)
+    # MODE_HH keeps full C and S volumes per call: bound the worker count by free host memory
+    try:
+        avail = [int(l.split()[1]) * 1024 for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0]
+        per_call = 6 * wl["H"] * wl["W"] * wl["D"] + (64 << 20)
+        threads = max(1, min(threads, int(0.6 * avail / per_call)))
+    except Exception:
+        pass
+    try:
+        import cv2
+        cv2.setNumThreads(1)
+        kind = "reference"
+
+        def one(i):
+            return cv2.StereoSGBM_create(**prm).compute(L[i], R[i])
+    except Exception:
+        import oracle
+        kind = "port"
+        threads = 1
+
+        def one(i):
+            return oracle.sgbm_compute(L[i], R[i], **prm)
+    t0 = time.perf_counter()
+    if threads == 1:
+        for i in range(npairs):
+            one(i)
+    else:
+        with ThreadPoolExecutor(threads) as ex:
+            list(ex.map(one, range(npairs)))
+    return time.perf_counter() - t0, kind, threads
+
+
+def run_reference_arm(args, wl, rank, world):
+    if rank != 0:
+        return
+    cores = len(os.sched_getaffinity(0))
+    sample = cores if args.ref_pairs <= 0 else args.ref_pairs
+    for _ in range(args.warmup):
+        cpu_reference_run(wl, min(sample, cores), cores)
+    tot, kind = 0.0, "reference"
+    for _ in range(args.steps):
+        dt, kind, used = cpu_reference_run(wl, sample, cores)
+        tot += dt
+    pairs_s = sample * args.steps / tot
+    unit = "pairs/s"
+    line = {
+        "impl": "reference", "metric": "stereo_pairs_per_sec", "value": pairs_s, "unit": unit,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16", "data": "synthetic",
+        "config": {"workload": args.workload, "H": wl["H"], "W": wl["W"], "numDisparities": wl["D"],
+                   "mode": wl["mode"], "pairs_per_step": sample,
+                   "gdisp_evals_per_s": pairs_s * wl["H"] * wl["W"] * wl["D"] / 1e9},
+        "cpu_baseline": {"value": pairs_s, "unit": unit, "cores": used, "kind": kind,
+                         "sample": f"{sample} distinct pairs per step, one pair per thread, cv2.setNumThreads(1)"},
+        "e2e": {"value": pairs_s, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="svb", choices=["svb", "reference"])
+    ap.add_argument("--workload", default="sgbm_1080p_d256_hh", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="pairs per GPU per step (0 = workload default)")
+    ap.add_argument("--ref-pairs", type=int, default=0, help="pairs per step of the CPU arm (0 = #cores)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, wl, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the svb arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    from stereovision_b200 import _lib
+    L = _lib.lib()
+    _lib.check(L.svb_init(local))
+
+    B = args.batch or wl["batch"]
+    H, W, D = wl["H"], wl["W"], wl["D"]
+    prm = sgbm_params(wl)
+    Lh, Rh = make_inputs(wl, B, seed0=1000 * rank)
+    # pinned host buffers for the end-to-end (host-in / host-out) leg
+    Lp = torch.from_numpy(Lh).pin_memory(); Rp = torch.from_numpy(Rh).pin_memory()
+    Op = torch.empty((B, H, W), dtype=torch.int16).pin_memory()
+    Ld, Rd = Lp.to(dev), Rp.to(dev)
+    Od = torch.empty((B, H, W), dtype=torch.int16, device=dev)
+
+    h = ctypes.c_void_p()
+    _lib.check(L.svb_sgbm_create(ctypes.byref(_lib.SgbmParams(*[prm[k] for k in (
+        "minDisparity", "numDisparities", "blockSize", "P1", "P2", "disp12MaxDiff", "preFilterCap",
+        "uniquenessRatio", "speckleWindowSize", "speckleRange", "mode")])), ctypes.byref(h)))
+    stream = torch.cuda.current_stream()
+    sp = ctypes.c_void_p(stream.cuda_stream)
+
+    def step_dev():
+        _lib.check(L.svb_sgbm_compute_dev(h, Ld.data_ptr(), Rd.data_ptr(), B, H, W, Od.data_ptr(), sp))
+
+    def step_host():
+        _lib.check(L.svb_sgbm_compute_host(h, Lp.data_ptr(), Rp.data_ptr(), B, H, W, Op.data_ptr()))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput (`value`)
+    for _ in range(args.warmup):
+        step_dev()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    L.svb_sgbm_set_profiling(h, 1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_dev()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = L.svb_sgbm_last_launches(h) * args.steps
+    names = ctypes.create_string_buffer(32 * 16)
+    pms = (ctypes.c_float * 16)(); pln = (ctypes.c_int * 16)()
+    nst = L.svb_sgbm_get_profile(h, 16, names, pms, pln)
+    L.svb_sgbm_set_profiling(h, 0)
+    stages = {names.raw[32 * i:32 * i + 32].split(b"\0")[0].decode(): (pms[i], pln[i]) for i in range(max(nst, 0))}
+
+    # ---- end-to-end through the host-buffer C-ABI call (`e2e`): H2D + compute + D2H each step
+    step_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_host()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    tmax = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(tmax[0]), float(tmax[1])
+
+    if rank == 0:
+        pairs = B * world * args.steps
+        value = pairs / (ms / 1e3)
+        e2e = pairs / (e2e_ms / 1e3)
+        balg = b_alg_bytes(wl)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        # dominant stage: all launches of the kernel with the largest share of the step
+        dom = max(stages, key=lambda k: stages[k][0]) if stages else None
+        sgbm_ms = sum(v[0] for v in stages.values())
+        roof = None
+        if dom:
+            dms, dl = stages[dom]
+            # the hot path as one unit: B_alg x pairs over the summed device time of its kernels
+            ach = balg * B * args.steps / (sgbm_ms / 1e3) / 1e9
+            roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                    "kernel": "sgbm chain (all stages)", "dominant_kernel": dom,
+                    "dominant_share": dms / sgbm_ms if sgbm_ms else None,
+                    "dominant_ms_per_launch": dms / max(dl, 1),
+                    "b_alg_bytes_per_pair": balg,
+                    "stages_ms_per_step": {k: v[0] / args.steps for k, v in stages.items()}}
+        line = {
+            "metric": "stereo_pairs_per_sec", "value": value, "unit": "pairs/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16",
+            "data": "synthetic",
+            "config": {"workload": args.workload, "H": H, "W": W, "numDisparities": D, "mode": wl["mode"],
+                       "blockSize": 5, "pairs_per_gpu_per_step": B, "l2_policy": "inputs+volumes >> L2 (126 MB)",
+                       "gdisp_evals_per_s": value * H * W * D / 1e9},
+            "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": 2 * B * H * W,
+                    "d2h_bytes_per_step": 2 * B * H * W},
+            "gpu_launches": launches,
+            "clocks": sampler.summary(),
+            "roofline": roof,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cores = len(os.sched_getaffinity(0))
+            dt, kind, used = cpu_reference_run(wl, cores, cores)
+            line["cpu_baseline"] = {"value": cores / dt, "unit": "pairs/s", "cores": used, "kind": kind,
+                                    "sample": f"{cores} distinct pairs once, one pair per thread (cv2.setNumThreads(1))"}
+        print(json.dumps(line), flush=True)
+    L.svb_sgbm_destroy(h)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -72,6 +72,12 @@ int svb_sgbm_debug_stages(svb_sgbm_t* h, uint16_t* C_host, uint16_t* S_host, int
 /* Number of kernel launches issued by the last compute call (bench.py's gpu_launches). */
 int svb_sgbm_last_launches(const svb_sgbm_t* h);
 
+/* Per-stage device timing (CUDA events on the launching stream) for bench.py's roofline.
+ * enable=1 starts/reset recording, 0 stops.  get_profile synchronises and returns the number
+ * of stages filled: names (max_stages x 32 chars), accumulated ms and launch counts. */
+int svb_sgbm_set_profiling(svb_sgbm_t* h, int enable);
+int svb_sgbm_get_profile(svb_sgbm_t* h, int max_stages, char* names, float* ms, int* launches);
+
 /* ---- cv2.StereoBM_create(numDisparities, blockSize) + setters (BASELINE config 2) */
 typedef struct {
     int minDisparity, numDisparities, blockSize, preFilterCap, textureThreshold;

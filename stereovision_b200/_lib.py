@@ -41,6 +41,8 @@ SIGNATURES = {
     "svb_sgbm_compute_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "svb_sgbm_debug_stages": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "svb_sgbm_last_launches": (c_int, [c_void_p]),
+    "svb_sgbm_set_profiling": (c_int, [c_void_p, c_int]),
+    "svb_sgbm_get_profile": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "svb_bm_create": (c_int, [ctypes.POINTER(BmParams), ctypes.POINTER(c_void_p)]),
     "svb_bm_destroy": (None, [c_void_p]),
     "svb_bm_compute_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),

@@ -17,6 +17,8 @@
 #include "svb_common.cuh"
 #include <algorithm>
 #include <new>
+#include <vector>
+#include <string.h>
 
 #define WALL 0x7fffu           // cv2's MAX_COST for the d=-1 / d=D neighbours and pad lanes
 #define WALL2 0x7fff7fffu
@@ -468,6 +470,10 @@ struct svb_sgbm {
     SvbBuf ws;
     SvbBuf stage_in, stage_out;     // device staging for the *_host entry point
     int launches = 0;
+    // optional per-stage timing with CUDA events on the launching stream (bench.py's roofline)
+    bool profiling = false;
+    struct Ev { int cat; cudaEvent_t a, b; };
+    std::vector<Ev> evs;
     // last compute (for debug_stages)
     SgbmGeo last_geo{};
     size_t off_C = 0, off_S = 0, off_raw = 0;
@@ -581,6 +587,21 @@ extern "C" int svb_sgbm_set_workspace_limit(svb_sgbm_t* h, size_t bytes)
 }
 extern "C" int svb_sgbm_last_launches(const svb_sgbm_t* h) { return h ? h->launches : 0; }
 
+enum { CAT_PREFILTER = 0, CAT_COST, CAT_PATH, CAT_WTA, CAT_LR, CAT_MEDIAN, CAT_SPECKLE, CAT_COUNT };
+static const char* const kCatNames[CAT_COUNT] = {"k_prefilter", "k_cost", "k_path", "k_wta", "k_lrcheck", "k_median3_s16", "k_ccl_*"};
+struct ProfScope {
+    svb_sgbm* h; cudaStream_t st; int idx = -1;
+    ProfScope(svb_sgbm* h_, int cat, cudaStream_t st_) : h(h_), st(st_)
+    {
+        if (!h->profiling) return;
+        svb_sgbm::Ev e; e.cat = cat;
+        cudaEventCreate(&e.a); cudaEventCreate(&e.b);
+        cudaEventRecord(e.a, st);
+        h->evs.push_back(e); idx = (int)h->evs.size() - 1;
+    }
+    ~ProfScope() { if (idx >= 0) cudaEventRecord(h->evs[idx].b, st); }
+};
+
 template <int NP>
 static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const uint8_t* left, const uint8_t* right,
                      int nb, int16_t* disp, cudaStream_t st)
@@ -595,7 +616,10 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     int32_t* scratch = (int32_t*)(ws + L.scratch);
     const int njobs = nb * g.nstripes;
 
-    k_prefilter<<<dim3(svb_ceil_div(g.W, 256), g.H, nb), 256, 0, st>>>(left, right, nb, g, ldesc, rdesc);
+    {
+        ProfScope ps(h, CAT_PREFILTER, st);
+        k_prefilter<<<dim3(svb_ceil_div(g.W, 256), g.H, nb), 256, 0, st>>>(left, right, nb, g, ldesc, rdesc);
+    }
     SVB_LAUNCH_CHECK(); h->launches++;
 
     // k_cost tiling: NW = TY + 2r warps, smem = (NW*bs + NW) * NP * 128 bytes
@@ -612,6 +636,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         const size_t smem = smem_of(TY);
         SVB_CUDA(cudaFuncSetAttribute(k_cost<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         dim3 grid(svb_ceil_div(g.width1, XSEG), svb_ceil_div(g.rowsMax, TY), njobs);
+        ProfScope ps(h, CAT_COST, st);
         k_cost<NP><<<grid, 32 * (TY + 2 * g.r), smem, st>>>(ldesc, rdesc, g, TY, XSEG, Cv);
         SVB_LAUNCH_CHECK(); h->launches++;
     }
@@ -624,6 +649,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         const int dx = g.mode == SVB_MODE_SGBM_3WAY ? dirs3[k][0] : dirs[k][0];
         const int dy = g.mode == SVB_MODE_SGBM_3WAY ? dirs3[k][1] : dirs[k][1];
         const long long lines = (long long)njobs * (dy == 0 ? g.rowsMax : g.width1);
+        ProfScope ps(h, CAT_PATH, st);
         k_path<NP><<<svb_ceil_div(lines * 32, 256), 256, 0, st>>>(Cv, Sv, g, dx, dy, k == 0, njobs);
         SVB_LAUNCH_CHECK(); h->launches++;
     }
@@ -634,20 +660,29 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     SVB_CUDA(cudaMemsetAsync(key, 0xff, npix * 4, st));
     {
         const long long warps = (long long)njobs * g.rowsMax * g.width1;
+        ProfScope ps(h, CAT_WTA, st);
         k_wta<NP><<<svb_ceil_div(warps * 32, 256), 256, 0, st>>>(Sv, g, njobs, 0, raw, key);
         SVB_LAUNCH_CHECK(); h->launches++;
     }
-    k_lrcheck<<<dim3(svb_ceil_div(g.width1, 256), g.H, nb), 256, 0, st>>>(raw, key, g, nb);
+    {
+        ProfScope ps(h, CAT_LR, st);
+        k_lrcheck<<<dim3(svb_ceil_div(g.width1, 256), g.H, nb), 256, 0, st>>>(raw, key, g, nb);
+    }
     SVB_LAUNCH_CHECK(); h->launches++;
 
-    int rc = svb_median3_s16_dev(raw, nb, g.H, g.W, disp, st);
+    int rc;
+    {
+        ProfScope ps(h, CAT_MEDIAN, st);
+        rc = svb_median3_s16_dev(raw, nb, g.H, g.W, disp, st);
+    }
     if (rc != SVB_OK) return rc;
     h->launches++;
     if (h->prm.speckleWindowSize > 0) {
+        ProfScope ps(h, CAT_SPECKLE, st);
         rc = svb_filter_speckles_s16_dev(disp, nb, g.H, g.W, g.INV, h->prm.speckleWindowSize,
                                          16 * h->prm.speckleRange, scratch, st);
         if (rc != SVB_OK) return rc;
-        h->launches += 5;
+        h->launches += 4;
     }
     return SVB_OK;
 }
@@ -729,4 +764,28 @@ extern "C" int svb_sgbm_debug_stages(svb_sgbm_t* h, uint16_t* C_host, uint16_t* 
     if (raw_host)
         SVB_CUDA(cudaMemcpy(raw_host, (const char*)h->ws.p + h->off_raw, (size_t)g.H * g.W * 2, cudaMemcpyDeviceToHost));
     return SVB_OK;
+}
+
+// ---- profiling hooks (bench.py): per-stage device time of all computes since enable/reset
+extern "C" int svb_sgbm_set_profiling(svb_sgbm_t* h, int enable)
+{
+    if (!h) return SVB_ERR_PARAM;
+    for (auto& e : h->evs) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    h->evs.clear();
+    h->profiling = enable != 0;
+    return SVB_OK;
+}
+extern "C" int svb_sgbm_get_profile(svb_sgbm_t* h, int max_stages, char* names /* max_stages x 32 */,
+                                    float* ms, int* launches)
+{
+    if (!h || !names || !ms || !launches) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
+    SVB_CUDA(cudaDeviceSynchronize());
+    const int n = std::min(max_stages, (int)CAT_COUNT);
+    for (int i = 0; i < n; ++i) { ms[i] = 0.f; launches[i] = 0; strncpy(names + 32 * i, kCatNames[i], 31); names[32 * i + 31] = 0; }
+    for (auto& e : h->evs) {
+        float t = 0.f;
+        SVB_CUDA(cudaEventElapsedTime(&t, e.a, e.b));
+        if (e.cat < n) { ms[e.cat] += t; launches[e.cat] += e.cat == CAT_SPECKLE ? 4 : 1; }
+    }
+    return n;
 }

@@ -138,3 +138,20 @@ def reproject_image_to_3d(disp, Q, handleMissingValues=False):
     lib().orc_reproject3d(_p(d, ctypes.c_float), d.shape[0], d.shape[1], _p(Q, ctypes.c_double),
                           int(bool(handleMissingValues)), _p(out, ctypes.c_float))
     return out
+
+
+def bm_compute(left, right, numDisparities=64, blockSize=21, minDisparity=0, preFilterCap=31,
+               textureThreshold=10, uniquenessRatio=15, speckleWindowSize=0, speckleRange=0, disp12MaxDiff=-1):
+    """cv2.StereoBM_create(numDisparities, blockSize).compute(left, right) restated."""
+    left = np.ascontiguousarray(left, np.uint8)
+    right = np.ascontiguousarray(right, np.uint8)
+    assert left.shape == right.shape and left.ndim == 2
+    H, W = left.shape
+    prm = _BmParams(minDisparity, numDisparities, blockSize, preFilterCap, textureThreshold,
+                    uniquenessRatio, speckleWindowSize, speckleRange, disp12MaxDiff)
+    disp = np.empty((H, W), np.int16)
+    rc = lib().orc_bm_compute(_p(left, ctypes.c_uint8), _p(right, ctypes.c_uint8), H, W, ctypes.byref(prm),
+                              _p(disp, ctypes.c_int16))
+    if rc != 0:
+        raise ValueError(f"orc_bm_compute rejected the parameters (code {rc})")
+    return disp

@@ -1,0 +1,100 @@
+/*
+ * oracle/bm_oracle.c -- TEST INFRASTRUCTURE ONLY (never on the product path).
+ *
+ * Plain-C CPU restatement of cv2.StereoBM_create(numDisparities, blockSize).compute
+ * (BASELINE.json config 2; the reference itself never calls StereoBM -- SURVEY 0).
+ * The arithmetic lives in OpenCV 4.13.0 (modules/calib3d/src/stereobm.cpp, not vendored);
+ * this restates SURVEY.md Appendix A.6.  Pinned against live cv2 and tests/golden/.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef struct {
+    int minDisparity, numDisparities, blockSize, preFilterCap, textureThreshold;
+    int uniquenessRatio, speckleWindowSize, speckleRange, disp12MaxDiff;
+} orc_bm_params;
+
+void orc_filter_speckles_s16(int16_t* img, int H, int W, int newVal, int maxSpeckleSize, int maxDiff);
+
+static inline int bclamp(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+/* A.6 prefilter (X-Sobel): rows are produced in pairs; the vertical neighbours of the
+ * first/last row are reflected (row -1 -> 1, row H -> H-2); columns 0 and W-1 = cap;
+ * for odd H the last row is all cap. */
+void orc_bm_prefilter_xsobel(const uint8_t* src, int H, int W, int cap, uint8_t* dst)
+{
+    for (int y = 0; y < H; ++y) {
+        uint8_t* d = dst + (size_t)y * W;
+        if ((H & 1) && y == H - 1) { memset(d, cap, W); continue; }
+        int ya = y > 0 ? y - 1 : (H > 1 ? 1 : 0);
+        int yb = y < H - 1 ? y + 1 : (H > 1 ? H - 2 : 0);
+        const uint8_t *r0 = src + (size_t)ya * W, *r1 = src + (size_t)y * W, *r2 = src + (size_t)yb * W;
+        d[0] = (uint8_t)cap;
+        if (W > 1) d[W - 1] = (uint8_t)cap;
+        for (int x = 1; x < W - 1; ++x) {
+            int g = (r0[x + 1] - r0[x - 1]) + 2 * (r1[x + 1] - r1[x - 1]) + (r2[x + 1] - r2[x - 1]);
+            d[x] = (uint8_t)(bclamp(g, -cap, cap) + cap);
+        }
+    }
+}
+
+/* returns 0, or <0 for what cv2 rejects */
+int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W, const orc_bm_params* p, int16_t* disp)
+{
+    const int D = p->numDisparities, minD = p->minDisparity, bs = p->blockSize, r = bs / 2;
+    const int cap = p->preFilterCap;
+    if (D <= 0 || D % 16 != 0) return -1;
+    if (bs < 5 || bs > 255 || bs % 2 == 0 || bs >= W || bs >= H) return -1;
+    if (cap < 1 || cap > 63) return -1;
+    if (p->textureThreshold < 0 || p->uniquenessRatio < 0) return -1;
+    const int FILTERED = (minD - 1) * 16;
+    for (size_t i = 0; i < (size_t)H * W; ++i) disp[i] = (int16_t)FILTERED;
+    const int lofs = D - 1 + minD > 0 ? D - 1 + minD : 0;
+    const int rofs = D - 1 + minD < 0 ? -(D - 1 + minD) : 0;
+    const int width1 = W - rofs - D + 1;
+    if (lofs >= W || rofs >= W || width1 < 1) return 0;
+
+    uint8_t* L = (uint8_t*)malloc((size_t)H * W);
+    uint8_t* R = (uint8_t*)malloc((size_t)H * W);
+    orc_bm_prefilter_xsobel(left, H, W, cap, L);
+    orc_bm_prefilter_xsobel(right, H, W, cap, R);
+    int* sad = (int*)malloc(sizeof(int) * (D + 2));
+    const int x_lo = lofs + r, x_hi = W - r;              /* valid ROI columns */
+    for (int y = r; y < H - r; ++y)
+        for (int xp = 0; xp < width1; ++xp) {
+            const int x = xp + lofs;
+            if (x < x_lo || x >= x_hi) continue;
+            int ts = 0;
+            for (int k = 0; k < D; ++k) sad[k + 1] = 0;
+            for (int j = -r; j <= r; ++j) {
+                const int lc = bclamp(xp + j + lofs, 0, W - 1);
+                const int rs = bclamp(xp + j + rofs, 0, W - D);
+                for (int i = -r; i <= r; ++i) {
+                    const int yy = bclamp(y + i, 0, H - 1);
+                    const int lv = L[(size_t)yy * W + lc];
+                    ts += abs(lv - cap);
+                    const uint8_t* rr = R + (size_t)yy * W + rs;
+                    for (int k = 0; k < D; ++k) sad[k + 1] += abs(lv - rr[k]);
+                }
+            }
+            if (ts < p->textureThreshold) continue;
+            int mind = 0, minsad = sad[1];
+            for (int k = 1; k < D; ++k) if (sad[k + 1] < minsad) { minsad = sad[k + 1]; mind = k; }
+            if (p->uniquenessRatio > 0) {
+                const int thresh = minsad + (minsad * p->uniquenessRatio / 100);
+                int k;
+                for (k = 0; k < D; ++k)
+                    if ((k < mind - 1 || k > mind + 1) && sad[k + 1] <= thresh) break;
+                if (k < D) continue;
+            }
+            sad[0] = sad[2]; sad[D + 1] = sad[D - 1];
+            const int pp = sad[mind + 2], n = sad[mind], dd = pp + n - 2 * sad[mind + 1] + abs(pp - n);
+            disp[(size_t)y * W + x] =
+                (int16_t)((((D - mind - 1 + minD) * 256 + (dd != 0 ? (pp - n) * 256 / dd : 0) + 15) >> 4));
+        }
+    free(L); free(R); free(sad);
+    if (p->speckleWindowSize > 0)
+        orc_filter_speckles_s16(disp, H, W, FILTERED, p->speckleWindowSize, p->speckleRange);
+    return 0;
+}

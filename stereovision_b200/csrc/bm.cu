@@ -1,9 +1,301 @@
-// bm.cu -- StereoBM (BASELINE config 2).  Placeholder until the kernels land: every entry
-// point fails loudly (no CPU fallback).
+// bm.cu -- StereoBM (cv2.StereoBM_create(numDisparities, blockSize).compute; BASELINE.json
+// config 2) for sm_100a, bit-exact on int16 output.
+//
+//   k_bm_prefilter  X-Sobel prefilter (cap-clipped), right image also as paired u16x2 planes
+//   k_bm<NP>        one warp per image row slides along x keeping the horizontal SAD box sum
+//                   for all disparities in registers; rows meet in shared memory, the first TY
+//                   warps add blockSize rows and finish the pixel in place: texture test, argmin,
+//                   uniqueness, subpixel.  The SAD volume never exists in HBM.
+//   speckle filter  (imgproc.cu) when speckleWindowSize > 0
 #include "svb_common.cuh"
-struct svb_bm { svb_bm_params prm; int launches; };
-extern "C" int svb_bm_create(const svb_bm_params*, svb_bm_t**) { svb_set_error("StereoBM kernels not built yet"); return SVB_ERR_UNSUPPORTED; }
-extern "C" void svb_bm_destroy(svb_bm_t*) {}
-extern "C" int svb_bm_compute_dev(svb_bm_t*, const uint8_t*, const uint8_t*, int, int, int, int16_t*, void*) { svb_set_error("StereoBM kernels not built yet"); return SVB_ERR_UNSUPPORTED; }
-extern "C" int svb_bm_compute_host(svb_bm_t*, const uint8_t*, const uint8_t*, int, int, int, int16_t*) { svb_set_error("StereoBM kernels not built yet"); return SVB_ERR_UNSUPPORTED; }
-extern "C" int svb_bm_last_launches(const svb_bm_t*) { return 0; }
+#include <algorithm>
+#include <new>
+
+struct BmGeo {
+    int H, W, D, NP, minD, bs, r, cap, tex, uniq, FILTERED;
+    int lofs, rofs, width1, Wh;
+};
+
+__global__ void __launch_bounds__(256) k_bm_prefilter(const uint8_t* __restrict__ left, const uint8_t* __restrict__ right,
+                                                      BmGeo g, uint8_t* __restrict__ lp, uint32_t* __restrict__ rdesc)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+    const int H = g.H, W = g.W, cap = g.cap;
+    if (x >= W) return;
+    auto pf = [&](const uint8_t* img, int xx) -> int {
+        if (xx <= 0 || xx >= W - 1) return cap;
+        if ((H & 1) && y == H - 1) return cap;
+        const int ya = y > 0 ? y - 1 : (H > 1 ? 1 : 0), yb = y < H - 1 ? y + 1 : (H > 1 ? H - 2 : 0);
+        const uint8_t *r0 = img + (size_t)ya * W, *r1 = img + (size_t)y * W, *r2 = img + (size_t)yb * W;
+        const int gx = ((int)r0[xx + 1] - r0[xx - 1]) + 2 * ((int)r1[xx + 1] - r1[xx - 1]) + ((int)r2[xx + 1] - r2[xx - 1]);
+        return max(-cap, min(cap, gx)) + cap;
+    };
+    const size_t io = (size_t)b * H * W;
+    lp[io + (size_t)y * W + x] = (uint8_t)pf(left + io, x);
+    const int v0 = pf(right + io, x), v1 = pf(right + io, max(x - 1, 0));
+    uint32_t* base = rdesc + (size_t)(b * H + y) * 4 * g.Wh + (size_t)(x & 1) * g.Wh + (x >> 1);
+    base[0] = (uint32_t)v0 | ((uint32_t)v1 << 16);
+    base[2 * g.Wh] = (uint32_t)((-v0) & 0xffff) | ((uint32_t)((-v1) & 0xffff) << 16);
+}
+
+// |u - v| per half: max(u - v, v - u) with the negated operands precomputed
+__device__ __forceinline__ uint32_t bm_absdiff(uint32_t U2, uint32_t nU2, uint32_t V2, uint32_t nV2)
+{
+    return __vmaxs2(__vadd2(U2, nV2), __vadd2(V2, nU2));
+}
+
+template <int NP>
+__global__ void __launch_bounds__(1024) k_bm(const uint8_t* __restrict__ lp, const uint32_t* __restrict__ rdesc,
+                                             BmGeo g, int TY, int XSEG, int16_t* __restrict__ disp)
+{
+    extern __shared__ uint32_t smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, NW = blockDim.x >> 5;
+    const int b = blockIdx.z;
+    const int y0 = blockIdx.y * TY;
+    const int xs = blockIdx.x * XSEG, xe = min(xs + XSEG, g.width1);
+    const int r = g.r, bs = 2 * r + 1, D = g.D, W = g.W;
+    uint32_t* hsb = smem;                                  // [NW][NP][32] horizontal sums
+    uint32_t* tsb = smem + (size_t)NW * NP * 32;           // [NW] horizontal texture sums
+    uint32_t* svb = tsb + NW;                              // [TY][NP*32] final SAD vectors (pairs)
+    const int yy = min(max(y0 - r + warp, 0), g.H - 1);
+    const uint8_t* lrow = lp + ((size_t)b * g.H + yy) * W;
+    const uint32_t* rrow = rdesc + (size_t)(b * g.H + yy) * 4 * g.Wh;
+    uint32_t hs[NP];
+#pragma unroll
+    for (int k = 0; k < NP; ++k) hs[k] = 0;
+    int hts = 0;
+    const int y = y0 + warp;
+    const bool out_warp = warp < TY && y < g.H;
+    const bool row_ok = y >= r && y < g.H - r;
+
+    // cost vector of window column j (A.6: left column and right start column clamp separately)
+    auto column = [&](int j, uint32_t (&c)[NP], int& t) {
+        const int lc = min(max(j + g.lofs, 0), W - 1);
+        const int rs = min(max(j + g.rofs, 0), W - D);
+        const int u = lrow[lc];
+        t = abs(u - g.cap);
+        const uint32_t U2 = pk_dup((uint32_t)u), nU2 = pk_dup((uint32_t)(-u));
+        const int xr0 = rs + D - 1;                        // right column of disparity index d' = 0
+        const uint32_t* rp = rrow + (size_t)(xr0 & 1) * g.Wh;
+#pragma unroll
+        for (int k = 0; k < NP; ++k) {
+            const int m = max((xr0 >> 1) - (32 * k + lane), 0);
+            c[k] = bm_absdiff(U2, nU2, __ldg(rp + m), __ldg(rp + 2 * g.Wh + m));
+        }
+    };
+
+    for (int j = xs - r; j < xe + r; ++j) {
+        uint32_t c[NP]; int t;
+        column(j, c, t);
+#pragma unroll
+        for (int k = 0; k < NP; ++k) hs[k] += c[k];
+        hts += t;
+        if (j - bs >= xs - r) {                            // column leaving the window
+            column(j - bs, c, t);
+#pragma unroll
+            for (int k = 0; k < NP; ++k) hs[k] -= c[k];
+            hts -= t;
+        }
+        if (j - r < xs) continue;
+        const int xp = j - r;
+#pragma unroll
+        for (int k = 0; k < NP; ++k) hsb[(warp * NP + k) * 32 + lane] = hs[k];
+        if (lane == 0) tsb[warp] = (uint32_t)hts;
+        __syncthreads();
+        if (out_warp) {
+            const int x = xp + g.lofs;
+            uint32_t s[NP];
+            int ts = 0;
+#pragma unroll
+            for (int k = 0; k < NP; ++k) s[k] = 0;
+            for (int t2 = 0; t2 < bs; ++t2) {
+#pragma unroll
+                for (int k = 0; k < NP; ++k) s[k] += hsb[((warp + t2) * NP + k) * 32 + lane];
+                ts += (int)tsb[warp + t2];
+            }
+            const bool roi = row_ok && x >= g.lofs + r && x < W - r;
+            if (roi && ts >= g.tex) {
+                // argmin over BM index kk = D-1-d' (lowest kk = largest disparity wins ties)
+                uint32_t key = 0xffffffffu;
+#pragma unroll
+                for (int k = 0; k < NP; ++k) {
+                    const int d0 = 2 * (32 * k + lane);
+                    if (d0 < D) key = min(key, ((s[k] & 0xffffu) << 16) | (uint32_t)(D - 1 - d0));
+                    if (d0 + 1 < D) key = min(key, ((s[k] >> 16) << 16) | (uint32_t)(D - 2 - d0));
+                }
+                key = __reduce_min_sync(0xffffffffu, key);
+                const int minsad = (int)(key >> 16), mind = (int)(key & 0xffffu);
+                bool rej = false;
+                if (g.uniq > 0) {
+                    const int thresh = minsad + (minsad * g.uniq / 100);
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) {
+                        const int d0 = 2 * (32 * k + lane);
+                        const int k0 = D - 1 - d0, k1 = D - 2 - d0;
+                        rej |= d0 < D && (k0 < mind - 1 || k0 > mind + 1) && (int)(s[k] & 0xffffu) <= thresh;
+                        rej |= d0 + 1 < D && (k1 < mind - 1 || k1 > mind + 1) && (int)(s[k] >> 16) <= thresh;
+                    }
+                }
+                rej = __any_sync(0xffffffffu, rej);
+                if (!rej) {
+                    uint32_t* sv = svb + (size_t)warp * NP * 32;
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) sv[32 * k + lane] = s[k];
+                    __syncwarp();
+                    if (lane == 0) {
+                        const uint16_t* sd = reinterpret_cast<const uint16_t*>(sv);     // indexed by d'
+                        auto sadk = [&](int kk) { return (int)sd[D - 1 - kk]; };
+                        const int p = mind + 1 < D ? sadk(mind + 1) : sadk(D - 2);
+                        const int n = mind - 1 >= 0 ? sadk(mind - 1) : sadk(1);
+                        const int dd = p + n - 2 * minsad + abs(p - n);
+                        const int v = ((D - mind - 1 + g.minD) * 256 + (dd != 0 ? (p - n) * 256 / dd : 0) + 15) >> 4;
+                        disp[((size_t)b * g.H + y) * W + x] = (int16_t)v;
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void k_bm_fill(int16_t* p, size_t n, int16_t v)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// ------------------------------------------------------------------------------------------
+struct svb_bm {
+    svb_bm_params prm;
+    SvbBuf ws, stage_in, stage_out;
+    int launches = 0;
+};
+
+static int bm_geo(const svb_bm_params& p, int H, int W, BmGeo& g, bool& trivial)
+{
+    // what cv2 4.13 rejects (stereobm.cpp: CV_Error StsOutOfRange / StsBadArg)
+    if (p.numDisparities <= 0 || p.numDisparities % 16 != 0) {
+        svb_set_error("numDisparities must be positive and divisible by 16"); return SVB_ERR_PARAM;
+    }
+    if (p.blockSize < 5 || p.blockSize > 255 || p.blockSize % 2 == 0) {
+        svb_set_error("SADWindowSize must be odd, be within 5..255"); return SVB_ERR_PARAM;
+    }
+    if (H > 0 && W > 0 && (p.blockSize >= W || p.blockSize >= H)) {
+        svb_set_error("SADWindowSize must not be larger than image width or height"); return SVB_ERR_PARAM;
+    }
+    if (p.preFilterCap < 1 || p.preFilterCap > 63) { svb_set_error("preFilterCap must be within 1..63"); return SVB_ERR_PARAM; }
+    if (p.textureThreshold < 0) { svb_set_error("texture threshold must be non-negative"); return SVB_ERR_PARAM; }
+    if (p.uniquenessRatio < 0) { svb_set_error("uniqueness ratio must be non-negative"); return SVB_ERR_PARAM; }
+    if (p.disp12MaxDiff >= 0) { svb_set_error("StereoBM disp12MaxDiff >= 0 (validateDisparity) is not implemented"); return SVB_ERR_UNSUPPORTED; }
+    if (p.blockSize > 31) { svb_set_error("blockSize %d > 31 unsupported by the BM kernel", p.blockSize); return SVB_ERR_UNSUPPORTED; }
+    if (p.numDisparities > 512) { svb_set_error("numDisparities > 512 unsupported"); return SVB_ERR_UNSUPPORTED; }
+    if ((long long)p.blockSize * p.blockSize * 2 * p.preFilterCap > 65535) {
+        svb_set_error("blockSize^2 * 2*preFilterCap exceeds the 16-bit SAD range of the BM kernel"); return SVB_ERR_UNSUPPORTED;
+    }
+    g.H = H; g.W = W; g.D = p.numDisparities; g.NP = (g.D + 63) / 64; g.minD = p.minDisparity;
+    g.bs = p.blockSize; g.r = p.blockSize / 2; g.cap = p.preFilterCap; g.tex = p.textureThreshold;
+    g.uniq = p.uniquenessRatio; g.FILTERED = (g.minD - 1) * 16;
+    const int s = g.D - 1 + g.minD;
+    g.lofs = std::max(s, 0); g.rofs = -std::min(s, 0);
+    g.width1 = W - g.rofs - g.D + 1;
+    g.Wh = (W + 1) / 2 + 4;
+    trivial = g.lofs >= W || g.rofs >= W || g.width1 < 1;   // cv2 returns an all-FILTERED map
+    return SVB_OK;
+}
+
+extern "C" int svb_bm_create(const svb_bm_params* p, svb_bm_t** out)
+{
+    if (!p || !out) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
+    BmGeo g; bool trivial;
+    int rc = bm_geo(*p, 0, 0, g, trivial);
+    if (rc != SVB_OK) return rc;
+    svb_bm* h = new (std::nothrow) svb_bm();
+    if (!h) return SVB_ERR_NOMEM;
+    h->prm = *p;
+    *out = h;
+    return SVB_OK;
+}
+extern "C" void svb_bm_destroy(svb_bm_t* h)
+{
+    if (!h) return;
+    h->ws.release(); h->stage_in.release(); h->stage_out.release();
+    delete h;
+}
+extern "C" int svb_bm_last_launches(const svb_bm_t* h) { return h ? h->launches : 0; }
+
+template <int NP>
+static int bm_launch(const BmGeo& g, const uint8_t* lp, const uint32_t* rdesc, int nb, int16_t* disp, cudaStream_t st)
+{
+    int TY = std::min(16, 32 - 2 * g.r);
+    const int NW = TY + 2 * g.r;
+    const size_t smem = ((size_t)NW * NP * 32 + NW + (size_t)TY * NP * 32) * 4;
+    const int XSEG = 160;
+    SVB_CUDA(cudaFuncSetAttribute(k_bm<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid(svb_ceil_div(g.width1, XSEG), svb_ceil_div(g.H, TY), nb);
+    k_bm<NP><<<grid, 32 * NW, smem, st>>>(lp, rdesc, g, TY, XSEG, disp);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+extern "C" int svb_bm_compute_dev(svb_bm_t* h, const uint8_t* left, const uint8_t* right, int B, int H, int W,
+                                  int16_t* disp, void* stream)
+{
+    if (!h || !left || !right || !disp) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
+    if (B <= 0 || H <= 0 || W <= 0) { svb_set_error("bad shape"); return SVB_ERR_PARAM; }
+    BmGeo g; bool trivial;
+    int rc = bm_geo(h->prm, H, W, g, trivial);
+    if (rc != SVB_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    h->launches = 0;
+    const size_t npix = (size_t)B * H * W;
+    k_bm_fill<<<svb_ceil_div(npix, 256), 256, 0, st>>>(disp, npix, (int16_t)g.FILTERED);
+    SVB_LAUNCH_CHECK(); h->launches++;
+    if (trivial) return SVB_OK;
+    const size_t lp_bytes = (npix + 255) & ~(size_t)255;
+    const size_t rd_bytes = ((size_t)B * H * 4 * g.Wh * 4 + 255) & ~(size_t)255;
+    const size_t sc_bytes = h->prm.speckleWindowSize > 0 ? npix * 8 : 0;
+    rc = h->ws.reserve(lp_bytes + rd_bytes + sc_bytes);
+    if (rc != SVB_OK) return rc;
+    uint8_t* lp = (uint8_t*)h->ws.p;
+    uint32_t* rdesc = (uint32_t*)((char*)h->ws.p + lp_bytes);
+    k_bm_prefilter<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(left, right, g, lp, rdesc);
+    SVB_LAUNCH_CHECK(); h->launches++;
+    switch (g.NP) {
+#define CASE(N) case N: rc = bm_launch<N>(g, lp, rdesc, B, disp, st); break;
+        CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
+#undef CASE
+        default: svb_set_error("bad NP"); rc = SVB_ERR_UNSUPPORTED;
+    }
+    if (rc != SVB_OK) return rc;
+    h->launches++;
+    if (h->prm.speckleWindowSize > 0) {
+        // stereobm.cpp passes speckleRange unscaled (SGBM scales it by 16) -- probed on cv2 4.13
+        rc = svb_filter_speckles_s16_dev(disp, B, H, W, g.FILTERED, h->prm.speckleWindowSize, h->prm.speckleRange,
+                                         (int32_t*)((char*)h->ws.p + lp_bytes + rd_bytes), st);
+        if (rc != SVB_OK) return rc;
+        h->launches += 4;
+    }
+    return SVB_OK;
+}
+
+extern "C" int svb_bm_compute_host(svb_bm_t* h, const uint8_t* left, const uint8_t* right, int B, int H, int W,
+                                   int16_t* disp)
+{
+    if (!h || !left || !right || !disp) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
+    if (B <= 0 || H <= 0 || W <= 0) { svb_set_error("bad shape"); return SVB_ERR_PARAM; }
+    const size_t n = (size_t)B * H * W;
+    int rc = h->stage_in.reserve(2 * n);
+    if (rc != SVB_OK) return rc;
+    rc = h->stage_out.reserve(2 * n);
+    if (rc != SVB_OK) return rc;
+    uint8_t* dl = (uint8_t*)h->stage_in.p;
+    uint8_t* dr = dl + n;
+    SVB_CUDA(cudaMemcpyAsync(dl, left, n, cudaMemcpyHostToDevice, 0));
+    SVB_CUDA(cudaMemcpyAsync(dr, right, n, cudaMemcpyHostToDevice, 0));
+    rc = svb_bm_compute_dev(h, dl, dr, B, H, W, (int16_t*)h->stage_out.p, 0);
+    if (rc != SVB_OK) return rc;
+    SVB_CUDA(cudaMemcpyAsync(disp, h->stage_out.p, 2 * n, cudaMemcpyDeviceToHost, 0));
+    SVB_CUDA(cudaStreamSynchronize(0));
+    return SVB_OK;
+}

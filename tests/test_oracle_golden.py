@@ -62,3 +62,20 @@ def test_sgbm_oracle_vs_live_cv2_random(have_cv2):
                    speckleRange=2, mode=mode)
         l, r, _ = make_pair(H, W, D, seed=500 + it)
         assert np.array_equal(cv2.StereoSGBM_create(**prm).compute(l, r), oracle.sgbm_compute(l, r, **prm)), prm
+
+
+def _bm_kwargs(c):
+    kw = dict(numDisparities=c["numDisparities"], blockSize=c["blockSize"])
+    m = {"MinDisparity": "minDisparity", "UniquenessRatio": "uniquenessRatio", "TextureThreshold": "textureThreshold",
+         "SpeckleWindowSize": "speckleWindowSize", "SpeckleRange": "speckleRange", "PreFilterCap": "preFilterCap"}
+    for k, v in c.get("set", {}).items():
+        kw[m[k]] = v
+    return kw
+
+
+def test_bm_oracle_matches_golden(golden):
+    from tests.golden_cases import BM_CASES
+    for i, c in enumerate(BM_CASES):
+        l, r, _ = make_pair(c["H"], c["W"], max(c["numDisparities"], 16), seed=c["seed"])
+        got = oracle.bm_compute(l, r, **_bm_kwargs(c))
+        assert np.array_equal(got, golden[f"bm_{i}"]), i

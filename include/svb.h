@@ -57,7 +57,7 @@ int svb_sgbm_create(const svb_sgbm_params* p, svb_sgbm_t** out);
 void svb_sgbm_destroy(svb_sgbm_t* h);
 /* Bytes of device workspace the handle will hold for this shape (grow-only, owned by the handle). */
 size_t svb_sgbm_workspace_bytes(const svb_sgbm_t* h, int B, int H, int W);
-/* Cap on the workspace; batches are processed in chunks that fit (0 = default 24 GiB). */
+/* Cap on the workspace; batches are processed in chunks that fit (0 = 60 % of the free device memory). */
 int svb_sgbm_set_workspace_limit(svb_sgbm_t* h, size_t bytes);
 /* stereo.compute(left, right) -> int16 disparity x16 (depth_map.py:909, fused_depth_map.py:1004).
  * left/right: u8 [B,H,W]; disp: s16 [B,H,W]. */
@@ -67,7 +67,9 @@ int svb_sgbm_compute_host(svb_sgbm_t* h, const uint8_t* left_host, const uint8_t
                           int B, int H, int W, int16_t* disp_host);
 /* Test hook: copy internal stages of the LAST compute (chunk 0, image 0) to host buffers
  * (any may be NULL).  C,S: u16 [rows,width1,D] (3WAY: kept rows only are meaningful),
- * raw: s16 [H,W] disparity before median/speckle. */
+ * raw: s16 [H,W] disparity before median/speckle.  The aggregated volume S only exists in
+ * HBM after svb_sgbm_set_debug(h, 1) (normally the last sweep consumes it in registers). */
+int svb_sgbm_set_debug(svb_sgbm_t* h, int enable);
 int svb_sgbm_debug_stages(svb_sgbm_t* h, uint16_t* C_host, uint16_t* S_host, int16_t* raw_host);
 /* Number of kernel launches issued by the last compute call (bench.py's gpu_launches). */
 int svb_sgbm_last_launches(const svb_sgbm_t* h);

@@ -5,15 +5,29 @@
 //
 // Pipeline (one CUDA stream, no host sync):
 //   k_prefilter   x-Sobel + raw channel, Birchfield-Tomasi interval descriptors
-//   k_cost        BT pixel cost (2 channels) + blockSize^2 box sum -> C volume (u16)
-//   k_path<NP>    one launch per path direction: L_r recurrence, S += L_r (saturating)
-//   k_wta<NP>     argmin / uniqueness / subpixel / right-view scatter-min
+//   k_cost        BT pixel cost (2 channels) + blockSize^2 box sum -> C volume (u16), one write
+//   k_sweep<..,0> sweep 1 (top-down, left-to-right): up to 4 paths (-> \ | /) per pixel in ONE pass
+//                 over C, partial sum S1 written once
+//   k_sweep<..,1> sweep 2 (bottom-up / right-to-left): remaining paths, S = S1 + sum, then
+//                 argmin / uniqueness / subpixel / right-view scatter-min fused (S never stored)
 //   k_lrcheck     left-right consistency
 //   median3 + speckle filter (imgproc.cu)
 //
-// Data layout in HBM: volumes are [job][row][xc][Dp] u16 with Dp = 64*NP >= D; the
-// disparity axis is innermost so that one warp owns one pixel's whole disparity
-// vector as NP packed u16x2 registers per lane (lane l holds d = 2*NP*l ... +2*NP-1).
+// HBM traffic per pair: C written once, read by each sweep; S1 written once, read once
+// (5 volume passes; the direction-decomposed v1 made 25).
+//
+// Data layout in HBM: volumes are [job][row][xc][Dp] u16 with Dp = 64*NP >= D.  One pixel's
+// disparity vector is HALF = Dp/2 u32 words; word w packs disparity index w (low half) and
+// w + HALF (high half), so the d-1 / d+1 neighbours of BOTH halves sit in the adjacent words
+// and the SGM recurrence needs no byte permutes.  A warp owns one pixel: lane l holds words
+// NP*l .. NP*l+NP-1 in registers.
+//
+// k_sweep is a persistent wavefront kernel: a CTA takes a band of SW_R consecutive rows (one
+// warp per row, skewed by SW_SK columns so that the diagonal predecessors are ready), the
+// L_r vectors of the row above travel through shared-memory rings, and the last row of a band
+// hands its L_r to the next band (another CTA) through an L2-resident carry buffer guarded by
+// per-band progress counters (release/acquire).  Bands are handed out by an atomic ticket in
+// dependency order, so a waiting CTA only ever waits on a CTA that is already running.
 #include "svb_common.cuh"
 #include <algorithm>
 #include <new>
@@ -22,11 +36,18 @@
 
 #define WALL 0x7fffu           // cv2's MAX_COST for the d=-1 / d=D neighbours and pad lanes
 #define WALL2 0x7fff7fffu
+#define FULLMASK 0xffffffffu
+
+#define SW_R 16                // rows (= warps) per band
+#define SW_SK 2                // column skew between consecutive rows of a band
+#define SW_RING 4              // ring slots per path between two rows
+#define SW_FLAG_EVERY 8        // carry progress is published every this many columns
+#define SW_SPIN_LIMIT (1 << 24)
 
 struct SgbmGeo {
-    int H, W, D, Dp, NP, minD, minX1, width1, bs, r, ftzero;
+    int H, W, D, Dp, NP, HALF, minD, minX1, width1, bs, r, ftzero;
     int P1, P2, uniq, d12, INV, mode, nstripes, rowsMax;
-    int Wh;                    // words per parity plane of the right descriptors
+    int Wp;                    // words per plane row of the right descriptors
 };
 
 __host__ __device__ inline void job_rows(const SgbmGeo& g, int n, int& ys, int& ye, int& keep)
@@ -43,10 +64,11 @@ __host__ __device__ inline void job_rows(const SgbmGeo& g, int n, int& ys, int& 
 
 // ------------------------------------------------------------------------------------------
 // k_prefilter: per image row, the two BT channels (A.1 step 1-2) and their half-pixel
-// interval bounds (A.1 step 3).  Left: one 32-byte record per pixel holding
-// {u, -u, u0, -u1} x 2 channels, each duplicated into both halves of a u32.
-// Right: 8 operand planes {v, -v, v0, -v1} x 2 channels; entry(xr) = a[xr] | a[xr-1]<<16,
-// split by parity of xr so that a warp reading xr, xr-2, xr-4 ... is contiguous.
+// interval bounds (A.1 step 3).
+// Left: one 32-byte record per pixel {u, -u, u0, -u1} x 2 channels, each duplicated into both
+// halves of a u32.
+// Right: 6 planes per row {v1, v0, -v} x 2 channels; entry(xr) = a[xr] | a[xr - HALF] << 16,
+// i.e. the operands of disparity index w (low) and w + HALF (high) for left pixel x = xr + w.
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ void bt_channels(const uint8_t* img, int H, int W, int y, int x, int ftzero,
                                             int& p0, int& p1)
@@ -88,153 +110,248 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
     }
     {
         const uint8_t* img = right + (size_t)b * H * W;
-        int c0[4], c1[4];   // columns x-2 .. x+1
+        int c0[3], c1[3];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) bt_channels(img, H, W, y, min(max(x + k - 2, 0), W - 1), g.ftzero, c0[k], c1[k]);
-        uint32_t* base = rdesc + (size_t)(b * H + y) * 16 * g.Wh + (size_t)(x & 1) * g.Wh + (x >> 1);
+        for (int k = 0; k < 3; ++k) bt_channels(img, H, W, y, min(max(x + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
+        uint16_t* base = reinterpret_cast<uint16_t*>(rdesc + (size_t)(b * H + y) * 6 * g.Wp);
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
             const int* p = c ? c1 : c0;
-            int v[2], v0[2], v1[2];
+            int v = p[1];
+            int va = x < W - 1 ? (v + p[2]) / 2 : v;
+            int vb = x > 0 ? (v + p[0]) / 2 : v;
+            int v0 = min(min(va, vb), v), v1 = max(max(va, vb), v);
+            const uint16_t ops[3] = {(uint16_t)v1, (uint16_t)v0, (uint16_t)(-v)};
 #pragma unroll
-            for (int s = 0; s < 2; ++s) {           // s=0: pixel x, s=1: pixel x-1
-                int xx = x - s;
-                int vv = p[2 - s];
-                int va = xx < W - 1 ? (vv + p[3 - s]) / 2 : vv;
-                int vb = xx > 0 ? (vv + p[1 - s]) / 2 : vv;
-                v[s] = vv; v0[s] = min(min(va, vb), vv); v1[s] = max(max(va, vb), vv);
+            for (int o = 0; o < 3; ++o) {
+                uint16_t* plane = base + (size_t)(c * 3 + o) * 2 * g.Wp;
+                plane[2 * x] = ops[o];                                   // low half of entry x
+                if (x + g.HALF < g.Wp) plane[2 * (x + g.HALF) + 1] = ops[o];   // high half of entry x + HALF
             }
-            uint32_t ops[4] = {
-                (uint32_t)(v[0] & 0xffff) | ((uint32_t)(v[1] & 0xffff) << 16),
-                (uint32_t)((-v[0]) & 0xffff) | ((uint32_t)((-v[1]) & 0xffff) << 16),
-                (uint32_t)(v0[0] & 0xffff) | ((uint32_t)(v0[1] & 0xffff) << 16),
-                (uint32_t)((-v1[0]) & 0xffff) | ((uint32_t)((-v1[1]) & 0xffff) << 16)};
-#pragma unroll
-            for (int o = 0; o < 4; ++o) base[(size_t)(c * 4 + o) * 2 * g.Wh] = ops[o];
         }
     }
 }
 
 // ------------------------------------------------------------------------------------------
-// k_cost: one block = TY output rows x one x-segment of one job; one warp per input row
-// (TY + 2r of them, rows clamped into [ys, H-1] = replicate border, A.2).  Each warp slides
-// along x keeping the horizontal box sum of the BT pixel cost (A.1 step 4) in registers
-// (ring of the last bs pixel-cost vectors in shared memory); per column the warps meet in
-// shared memory and the first TY warps add bs rows -> C(y, xc, :) -> HBM.
-// Lane mapping here is "interleaved" (reg k, lane l <-> disparity pair e = 32k + l) so that
-// right-image descriptor loads are contiguous; memory order of the volume is natural.
+// cp.async helpers (LDGSTS)
 // ------------------------------------------------------------------------------------------
-template <int NP>
-__global__ void __launch_bounds__(1024) k_cost(const uint32_t* __restrict__ ldesc, const uint32_t* __restrict__ rdesc,
-                                               SgbmGeo g, int TY, int XSEG, uint16_t* __restrict__ vol)
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem)
 {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// ------------------------------------------------------------------------------------------
+// k_cost: one CTA walks DOWN a strip of columns of one job (a row segment of it).  Per image
+// row: every warp computes the BT pixel-cost vectors (A.1 step 4) of two strip columns from
+// operands staged in shared memory (cp.async, one row ahead) and parks them in a shared
+// buffer; after ONE block barrier every warp sums 2r+1 neighbouring columns (horizontal box,
+// A.2), pushes the sum into a per-column ring of the last bs rows and keeps the vertical box
+// sum C(y) = C(y-1) + hs(y+r) - hs(y-r-1) in registers -> HBM.  Replicate borders: columns clamp
+// in the cost domain, rows clamp into [ys, H-1].
+// Lane mapping: (reg k, lane l) <-> word w = 32k + l (descriptor loads and volume stores are
+// contiguous across the warp).
+// ------------------------------------------------------------------------------------------
+#define CK_WARPS 16
+#define CK_PC 32               // pixel-cost columns per strip (2 per warp)
+
+struct CostArgs {
+    int OC;                    // output columns per strip = CK_PC - 2r (or less when the ring is large)
+    int nstrips, rseg, nsegs;  // strips per row, rows per segment, segments per job
+    int SE;                    // staged right-descriptor entries per plane = HALF + CK_PC
+};
+
+template <int NP>
+__global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const uint32_t* __restrict__ ldesc, const uint32_t* __restrict__ rdesc,
+                                                        SgbmGeo g, CostArgs ca, uint32_t* __restrict__ vol)
+{
+    constexpr int VW = NP * 32;
     extern __shared__ uint32_t smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, NW = blockDim.x >> 5;
-    const int job = blockIdx.z, b = job / g.nstripes, n = job % g.nstripes;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int r = g.r, bs = 2 * r + 1, OC = ca.OC, PC = OC + 2 * r, SE = ca.SE;
+    uint32_t* stage = smem;                                  // [2][6][SE]
+    uint32_t* lstage = stage + 2 * 6 * SE;                   // [2][CK_PC][8]
+    uint32_t* pixbuf = lstage + 2 * CK_PC * 8;               // [2][CK_PC][VW]
+    uint32_t* ring = pixbuf + 2 * CK_PC * VW;                // [OC][bs][VW]
+
+    const int strip = blockIdx.x % ca.nstrips, seg = blockIdx.x / ca.nstrips;
+    const int job = blockIdx.y, b = job / g.nstripes, n = job % g.nstripes;
     int ys, ye, keep;
     job_rows(g, n, ys, ye, keep);
-    const int y0 = ys + blockIdx.y * TY;
-    if (y0 >= ye) return;
-    const int xs = blockIdx.x * XSEG, xe = min(xs + XSEG, g.width1);
-    const int r = g.r, bs = 2 * r + 1;
-    uint32_t* ring = smem + (size_t)warp * bs * NP * 32;            // [slot][k][lane]
-    uint32_t* hsb = smem + (size_t)NW * bs * NP * 32;               // [warp][k][lane]
-    const int yy = min(max(y0 - r + warp, ys), g.H - 1);
-    const uint32_t* lrow = ldesc + (size_t)(b * g.H + yy) * g.W * 8;
-    const uint32_t* rrow = rdesc + (size_t)(b * g.H + yy) * 16 * g.Wh;
-    for (int i = lane; i < bs * NP * 32; i += 32) ring[i] = 0;
-    __syncwarp();
-    uint32_t hs[NP];
-#pragma unroll
-    for (int k = 0; k < NP; ++k) hs[k] = 0;
-    uint16_t* volrow = vol + ((size_t)job * g.rowsMax + (y0 - ys + warp)) * g.width1 * g.Dp;
-    const bool out_warp = warp < TY && (y0 + warp) < ye;
+    const int ya = ys + seg * ca.rseg, yb = min(ya + ca.rseg, ye);   // output rows of this CTA
+    if (ya >= yb) return;
+    const int xs = strip * OC;                               // first output column (cost domain)
+    const int w1 = g.width1;
 
-    for (int j = xs - r; j < xe + r; ++j) {
-        const int q = min(max(j, 0), g.width1 - 1);
-        const int x = q + g.minX1;
-        const uint4 l0 = *reinterpret_cast<const uint4*>(lrow + (size_t)x * 8);
-        const uint4 l1 = *reinterpret_cast<const uint4*>(lrow + (size_t)x * 8 + 4);
-        const int xr0 = x - g.minD;                  // right column of disparity index 0
-        const uint32_t* rp = rrow + (size_t)(xr0 & 1) * g.Wh;
-        const int slot = (j - (xs - r)) % bs;
-#pragma unroll
-        for (int k = 0; k < NP; ++k) {
-            const int m = max((xr0 >> 1) - (32 * k + lane), 0);
-            uint32_t o[8];
-#pragma unroll
-            for (int t = 0; t < 8; ++t) o[t] = __ldg(rp + (size_t)t * 2 * g.Wh + m);
-            // channel 0 (prefiltered): c0 = max(0, u - v1, v0 - u); c1 = max(0, v - u1, u0 - v)
-            uint32_t a = __vadd2(l0.x, o[3]);
-            uint32_t c0 = __viaddmax_s16x2_relu(o[2], l0.y, a);
-            uint32_t bb = __vadd2(o[0], l0.w);
-            uint32_t c1 = __viaddmax_s16x2_relu(l0.z, o[1], bb);
-            uint32_t pix = __vminu2(c0, c1);
-            // channel 1 (raw intensity), cost >> 2
-            a = __vadd2(l1.x, o[7]);
-            c0 = __viaddmax_s16x2_relu(o[6], l1.y, a);
-            bb = __vadd2(o[4], l1.w);
-            c1 = __viaddmax_s16x2_relu(l1.z, o[5], bb);
-            pix += (__vminu2(c0, c1) >> 2) & 0x3fff3fffu;
-            uint32_t* rs = ring + (slot * NP + k) * 32 + lane;
-            hs[k] += pix - *rs;
-            *rs = pix;
+    // pix column c (0..PC-1) <-> cost column clamp(xs - r + c) ; image column = + minX1
+    // staged entries cover xr in [xbase, xbase + SE): xbase = (xs - r + minX1 - minD) - (HALF - 1)
+    const int xbase = xs - r + g.minX1 - g.minD - (g.HALF - 1);
+
+    auto issue_row = [&](int v, int buf) {
+        const int yy = min(max(v, ys), g.H - 1);
+        const uint32_t* rrow = rdesc + (size_t)(b * g.H + yy) * 6 * g.Wp;
+        uint32_t* st = stage + buf * 6 * SE;
+        for (int i = threadIdx.x; i < 6 * SE; i += blockDim.x) {
+            const int p = i / SE, e = i - p * SE;
+            const int xr = min(max(xbase + e, 0), g.W - 1);
+            cp_async4(st + i, rrow + (size_t)p * g.Wp + xr);
         }
-        if (j - r >= xs) {
-            const int xc = j - r;
+        const uint32_t* lrow = ldesc + (size_t)(b * g.H + yy) * g.W * 8;
+        uint32_t* ls = lstage + buf * CK_PC * 8;
+        for (int i = threadIdx.x; i < PC * 2; i += blockDim.x) {
+            const int c = i >> 1, h = i & 1;
+            const int x = min(max(xs - r + c, 0), w1 - 1) + g.minX1;
+            cp_async16(ls + c * 8 + h * 4, lrow + (size_t)x * 8 + h * 4);
+        }
+    };
+
+    // pad mask for this lane's words (w = 32k + lane)
+    uint32_t padm[NP];
 #pragma unroll
-            for (int k = 0; k < NP; ++k) hsb[(warp * NP + k) * 32 + lane] = hs[k];
-            __syncthreads();
-            if (out_warp) {
-                uint32_t* dst = reinterpret_cast<uint32_t*>(volrow + (size_t)xc * g.Dp);
+    for (int k = 0; k < NP; ++k) {
+        const int w = 32 * k + lane;
+        padm[k] = (w >= g.D ? 0xffffu : 0u) | (w + g.HALF >= g.D ? 0xffff0000u : 0u);
+    }
+
+    uint32_t acc[2][NP];
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int k = 0; k < NP; ++k) acc[c][k] = 0;
+
+    const int v0 = ya - r, v1 = yb - 1 + r;                  // virtual input rows (clamped on use)
+    issue_row(v0, 0);
+    asm volatile("cp.async.commit_group;");
+    if (v0 + 1 <= v1) issue_row(v0 + 1, 1);
+    asm volatile("cp.async.commit_group;");
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncthreads();
+
+    for (int v = v0; v <= v1; ++v) {
+        const int it = v - v0, buf = it & 1;
+        const uint32_t* st = stage + buf * 6 * SE;
+        const uint32_t* ls = lstage + buf * CK_PC * 8;
+        uint32_t* pb = pixbuf + buf * CK_PC * VW;
+        // ---- pixel costs of this warp's two strip columns
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int c = 2 * warp + cc;
+            if (c < PC) {
+                const uint4 l0 = *reinterpret_cast<const uint4*>(ls + c * 8);
+                const uint4 l1 = *reinterpret_cast<const uint4*>(ls + c * 8 + 4);
+                // entry index of word w: (x_img - minD - w) - xbase, x_img = clamp(xs-r+c)+minX1
+                const int xq = min(max(xs - r + c, 0), w1 - 1);
+                const int e0 = (xq + g.minX1 - g.minD) - xbase - lane;
 #pragma unroll
                 for (int k = 0; k < NP; ++k) {
-                    uint32_t c = 0;
-                    for (int t = 0; t < bs; ++t) c += hsb[((warp + t) * NP + k) * 32 + lane];
-                    if (2 * (32 * k + lane) >= g.D) c = WALL2;
-                    dst[32 * k + lane] = c;
+                    const int e = e0 - 32 * k;
+                    const uint32_t v1a = st[0 * SE + e], v0a = st[1 * SE + e], nva = st[2 * SE + e];
+                    const uint32_t v1b = st[3 * SE + e], v0b = st[4 * SE + e], nvb = st[5 * SE + e];
+                    // channel 0: c0 = max(0, u - v1, v0 - u); c1 = max(0, v - u1, u0 - v)
+                    uint32_t a = __vsub2(l0.x, v1a);
+                    uint32_t c0 = __viaddmax_s16x2_relu(v0a, l0.y, a);
+                    uint32_t bb = __vsub2(l0.w, nva);
+                    uint32_t c1 = __viaddmax_s16x2_relu(l0.z, nva, bb);
+                    uint32_t pix = __vminu2(c0, c1);
+                    // channel 1 (raw intensity), cost >> 2
+                    a = __vsub2(l1.x, v1b);
+                    c0 = __viaddmax_s16x2_relu(v0b, l1.y, a);
+                    bb = __vsub2(l1.w, nvb);
+                    c1 = __viaddmax_s16x2_relu(l1.z, nvb, bb);
+                    pix += (__vminu2(c0, c1) >> 2) & 0x3fff3fffu;
+                    pb[c * VW + 32 * k + lane] = pix;
                 }
             }
-            __syncthreads();
+        }
+        cp_async_wait_all();
+        __syncthreads();
+        if (v + 2 <= v1) issue_row(v + 2, buf);
+        asm volatile("cp.async.commit_group;");
+        // ---- horizontal box over 2r+1 columns, vertical running sum, store
+        const int oc0 = 2 * warp;
+        if (oc0 < OC) {
+            uint32_t hs0[NP], hs1[NP];
+#pragma unroll
+            for (int k = 0; k < NP; ++k) hs0[k] = 0;
+            for (int j = 0; j < bs; ++j) {
+#pragma unroll
+                for (int k = 0; k < NP; ++k) hs0[k] += pb[(oc0 + j) * VW + 32 * k + lane];
+            }
+            const bool two = oc0 + 1 < OC;
+            if (two) {
+#pragma unroll
+                for (int k = 0; k < NP; ++k)
+                    hs1[k] = hs0[k] - pb[oc0 * VW + 32 * k + lane] + pb[(oc0 + bs) * VW + 32 * k + lane];
+            }
+            const int slot = it % bs;
+            const bool full = it >= bs;                       // ring holds hs(v - bs) in `slot`
+            const int y = v - r;                              // output row once the window is complete
+            const bool emit = it >= bs - 1;
+#pragma unroll
+            for (int cc = 0; cc < 2; ++cc) {
+                if (cc == 1 && !two) break;
+                const int oc = oc0 + cc;
+                uint32_t* rg = ring + ((size_t)oc * bs + slot) * VW;
+                const int xc = xs + oc;
+#pragma unroll
+                for (int k = 0; k < NP; ++k) {
+                    const uint32_t h = cc ? hs1[k] : hs0[k];
+                    const uint32_t old = full ? rg[32 * k + lane] : 0u;
+                    rg[32 * k + lane] = h;
+                    acc[cc][k] += h - old;
+                }
+                if (emit && xc < w1) {
+                    uint32_t* dst = vol + (((size_t)job * g.rowsMax + (y - ys)) * w1 + xc) * VW;
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) dst[32 * k + lane] = (acc[cc][k] & ~padm[k]) | (WALL2 & padm[k]);
+                }
+            }
         }
     }
 }
 
 // ------------------------------------------------------------------------------------------
-// Chunked per-lane view of one pixel's disparity vector: lane l, reg k <-> pair e = NP*l + k.
+// Vector helpers for the sweep: lane l <-> words NP*l .. NP*l+NP-1 of a pixel's vector.
 // ------------------------------------------------------------------------------------------
-template <int NP>
-__device__ __forceinline__ void load_vec(const uint16_t* p, int lane, uint32_t (&v)[NP])
+template <int NP, typename LD>
+__device__ __forceinline__ void vec_ld(const uint32_t* p, int lane, uint32_t (&v)[NP], LD ld4)
 {
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(p) + NP * lane;
+    const uint32_t* w = p + NP * lane;
     if constexpr (NP % 4 == 0) {
 #pragma unroll
         for (int i = 0; i < NP / 4; ++i) {
-            uint4 t = reinterpret_cast<const uint4*>(w)[i];
+            uint4 t = ld4(reinterpret_cast<const uint4*>(w) + i);
             v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
-        }
-    } else if constexpr (NP % 2 == 0) {
-#pragma unroll
-        for (int i = 0; i < NP / 2; ++i) {
-            uint2 t = reinterpret_cast<const uint2*>(w)[i];
-            v[2 * i] = t.x; v[2 * i + 1] = t.y;
         }
     } else {
 #pragma unroll
-        for (int i = 0; i < NP; ++i) v[i] = w[i];
+        for (int i = 0; i < NP; ++i) v[i] = ld4(w + i);
     }
 }
+struct LdPlain {
+    __device__ __forceinline__ uint4 operator()(const uint4* p) const { return *p; }
+    __device__ __forceinline__ uint32_t operator()(const uint32_t* p) const { return *p; }
+};
+struct LdNc {     // read-only data written by an earlier kernel
+    __device__ __forceinline__ uint4 operator()(const uint4* p) const { return __ldg(p); }
+    __device__ __forceinline__ uint32_t operator()(const uint32_t* p) const { return __ldg(p); }
+};
+struct LdCg {     // data written by another CTA of this kernel: bypass L1
+    __device__ __forceinline__ uint4 operator()(const uint4* p) const { return __ldcg(p); }
+    __device__ __forceinline__ uint32_t operator()(const uint32_t* p) const { return __ldcg(p); }
+};
 template <int NP>
-__device__ __forceinline__ void store_vec(uint16_t* p, int lane, const uint32_t (&v)[NP])
+__device__ __forceinline__ void vec_st(uint32_t* p, int lane, const uint32_t (&v)[NP])
 {
-    uint32_t* w = reinterpret_cast<uint32_t*>(p) + NP * lane;
+    uint32_t* w = p + NP * lane;
     if constexpr (NP % 4 == 0) {
 #pragma unroll
         for (int i = 0; i < NP / 4; ++i)
             reinterpret_cast<uint4*>(w)[i] = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-    } else if constexpr (NP % 2 == 0) {
-#pragma unroll
-        for (int i = 0; i < NP / 2; ++i) reinterpret_cast<uint2*>(w)[i] = make_uint2(v[2 * i], v[2 * i + 1]);
     } else {
 #pragma unroll
         for (int i = 0; i < NP; ++i) w[i] = v[i];
@@ -244,188 +361,309 @@ __device__ __forceinline__ void store_vec(uint16_t* p, int lane, const uint32_t 
 // One step of the SGM recurrence (A.3) for a whole disparity vector held by a warp.
 //   L(d) = C(d) + min(Lq(d), Lq(d-1)+P1, Lq(d+1)+P1, minLq+P2) - minLq
 // Lq is updated in place; returns the warp-wide min of the new L (minLq for the next step).
-template <int NP>
+template <int NP, bool FULL>
 __device__ __forceinline__ uint32_t sgm_step(uint32_t (&Lq)[NP], const uint32_t (&C)[NP], uint32_t minq,
-                                             uint32_t P1P1, uint32_t P2, int lane, int npairs_valid)
+                                             uint32_t P1P1, uint32_t P2, int lane, const uint32_t (&padm)[NP])
 {
-    // neighbours across lane boundaries; the vector ends see the wall
-    uint32_t prev_last = __shfl_up_sync(0xffffffffu, Lq[NP - 1], 1);
-    uint32_t next_first = __shfl_down_sync(0xffffffffu, Lq[0], 1);
-    if (lane == 0) prev_last = WALL2;
-    if (lane == 31) next_first = WALL2;
+    // neighbours across lane boundaries; both halves of a word move together, except at the
+    // two seams: word 0's high half continues word HALF-1's low half, and the ends see the wall
+    uint32_t prev = __shfl_sync(FULLMASK, Lq[NP - 1], (lane + 31) & 31);
+    uint32_t next = __shfl_sync(FULLMASK, Lq[0], (lane + 1) & 31);
+    if (lane == 0) prev = __byte_perm(prev, WALL2, 0x1054);     // (lo = wall, hi = lane31.lo)
+    if (lane == 31) next = __byte_perm(next, WALL2, 0x5432);    // (lo = lane0.hi, hi = wall)
     const uint32_t mq2 = pk_dup(minq);
     const uint32_t mqP2 = pk_dup(minq + P2);
-    uint32_t up = pk_shift_in(prev_last, Lq[0]);            // (Lq[d-1], Lq[d]) for reg 0
+    uint32_t up = prev;
     uint32_t mloc = 0xffffffffu;
 #pragma unroll
     for (int k = 0; k < NP; ++k) {
-        const uint32_t nxt = (k + 1 < NP) ? Lq[k + 1] : next_first;
-        const uint32_t dn = pk_shift_in(Lq[k], nxt);        // (Lq[d+1], Lq[d+2])
+        const uint32_t dn = (k + 1 < NP) ? Lq[k + 1] : next;
         uint32_t t = pk_min(up, dn);
         t = pk_addmin(t, P1P1, Lq[k]);
         t = pk_min(t, mqP2);
-        uint32_t L = C[k] + t - mq2;                        // halves stay in [0, 65535]: no carries
-        if (NP * lane + k >= npairs_valid) L = WALL2;       // pad lanes keep the wall
-        up = dn;
+        uint32_t L = C[k] + t - mq2;                         // halves stay in [0, 65535]: no carries
+        if (!FULL) L = (L & ~padm[k]) | (WALL2 & padm[k]);   // pad disparities keep the wall
+        up = Lq[k];
         Lq[k] = L;
         mloc = pk_min(mloc, L);
     }
-    return __reduce_min_sync(0xffffffffu, pk_hmin(mloc));
+    return __reduce_min_sync(FULLMASK, pk_hmin(mloc));
 }
 
-// ------------------------------------------------------------------------------------------
-// k_path: one warp follows one path line of direction (dx,dy) through the job's rows.
-// dy == 0: line = one row, x runs 0..w1-1 (dx>0) or back (dx<0).
-// dy != 0: line = start column x0; at step t the warp is at column (x0 + dx*t) mod w1 and
-// restarts (Lq = 0, minLq = 0: "outside" predecessor) whenever it wraps around an image edge,
-// so every warp does the same number of steps.
-// ------------------------------------------------------------------------------------------
-template <int NP>
-__global__ void __launch_bounds__(256) k_path(const uint16_t* __restrict__ Cvol, uint16_t* __restrict__ Svol,
-                                              SgbmGeo g, int dx, int dy, int first, int njobs)
+__device__ __forceinline__ int ld_acquire_gpu(const int* p)
 {
-    const int lane = threadIdx.x & 31;
-    const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v)
+{
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+struct SweepArgs {
+    const uint32_t* C;        // [job][rowsMax][w1][VW]
+    uint32_t* S;              // same shape: sweep 1 writes S1, sweep 2 reads it
+    uint32_t* carry;          // [job][2][w1][3][VW]   L_r of a band's last row (per path)
+    uint32_t* cmin;           // [job][2][w1][4]       their minima
+    int* prog;                // [job][bandsPerJob]    columns of the band's last row published
+    int* ticket;              // band dispenser
+    int* err;                 // set when a wait ran into the spin limit
+    int16_t* raw;             // [img][H][W]   (sweep 2)
+    uint32_t* key;            // [img][H][W]   right-view scatter-min keys (sweep 2)
+    int njobs, bandsPerJob;
+    int dir;                  // +1: rows top-down, columns left-to-right; -1: the opposite
+    int mask;                 // paths: 1 horizontal, 2 diagonal from behind, 4 vertical, 8 diagonal from ahead
+    int storeS;               // debug: sweep 2 writes the final S back
+};
+
+// VAR 0: D < Dp (pad disparities), saturating sums; 1: D == Dp, saturating sums;
+// 2: D == Dp and the per-sweep sum of L_r cannot reach 32768 -> plain adds.
+template <int NP, int VAR, bool LAST>
+__global__ void __launch_bounds__(SW_R * 32, 1) k_sweep(const SweepArgs a, const SgbmGeo g)
+{
+    constexpr bool FULL = VAR != 0, FAST = VAR == 2;
+    constexpr int VW = NP * 32;
+    extern __shared__ uint32_t smem[];
+    uint32_t* ring = smem;                                   // [SW_R][3][SW_RING][VW]: INPUT ring of each warp
+    uint32_t* rmin = ring + SW_R * 3 * SW_RING * VW;         // [SW_R][3][SW_RING]
+    uint32_t* wsc = rmin + SW_R * 3 * SW_RING;               // [SW_R][VW] (sweep 2: S vector for the subpixel taps)
+    __shared__ int s_ticket;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int w1 = g.width1;
-    const int npv = g.D >> 1;
     const uint32_t P1P1 = pk_dup(g.P1);
-    int job, ys, ye, keep;
-    uint32_t Lq[NP], C[NP], S[NP];
-#pragma unroll
-    for (int k = 0; k < NP; ++k) Lq[k] = 0;
-    uint32_t minq = 0;
-    if (dy == 0) {
-        job = (int)(gw / g.rowsMax);
-        if (job >= njobs) return;
-        job_rows(g, job % g.nstripes, ys, ye, keep);
-        const int row = (int)(gw % g.rowsMax);
-        if (row >= ye - ys) return;
-        const size_t base = ((size_t)job * g.rowsMax + row) * w1 * g.Dp;
-        for (int t = 0; t < w1; ++t) {
-            const int xc = dx > 0 ? t : w1 - 1 - t;
-            const size_t off = base + (size_t)xc * g.Dp;
-            load_vec<NP>(Cvol + off, lane, C);
-            if (!first) load_vec<NP>(Svol + off, lane, S);
-            minq = sgm_step<NP>(Lq, C, minq, P1P1, g.P2, lane, npv);
-#pragma unroll
-            for (int k = 0; k < NP; ++k) S[k] = first ? pk_min(Lq[k], WALL2) : pk_addmin(S[k], Lq[k], WALL2);
-            store_vec<NP>(Svol + off, lane, S);
-        }
-    } else {
-        job = (int)(gw / w1);
-        if (job >= njobs) return;
-        job_rows(g, job % g.nstripes, ys, ye, keep);
-        const int x0 = (int)(gw % w1);
-        const int nrows = ye - ys;
-        int xc = x0;
-        for (int t = 0; t < nrows; ++t) {
-            const int row = dy > 0 ? t : nrows - 1 - t;
-            if (t > 0 && dx != 0) {
-                xc += dx;
-                bool wrap = false;
-                if (xc >= w1) { xc = 0; wrap = true; }
-                if (xc < 0) { xc = w1 - 1; wrap = true; }
-                if (wrap) {
-#pragma unroll
-                    for (int k = 0; k < NP; ++k) Lq[k] = 0;
-                    minq = 0;
-                }
-            }
-            const size_t off = (((size_t)job * g.rowsMax + row) * w1 + xc) * g.Dp;
-            load_vec<NP>(Cvol + off, lane, C);
-            if (!first) load_vec<NP>(Svol + off, lane, S);
-            minq = sgm_step<NP>(Lq, C, minq, P1P1, g.P2, lane, npv);
-#pragma unroll
-            for (int k = 0; k < NP; ++k) S[k] = first ? pk_min(Lq[k], WALL2) : pk_addmin(S[k], Lq[k], WALL2);
-            store_vec<NP>(Svol + off, lane, S);
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------
-// k_wta: one warp per cost-domain pixel of a kept row (A.4): argmin (lowest d on ties,
-// fully saturated column -> invalid), uniqueness, subpixel parabola, right-view map by
-// atomicMin on key = minS<<16 | (0xffff - x): smallest cost wins, then the largest x, which is
-// the pixel cv2's right-to-left loop would have kept.
-// ------------------------------------------------------------------------------------------
-template <int NP>
-__global__ void __launch_bounds__(256) k_wta(const uint16_t* __restrict__ Svol, SgbmGeo g, int njobs, int img0,
-                                             int16_t* __restrict__ raw, uint32_t* __restrict__ disp2key)
-{
-    const int lane = threadIdx.x & 31;
-    const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int w1 = g.width1;
-    const long long per_job = (long long)g.rowsMax * w1;
-    const int job = (int)(gw / per_job);
-    if (job >= njobs) return;
-    int ys, ye, keep;
-    job_rows(g, job % g.nstripes, ys, ye, keep);
-    const int rem = (int)(gw % per_job);
-    const int row = rem / w1, xc = rem % w1;
-    const int y = ys + row;
-    if (y >= ye || y < keep) return;
-    const int b = job / g.nstripes;
-    uint32_t S[NP];
-    load_vec<NP>(Svol + (((size_t)job * g.rowsMax + row) * w1 + xc) * g.Dp, lane, S);
-    const int dbase = 2 * NP * lane;
-    uint32_t key = 0xffffffffu;
+    const int dir = a.dir, mask = a.mask;
+    uint32_t padm[NP];
 #pragma unroll
     for (int k = 0; k < NP; ++k) {
-        const int d = dbase + 2 * k;
-        uint32_t lo = S[k] & 0xffffu, hi = S[k] >> 16;
-        if (d < g.D) key = min(key, (lo << 16) | (uint32_t)d);
-        if (d + 1 < g.D) key = min(key, (hi << 16) | (uint32_t)(d + 1));
+        const int w = NP * lane + k;
+        padm[k] = (w >= g.D ? 0xffffu : 0u) | (w + g.HALF >= g.D ? 0xffff0000u : 0u);
     }
-    key = __reduce_min_sync(0xffffffffu, key);
-    const int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
-    const size_t pix = ((size_t)(img0 + b) * g.H + y) * g.W + (xc + g.minX1);
-    if (minS >= (int)WALL) { if (lane == 0) raw[pix] = (int16_t)g.INV; return; }
-    bool rej = false;
-    if (g.mode == SVB_MODE_SGBM_3WAY) {
-        // cv2's 3WAY vector loop: Sp[d] < (short)(100*minS/(100-u) + 1)  (see oracle/sgbm_oracle.c)
-        if (g.uniq > 0) {
-            const int th = (int)(int16_t)((100 * minS) / (100 - g.uniq) + 1);
-#pragma unroll
-            for (int k = 0; k < NP; ++k) {
-                const int d = dbase + 2 * k;
-                const int lo = (int)(int16_t)(S[k] & 0xffffu), hi = (int)(int16_t)(S[k] >> 16);
-                rej |= (d < g.D && abs(d - best) > 1 && lo < th);
-                rej |= (d + 1 < g.D && abs(d + 1 - best) > 1 && hi < th);
+    uint32_t* ring_in = ring + (size_t)warp * 3 * SW_RING * VW;
+    uint32_t* rmin_in = rmin + warp * 3 * SW_RING;
+    uint32_t* ring_out = ring_in + 3 * SW_RING * VW;         // input ring of warp + 1
+    uint32_t* rmin_out = rmin_in + 3 * SW_RING;
+    uint32_t* mysc = wsc + warp * VW;
+
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_ticket = atomicAdd(a.ticket, 1);
+        __syncthreads();
+        const int t = s_ticket;
+        if (t >= a.njobs * a.bandsPerJob) break;
+        const int job = t % a.njobs, band = t / a.njobs;
+        int ys, ye, keep;
+        job_rows(g, job % g.nstripes, ys, ye, keep);
+        const int nrows = ye - ys, r0 = band * SW_R;
+        const int nact = min(SW_R, nrows - r0);
+        if (nact <= 0) continue;
+
+        const bool active = warp < nact;
+        const int sr = r0 + warp;                            // row index in sweep order
+        const int row = dir > 0 ? sr : nrows - 1 - sr;       // storage row within the job
+        const int y = ys + row;
+        const bool havePred = sr > 0;
+        const bool vert = (mask & 14) != 0;                  // any path that crosses rows
+        const bool feed = vert && (warp == 0) && band > 0;   // warp 0 feeds its ring from the carry
+        const bool lastInBand = warp == nact - 1;
+        const bool succSmem = vert && active && !lastInBand;
+        const bool succGlob = vert && active && lastInBand && (r0 + nact < nrows);
+        const bool rowSkip = LAST && mask == 1 && y < keep;  // 3WAY overlap rows: nothing depends on them
+        const size_t rowbase = (((size_t)job * g.rowsMax + row) * w1) * VW;
+        const uint32_t* carry_in = a.carry + (((size_t)job * 2 + ((band + 1) & 1)) * w1) * 3 * VW;
+        const uint32_t* cmin_in = a.cmin + (((size_t)job * 2 + ((band + 1) & 1)) * w1) * 4;
+        uint32_t* carry_out = a.carry + (((size_t)job * 2 + (band & 1)) * w1) * 3 * VW;
+        uint32_t* cmin_out = a.cmin + (((size_t)job * 2 + (band & 1)) * w1) * 4;
+        const int* prog_pred = a.prog + (size_t)job * a.bandsPerJob + band - 1;
+        int* prog_mine = a.prog + (size_t)job * a.bandsPerJob + band;
+        const int b = job / g.nstripes;
+
+        // ---- warp 0 of a non-first band: columns 0,1 of the carry into the ring, column 2 in flight
+        uint32_t pre[3][NP];
+        uint32_t premin = 0;
+        int seen = 0;
+        auto wait_cols = [&](int need) {     // all lanes of warp 0
+            if (seen < need) {
+                if (lane == 0) {
+                    int spins = 0;
+                    while ((seen = ld_acquire_gpu(prog_pred)) < need) {
+                        if (++spins > SW_SPIN_LIMIT) { atomicExch(a.err, 1); break; }
+                        __nanosleep(40);
+                    }
+                }
+                seen = __shfl_sync(FULLMASK, seen, 0);
+                __syncwarp();
             }
-        }
-    } else {
-        const int lim = minS * 100, f = 100 - g.uniq;
+        };
+        auto fetch_col = [&](int c) {
 #pragma unroll
-        for (int k = 0; k < NP; ++k) {
-            const int d = dbase + 2 * k;
-            const int lo = (int)(S[k] & 0xffffu), hi = (int)(S[k] >> 16);
-            rej |= (d < g.D && abs(d - best) > 1 && lo * f < lim);
-            rej |= (d + 1 < g.D && abs(d + 1 - best) > 1 && hi * f < lim);
-        }
-    }
-    rej = __any_sync(0xffffffffu, rej);
-    if (rej) { if (lane == 0) raw[pix] = (int16_t)g.INV; return; }
-    // neighbours of best for the parabola
-    const uint32_t prev_last = __shfl_up_sync(0xffffffffu, S[NP - 1], 1) >> 16;
-    const uint32_t next_first = __shfl_down_sync(0xffffffffu, S[0], 1) & 0xffffu;
-    if (best >= dbase && best < dbase + 2 * NP) {
-        int sm1 = 0, sp1 = 0;
+            for (int p = 0; p < 3; ++p) vec_ld<NP>(carry_in + ((size_t)c * 3 + p) * VW, lane, pre[p], LdCg());
+            if (lane < 3) premin = __ldcg(cmin_in + (size_t)c * 4 + lane);
+        };
+        auto stash_col = [&](int c) {
+            const int slot = c & (SW_RING - 1);
 #pragma unroll
-        for (int j = 0; j < 2 * NP; ++j) {
-            if (dbase + j == best) {
-                sm1 = j == 0 ? (int)prev_last : (int)((j & 1) ? (S[j >> 1] & 0xffffu) : (S[(j - 1) >> 1] >> 16));
-                sp1 = j == 2 * NP - 1 ? (int)next_first : (int)((j & 1) ? (S[(j + 1) >> 1] & 0xffffu) : (S[j >> 1] >> 16));
+            for (int p = 0; p < 3; ++p) vec_st<NP>(ring_in + (p * SW_RING + slot) * VW, lane, pre[p]);
+            if (lane < 3) rmin_in[lane * SW_RING + slot] = premin;
+        };
+        if (feed) {
+            wait_cols(min(3, w1));
+            fetch_col(0); stash_col(0);
+            if (w1 > 1) { fetch_col(1); stash_col(1); }
+            if (w1 > 2) fetch_col(2);
+        }
+
+        uint32_t Lh[NP], Cn[NP], Sn[NP];
+#pragma unroll
+        for (int k = 0; k < NP; ++k) { Lh[k] = 0; Cn[k] = 0; Sn[k] = 0; }
+        uint32_t minh = 0;
+        const int nsteps = w1 + SW_SK * (nact - 1);
+        __syncthreads();
+
+        for (int s = 0; s < nsteps; ++s) {
+            const int i = s - SW_SK * warp;
+            if (active && !rowSkip && i >= 0 && i < w1) {
+                const int xc = dir > 0 ? i : w1 - 1 - i;
+                uint32_t C[NP], S[NP];
+                if (i == 0) {
+                    vec_ld<NP>(a.C + rowbase + (size_t)xc * VW, lane, Cn, LdNc());
+                    if (LAST) vec_ld<NP>(a.S + rowbase + (size_t)xc * VW, lane, Sn, LdPlain());
+                }
+#pragma unroll
+                for (int k = 0; k < NP; ++k) { C[k] = Cn[k]; S[k] = LAST ? Sn[k] : 0u; }
+                if (i + 1 < w1) {                            // next column's operands: one step ahead
+                    const int xn = xc + dir;
+                    vec_ld<NP>(a.C + rowbase + (size_t)xn * VW, lane, Cn, LdNc());
+                    if (LAST) vec_ld<NP>(a.S + rowbase + (size_t)xn * VW, lane, Sn, LdPlain());
+                }
+                uint32_t sum[NP];                            // FAST: plain sum of this sweep's L_r
+#pragma unroll
+                for (int k = 0; k < NP; ++k) sum[k] = 0;
+
+                // horizontal path: predecessor is this warp's previous column
+                if (mask & 1) {
+                    minh = sgm_step<NP, FULL>(Lh, C, minh, P1P1, (uint32_t)g.P2, lane, padm);
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) {
+                        if (FAST) sum[k] += Lh[k];
+                        else S[k] = pk_addmin(S[k], Lh[k], WALL2);
+                    }
+                }
+                // the three paths coming from the previous row of the sweep
+#pragma unroll
+                for (int p = 0; p < 3; ++p) {
+                    if (!(mask & (2 << p))) continue;
+                    const int cp = i - 1 + p;                // predecessor column (sweep order)
+                    const bool pv = havePred && cp >= 0 && cp < w1;
+                    uint32_t Lt[NP];
+                    uint32_t mq = 0;
+                    if (pv) {
+                        const int slot = cp & (SW_RING - 1);
+                        vec_ld<NP>(ring_in + (p * SW_RING + slot) * VW, lane, Lt, LdPlain());
+                        mq = rmin_in[p * SW_RING + slot];
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < NP; ++k) Lt[k] = 0;
+                    }
+                    const uint32_t m = sgm_step<NP, FULL>(Lt, C, mq, P1P1, (uint32_t)g.P2, lane, padm);
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) {
+                        if (FAST) sum[k] += Lt[k];
+                        else S[k] = pk_addmin(S[k], Lt[k], WALL2);
+                    }
+                    if (succSmem) {
+                        const int slot = i & (SW_RING - 1);
+                        vec_st<NP>(ring_out + (p * SW_RING + slot) * VW, lane, Lt);
+                        if (lane == 0) rmin_out[p * SW_RING + slot] = m;
+                    } else if (succGlob) {
+                        vec_st<NP>(carry_out + ((size_t)i * 3 + p) * VW, lane, Lt);
+                        if (lane == 0) cmin_out[(size_t)i * 4 + p] = m;
+                    }
+                }
+                if (FAST) {
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) S[k] = LAST ? pk_addmin(S[k], sum[k], WALL2) : sum[k];
+                }
+                if (succGlob && (((i & (SW_FLAG_EVERY - 1)) == SW_FLAG_EVERY - 1) || i == w1 - 1)) {
+                    __syncwarp();
+                    if (lane == 0) st_release_gpu(prog_mine, i + 1);
+                }
+
+                if (!LAST) {
+                    vec_st<NP>(a.S + rowbase + (size_t)xc * VW, lane, S);
+                } else {
+                    if (a.storeS) vec_st<NP>(a.S + rowbase + (size_t)xc * VW, lane, S);
+                    if (y >= keep) {
+                        // ---- WTA (A.4): argmin with lowest-d tie break via keys (S << 16 | d)
+                        uint32_t kmin = 0xffffffffu;
+                        const uint32_t dlo = NP * lane, dhi = NP * lane + g.HALF;
+#pragma unroll
+                        for (int k = 0; k < NP; ++k) {
+                            const uint32_t klo = (S[k] << 16) | (dlo + k);
+                            const uint32_t khi = __byte_perm(S[k], dhi + k, 0x3254);
+                            kmin = min(kmin, min(klo, khi));
+                        }
+                        kmin = __reduce_min_sync(FULLMASK, kmin);
+                        const int minS = (int)(kmin >> 16), best = (int)(kmin & 0xffffu);
+                        // uniqueness: count disparities with S < th; the ones at best-1..best+1 do not count
+                        int th;
+                        if (g.mode == SVB_MODE_SGBM_3WAY) {
+                            // cv2's 3WAY vector loop: Sp[d] < (short)(100*minS/(100-u) + 1) (oracle/sgbm_oracle.c)
+                            th = g.uniq > 0 ? (int)(int16_t)((100 * minS) / (100 - g.uniq) + 1) : 0;
+                            th = max(th, 0);
+                        } else {
+                            const int f = 100 - g.uniq;
+                            th = (minS * 100 + f - 1) / f;   // S*f < minS*100  <=>  S < ceil(minS*100/f)
+                        }
+                        th = min(th, 0x8000);
+                        const uint32_t th2 = pk_dup((uint32_t)th);
+                        uint32_t cnt2 = 0;
+#pragma unroll
+                        for (int k = 0; k < NP; ++k) {
+                            uint32_t lt = (__vsub2(S[k], th2) >> 15) & 0x00010001u;   // S, th in [0, 0x8000]
+                            if (!FULL) lt &= ~padm[k];
+                            cnt2 += lt;
+                        }
+                        const int cnt = (int)__reduce_add_sync(FULLMASK, (cnt2 & 0xffffu) + (cnt2 >> 16));
+                        vec_st<NP>(mysc, lane, S);
+                        __syncwarp();
+                        if (lane == 0) {
+                            const size_t pix = ((size_t)b * g.H + y) * g.W + (xc + g.minX1);
+                            int out = g.INV;
+                            if (minS < (int)WALL) {
+                                const uint16_t* sv = reinterpret_cast<const uint16_t*>(mysc);
+                                auto tap = [&](int d) { return (int)sv[d < g.HALF ? 2 * d : 2 * (d - g.HALF) + 1]; };
+                                const int sm1 = best > 0 ? tap(best - 1) : 0;
+                                const int sp1 = best < g.D - 1 ? tap(best + 1) : 0;
+                                const int excl = (minS < th) + (best > 0 && sm1 < th) + (best < g.D - 1 && sp1 < th);
+                                if (cnt <= excl) {
+                                    int dsub = best * 16;
+                                    if (best > 0 && best < g.D - 1) {
+                                        const int den = max(sm1 + sp1 - 2 * minS, 1);
+                                        dsub += ((sm1 - sp1) * 16 + den) / (2 * den);   // C division: truncates toward zero
+                                    }
+                                    out = dsub + g.minD * 16;
+                                    const int x = xc + g.minX1;
+                                    const int x2 = x - best - g.minD;
+                                    // smallest cost wins, then the largest x: the pixel cv2's right-to-left loop keeps
+                                    atomicMin(a.key + ((size_t)b * g.H + y) * g.W + x2,
+                                              ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+                                }
+                            }
+                            a.raw[pix] = (int16_t)out;
+                        }
+                        __syncwarp();
+                    }
+                }
             }
+            if (feed) {
+                const int cs = s + 2, cf = s + 3;
+                if (cs < w1) stash_col(cs);
+                if (cf < w1) { wait_cols(cf + 1); fetch_col(cf); }
+            }
+            __syncthreads();
         }
-        int dsub = best * 16;
-        if (best > 0 && best < g.D - 1) {
-            const int den = max(sm1 + sp1 - 2 * minS, 1);
-            dsub += ((sm1 - sp1) * 16 + den) / (2 * den);      // C division: truncates toward zero
-        }
-        raw[pix] = (int16_t)(dsub + g.minD * 16);
-        const int x = xc + g.minX1;
-        const int x2 = x - best - g.minD;
-        atomicMin(disp2key + ((size_t)(img0 + b) * g.H + y) * g.W + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
     }
 }
 
@@ -466,17 +704,19 @@ __global__ void k_fill_s16(int16_t* p, size_t n, int16_t v)
 // ------------------------------------------------------------------------------------------
 struct svb_sgbm {
     svb_sgbm_params prm;
-    size_t ws_limit = (size_t)24 << 30;
+    size_t ws_limit = 0;            // 0: 60 % of the free device memory at first use
     SvbBuf ws;
     SvbBuf stage_in, stage_out;     // device staging for the *_host entry point
     int launches = 0;
+    int num_sms = 0;
+    bool debug = false;             // keep the final S volume (debug_stages)
     // optional per-stage timing with CUDA events on the launching stream (bench.py's roofline)
     bool profiling = false;
     struct Ev { int cat; cudaEvent_t a, b; };
     std::vector<Ev> evs;
     // last compute (for debug_stages)
     SgbmGeo last_geo{};
-    size_t off_C = 0, off_S = 0, off_raw = 0;
+    size_t off_C = 0, off_S = 0, off_raw = 0, off_err = 0;
     bool have_last = false;
 };
 
@@ -492,7 +732,7 @@ static int make_geo(const svb_sgbm_params& p, int H, int W, SgbmGeo& g)
     if (p.mode == SVB_MODE_HH4) { svb_set_error("MODE_HH4 is not implemented"); return SVB_ERR_UNSUPPORTED; }
     if (p.mode < 0 || p.mode > 3) { svb_set_error("bad mode %d", p.mode); return SVB_ERR_PARAM; }
     g.H = H; g.W = W; g.D = p.numDisparities; g.minD = p.minDisparity;
-    g.NP = (g.D + 63) / 64; g.Dp = 64 * g.NP;
+    g.NP = (g.D + 63) / 64; g.Dp = 64 * g.NP; g.HALF = 32 * g.NP;
     if (g.NP > 8) { svb_set_error("numDisparities=%d > 512 unsupported", g.D); return SVB_ERR_UNSUPPORTED; }
     const int maxD = g.minD + g.D;
     g.minX1 = std::max(maxD, 0);
@@ -504,6 +744,7 @@ static int make_geo(const svb_sgbm_params& p, int H, int W, SgbmGeo& g)
         return SVB_ERR_PARAM;
     }
     if (W > 65535) { svb_set_error("width > 65535 unsupported"); return SVB_ERR_UNSUPPORTED; }
+    if (g.bs > 25) { svb_set_error("blockSize %d > 25 unsupported", g.bs); return SVB_ERR_UNSUPPORTED; }
     g.ftzero = std::max(p.preFilterCap, 15) | 1;
     g.P1 = p.P1 > 0 ? p.P1 : 2;
     g.P2 = std::max(p.P2 > 0 ? p.P2 : 5, g.P1 + 1);
@@ -526,30 +767,43 @@ static int make_geo(const svb_sgbm_params& p, int H, int W, SgbmGeo& g)
         int ys, ye, keep; job_rows(g, n, ys, ye, keep);
         g.rowsMax = std::max(g.rowsMax, ye - ys);
     }
-    g.Wh = (W + 1) / 2 + 4;
+    g.Wp = ((W + g.HALF + 3) & ~3) + 4;
     return SVB_OK;
 }
 
-struct SgbmLayout { size_t ldesc, rdesc, C, S, raw, key, scratch, total; };
+struct SgbmLayout { size_t ldesc, rdesc, C, S, carry, cmin, sync, raw, key, scratch, total; int bands; };
 static inline size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 static SgbmLayout make_layout(const SgbmGeo& g, int nb)
 {
     SgbmLayout L; size_t o = 0;
+    const size_t njobs = (size_t)nb * g.nstripes;
+    L.bands = (g.rowsMax + SW_R - 1) / SW_R;
     L.ldesc = o; o += al256((size_t)nb * g.H * g.W * 32);
-    L.rdesc = o; o += al256((size_t)nb * g.H * 16 * g.Wh * 4);
-    const size_t vol = (size_t)nb * g.nstripes * g.rowsMax * g.width1 * g.Dp * 2;
+    L.rdesc = o; o += al256((size_t)nb * g.H * 6 * g.Wp * 4);
+    const size_t vol = njobs * g.rowsMax * g.width1 * g.Dp * 2;
     L.C = o; o += al256(vol);
     L.S = o; o += al256(vol);
+    L.carry = o; o += al256(njobs * 2 * g.width1 * 3 * g.Dp * 2);
+    L.cmin = o; o += al256(njobs * 2 * g.width1 * 4 * 4);
+    L.sync = o; o += al256((njobs * L.bands + 64) * 4);      // [0] ticket, [1] err, [16..] prog
     L.raw = o; o += al256((size_t)nb * g.H * g.W * 2);
     L.key = o; o += al256((size_t)nb * g.H * g.W * 4);
     L.scratch = o; o += al256((size_t)nb * g.H * g.W * 8);
     L.total = o;
     return L;
 }
+static size_t ws_limit_of(const svb_sgbm* h)
+{
+    if (h->ws_limit) return h->ws_limit;
+    size_t fr = 0, tot = 0;
+    if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) { cudaGetLastError(); return (size_t)24 << 30; }
+    // what this handle already holds is "free" for its own purposes
+    return (size_t)(0.6 * (double)(fr + h->ws.cap));
+}
 static int pick_chunk(const svb_sgbm* h, const SgbmGeo& g, int B)
 {
     const size_t per = make_layout(g, 1).total;
-    size_t nb = h->ws_limit / per;
+    size_t nb = ws_limit_of(h) / per;
     if (nb < 1) nb = 1;
     return (int)std::min<size_t>(nb, (size_t)B);
 }
@@ -570,6 +824,7 @@ extern "C" int svb_sgbm_create(const svb_sgbm_params* p, svb_sgbm_t** out)
 extern "C" void svb_sgbm_destroy(svb_sgbm_t* h)
 {
     if (!h) return;
+    for (auto& e : h->evs) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     h->ws.release(); h->stage_in.release(); h->stage_out.release();
     delete h;
 }
@@ -582,13 +837,20 @@ extern "C" size_t svb_sgbm_workspace_bytes(const svb_sgbm_t* h, int B, int H, in
 extern "C" int svb_sgbm_set_workspace_limit(svb_sgbm_t* h, size_t bytes)
 {
     if (!h) return SVB_ERR_PARAM;
-    h->ws_limit = bytes ? bytes : ((size_t)24 << 30);
+    h->ws_limit = bytes;
+    return SVB_OK;
+}
+extern "C" int svb_sgbm_set_debug(svb_sgbm_t* h, int enable)
+{
+    if (!h) return SVB_ERR_PARAM;
+    h->debug = enable != 0;
     return SVB_OK;
 }
 extern "C" int svb_sgbm_last_launches(const svb_sgbm_t* h) { return h ? h->launches : 0; }
 
-enum { CAT_PREFILTER = 0, CAT_COST, CAT_PATH, CAT_WTA, CAT_LR, CAT_MEDIAN, CAT_SPECKLE, CAT_COUNT };
-static const char* const kCatNames[CAT_COUNT] = {"k_prefilter", "k_cost", "k_path", "k_wta", "k_lrcheck", "k_median3_s16", "k_ccl_*"};
+enum { CAT_PREFILTER = 0, CAT_COST, CAT_SWEEP1, CAT_SWEEP2, CAT_LR, CAT_MEDIAN, CAT_SPECKLE, CAT_COUNT };
+static const char* const kCatNames[CAT_COUNT] = {"k_prefilter", "k_cost", "k_sweep<first>", "k_sweep<last+wta>",
+                                                 "k_lrcheck", "k_median3_s16", "k_ccl_*"};
 struct ProfScope {
     svb_sgbm* h; cudaStream_t st; int idx = -1;
     ProfScope(svb_sgbm* h_, int cat, cudaStream_t st_) : h(h_), st(st_)
@@ -602,6 +864,34 @@ struct ProfScope {
     ~ProfScope() { if (idx >= 0) cudaEventRecord(h->evs[idx].b, st); }
 };
 
+template <int NP, int VAR, bool LAST>
+static int launch_sweep(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, cudaStream_t st)
+{
+    const size_t smem = ((size_t)SW_R * 3 * SW_RING * NP * 32 + SW_R * 3 * SW_RING + (size_t)SW_R * NP * 32) * 4;
+    auto kfn = k_sweep<NP, VAR, LAST>;
+    SVB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, SW_R * 32, smem));
+    if (per_sm < 1) { svb_set_error("k_sweep does not fit on an SM (smem %zu)", smem); return SVB_ERR_UNSUPPORTED; }
+    const long long tickets = (long long)a.njobs * a.bandsPerJob;
+    const int grid = (int)std::min<long long>(tickets, (long long)h->num_sms * per_sm);
+    // ticket = 0, err untouched, prog = 0
+    SVB_CUDA(cudaMemsetAsync(a.ticket, 0, 4, st));
+    SVB_CUDA(cudaMemsetAsync(a.prog, 0, (size_t)tickets * 4, st));
+    kfn<<<grid, SW_R * 32, smem, st>>>(a, g);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+template <int NP, bool LAST>
+static int launch_sweep_var(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, int var, cudaStream_t st)
+{
+    switch (var) {
+        case 0: return launch_sweep<NP, 0, LAST>(h, a, g, st);
+        case 1: return launch_sweep<NP, 1, LAST>(h, a, g, st);
+        default: return launch_sweep<NP, 2, LAST>(h, a, g, st);
+    }
+}
+
 template <int NP>
 static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const uint8_t* left, const uint8_t* right,
                      int nb, int16_t* disp, cudaStream_t st)
@@ -609,8 +899,9 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     char* ws = (char*)h->ws.p;
     uint32_t* ldesc = (uint32_t*)(ws + L.ldesc);
     uint32_t* rdesc = (uint32_t*)(ws + L.rdesc);
-    uint16_t* Cv = (uint16_t*)(ws + L.C);
-    uint16_t* Sv = (uint16_t*)(ws + L.S);
+    uint32_t* Cv = (uint32_t*)(ws + L.C);
+    uint32_t* Sv = (uint32_t*)(ws + L.S);
+    int* sync = (int*)(ws + L.sync);
     int16_t* raw = (int16_t*)(ws + L.raw);
     uint32_t* key = (uint32_t*)(ws + L.key);
     int32_t* scratch = (int32_t*)(ws + L.scratch);
@@ -622,35 +913,31 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     }
     SVB_LAUNCH_CHECK(); h->launches++;
 
-    // k_cost tiling: NW = TY + 2r warps, smem = (NW*bs + NW) * NP * 128 bytes
     {
-        const int bs = 2 * g.r + 1;
-        int TY = 16;
-        auto smem_of = [&](int ty) { return (size_t)(ty + 2 * g.r) * (bs + 1) * NP * 128; };
-        while (TY > 1 && (TY + 2 * g.r > 32 || smem_of(TY) > 200 * 1024)) --TY;
-        if (TY + 2 * g.r > 32 || smem_of(TY) > 200 * 1024) {
+        // k_cost tiling: ring of bs rows per output column in shared memory
+        const int bs = 2 * g.r + 1, VW = NP * 32;
+        CostArgs ca;
+        ca.SE = g.HALF + CK_PC;
+        const size_t fixed = ((size_t)2 * 6 * ca.SE + 2 * CK_PC * 8 + (size_t)2 * CK_PC * VW) * 4;
+        const size_t budget = 200 * 1024;
+        int OC = CK_PC - 2 * g.r;
+        while (OC > 1 && fixed + (size_t)OC * bs * VW * 4 > budget) --OC;
+        if (OC < 1 || fixed + (size_t)OC * bs * VW * 4 > budget) {
             svb_set_error("blockSize %d too large for the cost kernel at numDisparities %d", g.bs, g.D);
             return SVB_ERR_UNSUPPORTED;
         }
-        const int XSEG = 128;
-        const size_t smem = smem_of(TY);
+        ca.OC = OC;
+        ca.nstrips = svb_ceil_div(g.width1, OC);
+        // row segments: enough CTAs to balance the SMs, few enough to keep the bs-1 warm-up rows cheap
+        int nsegs = 1;
+        while ((long long)ca.nstrips * njobs * nsegs < 8LL * h->num_sms && g.rowsMax / (nsegs * 2) >= 16 * bs) nsegs *= 2;
+        ca.rseg = svb_ceil_div(g.rowsMax, nsegs);
+        ca.nsegs = svb_ceil_div(g.rowsMax, ca.rseg);
+        const size_t smem = fixed + (size_t)OC * bs * VW * 4;
         SVB_CUDA(cudaFuncSetAttribute(k_cost<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        dim3 grid(svb_ceil_div(g.width1, XSEG), svb_ceil_div(g.rowsMax, TY), njobs);
+        dim3 grid(ca.nstrips * ca.nsegs, njobs);
         ProfScope ps(h, CAT_COST, st);
-        k_cost<NP><<<grid, 32 * (TY + 2 * g.r), smem, st>>>(ldesc, rdesc, g, TY, XSEG, Cv);
-        SVB_LAUNCH_CHECK(); h->launches++;
-    }
-
-    // path directions (A.3): 3WAY {->, down, <-}; SGBM 5; HH 8
-    static const int dirs[8][2] = {{1, 0}, {1, 1}, {0, 1}, {-1, 1}, {-1, 0}, {-1, -1}, {0, -1}, {1, -1}};
-    static const int dirs3[3][2] = {{1, 0}, {0, 1}, {-1, 0}};
-    const int npaths = g.mode == SVB_MODE_SGBM_3WAY ? 3 : (g.mode == SVB_MODE_HH ? 8 : 5);
-    for (int k = 0; k < npaths; ++k) {
-        const int dx = g.mode == SVB_MODE_SGBM_3WAY ? dirs3[k][0] : dirs[k][0];
-        const int dy = g.mode == SVB_MODE_SGBM_3WAY ? dirs3[k][1] : dirs[k][1];
-        const long long lines = (long long)njobs * (dy == 0 ? g.rowsMax : g.width1);
-        ProfScope ps(h, CAT_PATH, st);
-        k_path<NP><<<svb_ceil_div(lines * 32, 256), 256, 0, st>>>(Cv, Sv, g, dx, dy, k == 0, njobs);
+        k_cost<NP><<<grid, CK_WARPS * 32, smem, st>>>(ldesc, rdesc, g, ca, Cv);
         SVB_LAUNCH_CHECK(); h->launches++;
     }
 
@@ -658,11 +945,35 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     k_fill_s16<<<svb_ceil_div(npix, 256), 256, 0, st>>>(raw, npix, (int16_t)g.INV);
     SVB_LAUNCH_CHECK(); h->launches++;
     SVB_CUDA(cudaMemsetAsync(key, 0xff, npix * 4, st));
+
+    // path sets (A.3): 3WAY {->, down | <-}; SGBM {->, \, |, / | <-}; HH {->, \, |, / | <-, \, |, /}
+    SweepArgs a;
+    a.C = Cv; a.S = Sv;
+    a.carry = (uint32_t*)(ws + L.carry); a.cmin = (uint32_t*)(ws + L.cmin);
+    a.ticket = sync; a.err = sync + 1; a.prog = sync + 16;
+    a.raw = raw; a.key = key;
+    a.njobs = njobs; a.bandsPerJob = L.bands;
+    a.storeS = h->debug ? 1 : 0;
+    const int mask1 = g.mode == SVB_MODE_SGBM_3WAY ? (1 | 4) : 15;
+    const int mask2 = g.mode == SVB_MODE_HH ? 15 : 1;
+    const int win = 2 * g.r + 1;
+    const long long lmax = (long long)win * win * (2 * g.ftzero + 63) + g.P2;
+    int var = g.D == g.Dp ? 1 : 0;
+    if (var == 1 && 4 * lmax <= 32767) var = 2;
+    int rc;
     {
-        const long long warps = (long long)njobs * g.rowsMax * g.width1;
-        ProfScope ps(h, CAT_WTA, st);
-        k_wta<NP><<<svb_ceil_div(warps * 32, 256), 256, 0, st>>>(Sv, g, njobs, 0, raw, key);
-        SVB_LAUNCH_CHECK(); h->launches++;
+        ProfScope ps(h, CAT_SWEEP1, st);
+        a.dir = 1; a.mask = mask1;
+        rc = launch_sweep_var<NP, false>(h, a, g, var, st);
+        if (rc != SVB_OK) return rc;
+        h->launches++;
+    }
+    {
+        ProfScope ps(h, CAT_SWEEP2, st);
+        a.dir = -1; a.mask = mask2;
+        rc = launch_sweep_var<NP, true>(h, a, g, var, st);
+        if (rc != SVB_OK) return rc;
+        h->launches++;
     }
     {
         ProfScope ps(h, CAT_LR, st);
@@ -670,7 +981,6 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     }
     SVB_LAUNCH_CHECK(); h->launches++;
 
-    int rc;
     {
         ProfScope ps(h, CAT_MEDIAN, st);
         rc = svb_median3_s16_dev(raw, nb, g.H, g.W, disp, st);
@@ -695,11 +1005,22 @@ extern "C" int svb_sgbm_compute_dev(svb_sgbm_t* h, const uint8_t* left, const ui
     SgbmGeo g;
     int rc = make_geo(h->prm, H, W, g);
     if (rc != SVB_OK) return rc;
+    if (!h->num_sms) {
+        int dev = 0;
+        SVB_CUDA(cudaGetDevice(&dev));
+        SVB_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, dev));
+    }
     const int nb = pick_chunk(h, g, B);
     const SgbmLayout L = make_layout(g, nb);
-    rc = h->ws.reserve(L.total);
-    if (rc != SVB_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
+    if (L.total > h->ws.cap) {
+        rc = h->ws.reserve(L.total);
+        if (rc != SVB_OK) return rc;
+        // right-descriptor planes have never-written halves (xr < HALF): keep them defined
+        SVB_CUDA(cudaMemsetAsync(h->ws.p, 0, L.total, st));
+    } else {
+        SVB_CUDA(cudaMemsetAsync((char*)h->ws.p + L.sync, 0, 64, st));
+    }
     h->launches = 0;
     for (int b0 = 0; b0 < B; b0 += nb) {
         const int n = std::min(nb, B - b0);
@@ -712,7 +1033,17 @@ extern "C" int svb_sgbm_compute_dev(svb_sgbm_t* h, const uint8_t* left, const ui
         }
         if (rc != SVB_OK) return rc;
     }
-    h->last_geo = g; h->off_C = L.C; h->off_S = L.S; h->off_raw = L.raw; h->have_last = true;
+    h->last_geo = g; h->off_C = L.C; h->off_S = L.S; h->off_raw = L.raw; h->off_err = L.sync + 4; h->have_last = true;
+    return SVB_OK;
+}
+
+// Synchronise and report a wavefront wait that hit its spin limit (cannot happen unless the
+// device was reset underneath us; results of that call are invalid).
+static int check_sweep_err(svb_sgbm* h)
+{
+    int e = 0;
+    SVB_CUDA(cudaMemcpy(&e, (const char*)h->ws.p + h->off_err, 4, cudaMemcpyDeviceToHost));
+    if (e) { svb_set_error("k_sweep: inter-band wait exceeded its spin limit"); return SVB_ERR_CUDA; }
     return SVB_OK;
 }
 
@@ -734,16 +1065,26 @@ extern "C" int svb_sgbm_compute_host(svb_sgbm_t* h, const uint8_t* left, const u
     if (rc != SVB_OK) return rc;
     SVB_CUDA(cudaMemcpyAsync(disp, h->stage_out.p, 2 * n, cudaMemcpyDeviceToHost, 0));
     SVB_CUDA(cudaStreamSynchronize(0));
-    return SVB_OK;
+    return check_sweep_err(h);
+}
+
+// Unpack one pixel's vector (HALF words, word w = d | (d+HALF) << 16) into D u16 values.
+static void unpack_vec(const uint32_t* src, int HALF, int D, uint16_t* dst)
+{
+    for (int d = 0; d < D; ++d) {
+        const uint32_t w = src[d < HALF ? d : d - HALF];
+        dst[d] = (uint16_t)(d < HALF ? (w & 0xffffu) : (w >> 16));
+    }
 }
 
 extern "C" int svb_sgbm_debug_stages(svb_sgbm_t* h, uint16_t* C_host, uint16_t* S_host, int16_t* raw_host)
 {
     if (!h || !h->have_last) { svb_set_error("no previous compute"); return SVB_ERR_PARAM; }
+    if (S_host && !h->debug) { svb_set_error("S is only kept after svb_sgbm_set_debug(h, 1)"); return SVB_ERR_PARAM; }
     const SgbmGeo& g = h->last_geo;
     SVB_CUDA(cudaDeviceSynchronize());
-    const size_t rowp = (size_t)g.width1 * g.Dp;
-    uint16_t* tmp = (uint16_t*)malloc(rowp * 2);
+    const size_t roww = (size_t)g.width1 * g.HALF;           // u32 words per volume row
+    uint32_t* tmp = (uint32_t*)malloc(roww * 4);
     if (!tmp) return SVB_ERR_NOMEM;
     for (int which = 0; which < 2; ++which) {
         uint16_t* dst = which ? S_host : C_host;
@@ -752,18 +1093,18 @@ extern "C" int svb_sgbm_debug_stages(svb_sgbm_t* h, uint16_t* C_host, uint16_t* 
         for (int n = 0; n < g.nstripes; ++n) {
             int ys, ye, keep; job_rows(g, n, ys, ye, keep);
             for (int y = std::max(ys, keep); y < ye; ++y) {
-                cudaError_t e = cudaMemcpy(tmp, src + (((size_t)n * g.rowsMax + (y - ys)) * rowp) * 2, rowp * 2,
+                cudaError_t e = cudaMemcpy(tmp, src + (((size_t)n * g.rowsMax + (y - ys)) * roww) * 4, roww * 4,
                                            cudaMemcpyDeviceToHost);
                 if (e != cudaSuccess) { free(tmp); svb_set_error("memcpy: %s", cudaGetErrorString(e)); return SVB_ERR_CUDA; }
                 for (int x = 0; x < g.width1; ++x)
-                    memcpy(dst + ((size_t)y * g.width1 + x) * g.D, tmp + (size_t)x * g.Dp, (size_t)g.D * 2);
+                    unpack_vec(tmp + (size_t)x * g.HALF, g.HALF, g.D, dst + ((size_t)y * g.width1 + x) * g.D);
             }
         }
     }
     free(tmp);
     if (raw_host)
         SVB_CUDA(cudaMemcpy(raw_host, (const char*)h->ws.p + h->off_raw, (size_t)g.H * g.W * 2, cudaMemcpyDeviceToHost));
-    return SVB_OK;
+    return check_sweep_err(h);
 }
 
 // ---- profiling hooks (bench.py): per-stage device time of all computes since enable/reset

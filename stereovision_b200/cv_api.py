@@ -123,6 +123,7 @@ class _Matcher:
             torch = _torch()
             dev = _ensure_device(left.device.index)
             h = _handle(self._kind, self._params(), dev)
+            self._pre_compute(h)
             l, r = left.contiguous(), right.contiguous()
             out = torch.empty(left.shape, dtype=torch.int16, device=left.device)
             _lib.check(dev_fn(h, l.data_ptr(), r.data_ptr(), B, H, W, out.data_ptr(), _stream_ptr()))
@@ -130,12 +131,16 @@ class _Matcher:
             return out
         dev = _ensure_device()
         h = _handle(self._kind, self._params(), dev)
+        self._pre_compute(h)
         l = np.ascontiguousarray(left)
         r = np.ascontiguousarray(right)
         out = np.empty(left.shape, np.int16)
         _lib.check(host_fn(h, l.ctypes.data, r.ctypes.data, B, H, W, out.ctypes.data))
         self._last = h
         return out
+
+    def _pre_compute(self, h):
+        pass
 
     def last_launches(self):
         L = _lib.lib()
@@ -161,8 +166,17 @@ class StereoSGBM(_Matcher):
     def _params(self):
         return tuple(getattr(self, "_" + n) for n in self._names)
 
+    def setDebugStages(self, enable=True):
+        """Test hook: keep the aggregated volume S of the next compute() in device memory
+        (normally the last sweep consumes it in registers) so debug_stages() can return it."""
+        self._debug = bool(enable)
+
+    def _pre_compute(self, h):
+        _lib.check(_lib.lib().svb_sgbm_set_debug(h, int(getattr(self, "_debug", False))))
+
     def debug_stages(self, H, W):
-        """Test hook: (C, S, raw) of image 0 of the last compute as NumPy arrays."""
+        """Test hook: (C, S, raw) of image 0 of the last compute as NumPy arrays
+        (call setDebugStages() before compute())."""
         L = _lib.lib()
         D, minD = self._numDisparities, self._minDisparity
         w1 = W + min(minD, 0) - max(minD + D, 0)

@@ -24,6 +24,7 @@ def test_sgbm_matches_golden_and_oracle(golden, i):
     c = SGBM_CASES[i]
     l, r, _ = make_pair(c["H"], c["W"], max(c["prm"]["numDisparities"], 16), seed=c["seed"])
     m = svb.StereoSGBM_create(**c["prm"])
+    m.setDebugStages(True)
     got = m.compute(l, r)
     assert got.dtype == np.int16 and got.shape == l.shape
     ref, st = oracle.sgbm_compute(l, r, stages=True, **c["prm"])
@@ -44,6 +45,7 @@ def test_sgbm_stages_match_oracle(mode):
     prm = dict(minDisparity=0, numDisparities=D, blockSize=bs, P1=8 * bs * bs, P2=32 * bs * bs, disp12MaxDiff=1,
                preFilterCap=63, uniquenessRatio=10, speckleWindowSize=0, speckleRange=0, mode=mode)
     m = svb.StereoSGBM_create(**prm)
+    m.setDebugStages(True)
     got = m.compute(l, r)
     ref, st = oracle.sgbm_compute(l, r, stages=True, **prm)
     C, S, raw = m.debug_stages(H, W)

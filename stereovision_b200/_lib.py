@@ -9,7 +9,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "libsvb.so")
+_SO = os.environ.get("SVB_LIBRARY") or os.path.join(_HERE, "libsvb.so")   # SVB_LIBRARY: developer override (experiments)
 _lib = None
 
 c_int, c_size_t, c_void_p, c_double = ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_double

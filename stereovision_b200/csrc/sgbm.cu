@@ -38,11 +38,28 @@
 #define WALL2 0x7fff7fffu
 #define FULLMASK 0xffffffffu
 
-#define SW_R 16                // rows (= warps) per band
-#define SW_SK 2                // column skew between consecutive rows of a band
-#define SW_RING 4              // ring slots per path between two rows
+// rows (= warps) per band
+__host__ __device__ constexpr int sw_rows(int NP) { return NP <= 5 ? 16 : 8; }
+#define SW_SK 2                // minimum column lag between consecutive rows of a band
+// ring slots per path between two rows (>= 4; every extra slot is a column of slack between rows)
+#ifndef SW_RING_FIRST
+#define SW_RING_FIRST 6
+#define SW_RING_LAST 5
+#define SW_STAGE 4
+#endif
+__host__ __device__ constexpr int sw_ring(int NP, bool last) { return NP <= 4 ? (last ? SW_RING_LAST : SW_RING_FIRST) : 4; }
+// slots of the per-row cp.async staging ring for C (and S1 in the last sweep); prefetch distance = slots - 1
+__host__ __device__ constexpr int sw_stage(int NP, bool last) { return NP <= 4 ? SW_STAGE : 4; }
+__host__ __device__ constexpr size_t sw_smem_words(int NP, bool last)
+{
+    return (size_t)(sw_rows(NP) + 1) * 3 * sw_ring(NP, last) * NP * 32 + (((sw_rows(NP) + 1) * 3 * sw_ring(NP, last) + 3) & ~3) +
+           (size_t)sw_rows(NP) * NP * 32 + (size_t)sw_rows(NP) * sw_stage(NP, last) * NP * 32 * (last ? 2 : 1);
+}
 #define SW_FLAG_EVERY 8        // carry progress is published every this many columns
 #define SW_SPIN_LIMIT (1 << 24)
+#ifndef SW_EXPERIMENT
+#define SW_EXPERIMENT 0        // timing experiments only (results are wrong): 1 = no intra-band waits, 2 = also no inter-band waits/fences
+#endif
 
 struct SgbmGeo {
     int H, W, D, Dp, NP, HALF, minD, minX1, width1, bs, r, ftzero;
@@ -142,6 +159,18 @@ __device__ __forceinline__ void cp_async4(void* smem, const void* gmem)
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
 {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+// one lane's NP-word slice of a pixel vector (16-byte copies when NP is a multiple of 4)
+template <int NP>
+__device__ __forceinline__ void cp_async_vec(uint32_t* smem_dst, const uint32_t* gsrc)
+{
+    if constexpr (NP % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < NP / 4; ++i) cp_async16(smem_dst + 4 * i, gsrc + 4 * i);
+    } else {
+#pragma unroll
+        for (int i = 0; i < NP; ++i) cp_async4(smem_dst + i, gsrc + i);
+    }
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
@@ -362,17 +391,17 @@ __device__ __forceinline__ void vec_st(uint32_t* p, int lane, const uint32_t (&v
 //   L(d) = C(d) + min(Lq(d), Lq(d-1)+P1, Lq(d+1)+P1, minLq+P2) - minLq
 // Lq is updated in place; returns the warp-wide min of the new L (minLq for the next step).
 template <int NP, bool FULL>
-__device__ __forceinline__ uint32_t sgm_step(uint32_t (&Lq)[NP], const uint32_t (&C)[NP], uint32_t minq,
-                                             uint32_t P1P1, uint32_t P2, int lane, const uint32_t (&padm)[NP])
+__device__ __forceinline__ uint32_t sgm_step(uint32_t (&Lq)[NP], const uint32_t (&C)[NP], uint32_t mq2,
+                                             uint32_t P1P1, uint32_t P2P2, int lane, const uint32_t (&padm)[NP])
 {
+    // mq2 = minLq in both halves; returns the warp-wide min of the new L, again in both halves.
     // neighbours across lane boundaries; both halves of a word move together, except at the
     // two seams: word 0's high half continues word HALF-1's low half, and the ends see the wall
     uint32_t prev = __shfl_sync(FULLMASK, Lq[NP - 1], (lane + 31) & 31);
     uint32_t next = __shfl_sync(FULLMASK, Lq[0], (lane + 1) & 31);
     if (lane == 0) prev = __byte_perm(prev, WALL2, 0x1054);     // (lo = wall, hi = lane31.lo)
     if (lane == 31) next = __byte_perm(next, WALL2, 0x5432);    // (lo = lane0.hi, hi = wall)
-    const uint32_t mq2 = pk_dup(minq);
-    const uint32_t mqP2 = pk_dup(minq + P2);
+    const uint32_t mqP2 = mq2 + P2P2;                        // halves < 65536: no carry
     uint32_t up = prev;
     uint32_t mloc = 0xffffffffu;
 #pragma unroll
@@ -387,7 +416,7 @@ __device__ __forceinline__ uint32_t sgm_step(uint32_t (&Lq)[NP], const uint32_t 
         Lq[k] = L;
         mloc = pk_min(mloc, L);
     }
-    return __reduce_min_sync(FULLMASK, pk_hmin(mloc));
+    return pk_dup(__reduce_min_sync(FULLMASK, pk_hmin(mloc)));
 }
 
 __device__ __forceinline__ int ld_acquire_gpu(const int* p)
@@ -401,6 +430,20 @@ __device__ __forceinline__ void st_release_gpu(int* p, int v)
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+__device__ __forceinline__ int lds_acquire_cta(const int* p)
+{
+    int v;
+    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((uint32_t)__cvta_generic_to_shared(p)) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_release_cta(int* p, int v)
+{
+    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+#define SW_PF 12               // columns of C (and S1) requested into L2 ahead of use
+
 struct SweepArgs {
     const uint32_t* C;        // [job][rowsMax][w1][VW]
     uint32_t* S;              // same shape: sweep 1 writes S1, sweep 2 reads it
@@ -413,27 +456,32 @@ struct SweepArgs {
     uint32_t* key;            // [img][H][W]   right-view scatter-min keys (sweep 2)
     int njobs, bandsPerJob;
     int dir;                  // +1: rows top-down, columns left-to-right; -1: the opposite
-    int mask;                 // paths: 1 horizontal, 2 diagonal from behind, 4 vertical, 8 diagonal from ahead
     int storeS;               // debug: sweep 2 writes the final S back
 };
 
 // VAR 0: D < Dp (pad disparities), saturating sums; 1: D == Dp, saturating sums;
 // 2: D == Dp and the per-sweep sum of L_r cannot reach 32768 -> plain adds.
-template <int NP, int VAR, bool LAST>
-__global__ void __launch_bounds__(SW_R * 32, 1) k_sweep(const SweepArgs a, const SgbmGeo g)
+// MASK: paths of this sweep: 1 horizontal, 2 diagonal from behind, 4 vertical, 8 diagonal from ahead.
+template <int NP, int VAR, int MASK, bool LAST>
+__global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a, const SgbmGeo g)
 {
     constexpr bool FULL = VAR != 0, FAST = VAR == 2;
+    constexpr bool VERT = (MASK & 14) != 0;                  // any path that crosses rows
     constexpr int VW = NP * 32;
+    constexpr int SW_R = sw_rows(NP), SW_RING = sw_ring(NP, LAST), NS = sw_stage(NP, LAST), PFD = NS - 1;
     extern __shared__ uint32_t smem[];
-    uint32_t* ring = smem;                                   // [SW_R][3][SW_RING][VW]: INPUT ring of each warp
-    uint32_t* rmin = ring + SW_R * 3 * SW_RING * VW;         // [SW_R][3][SW_RING]
-    uint32_t* wsc = rmin + SW_R * 3 * SW_RING;               // [SW_R][VW] (sweep 2: S vector for the subpixel taps)
+    uint32_t* ring = smem;                                   // [SW_R + 1][3][SW_RING][VW]: INPUT ring of each warp (+ a dump)
+    uint32_t* rmin = ring + (SW_R + 1) * 3 * SW_RING * VW;   // [SW_R + 1][3][SW_RING]
+    uint32_t* wsc = rmin + (((SW_R + 1) * 3 * SW_RING + 3) & ~3);   // [SW_R][VW] (sweep 2: S vector for the subpixel taps)
+    uint32_t* cstage = wsc + SW_R * VW;                      // [SW_R][NS][VW] cp.async ring of C columns
+    uint32_t* sstage = cstage + SW_R * NS * VW;              // [SW_R][NS][VW] (sweep 2) ... and of S1 columns
     __shared__ int s_ticket;
+    __shared__ int s_done[SW_R + 1];                         // columns completed by each warp in this band
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int w1 = g.width1;
-    const uint32_t P1P1 = pk_dup(g.P1);
-    const int dir = a.dir, mask = a.mask;
+    const uint32_t P1P1 = pk_dup(g.P1), P2P2 = pk_dup(g.P2);
+    const int dir = a.dir;
     uint32_t padm[NP];
 #pragma unroll
     for (int k = 0; k < NP; ++k) {
@@ -442,7 +490,7 @@ __global__ void __launch_bounds__(SW_R * 32, 1) k_sweep(const SweepArgs a, const
     }
     uint32_t* ring_in = ring + (size_t)warp * 3 * SW_RING * VW;
     uint32_t* rmin_in = rmin + warp * 3 * SW_RING;
-    uint32_t* ring_out = ring_in + 3 * SW_RING * VW;         // input ring of warp + 1
+    uint32_t* ring_out = ring_in + 3 * SW_RING * VW;         // input ring of warp + 1 (warp SW_R-1: the dump)
     uint32_t* rmin_out = rmin_in + 3 * SW_RING;
     uint32_t* mysc = wsc + warp * VW;
 
@@ -464,12 +512,9 @@ __global__ void __launch_bounds__(SW_R * 32, 1) k_sweep(const SweepArgs a, const
         const int row = dir > 0 ? sr : nrows - 1 - sr;       // storage row within the job
         const int y = ys + row;
         const bool havePred = sr > 0;
-        const bool vert = (mask & 14) != 0;                  // any path that crosses rows
-        const bool feed = vert && (warp == 0) && band > 0;   // warp 0 feeds its ring from the carry
-        const bool lastInBand = warp == nact - 1;
-        const bool succSmem = vert && active && !lastInBand;
-        const bool succGlob = vert && active && lastInBand && (r0 + nact < nrows);
-        const bool rowSkip = LAST && mask == 1 && y < keep;  // 3WAY overlap rows: nothing depends on them
+        const bool feed = VERT && (warp == 0) && band > 0;   // warp 0 feeds its ring from the carry
+        const bool succGlob = VERT && active && (warp == nact - 1) && (r0 + nact < nrows);
+        const bool rowSkip = LAST && !VERT && y < keep;      // 3WAY overlap rows: nothing depends on them
         const size_t rowbase = (((size_t)job * g.rowsMax + row) * w1) * VW;
         const uint32_t* carry_in = a.carry + (((size_t)job * 2 + ((band + 1) & 1)) * w1) * 3 * VW;
         const uint32_t* cmin_in = a.cmin + (((size_t)job * 2 + ((band + 1) & 1)) * w1) * 4;
@@ -484,7 +529,7 @@ __global__ void __launch_bounds__(SW_R * 32, 1) k_sweep(const SweepArgs a, const
         uint32_t premin = 0;
         int seen = 0;
         auto wait_cols = [&](int need) {     // all lanes of warp 0
-            if (seen < need) {
+            if (SW_EXPERIMENT < 2 && seen < need) {
                 if (lane == 0) {
                     int spins = 0;
                     while ((seen = ld_acquire_gpu(prog_pred)) < need) {
@@ -502,7 +547,7 @@ __global__ void __launch_bounds__(SW_R * 32, 1) k_sweep(const SweepArgs a, const
             if (lane < 3) premin = __ldcg(cmin_in + (size_t)c * 4 + lane);
         };
         auto stash_col = [&](int c) {
-            const int slot = c & (SW_RING - 1);
+            const int slot = c % SW_RING;
 #pragma unroll
             for (int p = 0; p < 3; ++p) vec_st<NP>(ring_in + (p * SW_RING + slot) * VW, lane, pre[p]);
             if (lane < 3) rmin_in[lane * SW_RING + slot] = premin;
@@ -514,156 +559,218 @@ __global__ void __launch_bounds__(SW_R * 32, 1) k_sweep(const SweepArgs a, const
             if (w1 > 2) fetch_col(2);
         }
 
-        uint32_t Lh[NP], Cn[NP], Sn[NP];
+        uint32_t Lh[NP];
 #pragma unroll
-        for (int k = 0; k < NP; ++k) { Lh[k] = 0; Cn[k] = 0; Sn[k] = 0; }
-        uint32_t minh = 0;
-        const int nsteps = w1 + SW_SK * (nact - 1);
+        for (int k = 0; k < NP; ++k) Lh[k] = 0;
+        uint32_t minh2 = 0;                                  // min of the horizontal L_r, in both halves
+        if (lane == 0) s_done[warp] = 0;
+        if (VERT && active) {
+            // Virtual columns -1 and w1 of the previous row read as zero vectors ("outside" predecessors,
+            // A.3); a first row has no previous row at all.  Column -1 lives in slot RING-1.
+            const uint32_t z[NP] = {};
+            if (!havePred) {
+                for (int q = 0; q < 3 * SW_RING; ++q) vec_st<NP>(ring_in + q * VW, lane, z);
+                if (lane < 3 * SW_RING) rmin_in[lane] = 0;
+            } else {
+                vec_st<NP>(ring_in + (0 * SW_RING + SW_RING - 1) * VW, lane, z);
+                if (lane == 0) rmin_in[0 * SW_RING + SW_RING - 1] = 0;
+            }
+        }
         __syncthreads();
+        // Rows of a band run decoupled: warp k may start column i once warp k-1 has finished
+        // column i+1 (diagonal-from-ahead predecessor), and may not lap the ring of warp k+1.
+        const bool waitPred = SW_EXPERIMENT == 0 && VERT && warp > 0;
+        const bool waitSucc = SW_EXPERIMENT == 0 && VERT && (warp + 1 < nact);
+        int seenP = 0, seenS = 0;
 
-        for (int s = 0; s < nsteps; ++s) {
-            const int i = s - SW_SK * warp;
-            if (active && !rowSkip && i >= 0 && i < w1) {
-                const int xc = dir > 0 ? i : w1 - 1 - i;
-                uint32_t C[NP], S[NP];
-                if (i == 0) {
-                    vec_ld<NP>(a.C + rowbase + (size_t)xc * VW, lane, Cn, LdNc());
-                    if (LAST) vec_ld<NP>(a.S + rowbase + (size_t)xc * VW, lane, Sn, LdPlain());
-                }
-#pragma unroll
-                for (int k = 0; k < NP; ++k) { C[k] = Cn[k]; S[k] = LAST ? Sn[k] : 0u; }
-                if (i + 1 < w1) {                            // next column's operands: one step ahead
-                    const int xn = xc + dir;
-                    vec_ld<NP>(a.C + rowbase + (size_t)xn * VW, lane, Cn, LdNc());
-                    if (LAST) vec_ld<NP>(a.S + rowbase + (size_t)xn * VW, lane, Sn, LdPlain());
-                }
-                uint32_t sum[NP];                            // FAST: plain sum of this sweep's L_r
-#pragma unroll
-                for (int k = 0; k < NP; ++k) sum[k] = 0;
+        // running addresses (words): this lane's slice of the current column of C / S, ring slots of the
+        // previous row's columns i-1, i, i+1, and the L2 prefetch SW_PF columns ahead
+        const int x0 = dir > 0 ? 0 : w1 - 1;
+        const ptrdiff_t cstep = (ptrdiff_t)dir * VW;
+        const uint32_t* pC0 = a.C + rowbase + (size_t)x0 * VW + NP * lane;
+        const uint32_t* pS0 = a.S + rowbase + (size_t)x0 * VW + NP * lane;
+        uint32_t* pS = a.S + rowbase + (size_t)x0 * VW + NP * lane;
+        int sm1 = SW_RING - 1, s0 = 0, sp1 = 1;              // slots of columns i-1, i, i+1
+        const int nloop = active && !rowSkip ? w1 : 0;
 
-                // horizontal path: predecessor is this warp's previous column
-                if (mask & 1) {
-                    minh = sgm_step<NP, FULL>(Lh, C, minh, P1P1, (uint32_t)g.P2, lane, padm);
+        // C (and S1) columns are staged PFD columns ahead through a per-row cp.async ring: every lane
+        // copies and later reads back only its own slice, so a per-thread wait_group is all it takes
+        uint32_t* cst = cstage + (size_t)warp * NS * VW + NP * lane;
+        uint32_t* sst = sstage + (size_t)warp * NS * VW + NP * lane;
+        auto issue = [&](int col) {
+            if (SW_EXPERIMENT != 3 && col < nloop) {
+                const int slot = col % NS;
+                cp_async_vec<NP>(cst + slot * VW, pC0 + (ptrdiff_t)col * cstep);
+                if (LAST) cp_async_vec<NP>(sst + slot * VW, pS0 + (ptrdiff_t)col * cstep);
+            }
+            asm volatile("cp.async.commit_group;");
+        };
 #pragma unroll
-                    for (int k = 0; k < NP; ++k) {
-                        if (FAST) sum[k] += Lh[k];
-                        else S[k] = pk_addmin(S[k], Lh[k], WALL2);
-                    }
+        for (int c = 0; c < PFD; ++c) issue(c);
+        int cslot = 0;
+        for (int i = 0; i < nloop; ++i) {
+            if (waitPred) {
+                const int need = min(i + SW_SK, w1);
+                if (seenP < need) {
+                    if (lane == 0) { while ((seenP = lds_acquire_cta(&s_done[warp - 1])) < need) __nanosleep(20); }
+                    seenP = __shfl_sync(FULLMASK, seenP, 0);
                 }
-                // the three paths coming from the previous row of the sweep
+            }
+            if (waitSucc && i >= SW_RING - SW_SK) {
+                const int need = i - SW_RING + SW_SK;
+                if (seenS < need) {
+                    if (lane == 0) { while ((seenS = lds_acquire_cta(&s_done[warp + 1])) < need) __nanosleep(20); }
+                    seenS = __shfl_sync(FULLMASK, seenS, 0);
+                }
+            }
+            if (VERT && i == w1 - 1) {                       // virtual column w1 of the diagonal-from-ahead path
+                const uint32_t z[NP] = {};
+                vec_st<NP>(ring_in + (2 * SW_RING + sp1) * VW, lane, z);
+                if (lane == 0) rmin_in[2 * SW_RING + sp1] = 0;
+                __syncwarp();
+            }
+            issue(i + PFD);
+            asm volatile("cp.async.wait_group %0;" ::"n"(PFD) : "memory");
+            uint32_t C[NP], S[NP];
+            vec_ld<NP>(cst + cslot * VW - NP * lane, lane, C, LdPlain());
+            if (LAST) vec_ld<NP>(sst + cslot * VW - NP * lane, lane, S, LdPlain());
+            else {
+#pragma unroll
+                for (int k = 0; k < NP; ++k) S[k] = 0u;
+            }
+            // predecessors on the previous row of the sweep
+            uint32_t Lt[3][NP], mq2[3];
+            if (VERT) {
 #pragma unroll
                 for (int p = 0; p < 3; ++p) {
-                    if (!(mask & (2 << p))) continue;
-                    const int cp = i - 1 + p;                // predecessor column (sweep order)
-                    const bool pv = havePred && cp >= 0 && cp < w1;
-                    uint32_t Lt[NP];
-                    uint32_t mq = 0;
-                    if (pv) {
-                        const int slot = cp & (SW_RING - 1);
-                        vec_ld<NP>(ring_in + (p * SW_RING + slot) * VW, lane, Lt, LdPlain());
-                        mq = rmin_in[p * SW_RING + slot];
-                    } else {
+                    if (!(MASK & (2 << p))) continue;
+                    const int slot = p == 0 ? sm1 : (p == 1 ? s0 : sp1);
+                    vec_ld<NP>(ring_in + (p * SW_RING + slot) * VW, lane, Lt[p], LdPlain());
+                    mq2[p] = rmin_in[p * SW_RING + slot];
+                }
+            }
+            uint32_t sum[NP];                                // FAST: plain sum of this sweep's L_r
 #pragma unroll
-                        for (int k = 0; k < NP; ++k) Lt[k] = 0;
-                    }
-                    const uint32_t m = sgm_step<NP, FULL>(Lt, C, mq, P1P1, (uint32_t)g.P2, lane, padm);
+            for (int k = 0; k < NP; ++k) sum[k] = 0;
+            if (MASK & 1) {                                  // horizontal: predecessor is the previous column
+                minh2 = sgm_step<NP, FULL>(Lh, C, minh2, P1P1, P2P2, lane, padm);
+#pragma unroll
+                for (int k = 0; k < NP; ++k) {
+                    if (FAST) sum[k] += Lh[k];
+                    else S[k] = pk_addmin(S[k], Lh[k], WALL2);
+                }
+            }
+            if (VERT) {
+#pragma unroll
+                for (int p = 0; p < 3; ++p) {
+                    if (!(MASK & (2 << p))) continue;
+                    const uint32_t m2 = sgm_step<NP, FULL>(Lt[p], C, mq2[p], P1P1, P2P2, lane, padm);
 #pragma unroll
                     for (int k = 0; k < NP; ++k) {
-                        if (FAST) sum[k] += Lt[k];
-                        else S[k] = pk_addmin(S[k], Lt[k], WALL2);
+                        if (FAST) sum[k] += Lt[p][k];
+                        else S[k] = pk_addmin(S[k], Lt[p][k], WALL2);
                     }
-                    if (succSmem) {
-                        const int slot = i & (SW_RING - 1);
-                        vec_st<NP>(ring_out + (p * SW_RING + slot) * VW, lane, Lt);
-                        if (lane == 0) rmin_out[p * SW_RING + slot] = m;
-                    } else if (succGlob) {
-                        vec_st<NP>(carry_out + ((size_t)i * 3 + p) * VW, lane, Lt);
-                        if (lane == 0) cmin_out[(size_t)i * 4 + p] = m;
-                    }
+                    vec_st<NP>(ring_out + (p * SW_RING + s0) * VW, lane, Lt[p]);
+                    rmin_out[p * SW_RING + s0] = m2;         // same value from every lane
                 }
-                if (FAST) {
+            }
+            if (FAST) {
 #pragma unroll
-                    for (int k = 0; k < NP; ++k) S[k] = LAST ? pk_addmin(S[k], sum[k], WALL2) : sum[k];
+                for (int k = 0; k < NP; ++k) S[k] = LAST ? pk_addmin(S[k], sum[k], WALL2) : sum[k];
+            }
+            if (!LAST && SW_EXPERIMENT != 4) vec_st<NP>(pS - NP * lane, lane, S);
+            if (succGlob) {
+                // last row of the band: hand L_r to the next band through the carry
+#pragma unroll
+                for (int p = 0; p < 3; ++p) {
+                    if (!(MASK & (2 << p))) continue;
+                    vec_st<NP>(carry_out + ((size_t)i * 3 + p) * VW, lane, Lt[p]);
                 }
-                if (succGlob && (((i & (SW_FLAG_EVERY - 1)) == SW_FLAG_EVERY - 1) || i == w1 - 1)) {
+                if (lane < 3) cmin_out[(size_t)i * 4 + lane] = rmin_out[lane * SW_RING + s0];
+                if (((i & (SW_FLAG_EVERY - 1)) == SW_FLAG_EVERY - 1) || i == w1 - 1) {
                     __syncwarp();
-                    if (lane == 0) st_release_gpu(prog_mine, i + 1);
+                    if (SW_EXPERIMENT < 2 && lane == 0) st_release_gpu(prog_mine, i + 1);
                 }
-
-                if (!LAST) {
-                    vec_st<NP>(a.S + rowbase + (size_t)xc * VW, lane, S);
-                } else {
-                    if (a.storeS) vec_st<NP>(a.S + rowbase + (size_t)xc * VW, lane, S);
-                    if (y >= keep) {
-                        // ---- WTA (A.4): argmin with lowest-d tie break via keys (S << 16 | d)
-                        uint32_t kmin = 0xffffffffu;
-                        const uint32_t dlo = NP * lane, dhi = NP * lane + g.HALF;
+            }
+            if (LAST) {
+                if (a.storeS) vec_st<NP>(pS - NP * lane, lane, S);
+                if (y >= keep) {
+                    const int xc = dir > 0 ? i : w1 - 1 - i;
+                    // ---- WTA (A.4): argmin with lowest-d tie break via keys (S << 16 | d)
+                    uint32_t kmin = 0xffffffffu;
+                    const uint32_t dlo = NP * lane, dhi = NP * lane + g.HALF;
 #pragma unroll
-                        for (int k = 0; k < NP; ++k) {
-                            const uint32_t klo = (S[k] << 16) | (dlo + k);
-                            const uint32_t khi = __byte_perm(S[k], dhi + k, 0x3254);
-                            kmin = min(kmin, min(klo, khi));
-                        }
-                        kmin = __reduce_min_sync(FULLMASK, kmin);
-                        const int minS = (int)(kmin >> 16), best = (int)(kmin & 0xffffu);
-                        // uniqueness: count disparities with S < th; the ones at best-1..best+1 do not count
-                        int th;
-                        if (g.mode == SVB_MODE_SGBM_3WAY) {
-                            // cv2's 3WAY vector loop: Sp[d] < (short)(100*minS/(100-u) + 1) (oracle/sgbm_oracle.c)
-                            th = g.uniq > 0 ? (int)(int16_t)((100 * minS) / (100 - g.uniq) + 1) : 0;
-                            th = max(th, 0);
-                        } else {
-                            const int f = 100 - g.uniq;
-                            th = (minS * 100 + f - 1) / f;   // S*f < minS*100  <=>  S < ceil(minS*100/f)
-                        }
-                        th = min(th, 0x8000);
-                        const uint32_t th2 = pk_dup((uint32_t)th);
-                        uint32_t cnt2 = 0;
-#pragma unroll
-                        for (int k = 0; k < NP; ++k) {
-                            uint32_t lt = (__vsub2(S[k], th2) >> 15) & 0x00010001u;   // S, th in [0, 0x8000]
-                            if (!FULL) lt &= ~padm[k];
-                            cnt2 += lt;
-                        }
-                        const int cnt = (int)__reduce_add_sync(FULLMASK, (cnt2 & 0xffffu) + (cnt2 >> 16));
-                        vec_st<NP>(mysc, lane, S);
-                        __syncwarp();
-                        if (lane == 0) {
-                            const size_t pix = ((size_t)b * g.H + y) * g.W + (xc + g.minX1);
-                            int out = g.INV;
-                            if (minS < (int)WALL) {
-                                const uint16_t* sv = reinterpret_cast<const uint16_t*>(mysc);
-                                auto tap = [&](int d) { return (int)sv[d < g.HALF ? 2 * d : 2 * (d - g.HALF) + 1]; };
-                                const int sm1 = best > 0 ? tap(best - 1) : 0;
-                                const int sp1 = best < g.D - 1 ? tap(best + 1) : 0;
-                                const int excl = (minS < th) + (best > 0 && sm1 < th) + (best < g.D - 1 && sp1 < th);
-                                if (cnt <= excl) {
-                                    int dsub = best * 16;
-                                    if (best > 0 && best < g.D - 1) {
-                                        const int den = max(sm1 + sp1 - 2 * minS, 1);
-                                        dsub += ((sm1 - sp1) * 16 + den) / (2 * den);   // C division: truncates toward zero
-                                    }
-                                    out = dsub + g.minD * 16;
-                                    const int x = xc + g.minX1;
-                                    const int x2 = x - best - g.minD;
-                                    // smallest cost wins, then the largest x: the pixel cv2's right-to-left loop keeps
-                                    atomicMin(a.key + ((size_t)b * g.H + y) * g.W + x2,
-                                              ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
-                                }
-                            }
-                            a.raw[pix] = (int16_t)out;
-                        }
-                        __syncwarp();
+                    for (int k = 0; k < NP; ++k) {
+                        const uint32_t klo = (S[k] << 16) | (dlo + k);
+                        const uint32_t khi = __byte_perm(S[k], dhi + k, 0x3254);
+                        kmin = min(kmin, min(klo, khi));
                     }
+                    kmin = __reduce_min_sync(FULLMASK, kmin);
+                    const int minS = (int)(kmin >> 16), best = (int)(kmin & 0xffffu);
+                    // uniqueness: count disparities with S < th; the ones at best-1..best+1 do not count
+                    int th;
+                    if (g.mode == SVB_MODE_SGBM_3WAY) {
+                        // cv2's 3WAY vector loop: Sp[d] < (short)(100*minS/(100-u) + 1) (oracle/sgbm_oracle.c)
+                        th = g.uniq > 0 ? (int)(int16_t)((100 * minS) / (100 - g.uniq) + 1) : 0;
+                        th = max(th, 0);
+                    } else {
+                        const int f = 100 - g.uniq;
+                        th = (minS * 100 + f - 1) / f;       // S*f < minS*100  <=>  S < ceil(minS*100/f)
+                    }
+                    th = min(th, 0x8000);
+                    const uint32_t th2 = pk_dup((uint32_t)th);
+                    uint32_t cnt2 = 0;
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) {
+                        uint32_t lt = (__vsub2(S[k], th2) >> 15) & 0x00010001u;   // S, th in [0, 0x8000]
+                        if (!FULL) lt &= ~padm[k];
+                        cnt2 += lt;
+                    }
+                    const int cnt = (int)__reduce_add_sync(FULLMASK, (cnt2 & 0xffffu) + (cnt2 >> 16));
+                    vec_st<NP>(mysc, lane, S);
+                    __syncwarp();
+                    if (lane == 0) {
+                        const size_t pix = ((size_t)b * g.H + y) * g.W + (xc + g.minX1);
+                        int out = g.INV;
+                        if (minS < (int)WALL) {
+                            const uint16_t* sv = reinterpret_cast<const uint16_t*>(mysc);
+                            auto tap = [&](int d) { return (int)sv[d < g.HALF ? 2 * d : 2 * (d - g.HALF) + 1]; };
+                            const int sm1v = best > 0 ? tap(best - 1) : 0;
+                            const int sp1v = best < g.D - 1 ? tap(best + 1) : 0;
+                            const int excl = (minS < th) + (best > 0 && sm1v < th) + (best < g.D - 1 && sp1v < th);
+                            if (cnt <= excl) {
+                                int dsub = best * 16;
+                                if (best > 0 && best < g.D - 1) {
+                                    const int den = max(sm1v + sp1v - 2 * minS, 1);
+                                    dsub += ((sm1v - sp1v) * 16 + den) / (2 * den);   // C division: truncates toward zero
+                                }
+                                out = dsub + g.minD * 16;
+                                const int x = xc + g.minX1;
+                                const int x2 = x - best - g.minD;
+                                // smallest cost wins, then the largest x: the pixel cv2's right-to-left loop keeps
+                                atomicMin(a.key + ((size_t)b * g.H + y) * g.W + x2,
+                                          ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+                            }
+                        }
+                        a.raw[pix] = (int16_t)out;
+                    }
+                    __syncwarp();
                 }
             }
             if (feed) {
-                const int cs = s + 2, cf = s + 3;
+                const int cs = i + 2, cf = i + 3;
                 if (cs < w1) stash_col(cs);
                 if (cf < w1) { wait_cols(cf + 1); fetch_col(cf); }
             }
-            __syncthreads();
+            if (VERT) {
+                __syncwarp();
+                if (SW_EXPERIMENT == 0 && lane == 0) sts_release_cta(&s_done[warp], i + 1);
+            }
+            pS += cstep;
+            sm1 = s0; s0 = sp1; sp1 = sp1 + 1 == SW_RING ? 0 : sp1 + 1;
+            cslot = cslot + 1 == NS ? 0 : cslot + 1;
         }
+        asm volatile("cp.async.wait_all;" ::: "memory");
     }
 }
 
@@ -777,7 +884,7 @@ static SgbmLayout make_layout(const SgbmGeo& g, int nb)
 {
     SgbmLayout L; size_t o = 0;
     const size_t njobs = (size_t)nb * g.nstripes;
-    L.bands = (g.rowsMax + SW_R - 1) / SW_R;
+    L.bands = (g.rowsMax + sw_rows(g.NP) - 1) / sw_rows(g.NP);
     L.ldesc = o; o += al256((size_t)nb * g.H * g.W * 32);
     L.rdesc = o; o += al256((size_t)nb * g.H * 6 * g.Wp * 4);
     const size_t vol = njobs * g.rowsMax * g.width1 * g.Dp * 2;
@@ -864,11 +971,12 @@ struct ProfScope {
     ~ProfScope() { if (idx >= 0) cudaEventRecord(h->evs[idx].b, st); }
 };
 
-template <int NP, int VAR, bool LAST>
+template <int NP, int VAR, int MASK, bool LAST>
 static int launch_sweep(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, cudaStream_t st)
 {
-    const size_t smem = ((size_t)SW_R * 3 * SW_RING * NP * 32 + SW_R * 3 * SW_RING + (size_t)SW_R * NP * 32) * 4;
-    auto kfn = k_sweep<NP, VAR, LAST>;
+    constexpr int SW_R = sw_rows(NP);
+    const size_t smem = sw_smem_words(NP, LAST) * 4;
+    auto kfn = k_sweep<NP, VAR, MASK, LAST>;
     SVB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, SW_R * 32, smem));
@@ -882,13 +990,13 @@ static int launch_sweep(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, cudaS
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
-template <int NP, bool LAST>
+template <int NP, int MASK, bool LAST>
 static int launch_sweep_var(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, int var, cudaStream_t st)
 {
     switch (var) {
-        case 0: return launch_sweep<NP, 0, LAST>(h, a, g, st);
-        case 1: return launch_sweep<NP, 1, LAST>(h, a, g, st);
-        default: return launch_sweep<NP, 2, LAST>(h, a, g, st);
+        case 0: return launch_sweep<NP, 0, MASK, LAST>(h, a, g, st);
+        case 1: return launch_sweep<NP, 1, MASK, LAST>(h, a, g, st);
+        default: return launch_sweep<NP, 2, MASK, LAST>(h, a, g, st);
     }
 }
 
@@ -954,8 +1062,6 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     a.raw = raw; a.key = key;
     a.njobs = njobs; a.bandsPerJob = L.bands;
     a.storeS = h->debug ? 1 : 0;
-    const int mask1 = g.mode == SVB_MODE_SGBM_3WAY ? (1 | 4) : 15;
-    const int mask2 = g.mode == SVB_MODE_HH ? 15 : 1;
     const int win = 2 * g.r + 1;
     const long long lmax = (long long)win * win * (2 * g.ftzero + 63) + g.P2;
     int var = g.D == g.Dp ? 1 : 0;
@@ -963,15 +1069,17 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     int rc;
     {
         ProfScope ps(h, CAT_SWEEP1, st);
-        a.dir = 1; a.mask = mask1;
-        rc = launch_sweep_var<NP, false>(h, a, g, var, st);
+        a.dir = 1;
+        rc = g.mode == SVB_MODE_SGBM_3WAY ? launch_sweep_var<NP, 5, false>(h, a, g, var, st)
+                                          : launch_sweep_var<NP, 15, false>(h, a, g, var, st);
         if (rc != SVB_OK) return rc;
         h->launches++;
     }
     {
         ProfScope ps(h, CAT_SWEEP2, st);
-        a.dir = -1; a.mask = mask2;
-        rc = launch_sweep_var<NP, true>(h, a, g, var, st);
+        a.dir = -1;
+        rc = g.mode == SVB_MODE_HH ? launch_sweep_var<NP, 15, true>(h, a, g, var, st)
+                                   : launch_sweep_var<NP, 1, true>(h, a, g, var, st);
         if (rc != SVB_OK) return rc;
         h->launches++;
     }

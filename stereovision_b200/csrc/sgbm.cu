@@ -42,6 +42,9 @@
 __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 5 ? 16 : 8; }
 #define SW_SK 2                // minimum column lag between consecutive rows of a band
 // ring slots per path between two rows (>= 4; every extra slot is a column of slack between rows)
+#ifndef SW_LOCKSTEP
+#define SW_LOCKSTEP 0          // 1: one block barrier per column step instead of per-row progress flags
+#endif
 #ifndef SW_RING_FIRST
 #define SW_RING_FIRST 6
 #define SW_RING_LAST 5
@@ -579,8 +582,8 @@ __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a
         __syncthreads();
         // Rows of a band run decoupled: warp k may start column i once warp k-1 has finished
         // column i+1 (diagonal-from-ahead predecessor), and may not lap the ring of warp k+1.
-        const bool waitPred = SW_EXPERIMENT == 0 && VERT && warp > 0;
-        const bool waitSucc = SW_EXPERIMENT == 0 && VERT && (warp + 1 < nact);
+        const bool waitPred = !SW_LOCKSTEP && SW_EXPERIMENT == 0 && VERT && warp > 0;
+        const bool waitSucc = !SW_LOCKSTEP && SW_EXPERIMENT == 0 && VERT && (warp + 1 < nact);
         int seenP = 0, seenS = 0;
 
         // running addresses (words): this lane's slice of the current column of C / S, ring slots of the
@@ -608,7 +611,14 @@ __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a
 #pragma unroll
         for (int c = 0; c < PFD; ++c) issue(c);
         int cslot = 0;
+#if SW_LOCKSTEP
+        const int nsteps = VERT ? w1 + SW_SK * (nact - 1) : w1;
+        for (int st = 0; st < nsteps; ++st) {
+            const int i = VERT ? st - SW_SK * warp : st;
+            if (i < 0 || i >= nloop) { if (VERT) __syncthreads(); continue; }
+#else
         for (int i = 0; i < nloop; ++i) {
+#endif
             if (waitPred) {
                 const int need = min(i + SW_SK, w1);
                 if (seenP < need) {
@@ -762,10 +772,14 @@ __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a
                 if (cs < w1) stash_col(cs);
                 if (cf < w1) { wait_cols(cf + 1); fetch_col(cf); }
             }
+#if SW_LOCKSTEP
+            if (VERT) __syncthreads();
+#else
             if (VERT) {
                 __syncwarp();
                 if (SW_EXPERIMENT == 0 && lane == 0) sts_release_cta(&s_done[warp], i + 1);
             }
+#endif
             pS += cstep;
             sm1 = s0; s0 = sp1; sp1 = sp1 + 1 == SW_RING ? 0 : sp1 + 1;
             cslot = cslot + 1 == NS ? 0 : cslot + 1;

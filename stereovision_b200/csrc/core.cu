@@ -43,3 +43,33 @@ extern "C" int svb_init(int device)
     SVB_CUDA(cudaFree(0));
     return SVB_OK;
 }
+
+#include <cuda.h>
+typedef CUresult (*svb_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                        const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                        CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+int svb_make_tmap_2d_u32(void* tmap_out, const void* base, uint64_t inner, uint64_t rows, uint64_t pitch_bytes,
+                         uint32_t box_inner, uint32_t box_rows)
+{
+    static svb_encode_tiled_fn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        SVB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (!p || q != cudaDriverEntryPointSuccess) { svb_set_error("cuTensorMapEncodeTiled is not available"); return SVB_ERR_CUDA; }
+        fn = (svb_encode_tiled_fn)p;
+    }
+    const cuuint64_t dims[2] = {inner, rows};
+    const cuuint64_t strides[1] = {pitch_bytes};
+    const cuuint32_t box[2] = {box_inner, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn((CUtensorMap*)tmap_out, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        svb_set_error("cuTensorMapEncodeTiled failed (%d): inner %llu rows %llu pitch %llu box %ux%u", (int)r,
+                      (unsigned long long)inner, (unsigned long long)rows, (unsigned long long)pitch_bytes, box_inner, box_rows);
+        return SVB_ERR_CUDA;
+    }
+    return SVB_OK;
+}

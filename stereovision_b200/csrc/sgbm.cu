@@ -178,175 +178,6 @@ __device__ __forceinline__ void cp_async_vec(uint32_t* smem_dst, const uint32_t*
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // ------------------------------------------------------------------------------------------
-// k_cost: one CTA walks DOWN a strip of columns of one job (a row segment of it).  Per image
-// row: every warp computes the BT pixel-cost vectors (A.1 step 4) of two strip columns from
-// operands staged in shared memory (cp.async, one row ahead) and parks them in a shared
-// buffer; after ONE block barrier every warp sums 2r+1 neighbouring columns (horizontal box,
-// A.2), pushes the sum into a per-column ring of the last bs rows and keeps the vertical box
-// sum C(y) = C(y-1) + hs(y+r) - hs(y-r-1) in registers -> HBM.  Replicate borders: columns clamp
-// in the cost domain, rows clamp into [ys, H-1].
-// Lane mapping: (reg k, lane l) <-> word w = 32k + l (descriptor loads and volume stores are
-// contiguous across the warp).
-// ------------------------------------------------------------------------------------------
-#define CK_WARPS 16
-#define CK_PC 32               // pixel-cost columns per strip (2 per warp)
-
-struct CostArgs {
-    int OC;                    // output columns per strip = CK_PC - 2r (or less when the ring is large)
-    int nstrips, rseg, nsegs;  // strips per row, rows per segment, segments per job
-    int SE;                    // staged right-descriptor entries per plane = HALF + CK_PC
-};
-
-template <int NP>
-__global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const uint32_t* __restrict__ ldesc, const uint32_t* __restrict__ rdesc,
-                                                        SgbmGeo g, CostArgs ca, uint32_t* __restrict__ vol)
-{
-    constexpr int VW = NP * 32;
-    extern __shared__ uint32_t smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int r = g.r, bs = 2 * r + 1, OC = ca.OC, PC = OC + 2 * r, SE = ca.SE;
-    uint32_t* stage = smem;                                  // [2][6][SE]
-    uint32_t* lstage = stage + 2 * 6 * SE;                   // [2][CK_PC][8]
-    uint32_t* pixbuf = lstage + 2 * CK_PC * 8;               // [2][CK_PC][VW]
-    uint32_t* ring = pixbuf + 2 * CK_PC * VW;                // [OC][bs][VW]
-
-    const int strip = blockIdx.x % ca.nstrips, seg = blockIdx.x / ca.nstrips;
-    const int job = blockIdx.y, b = job / g.nstripes, n = job % g.nstripes;
-    int ys, ye, keep;
-    job_rows(g, n, ys, ye, keep);
-    const int ya = ys + seg * ca.rseg, yb = min(ya + ca.rseg, ye);   // output rows of this CTA
-    if (ya >= yb) return;
-    const int xs = strip * OC;                               // first output column (cost domain)
-    const int w1 = g.width1;
-
-    // pix column c (0..PC-1) <-> cost column clamp(xs - r + c) ; image column = + minX1
-    // staged entries cover xr in [xbase, xbase + SE): xbase = (xs - r + minX1 - minD) - (HALF - 1)
-    const int xbase = xs - r + g.minX1 - g.minD - (g.HALF - 1);
-
-    auto issue_row = [&](int v, int buf) {
-        const int yy = min(max(v, ys), g.H - 1);
-        const uint32_t* rrow = rdesc + (size_t)(b * g.H + yy) * 6 * g.Wp;
-        uint32_t* st = stage + buf * 6 * SE;
-        for (int i = threadIdx.x; i < 6 * SE; i += blockDim.x) {
-            const int p = i / SE, e = i - p * SE;
-            const int xr = min(max(xbase + e, 0), g.W - 1);
-            cp_async4(st + i, rrow + (size_t)p * g.Wp + xr);
-        }
-        const uint32_t* lrow = ldesc + (size_t)(b * g.H + yy) * g.W * 8;
-        uint32_t* ls = lstage + buf * CK_PC * 8;
-        for (int i = threadIdx.x; i < PC * 2; i += blockDim.x) {
-            const int c = i >> 1, h = i & 1;
-            const int x = min(max(xs - r + c, 0), w1 - 1) + g.minX1;
-            cp_async16(ls + c * 8 + h * 4, lrow + (size_t)x * 8 + h * 4);
-        }
-    };
-
-    // pad mask for this lane's words (w = 32k + lane)
-    uint32_t padm[NP];
-#pragma unroll
-    for (int k = 0; k < NP; ++k) {
-        const int w = 32 * k + lane;
-        padm[k] = (w >= g.D ? 0xffffu : 0u) | (w + g.HALF >= g.D ? 0xffff0000u : 0u);
-    }
-
-    uint32_t acc[2][NP];
-#pragma unroll
-    for (int c = 0; c < 2; ++c)
-#pragma unroll
-        for (int k = 0; k < NP; ++k) acc[c][k] = 0;
-
-    const int v0 = ya - r, v1 = yb - 1 + r;                  // virtual input rows (clamped on use)
-    issue_row(v0, 0);
-    asm volatile("cp.async.commit_group;");
-    if (v0 + 1 <= v1) issue_row(v0 + 1, 1);
-    asm volatile("cp.async.commit_group;");
-    asm volatile("cp.async.wait_group 1;" ::: "memory");
-    __syncthreads();
-
-    for (int v = v0; v <= v1; ++v) {
-        const int it = v - v0, buf = it & 1;
-        const uint32_t* st = stage + buf * 6 * SE;
-        const uint32_t* ls = lstage + buf * CK_PC * 8;
-        uint32_t* pb = pixbuf + buf * CK_PC * VW;
-        // ---- pixel costs of this warp's two strip columns
-#pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-            const int c = 2 * warp + cc;
-            if (c < PC) {
-                const uint4 l0 = *reinterpret_cast<const uint4*>(ls + c * 8);
-                const uint4 l1 = *reinterpret_cast<const uint4*>(ls + c * 8 + 4);
-                // entry index of word w: (x_img - minD - w) - xbase, x_img = clamp(xs-r+c)+minX1
-                const int xq = min(max(xs - r + c, 0), w1 - 1);
-                const int e0 = (xq + g.minX1 - g.minD) - xbase - lane;
-#pragma unroll
-                for (int k = 0; k < NP; ++k) {
-                    const int e = e0 - 32 * k;
-                    const uint32_t v1a = st[0 * SE + e], v0a = st[1 * SE + e], nva = st[2 * SE + e];
-                    const uint32_t v1b = st[3 * SE + e], v0b = st[4 * SE + e], nvb = st[5 * SE + e];
-                    // channel 0: c0 = max(0, u - v1, v0 - u); c1 = max(0, v - u1, u0 - v)
-                    uint32_t a = __vsub2(l0.x, v1a);
-                    uint32_t c0 = __viaddmax_s16x2_relu(v0a, l0.y, a);
-                    uint32_t bb = __vsub2(l0.w, nva);
-                    uint32_t c1 = __viaddmax_s16x2_relu(l0.z, nva, bb);
-                    uint32_t pix = __vminu2(c0, c1);
-                    // channel 1 (raw intensity), cost >> 2
-                    a = __vsub2(l1.x, v1b);
-                    c0 = __viaddmax_s16x2_relu(v0b, l1.y, a);
-                    bb = __vsub2(l1.w, nvb);
-                    c1 = __viaddmax_s16x2_relu(l1.z, nvb, bb);
-                    pix += (__vminu2(c0, c1) >> 2) & 0x3fff3fffu;
-                    pb[c * VW + 32 * k + lane] = pix;
-                }
-            }
-        }
-        cp_async_wait_all();
-        __syncthreads();
-        if (v + 2 <= v1) issue_row(v + 2, buf);
-        asm volatile("cp.async.commit_group;");
-        // ---- horizontal box over 2r+1 columns, vertical running sum, store
-        const int oc0 = 2 * warp;
-        if (oc0 < OC) {
-            uint32_t hs0[NP], hs1[NP];
-#pragma unroll
-            for (int k = 0; k < NP; ++k) hs0[k] = 0;
-            for (int j = 0; j < bs; ++j) {
-#pragma unroll
-                for (int k = 0; k < NP; ++k) hs0[k] += pb[(oc0 + j) * VW + 32 * k + lane];
-            }
-            const bool two = oc0 + 1 < OC;
-            if (two) {
-#pragma unroll
-                for (int k = 0; k < NP; ++k)
-                    hs1[k] = hs0[k] - pb[oc0 * VW + 32 * k + lane] + pb[(oc0 + bs) * VW + 32 * k + lane];
-            }
-            const int slot = it % bs;
-            const bool full = it >= bs;                       // ring holds hs(v - bs) in `slot`
-            const int y = v - r;                              // output row once the window is complete
-            const bool emit = it >= bs - 1;
-#pragma unroll
-            for (int cc = 0; cc < 2; ++cc) {
-                if (cc == 1 && !two) break;
-                const int oc = oc0 + cc;
-                uint32_t* rg = ring + ((size_t)oc * bs + slot) * VW;
-                const int xc = xs + oc;
-#pragma unroll
-                for (int k = 0; k < NP; ++k) {
-                    const uint32_t h = cc ? hs1[k] : hs0[k];
-                    const uint32_t old = full ? rg[32 * k + lane] : 0u;
-                    rg[32 * k + lane] = h;
-                    acc[cc][k] += h - old;
-                }
-                if (emit && xc < w1) {
-                    uint32_t* dst = vol + (((size_t)job * g.rowsMax + (y - ys)) * w1 + xc) * VW;
-#pragma unroll
-                    for (int k = 0; k < NP; ++k) dst[32 * k + lane] = (acc[cc][k] & ~padm[k]) | (WALL2 & padm[k]);
-                }
-            }
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------
 // Vector helpers for the sweep: lane l <-> words NP*l .. NP*l+NP-1 of a pixel's vector.
 // ------------------------------------------------------------------------------------------
 template <int NP, typename LD>
@@ -387,6 +218,205 @@ __device__ __forceinline__ void vec_st(uint32_t* p, int lane, const uint32_t (&v
     } else {
 #pragma unroll
         for (int i = 0; i < NP; ++i) w[i] = v[i];
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_cost: one CTA walks DOWN a strip of columns of one job (a row segment of it).  Per image
+// row one elected thread asks the TMA for two tiles (cp.async.bulk.tensor, one row ahead,
+// completion on an mbarrier): the 6 right-descriptor planes over the strip's disparity window
+// and the strip's left records.  Every warp then computes the BT pixel-cost vectors (A.1
+// step 4) of two strip columns and parks them in a shared buffer; after ONE block barrier every
+// warp sums 2r+1 neighbouring columns (horizontal box, A.2), pushes the sum into a per-column
+// ring of the last bs rows and keeps the vertical box sum C(y) = C(y-1) + hs(y+r) - hs(y-r-1)
+// in registers -> HBM.  Replicate borders: columns clamp in the cost domain, rows clamp into
+// [ys, H-1].
+// Lane mappings: the pixel-cost phase uses (reg k, lane l) <-> word 32k + l (descriptor loads
+// are contiguous across the warp); the box-sum phase is element-wise and uses the sweep's
+// mapping (lane l <-> words NP*l..) so that shared and global accesses are 128-bit.
+// ------------------------------------------------------------------------------------------
+#define CK_WARPS 16
+#define CK_PC 32               // pixel-cost columns per strip (2 per warp)
+// staged entries per plane: the disparity window of the strip + 8 so that the window can start on a
+// 16-byte boundary (TMA needs the inner coordinate's byte offset 16-byte aligned -- measured, tools/tma_test.cu)
+__host__ __device__ constexpr int ck_se(int NP) { return 32 * NP + CK_PC + 8; }
+__host__ __device__ constexpr int ck_nblk(int NP) { return ck_se(NP) > 256 ? 2 : 1; }   // TMA boxes are <= 256 wide
+__host__ __device__ constexpr int ck_blkw(int NP) { return (6 * (ck_se(NP) / ck_nblk(NP)) + 31) & ~31; }   // words per staged box, 128-byte padded
+
+struct CostArgs {
+    int OC;                    // output columns per strip = CK_PC - 2r (or less when the ring is large)
+    int nstrips, rseg, nsegs;  // strips per row, rows per segment, segments per job
+};
+
+template <int NP, bool FULL>
+__global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ CUtensorMap tmR,
+                                                        const __grid_constant__ CUtensorMap tmL,
+                                                        SgbmGeo g, CostArgs ca, uint32_t* __restrict__ vol)
+{
+    constexpr int VW = NP * 32, SE = ck_se(NP), NBLK = ck_nblk(NP), BW = SE / NBLK, BLKW = ck_blkw(NP);
+    extern __shared__ __align__(128) uint32_t smem[];
+    __shared__ __align__(8) uint64_t mbar[2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int r = g.r, bs = 2 * r + 1, OC = ca.OC, PC = OC + 2 * r;
+    uint32_t* stage = smem;                                  // [2][NBLK][6][BW] (each box padded to BLKW words)
+    uint32_t* lstage = stage + 2 * NBLK * BLKW;                   // [2][CK_PC][8]
+    uint32_t* pixbuf = lstage + 2 * CK_PC * 8;               // [2][CK_PC][VW]
+    uint32_t* ring = pixbuf + 2 * CK_PC * VW;                // [OC][bs][VW]
+
+    const int strip = blockIdx.x % ca.nstrips, seg = blockIdx.x / ca.nstrips;
+    const int job = blockIdx.y, b = job / g.nstripes, n = job % g.nstripes;
+    int ys, ye, keep;
+    job_rows(g, n, ys, ye, keep);
+    const int ya = ys + seg * ca.rseg, yb = min(ya + ca.rseg, ye);   // output rows of this CTA
+    if (ya >= yb) return;
+    const int xs = strip * OC;                               // first output column (cost domain)
+    const int w1 = g.width1;
+
+    // pix column c (0..PC-1) <-> cost column clamp(xs - r + c); image column = + minX1.
+    // The staged window is NOT clamped (TMA zero-fills outside the tensor); indices into it are.
+    // right entries cover xr in [xbase, xbase + SE): xbase = (xs - r + minX1 - minD) - (HALF - 1)
+    const int xbase0 = xs - r + g.minX1 - g.minD - (g.HALF - 1);
+    const int xbase = xbase0 & ~3;                           // floor to a multiple of 4 entries (16 bytes)
+    const int xl0 = xs - r + g.minX1;                        // image column of left record 0
+
+    auto issue_row = [&](int v, int buf) {                   // one thread
+        const int yy = min(max(v, ys), g.H - 1);
+        mbar_expect_tx(&mbar[buf], (6 * SE + CK_PC * 8) * 4);
+#pragma unroll
+        for (int q = 0; q < NBLK; ++q)
+            tma_load_2d(stage + (buf * NBLK + q) * BLKW, &tmR, xbase + q * BW, (b * g.H + yy) * 6, &mbar[buf]);
+        tma_load_2d(lstage + buf * CK_PC * 8, &tmL, xl0 * 8, b * g.H + yy, &mbar[buf]);
+    };
+
+    if (threadIdx.x == 0) {
+        mbar_init(&mbar[0], 1);
+        mbar_init(&mbar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const int v0 = ya - r, v1 = yb - 1 + r;                  // virtual input rows (clamped on use)
+    if (threadIdx.x == 0) {
+        issue_row(v0, 0);
+        if (v0 + 1 <= v1) issue_row(v0 + 1, 1);
+    }
+
+    // pad masks: pix phase (w = 32k + lane) is not needed (masking happens at the store);
+    // box phase mapping w = NP*lane + k
+    uint32_t padm[NP];
+#pragma unroll
+    for (int k = 0; k < NP; ++k) {
+        const int w = NP * lane + k;
+        padm[k] = (w >= g.D ? 0xffffu : 0u) | (w + g.HALF >= g.D ? 0xffff0000u : 0u);
+    }
+    uint32_t acc[2][NP];
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int k = 0; k < NP; ++k) acc[c][k] = 0;
+
+    // this warp's two pix columns: clamped column, index into the staged windows
+    int eoff[2], loff[2];
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+        const int c = 2 * warp + cc;
+        const int xq = min(max(xs - r + c, 0), w1 - 1);
+        const int cq = xq - (xs - r);                        // column inside the window
+        eoff[cc] = cq + g.HALF - 1 - lane + (xbase0 - xbase);   // entry of word w = lane; word 32k+lane: - 32k
+        loff[cc] = cq * 8;
+    }
+    const int oc0 = 2 * warp;
+    const bool two = oc0 + 1 < OC;
+    int slot = 0;
+
+    for (int v = v0; v <= v1; ++v) {
+        const int it = v - v0, buf = it & 1;
+        const uint32_t* st = stage + buf * NBLK * BLKW;
+        const uint32_t* ls = lstage + buf * CK_PC * 8;
+        uint32_t* pb = pixbuf + buf * CK_PC * VW;
+        mbar_wait(&mbar[buf], (it >> 1) & 1);
+        // ---- pixel costs of this warp's two strip columns
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int c = 2 * warp + cc;
+            if (c < PC) {
+                const uint4 l0 = *reinterpret_cast<const uint4*>(ls + loff[cc]);
+                const uint4 l1 = *reinterpret_cast<const uint4*>(ls + loff[cc] + 4);
+#pragma unroll
+                for (int k = 0; k < NP; ++k) {
+                    int e = eoff[cc] - 32 * k;
+                    const uint32_t* sp = st;
+                    if (NBLK > 1) { if (e >= BW) { e -= BW; sp += BLKW; } }
+                    const uint32_t v1a = sp[0 * BW + e], v0a = sp[1 * BW + e], nva = sp[2 * BW + e];
+                    const uint32_t v1b = sp[3 * BW + e], v0b = sp[4 * BW + e], nvb = sp[5 * BW + e];
+                    // channel 0: c0 = max(0, u - v1, v0 - u); c1 = max(0, v - u1, u0 - v)
+                    uint32_t a = __vsub2(l0.x, v1a);
+                    uint32_t c0 = __viaddmax_s16x2_relu(v0a, l0.y, a);
+                    uint32_t bb = __vsub2(l0.w, nva);
+                    uint32_t c1 = __viaddmax_s16x2_relu(l0.z, nva, bb);
+                    uint32_t pix = __vminu2(c0, c1);
+                    // channel 1 (raw intensity), cost >> 2
+                    a = __vsub2(l1.x, v1b);
+                    c0 = __viaddmax_s16x2_relu(v0b, l1.y, a);
+                    bb = __vsub2(l1.w, nvb);
+                    c1 = __viaddmax_s16x2_relu(l1.z, nvb, bb);
+                    pix += (__vminu2(c0, c1) >> 2) & 0x3fff3fffu;
+                    pb[c * VW + 32 * k + lane] = pix;
+                }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0 && v + 2 <= v1) issue_row(v + 2, buf);
+        // ---- horizontal box over 2r+1 columns, vertical running sum, store
+        if (oc0 < OC) {
+            uint32_t hs0[NP], hs1[NP], t[NP];
+            const uint32_t* pcol = pb + oc0 * VW;
+            vec_ld<NP>(pcol, lane, hs0, LdPlain());
+            uint32_t first[NP];
+#pragma unroll
+            for (int k = 0; k < NP; ++k) first[k] = hs0[k];
+            for (int j = 1; j < bs; ++j) {
+                vec_ld<NP>(pcol + j * VW, lane, t, LdPlain());
+#pragma unroll
+                for (int k = 0; k < NP; ++k) hs0[k] += t[k];
+            }
+            if (two) {
+                vec_ld<NP>(pcol + bs * VW, lane, t, LdPlain());
+#pragma unroll
+                for (int k = 0; k < NP; ++k) hs1[k] = hs0[k] - first[k] + t[k];
+            }
+            const bool full = it >= bs;                       // ring holds hs(v - bs) in `slot`
+            const int y = v - r;                              // output row once the window is complete
+            const bool emit = it >= bs - 1;
+#pragma unroll
+            for (int cc = 0; cc < 2; ++cc) {
+                if (cc == 1 && !two) break;
+                const int oc = oc0 + cc;
+                uint32_t* rg = ring + ((size_t)oc * bs + slot) * VW;
+                const int xc = xs + oc;
+                if (full) {
+                    vec_ld<NP>(rg, lane, t, LdPlain());
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) acc[cc][k] -= t[k];
+                }
+                if (cc == 0) {
+                    vec_st<NP>(rg, lane, hs0);
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) acc[0][k] += hs0[k];
+                } else {
+                    vec_st<NP>(rg, lane, hs1);
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) acc[1][k] += hs1[k];
+                }
+                if (emit && xc < w1) {
+                    uint32_t* dst = vol + (((size_t)job * g.rowsMax + (y - ys)) * w1 + xc) * VW;
+                    uint32_t o[NP];
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) o[k] = FULL ? acc[cc][k] : ((acc[cc][k] & ~padm[k]) | (WALL2 & padm[k]));
+                    vec_st<NP>(dst, lane, o);
+                }
+            }
+        }
+        slot = slot + 1 == bs ? 0 : slot + 1;
     }
 }
 
@@ -1039,8 +1069,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         // k_cost tiling: ring of bs rows per output column in shared memory
         const int bs = 2 * g.r + 1, VW = NP * 32;
         CostArgs ca;
-        ca.SE = g.HALF + CK_PC;
-        const size_t fixed = ((size_t)2 * 6 * ca.SE + 2 * CK_PC * 8 + (size_t)2 * CK_PC * VW) * 4;
+        const size_t fixed = ((size_t)2 * ck_nblk(NP) * ck_blkw(NP) + 2 * CK_PC * 8 + (size_t)2 * CK_PC * VW) * 4;
         const size_t budget = 200 * 1024;
         int OC = CK_PC - 2 * g.r;
         while (OC > 1 && fixed + (size_t)OC * bs * VW * 4 > budget) --OC;
@@ -1056,10 +1085,22 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         ca.rseg = svb_ceil_div(g.rowsMax, nsegs);
         ca.nsegs = svb_ceil_div(g.rowsMax, ca.rseg);
         const size_t smem = fixed + (size_t)OC * bs * VW * 4;
-        SVB_CUDA(cudaFuncSetAttribute(k_cost<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        // TMA views: right planes [nb*H*6][Wp] u32 (box 6 x BW), left records [nb*H][W*8] u32 (box 1 x 256)
+        CUtensorMap tmR, tmL;
+        int rc = svb_make_tmap_2d_u32(&tmR, rdesc, (uint64_t)g.Wp, (uint64_t)nb * g.H * 6, (uint64_t)g.Wp * 4,
+                                      ck_se(NP) / ck_nblk(NP), 6);
+        if (rc != SVB_OK) return rc;
+        rc = svb_make_tmap_2d_u32(&tmL, ldesc, (uint64_t)g.W * 8, (uint64_t)nb * g.H, (uint64_t)g.W * 32, CK_PC * 8, 1);
+        if (rc != SVB_OK) return rc;
         dim3 grid(ca.nstrips * ca.nsegs, njobs);
         ProfScope ps(h, CAT_COST, st);
-        k_cost<NP><<<grid, CK_WARPS * 32, smem, st>>>(ldesc, rdesc, g, ca, Cv);
+        if (g.D == g.Dp) {
+            SVB_CUDA(cudaFuncSetAttribute(k_cost<NP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_cost<NP, true><<<grid, CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv);
+        } else {
+            SVB_CUDA(cudaFuncSetAttribute(k_cost<NP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_cost<NP, false><<<grid, CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv);
+        }
         SVB_LAUNCH_CHECK(); h->launches++;
     }
 

@@ -59,3 +59,37 @@ __device__ __forceinline__ uint32_t pk_hmin(uint32_t a) { return min(a & 0xffffu
 // (hi16 of a -> lo, lo16 of b -> hi)
 __device__ __forceinline__ uint32_t pk_shift_in(uint32_t a, uint32_t b) { return __byte_perm(a, b, 0x5432); }
 #endif
+
+#ifdef __CUDACC__
+// ---- TMA (cp.async.bulk.tensor) + mbarrier helpers, sm_100a
+#include <cuda.h>
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+// 2-D tile global -> shared, completion counted in bytes on `bar` (x = inner coordinate)
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, int x, int y, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(x), "r"(y), "r"(smem_u32(bar)) : "memory");
+}
+#endif
+
+// Host: encode a 2-D u32 tensor map (row pitch in bytes must be a multiple of 16); the driver
+// entry point is resolved through the runtime, libsvb does not link libcuda.
+int svb_make_tmap_2d_u32(void* tmap_out /* CUtensorMap */, const void* base, uint64_t inner, uint64_t rows,
+                         uint64_t pitch_bytes, uint32_t box_inner, uint32_t box_rows);

@@ -140,8 +140,9 @@ extern "C" int svb_disp_to_depth_dev(const int16_t* disp16, int B, int H, int W,
 
 // ---------------------------------------------------------------------------------------
 // filterSpeckles = connected-component labelling (4-neighbourhood, |a-b| <= maxDiff, both
-// != newVal) + size threshold.  Union-find with atomicMin hooking (roots are the smallest
-// linear index of their component), so the outcome is deterministic.
+// != newVal) + size threshold.  Horizontal runs are labelled without atomics; union-find with
+// atomicMin hooking (roots are the smallest linear index of their component) joins the runs
+// vertically, so the outcome is deterministic.
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ int ccl_find(const int32_t* label, int a)
 {
@@ -161,49 +162,81 @@ __device__ __forceinline__ void ccl_union(int32_t* label, int a, int b)
         a = old;
     }
 }
-__global__ void __launch_bounds__(256) k_ccl_init(const int16_t* __restrict__ img, size_t n, int newVal,
-                                                  int32_t* __restrict__ label, int32_t* __restrict__ count)
+// Rows first: a warp walks one image row in 32-pixel chunks and labels every pixel with the
+// linear index of the first pixel of its horizontal run (ballot + clz, no atomics).  Only the
+// run heads are union-find nodes afterwards.
+__global__ void __launch_bounds__(256) k_ccl_runs(const int16_t* __restrict__ img, int rows, int W, int newVal,
+                                                  int maxDiff, int32_t* __restrict__ label, int32_t* __restrict__ count)
 {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    label[i] = img[i] != newVal ? (int32_t)i : -1;
-    count[i] = 0;
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const size_t base = (size_t)row * W;
+    int carry = -1, lastv = newVal;
+    for (int x0 = 0; x0 < W; x0 += 32) {
+        const int x = x0 + lane;
+        const int v = x < W ? (int)img[base + x] : newVal;
+        int left = __shfl_up_sync(0xffffffffu, v, 1);
+        if (lane == 0) left = lastv;
+        const bool valid = v != newVal;
+        const bool start = valid && !(left != newVal && abs(v - left) <= maxDiff);
+        const unsigned smask = __ballot_sync(0xffffffffu, start);
+        const unsigned m = smask & ((2u << lane) - 1u);
+        const int rs = m ? x0 + 31 - __clz(m) : carry;
+        if (x < W) {
+            label[base + x] = valid ? (int32_t)(base + rs) : -1;
+            count[base + x] = 0;
+        }
+        carry = __shfl_sync(0xffffffffu, valid ? rs : -1, 31);
+        lastv = __shfl_sync(0xffffffffu, v, 31);
+    }
 }
-__global__ void __launch_bounds__(256) k_ccl_merge(const int16_t* __restrict__ img, int H, int W, int newVal,
-                                                   int maxDiff, int32_t* __restrict__ label)
+// Vertical links: one union per (run, run above) contact stretch -- a pixel whose left neighbour is in
+// the same run on both rows and is itself linked upwards leaves the union to that neighbour.
+__global__ void __launch_bounds__(256) k_ccl_vmerge(const int16_t* __restrict__ img, int H, int W, int newVal,
+                                                    int maxDiff, int32_t* __restrict__ label)
 {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y + 1;
     if (x >= W) return;
     const int p = (int)(((size_t)blockIdx.z * H + y) * W + x);
     const int v = img[p];
     if (v == newVal) return;
+    const int u = img[p - W];
+    if (u == newVal || abs(v - u) > maxDiff) return;
     if (x > 0) {
-        const int q = img[p - 1];
-        if (q != newVal && abs(v - q) <= maxDiff) ccl_union(label, p, p - 1);
+        const int vl = img[p - 1], ul = img[p - W - 1];
+        if (vl != newVal && ul != newVal && abs(v - vl) <= maxDiff && abs(u - ul) <= maxDiff && abs(vl - ul) <= maxDiff) return;
     }
-    if (y > 0) {
-        const int q = img[p - W];
-        if (q != newVal && abs(v - q) <= maxDiff) ccl_union(label, p, p - W);
-    }
+    ccl_union(label, p, p - W);
 }
-__global__ void __launch_bounds__(256) k_ccl_count(size_t n, int32_t* __restrict__ label, int32_t* __restrict__ count)
+// Component sizes: the last pixel of every run adds the run length to its root, and points the run
+// head straight at the root.
+__global__ void __launch_bounds__(256) k_ccl_count(const int16_t* __restrict__ img, int W, int newVal, int maxDiff,
+                                                   int32_t* __restrict__ label, int32_t* __restrict__ count)
 {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int root = -1;
-    if (i < n && label[i] >= 0) { root = ccl_find(label, (int)i); label[i] = root; }
-    // warp-aggregated increment: one atomic per distinct root per warp
-    const unsigned peers = __match_any_sync(0xffffffffu, root);
-    if (root >= 0 && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&count[root], __popc(peers));
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= W) return;
+    const int p = (int)(((size_t)blockIdx.z * gridDim.y + blockIdx.y) * W + x);
+    const int v = img[p];
+    if (v == newVal) return;
+    if (x + 1 < W) {
+        const int vn = img[p + 1];
+        if (vn != newVal && abs(vn - v) <= maxDiff) return;           // not the end of its run
+    }
+    bool head = x == 0;
+    if (!head) { const int vl = img[p - 1]; head = vl == newVal || abs(v - vl) > maxDiff; }
+    const int rs = head ? p : label[p];
+    const int root = ccl_find(label, rs);
+    atomicAdd(&count[root], p - rs + 1);
+    if (root != rs) label[rs] = root;
 }
 __global__ void __launch_bounds__(256) k_ccl_apply(int16_t* __restrict__ img, size_t n, int newVal, int maxSize,
                                                    const int32_t* __restrict__ label, const int32_t* __restrict__ count)
 {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const int l = label[i];
-    // label[i] may still point at a non-root written before flattening finished elsewhere: chase it
-    if (l >= 0) {
-        const int root = ccl_find(label, l);
+    if (label[i] >= 0) {
+        const int root = ccl_find(label, (int)i);
         if (count[root] <= maxSize) img[i] = (int16_t)newVal;
     }
 }
@@ -217,14 +250,16 @@ extern "C" int svb_filter_speckles_s16_dev(int16_t* img, int B, int H, int W, in
     cudaStream_t st = (cudaStream_t)stream;
     int32_t* label = scratch;
     int32_t* count = scratch + n;
-    const int nb = svb_ceil_div(n, 256);
-    k_ccl_init<<<nb, 256, 0, st>>>(img, n, newVal, label, count);
+    const int rows = B * H;
+    k_ccl_runs<<<svb_ceil_div(rows, 8), 256, 0, st>>>(img, rows, W, newVal, maxDiff, label, count);
     SVB_LAUNCH_CHECK();
-    k_ccl_merge<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(img, H, W, newVal, maxDiff, label);
+    if (H > 1) {
+        k_ccl_vmerge<<<dim3(svb_ceil_div(W, 256), H - 1, B), 256, 0, st>>>(img, H, W, newVal, maxDiff, label);
+        SVB_LAUNCH_CHECK();
+    }
+    k_ccl_count<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(img, W, newVal, maxDiff, label, count);
     SVB_LAUNCH_CHECK();
-    k_ccl_count<<<nb, 256, 0, st>>>(n, label, count);
-    SVB_LAUNCH_CHECK();
-    k_ccl_apply<<<nb, 256, 0, st>>>(img, n, newVal, maxSpeckleSize, label, count);
+    k_ccl_apply<<<svb_ceil_div(n, 256), 256, 0, st>>>(img, n, newVal, maxSpeckleSize, label, count);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

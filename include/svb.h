@@ -124,6 +124,54 @@ int svb_disp_to_depth_dev(const int16_t* disp16_dev, int B, int H, int W, double
 int svb_reproject3d_dev(const void* disp_dev, int is_s16, int B, int H, int W, const double* Q_host16,
                         int handleMissingValues, float* minscratch_dev, float* out_dev, void* stream);
 
+/* ==== Fusion chain of fused_depth_map.py.  All maps are f32 [B,H,W] on the
+ *      device; no call synchronises the stream.  Scratch is caller-owned (sizes from the *_scratch_bytes
+ *      functions). */
+
+/* fused_depth_map.py:1010-1029: norm = uint8((clip(d, min, min+num-1) - min) / num * 255) as f32,
+ * conf = 1 where min+1 < d < min+num-1 else 0. */
+int svb_normalize_disparity_dev(const float* disp_dev, int B, int H, int W, int min_disp, int num_disp,
+                                float* norm_dev, float* conf_dev, void* stream);
+
+/* Scratch for svb_calibrate_midas_dev / svb_normalize_to_stereo_range_dev / svb_percentiles_f32_dev. */
+size_t svb_range_scratch_bytes(int B);
+/* calibrate_midas_to_stereo (fused_depth_map.py:1169-1257): np.percentile 10/90 over conf > 0.7
+ * (5/95 over everything when fewer than 100 reliable pixels), then the affine / min-max mapping. */
+int svb_calibrate_midas_dev(const float* midas_dev, const float* stereo_disp_dev, const float* stereo_conf_dev,
+                            int B, int H, int W, float* out_dev, void* scratch_dev, size_t scratch_bytes, void* stream);
+/* normalize_to_stereo_range (fused_depth_map.py:1503-1554). */
+int svb_normalize_to_stereo_range_dev(const float* depth_dev, const float* stereo_disp_dev, int B, int H, int W,
+                                      float* out_dev, void* scratch_dev, size_t scratch_bytes, void* stream);
+/* np.percentile(vals[mask], 5 / 95) (exact order statistics + NumPy's linear interpolation).
+ * mask_mode 0: all; 1: mask > mask_thr; 2: vals > 0; 3: mask > mask_thr when at least 100 such
+ * pixels (then q = 10 / 90 in float64, as np.percentile(v, [10, 90])), else all.
+ * out_dev: double [B][2]; count_dev: unsigned [B] selected elements (may be NULL). */
+int svb_percentiles_f32_dev(const float* vals_dev, const float* mask_dev, float mask_thr, int mask_mode, int B,
+                            size_t n, double* out_dev, unsigned* count_dev, void* scratch_dev, size_t scratch_bytes,
+                            void* stream);
+
+/* fuse_depth_maps (fused_depth_map.py:1560-1698); the module-global fusion_params / FUSION_SMOOTHING /
+ * FUSION_METHODS dictionaries (fused_depth_map.py:80-116) become this struct. */
+typedef struct svb_fuse_params {
+    double stereo_weight, midas_fill_weight, flow_fill_weight, stereo_conf_threshold, flow_hole_threshold;
+    double bilateral_sigma_color, bilateral_sigma_space;
+    int blend_ksize, bilateral_d, use_midas_fill, use_flow_fill;
+} svb_fuse_params;
+size_t svb_fuse_scratch_bytes(int B, int H, int W);
+/* stereo_dev / midas_dev / flow_dev may be NULL (method absent or disabled; flow_dev NULL when the
+ * camera is not moving); conf_dev NULL = confidence 1.  out_u8_dev: the fused map; out_f32_dev
+ * (may be NULL): the value before the uint8 cast. */
+int svb_fuse_depth_maps_dev(const float* stereo_dev, const float* conf_dev, const float* midas_dev,
+                            const float* flow_dev, int B, int H, int W, const svb_fuse_params* p,
+                            uint8_t* out_u8_dev, float* out_f32_dev, void* scratch_dev, size_t scratch_bytes,
+                            void* stream);
+
+/* detect_camera_occlusion statistics (fused_depth_map.py:170-240) of u8 gray [B,H,W]:
+ * stats_dev double [B][5] = {mean block std, low-variance block ratio, global std, entropy, mean}. */
+size_t svb_occlusion_scratch_bytes(int B, int H, int W, int block);
+int svb_occlusion_stats_u8_dev(const uint8_t* gray_dev, int B, int H, int W, int block, double* stats_dev,
+                               void* scratch_dev, size_t scratch_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,4 +13,9 @@ from .cv_api import (  # noqa: F401
     release_workspaces,
 )
 
+from .fusion import (  # noqa: F401
+    normalize_disparity, calibrate_midas_to_stereo, normalize_to_stereo_range, fuse_depth_maps,
+    detect_camera_occlusion, occlusion_stats, percentiles,
+)
+
 __version__ = "0.1.0"

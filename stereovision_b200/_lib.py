@@ -27,6 +27,13 @@ class BmParams(ctypes.Structure):
         "uniquenessRatio", "speckleWindowSize", "speckleRange", "disp12MaxDiff")]
 
 
+class FuseParams(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_double) for n in (
+        "stereo_weight", "midas_fill_weight", "flow_fill_weight", "stereo_conf_threshold", "flow_hole_threshold",
+        "bilateral_sigma_color", "bilateral_sigma_space")] + [(n, ctypes.c_int) for n in (
+        "blend_ksize", "bilateral_d", "use_midas_fill", "use_flow_fill")]
+
+
 # name -> (restype, argtypes); every symbol include/svb.h declares
 SIGNATURES = {
     "svb_last_error": (ctypes.c_char_p, []),
@@ -59,6 +66,20 @@ SIGNATURES = {
                                       c_double, c_void_p, c_void_p, c_void_p]),
     "svb_reproject3d_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, ctypes.POINTER(c_double), c_int,
                                     c_void_p, c_void_p, c_void_p]),
+    "svb_normalize_disparity_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "svb_range_scratch_bytes": (c_size_t, [c_int]),
+    "svb_calibrate_midas_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p,
+                                        c_size_t, c_void_p]),
+    "svb_normalize_to_stereo_range_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p,
+                                                  c_size_t, c_void_p]),
+    "svb_percentiles_f32_dev": (c_int, [c_void_p, c_void_p, ctypes.c_float, c_int, c_int, c_size_t, c_void_p,
+                                        c_void_p, c_void_p, c_size_t, c_void_p]),
+    "svb_fuse_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "svb_fuse_depth_maps_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                        ctypes.POINTER(FuseParams), c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "svb_occlusion_scratch_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "svb_occlusion_stats_u8_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t,
+                                           c_void_p]),
 }
 
 

@@ -1,0 +1,794 @@
+// Fusion chain of fused_depth_map.py on the device:
+//   normalise + confidence            fused_depth_map.py:1010-1029
+//   calibrate_midas_to_stereo         fused_depth_map.py:1169-1257   (np.percentile -> exact radix select)
+//   normalize_to_stereo_range         fused_depth_map.py:1503-1554
+//   fuse_depth_maps                   fused_depth_map.py:1560-1698   (GaussianBlur 15, bilateralFilter 9/75/75)
+//   detect_camera_occlusion stats     fused_depth_map.py:170-240
+// All of it is streaming float work bound by HBM; nothing here synchronises the stream: the
+// data-dependent scalars (percentiles, min/max, branch choices) stay in device memory and are
+// read by the kernel that needs them.
+#include "svb_common.cuh"
+#include <math.h>
+#include <float.h>
+
+// ------------------------------------------------------------------------------------------
+// a13: disparity -> (normalised 0..254 as float, confidence 0/1)
+// ------------------------------------------------------------------------------------------
+__global__ void k_norm_conf(const float* __restrict__ disp, size_t n, float lo, float hi, float numD,
+                            float c_lo, float c_hi, float* __restrict__ norm, float* __restrict__ conf)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float d = disp[i];
+        const float c = fminf(fmaxf(d, lo), hi);
+        const float v = __fmul_rn(__fdiv_rn(__fsub_rn(c, lo), numD), 255.0f);
+        norm[i] = (float)(unsigned char)(int)v;
+        conf[i] = (d > c_lo && d < c_hi) ? 1.0f : 0.0f;
+    }
+}
+
+extern "C" int svb_normalize_disparity_dev(const float* disp_dev, int B, int H, int W, int min_disp, int num_disp,
+                                           float* norm_dev, float* conf_dev, void* stream)
+{
+    if (!disp_dev || !norm_dev || !conf_dev || B < 1 || H < 1 || W < 1 || num_disp < 1) {
+        svb_set_error("svb_normalize_disparity_dev: bad argument");
+        return SVB_ERR_PARAM;
+    }
+    const size_t n = (size_t)B * H * W;
+    const int grid = (int)min((size_t)148 * 16, (n + 255) / 256);
+    k_norm_conf<<<grid, 256, 0, (cudaStream_t)stream>>>(disp_dev, n, (float)min_disp, (float)(min_disp + num_disp - 1),
+                                                        (float)num_disp, (float)(min_disp + 1),
+                                                        (float)(min_disp + num_disp - 1), norm_dev, conf_dev);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Exact order statistics: 3-pass radix select (11 + 11 + 10 bits) on order-preserving keys.
+// One "selection" = the values of one image under a mask; each asks for two percentiles =
+// four ranks (floor and floor+1 of each virtual index).  Two selections run side by side
+// (blockIdx.z), one image per blockIdx.y.
+// ------------------------------------------------------------------------------------------
+#define SEL_NR 4
+#define SEL_BINS 2048
+
+enum { MASK_NONE = 0, MASK_GT = 1, MASK_SELF_POS = 2, MASK_GT_IF_ENOUGH = 3 };
+
+struct SelDesc {
+    const float* vals;      // [B][n]
+    const float* mask;      // [B][n] or null
+    int mode;               // MASK_*
+    float thr;
+};
+
+struct SelState {           // per (selection, image)
+    unsigned hist[SEL_NR][SEL_BINS];
+    unsigned pre[SEL_NR];   // key prefix found so far
+    unsigned rem[SEL_NR];   // rank inside the prefix
+    unsigned count;         // selected elements
+    int f64;                // percentiles interpolate in double (list q) or float (scalar q)
+    int few;                // MASK_GT_IF_ENOUGH fell back to "no mask"
+    double gam[2];
+    float val[SEL_NR];
+    double pct[2];          // the two percentiles
+};
+
+__device__ __forceinline__ unsigned f2key(float f)
+{
+    const unsigned u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key2f(unsigned k)
+{
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+__global__ void k_count_gt(const float* __restrict__ m, size_t n, float thr, unsigned* __restrict__ cnt)
+{
+    const int b = blockIdx.y;
+    const float* p = m + (size_t)b * n;
+    unsigned c = 0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        c += p[i] > thr;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&cnt[b], c);
+}
+
+template <int PASS>
+__global__ void __launch_bounds__(512) k_sel_hist(SelDesc d0, SelDesc d1, size_t n, SelState* __restrict__ st,
+                                                  const unsigned* __restrict__ relcnt, int B)
+{
+    constexpr int NH = PASS == 0 ? 1 : SEL_NR;
+    __shared__ unsigned sh[NH][SEL_BINS];
+    const int b = blockIdx.y, z = blockIdx.z;
+    const SelDesc d = z ? d1 : d0;
+    SelState* s = st + (size_t)z * B + b;
+    for (int i = threadIdx.x; i < NH * SEL_BINS; i += blockDim.x) (&sh[0][0])[i] = 0;
+    int mode = d.mode;
+    if (mode == MASK_GT_IF_ENOUGH) mode = relcnt[b] < 100u ? MASK_NONE : MASK_GT;
+    unsigned pre[SEL_NR];
+    bool dup[SEL_NR];
+    if (PASS > 0) {
+#pragma unroll
+        for (int r = 0; r < SEL_NR; ++r) {
+            pre[r] = s->pre[r];
+            dup[r] = false;
+#pragma unroll
+            for (int q = 0; q < r; ++q) dup[r] = dup[r] || pre[q] == pre[r];   // same prefix: count once, copy later
+        }
+    }
+    __syncthreads();
+    const float* v = d.vals + (size_t)b * n;
+    const float* m = d.mask ? d.mask + (size_t)b * n : nullptr;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float x = v[i];
+        bool sel = true;
+        if (mode == MASK_GT) sel = m[i] > d.thr;
+        else if (mode == MASK_SELF_POS) sel = x > 0.0f;
+        if (!sel) continue;
+        const unsigned k = f2key(x);
+        if (PASS == 0) {
+            atomicAdd(&sh[0][k >> 21], 1u);
+        } else {
+            const unsigned hi = PASS == 1 ? k >> 21 : k >> 10;
+            const unsigned dig = PASS == 1 ? (k >> 10) & 0x7ffu : k & 0x3ffu;
+#pragma unroll
+            for (int r = 0; r < SEL_NR; ++r)
+                if (!dup[r] && hi == pre[r]) atomicAdd(&sh[r][dig], 1u);
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < NH * SEL_BINS; i += blockDim.x) {
+        const unsigned c = (&sh[0][0])[i];
+        if (c) atomicAdd(&(&s->hist[0][0])[i], c);
+    }
+}
+
+// One block (256 threads) per (selection, image): find each rank's bin in this pass's histogram.
+template <int PASS>
+__global__ void __launch_bounds__(256) k_sel_pick(SelState* __restrict__ st, const unsigned* __restrict__ relcnt,
+                                                  int mode0, int mode1, int B)
+{
+    __shared__ unsigned sh[SEL_NR][SEL_BINS];
+    __shared__ unsigned part[SEL_NR][8];
+    __shared__ unsigned tot;
+    const int b = blockIdx.x, z = blockIdx.y;
+    SelState* s = st + (size_t)z * B + b;
+    const int mode = z ? mode1 : mode0;
+    constexpr int NH = PASS == 0 ? 1 : SEL_NR;
+    for (int i = threadIdx.x; i < NH * SEL_BINS; i += blockDim.x) {
+        (&sh[0][0])[i] = (&s->hist[0][0])[i];
+        (&s->hist[0][0])[i] = 0;                         // ready for the next pass / next call
+    }
+    __syncthreads();
+    if (PASS == 0) {
+        if (threadIdx.x == 0) tot = 0;
+        __syncthreads();
+        unsigned c = 0;
+        for (int i = threadIdx.x; i < SEL_BINS; i += blockDim.x) c += sh[0][i];
+        c = __reduce_add_sync(0xffffffffu, c);
+        if ((threadIdx.x & 31) == 0) atomicAdd(&tot, c);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            // np.percentile(a, q), method 'linear': virtual index (n-1)*q/100 in q's dtype
+            const unsigned n = tot;
+            const bool few = mode == MASK_GT_IF_ENOUGH && relcnt[b] < 100u;
+            const bool f64 = mode == MASK_GT_IF_ENOUGH && !few;     // np.percentile(v, [10, 90])
+            const float ql = f64 ? 10.f : 5.f, qh = f64 ? 90.f : 95.f;
+            s->count = n;
+            s->f64 = f64;
+            s->few = few;
+            for (int q = 0; q < 2; ++q) {
+                unsigned lo = 0, hi = 0;
+                double g = 0.0;
+                if (n > 0) {
+                    if (f64) {
+                        const double qq = (double)(q ? qh : ql) / 100.0;
+                        const double vi = __dmul_rn((double)(n - 1), qq);
+                        if (vi >= (double)(n - 1)) lo = hi = n - 1;
+                        else { lo = (unsigned)floor(vi); hi = lo + 1; g = vi - floor(vi); }
+                    } else {
+                        const float qq = __fdiv_rn(q ? qh : ql, 100.0f);
+                        const float vi = __fmul_rn((float)(n - 1), qq);
+                        if (vi >= (float)(n - 1)) lo = hi = n - 1;
+                        else { lo = (unsigned)floorf(vi); hi = lo + 1; g = (double)__fsub_rn(vi, floorf(vi)); }
+                    }
+                }
+                s->rem[2 * q] = lo;
+                s->rem[2 * q + 1] = hi;
+                s->gam[q] = g;
+            }
+        }
+        __syncthreads();
+    }
+    // rank r is handled by warp r: lanes own 64 consecutive bins
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp < SEL_NR) {
+        const int r = warp;
+        int src = r;                                       // histogram of the first rank with the same prefix
+        if (PASS > 0)
+            for (int q = r - 1; q >= 0; --q)
+                if (s->pre[q] == s->pre[r]) src = q;
+        const unsigned* h = sh[PASS == 0 ? 0 : src];
+        constexpr int PER = SEL_BINS / 32;
+        unsigned sum = 0;
+        for (int i = 0; i < PER; ++i) sum += h[lane * PER + i];
+        unsigned inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        const unsigned exc = inc - sum;
+        const unsigned k = s->rem[r];
+        const bool mine = k >= exc && k < inc;
+        if (mine) {
+            unsigned acc = exc;
+            int bin = lane * PER;
+            for (int i = 0; i < PER; ++i) {
+                const unsigned c = h[lane * PER + i];
+                if (k < acc + c) { bin = lane * PER + i; break; }
+                acc += c;
+            }
+            part[r][0] = (unsigned)bin;
+            part[r][1] = k - acc;
+        }
+        __syncwarp();
+        const unsigned any = __ballot_sync(0xffffffffu, mine);
+        if (lane == 0) {
+            if (any) {
+                const unsigned bin = part[r][0];
+                const unsigned pre = PASS == 0 ? bin : (PASS == 1 ? (s->pre[r] << 11) | bin : (s->pre[r] << 10) | bin);
+                part[r][2] = pre;
+            } else {
+                part[r][1] = 0;
+                part[r][2] = PASS == 0 ? 0u : (PASS == 1 ? s->pre[r] << 11 : s->pre[r] << 10);   // empty selection
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < SEL_NR) {
+        s->pre[threadIdx.x] = part[threadIdx.x][2];
+        s->rem[threadIdx.x] = part[threadIdx.x][1];
+        if (PASS == 2) s->val[threadIdx.x] = key2f(part[threadIdx.x][2]);
+    }
+    if (PASS == 2) {
+        __syncthreads();
+        if (threadIdx.x < 2) {
+            // numpy _lerp: a + (b-a)*t, replaced by b - (b-a)*(1-t) where t >= 0.5
+            const int q = threadIdx.x;
+            const float x = key2f(part[2 * q][2]), y = key2f(part[2 * q + 1][2]);
+            const float df = __fsub_rn(y, x);
+            double res;
+            if (s->f64) {
+                const double g = s->gam[q];
+                res = g < 0.5 ? __dadd_rn((double)x, __dmul_rn((double)df, g))
+                              : __dsub_rn((double)y, __dmul_rn((double)df, __dsub_rn(1.0, g)));
+            } else {
+                const float g = (float)s->gam[q];
+                res = g < 0.5f ? (double)__fadd_rn(x, __fmul_rn(df, g))
+                               : (double)__fsub_rn(y, __fmul_rn(df, __fsub_rn(1.0f, g)));
+            }
+            s->pct[q] = s->count ? res : (double)NAN;
+        }
+    }
+}
+
+static int run_select(const SelDesc& d0, const SelDesc& d1, int B, size_t n, SelState* st, const unsigned* relcnt,
+                      cudaStream_t s)
+{
+    const int nb = (int)min((size_t)svb_ceil_div(148 * 4, 2 * B) + 1, (n + 2047) / 2048);
+    dim3 grid(max(nb, 1), B, 2);
+    k_sel_hist<0><<<grid, 512, 0, s>>>(d0, d1, n, st, relcnt, B);
+    k_sel_pick<0><<<dim3(B, 2), 256, 0, s>>>(st, relcnt, d0.mode, d1.mode, B);
+    k_sel_hist<1><<<grid, 512, 0, s>>>(d0, d1, n, st, relcnt, B);
+    k_sel_pick<1><<<dim3(B, 2), 256, 0, s>>>(st, relcnt, d0.mode, d1.mode, B);
+    k_sel_hist<2><<<grid, 512, 0, s>>>(d0, d1, n, st, relcnt, B);
+    k_sel_pick<2><<<dim3(B, 2), 256, 0, s>>>(st, relcnt, d0.mode, d1.mode, B);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ---- range mapping: out = f(src; percentiles).  kind 0: calibrate_midas_to_stereo, 1: normalize_to_stereo_range.
+// selection 0 = stereo disparity, selection 1 = the map being calibrated.
+__global__ void k_range_apply(const float* __restrict__ src, size_t n, const SelState* __restrict__ st, int B, int kind,
+                              float* __restrict__ out)
+{
+    const int b = blockIdx.y;
+    const SelState* ss = st + b;
+    const SelState* sm = st + B + b;
+    const float* p = src + (size_t)b * n;
+    float* o = out + (size_t)b * n;
+    int mode;                 // 0 constant, 1 float32 min/max normalisation, 2 float64 affine
+    float cst = 0.f, mmin = 0.f, den = 1.f, smin = 0.f, srng = 0.f;
+    double scale = 1.0, offset = 0.0;
+    if (kind == 0 && !ss->few) {
+        const double s0 = ss->pct[0], s1 = ss->pct[1], m0 = sm->pct[0], m1 = sm->pct[1];
+        scale = (m1 - m0) < 1e-6 ? 1.0 : __ddiv_rn(s1 - s0, __dadd_rn(m1 - m0, 1e-8));
+        offset = __dsub_rn(s0, __dmul_rn(m0, scale));
+        mode = 2;
+    } else {
+        float s0 = (float)ss->pct[0], s1 = (float)ss->pct[1];
+        if (kind == 1 && ss->count == 0) { s0 = 0.f; s1 = 255.f; }
+        const float m0 = (float)sm->pct[0], m1 = (float)sm->pct[1];
+        const float dm = __fsub_rn(m1, m0);
+        if (dm < 1e-6f) {
+            cst = __fdiv_rn(__fadd_rn(s0, s1), 2.0f);
+            mode = 0;
+        } else {
+            mmin = m0;
+            den = __fadd_rn(dm, 1e-8f);
+            smin = s0;
+            srng = __fsub_rn(s1, s0);
+            mode = 1;
+        }
+    }
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float x = p[i];
+        float r;
+        if (mode == 2) r = (float)__dadd_rn(__dmul_rn((double)x, scale), offset);
+        else if (mode == 1) r = __fadd_rn(smin, __fmul_rn(__fdiv_rn(__fsub_rn(x, mmin), den), srng));
+        else r = cst;
+        o[i] = r;
+    }
+}
+
+extern "C" size_t svb_range_scratch_bytes(int B) { return (size_t)2 * B * sizeof(SelState) + (size_t)B * sizeof(unsigned) + 64; }
+
+static int range_map(int kind, const float* src, const float* stereo, const float* conf, int B, int H, int W, float* out,
+                     void* scratch, size_t scratch_bytes, void* stream)
+{
+    if (!src || !stereo || !out || !scratch || B < 1 || H < 1 || W < 1 || (kind == 0 && !conf)) {
+        svb_set_error("svb range mapping: bad argument");
+        return SVB_ERR_PARAM;
+    }
+    if (scratch_bytes < svb_range_scratch_bytes(B)) {
+        svb_set_error("svb range mapping: scratch too small (%zu < %zu)", scratch_bytes, svb_range_scratch_bytes(B));
+        return SVB_ERR_PARAM;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t n = (size_t)H * W;
+    SelState* st = (SelState*)scratch;
+    unsigned* relcnt = (unsigned*)((char*)scratch + (size_t)2 * B * sizeof(SelState));
+    SVB_CUDA(cudaMemsetAsync(scratch, 0, svb_range_scratch_bytes(B), s));
+    const int nb = (int)min((size_t)svb_ceil_div(148 * 8, B), (n + 1023) / 1024);
+    SelDesc d0, d1;
+    if (kind == 0) {
+        k_count_gt<<<dim3(nb, B), 256, 0, s>>>(conf, n, 0.7f, relcnt);
+        d0 = SelDesc{stereo, conf, MASK_GT_IF_ENOUGH, 0.7f};
+        d1 = SelDesc{src, conf, MASK_GT_IF_ENOUGH, 0.7f};
+    } else {
+        d0 = SelDesc{stereo, nullptr, MASK_SELF_POS, 0.f};
+        d1 = SelDesc{src, nullptr, MASK_NONE, 0.f};
+    }
+    int rc = run_select(d0, d1, B, n, st, relcnt, s);
+    if (rc != SVB_OK) return rc;
+    k_range_apply<<<dim3(nb, B), 256, 0, s>>>(src, n, st, B, kind, out);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+extern "C" int svb_calibrate_midas_dev(const float* midas_dev, const float* stereo_disp_dev, const float* stereo_conf_dev,
+                                       int B, int H, int W, float* out_dev, void* scratch_dev, size_t scratch_bytes,
+                                       void* stream)
+{
+    return range_map(0, midas_dev, stereo_disp_dev, stereo_conf_dev, B, H, W, out_dev, scratch_dev, scratch_bytes, stream);
+}
+
+extern "C" int svb_normalize_to_stereo_range_dev(const float* depth_dev, const float* stereo_disp_dev, int B, int H, int W,
+                                                 float* out_dev, void* scratch_dev, size_t scratch_bytes, void* stream)
+{
+    return range_map(1, depth_dev, stereo_disp_dev, nullptr, B, H, W, out_dev, scratch_dev, scratch_bytes, stream);
+}
+
+// np.percentile(vals[mask], q_lo/q_hi) on its own (tests, and callers that want the numbers).
+extern "C" int svb_percentiles_f32_dev(const float* vals_dev, const float* mask_dev, float mask_thr, int mask_mode, int B,
+                                       size_t n, double* out_dev /*[B][2]: 5/95 */, unsigned* count_dev,
+                                       void* scratch_dev, size_t scratch_bytes, void* stream);
+
+__global__ void k_sel_export(const SelState* __restrict__ st, int B, double* __restrict__ out, unsigned* __restrict__ cnt)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    out[2 * b] = st[b].pct[0];
+    out[2 * b + 1] = st[b].pct[1];
+    if (cnt) cnt[b] = st[b].count;
+}
+
+extern "C" int svb_percentiles_f32_dev(const float* vals_dev, const float* mask_dev, float mask_thr, int mask_mode, int B,
+                                       size_t n, double* out_dev, unsigned* count_dev, void* scratch_dev,
+                                       size_t scratch_bytes, void* stream)
+{
+    if (!vals_dev || !out_dev || !scratch_dev || B < 1 || n < 1 || mask_mode < 0 || mask_mode > 3 ||
+        ((mask_mode == MASK_GT || mask_mode == MASK_GT_IF_ENOUGH) && !mask_dev)) {
+        svb_set_error("svb_percentiles_f32_dev: bad argument");
+        return SVB_ERR_PARAM;
+    }
+    if (scratch_bytes < svb_range_scratch_bytes(B)) {
+        svb_set_error("svb_percentiles_f32_dev: scratch too small");
+        return SVB_ERR_PARAM;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    SelState* st = (SelState*)scratch_dev;
+    unsigned* relcnt = (unsigned*)((char*)scratch_dev + (size_t)2 * B * sizeof(SelState));
+    SVB_CUDA(cudaMemsetAsync(scratch_dev, 0, svb_range_scratch_bytes(B), s));
+    if (mask_mode == MASK_GT_IF_ENOUGH) {
+        const int nb = (int)min((size_t)svb_ceil_div(148 * 8, B), (n + 1023) / 1024);
+        k_count_gt<<<dim3(nb, B), 256, 0, s>>>(mask_dev, n, mask_thr, relcnt);
+    }
+    SelDesc d{vals_dev, mask_dev, mask_mode, mask_thr};
+    int rc = run_select(d, d, B, n, st, relcnt, s);
+    if (rc != SVB_OK) return rc;
+    k_sel_export<<<svb_ceil_div(B, 128), 128, 0, s>>>(st, B, out_dev, count_dev);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// a16: fuse_depth_maps.  Kernels:
+//   k_fill_rows   (1 - conf) * w_midas, horizontal Gaussian taps (BORDER_REFLECT_101) -> tmp
+//   k_blend       vertical taps + clip -> fill weight; stereo*w, MiDaS fill, flow fill -> fused f32,
+//                 per-image min/max (ordered-int atomics)
+//   k_bilat_lut   cv2's 4096-bin exp table for this image's value range
+//   k_bilateral   circular 9x9 window, table lookups with linear interpolation, clip -> u8
+// ------------------------------------------------------------------------------------------
+#define FUSE_MAXK 31
+#define FUSE_MAXD 15
+#define LUT_BINS 4096
+
+struct GaussTaps { int k; float w[FUSE_MAXK]; };
+struct BilatTaps { int d; float gc; float sw[FUSE_MAXD * FUSE_MAXD]; };   // sw < 0: outside the circle
+
+struct FuseState {          // per image
+    unsigned kmin, kmax;    // ordered keys of min / max of the fused map
+    float scale;            // LUT_BINS / (max - min)
+    int filter;             // run the bilateral filter (max > 10 and a non-degenerate range)
+    float lut[LUT_BINS + 2];
+};
+
+__device__ __forceinline__ int reflect101(int i, int n)
+{
+    if (n == 1) return 0;
+    while (i < 0 || i >= n) i = i < 0 ? -i : 2 * (n - 1) - i;
+    return i;
+}
+
+__global__ void k_fill_rows(const float* __restrict__ conf, int H, int W, float wm, GaussTaps g, float* __restrict__ tmp)
+{
+    const int b = blockIdx.z, y = blockIdx.y, x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= W) return;
+    const float* row = conf + ((size_t)b * H + y) * W;
+    const int r = g.k / 2;
+    float s = 0.f;
+    for (int i = 0; i < g.k; ++i) {
+        const float c = row[reflect101(x - r + i, W)];
+        const float v = __fmul_rn(__fsub_rn(1.0f, c), wm);
+        s = i == 0 ? __fmul_rn(g.w[0], v) : __fadd_rn(s, __fmul_rn(g.w[i], v));
+    }
+    tmp[((size_t)b * H + y) * W + x] = s;
+}
+
+struct BlendArgs {
+    const float* stereo; const float* conf; const float* midas; const float* flow; const float* tmp;
+    float ws, thr_conf, hole, wf, wf1;   // wf1 = (float)(1 - w_flow)
+    int base;                            // 0 stereo, 1 midas, 2 flow
+    int midas_fill, flow_fill;
+};
+
+__global__ void k_blend(BlendArgs a, int H, int W, GaussTaps g, float* __restrict__ fused, FuseState* __restrict__ fs)
+{
+    const int b = blockIdx.z, y = blockIdx.y, x = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned kmin = 0xffffffffu, kmax = 0;
+    if (x < W) {
+        const size_t i = ((size_t)b * H + y) * W + x;
+        float f;
+        if (a.base == 0) {
+            f = __fmul_rn(a.stereo[i], a.ws);
+            if (a.midas_fill) {
+                const float c = a.conf ? a.conf[i] : 1.0f;
+                if (c < a.thr_conf) {
+                    const int r = g.k / 2;
+                    float s = 0.f;
+                    for (int t = 0; t < g.k; ++t) {
+                        const float v = a.tmp[((size_t)b * H + reflect101(y - r + t, H)) * W + x];
+                        s = t == 0 ? __fmul_rn(g.w[0], v) : __fadd_rn(s, __fmul_rn(g.w[t], v));
+                    }
+                    const float fw = fminf(fmaxf(s, 0.0f), 1.0f);
+                    if (fw > 0.1f)
+                        f = __fadd_rn(__fmul_rn(f, __fsub_rn(1.0f, fw)), __fmul_rn(a.midas[i], fw));
+                }
+            }
+        } else if (a.base == 1) {
+            f = a.midas[i];
+        } else {
+            f = a.flow[i];
+        }
+        if (a.base != 2 && a.flow_fill && (f < a.hole || f == 0.0f))
+            f = __fadd_rn(__fmul_rn(f, a.wf1), __fmul_rn(a.flow[i], a.wf));
+        fused[i] = f;
+        kmin = kmax = f2key(f);
+    }
+    kmin = __reduce_min_sync(0xffffffffu, kmin);
+    kmax = __reduce_max_sync(0xffffffffu, kmax);
+    if ((threadIdx.x & 31) == 0) {
+        if (kmin != 0xffffffffu) atomicMin(&fs[b].kmin, kmin);
+        if (kmax) atomicMax(&fs[b].kmax, kmax);
+    }
+}
+
+__global__ void k_fuse_init(FuseState* fs, int B)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < B) { fs[b].kmin = 0xffffffffu; fs[b].kmax = 0; }
+}
+
+__global__ void k_bilat_lut(FuseState* __restrict__ fs, float gc)
+{
+    FuseState* s = fs + blockIdx.x;
+    const float mn = key2f(s->kmin), mx = key2f(s->kmax);
+    const float len = __fsub_rn(mx, mn);
+    const bool filter = mx > 10.0f && len > FLT_EPSILON;
+    const float scale = filter ? __fdiv_rn((float)LUT_BINS, len) : 0.f;
+    __syncthreads();
+    if (threadIdx.x == 0) { s->filter = filter; s->scale = scale; }
+    if (!filter) return;
+    // cv2 stops evaluating exp() once it has underflowed to 0; exp is monotone here, so the
+    // entries after the first zero are zero anyway.
+    for (int i = threadIdx.x; i < LUT_BINS + 2; i += blockDim.x) {
+        const double v = (double)i / (double)scale;
+        s->lut[i] = (float)exp(v * v * (double)gc);
+    }
+}
+
+#define BT_X 32
+#define BT_Y 8
+__global__ void __launch_bounds__(BT_X * BT_Y) k_bilateral(const float* __restrict__ fused, int H, int W, BilatTaps bt,
+                                                          const FuseState* __restrict__ fs, unsigned char* __restrict__ out8,
+                                                          float* __restrict__ outf)
+{
+    __shared__ float tile[BT_Y + FUSE_MAXD - 1][BT_X + FUSE_MAXD - 1];
+    __shared__ float lut[LUT_BINS + 2];
+    const int b = blockIdx.z;
+    const FuseState* s = fs + b;
+    const int r = bt.d / 2, tw = BT_X + 2 * r, th = BT_Y + 2 * r;
+    const int x0 = blockIdx.x * BT_X, y0 = blockIdx.y * BT_Y;
+    const int tid = threadIdx.y * BT_X + threadIdx.x;
+    const bool filter = s->filter != 0;
+    const float* img = fused + (size_t)b * H * W;
+    if (filter) {
+        for (int i = tid; i < LUT_BINS + 2; i += BT_X * BT_Y) lut[i] = s->lut[i];
+        for (int i = tid; i < tw * th; i += BT_X * BT_Y) {
+            const int ty = i / tw, tx = i - ty * tw;
+            tile[ty][tx] = img[(size_t)reflect101(y0 - r + ty, H) * W + reflect101(x0 - r + tx, W)];
+        }
+    }
+    __syncthreads();
+    const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+    if (x >= W || y >= H) return;
+    float res;
+    if (filter) {
+        const float c = tile[threadIdx.y + r][threadIdx.x + r];
+        const float scale = s->scale;
+        float sum = 0.f, wsum = 0.f;
+        for (int i = 0; i < bt.d; ++i)
+            for (int j = 0; j < bt.d; ++j) {
+                const float sw = bt.sw[i * bt.d + j];
+                if (sw < 0.f) continue;
+                const float v = tile[threadIdx.y + i][threadIdx.x + j];
+                float al = __fmul_rn(fabsf(__fsub_rn(v, c)), scale);
+                const int idx = (int)al;
+                al = __fsub_rn(al, (float)idx);
+                const float l0 = lut[idx], l1 = lut[idx + 1];
+                const float w = __fmul_rn(sw, __fadd_rn(l0, __fmul_rn(al, __fsub_rn(l1, l0))));
+                sum = __fmaf_rn(v, w, sum);
+                wsum = __fadd_rn(wsum, w);
+            }
+        res = __fdiv_rn(sum, wsum);
+    } else {
+        res = img[(size_t)y * W + x];
+    }
+    res = fminf(fmaxf(res, 0.0f), 255.0f);
+    const size_t o = ((size_t)b * H + y) * W + x;
+    out8[o] = (unsigned char)(int)res;
+    if (outf) outf[o] = res;
+}
+
+extern "C" size_t svb_fuse_scratch_bytes(int B, int H, int W)
+{
+    return (size_t)2 * B * H * W * sizeof(float) + (size_t)B * sizeof(FuseState) + 256;
+}
+
+extern "C" int svb_fuse_depth_maps_dev(const float* stereo_dev, const float* conf_dev, const float* midas_dev,
+                                       const float* flow_dev, int B, int H, int W, const svb_fuse_params* p,
+                                       uint8_t* out_u8_dev, float* out_f32_dev, void* scratch_dev, size_t scratch_bytes,
+                                       void* stream)
+{
+    if (!p || !out_u8_dev || !scratch_dev || B < 1 || H < 1 || W < 1 || (!stereo_dev && !midas_dev && !flow_dev)) {
+        svb_set_error("svb_fuse_depth_maps_dev: bad argument (at least one of stereo/midas/flow is needed)");
+        return SVB_ERR_PARAM;
+    }
+    if (p->blend_ksize < 1 || p->blend_ksize > FUSE_MAXK || !(p->blend_ksize & 1) || p->bilateral_d < 1 ||
+        p->bilateral_d > FUSE_MAXD || !(p->bilateral_d & 1)) {
+        svb_set_error("svb_fuse_depth_maps_dev: blend_ksize must be odd <= %d, bilateral_d odd <= %d", FUSE_MAXK, FUSE_MAXD);
+        return SVB_ERR_UNSUPPORTED;
+    }
+    if (scratch_bytes < svb_fuse_scratch_bytes(B, H, W)) {
+        svb_set_error("svb_fuse_depth_maps_dev: scratch too small (%zu < %zu)", scratch_bytes, svb_fuse_scratch_bytes(B, H, W));
+        return SVB_ERR_PARAM;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t n = (size_t)B * H * W;
+    float* tmp = (float*)scratch_dev;
+    float* fused = tmp + n;
+    FuseState* fs = (FuseState*)(((uintptr_t)(fused + n) + 127) & ~(uintptr_t)127);
+
+    // cv2.getGaussianKernel(k, sigma <= 0): sigma = 0.3*((k-1)*0.5 - 1) + 0.8, normalised, as float
+    GaussTaps g;
+    g.k = p->blend_ksize;
+    {
+        const double sigma = 0.3 * ((g.k - 1) * 0.5 - 1) + 0.8;
+        double kd[FUSE_MAXK], sum = 0;
+        for (int i = 0; i < g.k; ++i) {
+            const double x = i - (g.k - 1) * 0.5;
+            kd[i] = exp(-x * x / (2 * sigma * sigma));
+            sum += kd[i];
+        }
+        for (int i = 0; i < g.k; ++i) g.w[i] = (float)(kd[i] / sum);
+    }
+    BilatTaps bt;
+    bt.d = p->bilateral_d;
+    {
+        const double sc = p->bilateral_sigma_color > 0 ? p->bilateral_sigma_color : 1.0;
+        const double ss = p->bilateral_sigma_space > 0 ? p->bilateral_sigma_space : 1.0;
+        bt.gc = (float)(-0.5 / (sc * sc));
+        const double gs = -0.5 / (ss * ss);
+        const int r = bt.d / 2;
+        for (int i = -r; i <= r; ++i)
+            for (int j = -r; j <= r; ++j) {
+                const double rr = sqrt((double)i * i + (double)j * j);
+                bt.sw[(i + r) * bt.d + (j + r)] = rr > r ? -1.f : (float)exp(rr * rr * gs);
+            }
+    }
+    BlendArgs a;
+    a.stereo = stereo_dev; a.conf = conf_dev; a.midas = midas_dev; a.flow = flow_dev; a.tmp = tmp;
+    a.ws = (float)p->stereo_weight; a.thr_conf = (float)p->stereo_conf_threshold; a.hole = (float)p->flow_hole_threshold;
+    a.wf = (float)p->flow_fill_weight; a.wf1 = (float)(1.0 - p->flow_fill_weight);    // NumPy: array * (1 - w), w a Python float
+    a.base = stereo_dev ? 0 : (midas_dev ? 1 : 2);
+    a.midas_fill = stereo_dev && midas_dev && p->use_midas_fill;
+    a.flow_fill = flow_dev && p->use_flow_fill && a.base != 2;
+
+    k_fuse_init<<<svb_ceil_div(B, 128), 128, 0, s>>>(fs, B);
+    dim3 grid(svb_ceil_div(W, 128), H, B);
+    if (a.midas_fill) {
+        const float* c = conf_dev;
+        if (c) k_fill_rows<<<grid, 128, 0, s>>>(c, H, W, (float)p->midas_fill_weight, g, tmp);
+        else SVB_CUDA(cudaMemsetAsync(tmp, 0, n * sizeof(float), s));      // conf == 1 everywhere -> weight 0
+    }
+    k_blend<<<grid, 128, 0, s>>>(a, H, W, g, fused, fs);
+    k_bilat_lut<<<B, 256, 0, s>>>(fs, bt.gc);
+    dim3 bgrid(svb_ceil_div(W, BT_X), svb_ceil_div(H, BT_Y), B);
+    k_bilateral<<<bgrid, dim3(BT_X, BT_Y), 0, s>>>(fused, H, W, bt, fs, out_u8_dev, out_f32_dev);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// a17: the five image statistics of detect_camera_occlusion (fused_depth_map.py:170-240).
+//   stats[b] = { mean block std, low-variance block ratio, global std, histogram entropy, mean }
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_occ_blocks(const unsigned char* __restrict__ gray, int H, int W, int block, int bh,
+                                                    int bw, double* __restrict__ stds)
+{
+    const int b = blockIdx.z, bi = blockIdx.y, bj = blockIdx.x;
+    const int y1 = bi * block, y2 = min((bi + 1) * block, H), x1 = bj * block, x2 = min((bj + 1) * block, W);
+    const int bwid = x2 - x1, cnt = (y2 - y1) * bwid;
+    const unsigned char* img = gray + (size_t)b * H * W;
+    unsigned long long s1 = 0, s2 = 0;
+    for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+        const int yy = i / bwid, xx = i - yy * bwid;
+        const unsigned v = img[(size_t)(y1 + yy) * W + x1 + xx];
+        s1 += v;
+        s2 += v * v;
+    }
+    __shared__ unsigned long long r1[8], r2[8];
+    for (int o = 16; o; o >>= 1) {
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    if ((threadIdx.x & 31) == 0) { r1[threadIdx.x >> 5] = s1; r2[threadIdx.x >> 5] = s2; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s1 = s2 = 0;
+        for (int i = 0; i < 8; ++i) { s1 += r1[i]; s2 += r2[i]; }
+        // var = (n*S2 - S1^2) / n^2, exact integer numerator
+        const double num = (double)((unsigned long long)cnt * s2 - s1 * s1);
+        stds[((size_t)b * bh + bi) * bw + bj] = cnt ? sqrt(num / ((double)cnt * (double)cnt)) : 0.0;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_occ_hist(const unsigned char* __restrict__ gray, size_t n, unsigned* __restrict__ hist)
+{
+    __shared__ unsigned sh[256];
+    const int b = blockIdx.y;
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    const unsigned char* p = gray + (size_t)b * n;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        atomicAdd(&sh[p[i]], 1u);
+    __syncthreads();
+    if (sh[threadIdx.x]) atomicAdd(&hist[b * 256 + threadIdx.x], sh[threadIdx.x]);
+}
+
+__device__ double block_sum_256(double v, double* red)
+{
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0;
+    for (int i = 0; i < 8; ++i) t += red[i];
+    return t;
+}
+
+__global__ void __launch_bounds__(256) k_occ_final(const double* __restrict__ stds, int nblk, const unsigned* __restrict__ hist,
+                                                   double n, double* __restrict__ stats)
+{
+    __shared__ double red[8];
+    const int b = blockIdx.x;
+    double a = 0, l = 0;
+    for (int i = threadIdx.x; i < nblk; i += 256) {
+        const double s = stds[(size_t)b * nblk + i];
+        a += s;
+        l += s < 12.0;
+    }
+    a = block_sum_256(a, red);
+    l = block_sum_256(l, red);
+    const unsigned h = hist[b * 256 + threadIdx.x];
+    const double v = (double)threadIdx.x;
+    const double mean = block_sum_256(v * h, red) / n;
+    const double var = block_sum_256((v - mean) * (v - mean) * h, red) / n;
+    // hist (float32, as cv2.calcHist returns) + 1e-10, normalised, Shannon entropy with log2(p + 1e-10)
+    const float hf = __fadd_rn((float)h, 1e-10f);
+    const float tot = (float)block_sum_256((double)hf, red);
+    const float pr = __fdiv_rn(hf, tot);
+    const double ent = -block_sum_256((double)__fmul_rn(pr, log2f(__fadd_rn(pr, 1e-10f))), red);
+    if (threadIdx.x == 0) {
+        double* o = stats + 5 * b;
+        o[0] = nblk ? a / nblk : 0.0;
+        o[1] = l / (nblk > 0 ? nblk : 1);
+        o[2] = sqrt(var);
+        o[3] = ent;
+        o[4] = mean;
+    }
+}
+
+extern "C" size_t svb_occlusion_scratch_bytes(int B, int H, int W, int block)
+{
+    if (block < 1) block = 48;
+    const int bh = H / block > 1 ? H / block : 1, bw = W / block > 1 ? W / block : 1;
+    return (size_t)B * bh * bw * sizeof(double) + (size_t)B * 256 * sizeof(unsigned) + 64;
+}
+
+extern "C" int svb_occlusion_stats_u8_dev(const uint8_t* gray_dev, int B, int H, int W, int block, double* stats_dev,
+                                          void* scratch_dev, size_t scratch_bytes, void* stream)
+{
+    if (!gray_dev || !stats_dev || !scratch_dev || B < 1 || H < 1 || W < 1 || block < 1) {
+        svb_set_error("svb_occlusion_stats_u8_dev: bad argument");
+        return SVB_ERR_PARAM;
+    }
+    if (scratch_bytes < svb_occlusion_scratch_bytes(B, H, W, block)) {
+        svb_set_error("svb_occlusion_stats_u8_dev: scratch too small");
+        return SVB_ERR_PARAM;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const int bh = H / block > 1 ? H / block : 1, bw = W / block > 1 ? W / block : 1;
+    double* stds = (double*)scratch_dev;
+    unsigned* hist = (unsigned*)(stds + (size_t)B * bh * bw);
+    SVB_CUDA(cudaMemsetAsync(hist, 0, (size_t)B * 256 * sizeof(unsigned), s));
+    k_occ_blocks<<<dim3(bw, bh, B), 256, 0, s>>>(gray_dev, H, W, block, bh, bw, stds);
+    const size_t n = (size_t)H * W;
+    const int nb = (int)min((size_t)svb_ceil_div(148 * 8, B), (n + 4095) / 4096);
+    k_occ_hist<<<dim3(max(nb, 1), B), 256, 0, s>>>(gray_dev, n, hist);
+    k_occ_final<<<B, 256, 0, s>>>(stds, bh * bw, hist, (double)n, stats_dev);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}

@@ -62,3 +62,21 @@ def to_bgr(gray):
     """gray replicated x3 with per-channel gain 0.9/1.0/1.1."""
     g = gray.astype(np.float32)
     return np.clip(np.stack([g * 0.9, g, g * 1.1], -1), 0, 255).astype(np.uint8)
+
+
+def make_aux_depths(disp_true, seed=0):
+    """Stand-ins for the two learned/flow inputs of the fusion chain (fused_depth_map.py:1560):
+    a MiDaS-like relative inverse depth (smooth, arbitrary scale and offset, float32) and a
+    flow-derived depth already scaled to 0..255 (float32, noisy, with zero patches)."""
+    rng = np.random.default_rng(1000 + seed)
+    d = disp_true.astype(np.float64)
+    H, W = d.shape
+    midas = _gauss_blur(d, 2.0) * rng.uniform(20.0, 60.0) + rng.uniform(100.0, 900.0)
+    midas += _gauss_blur(rng.normal(0, 1, (H, W)), 3.0) * 40.0
+    flow = _gauss_blur(d, 4.0)
+    flow = (flow - flow.min()) / max(flow.max() - flow.min(), 1e-9) * 255.0
+    flow += rng.normal(0, 4.0, (H, W))
+    for _ in range(3):
+        y0, x0 = int(rng.integers(0, H - H // 6)), int(rng.integers(0, W - W // 6))
+        flow[y0:y0 + H // 6, x0:x0 + W // 6] = 0.0
+    return midas.astype(np.float32), np.clip(flow, 0, 255).astype(np.float32)

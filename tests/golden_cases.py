@@ -51,3 +51,25 @@ def synth_calibration(W, H):
     m1r, m2r = cv2.initUndistortRectifyMap(K, dr, R2, P2, (W, H), cv2.CV_16SC2)
     return dict(mtx_left=K, dist_left=dl, mtx_right=K, dist_right=dr, R=R, T=T, img_size=(W, H),
                 left_map1=m1l, left_map2=m2l, right_map1=m1r, right_map2=m2r, Q=Q)
+
+
+# Fusion chain (fused_depth_map.py): stereo (min_disp, num_disp, window) as the reference's scaled
+# settings give them, plus what the golden generator perturbs.
+FUSION_CASES = [
+    dict(H=96, W=160, seed=41, min_disp=0, num_disp=48, window=5, moving=True, params={}),
+    dict(H=120, W=176, seed=42, min_disp=0, num_disp=64, window=7, moving=False, params={}),
+    dict(H=90, W=150, seed=43, min_disp=0, num_disp=32, window=5, moving=True,
+         params=dict(stereo_weight=1.1, midas_fill_weight=0.6, flow_fill_weight=0.3,
+                     stereo_conf_threshold=0.4, flow_hole_threshold=25)),
+    dict(H=96, W=144, seed=44, min_disp=0, num_disp=48, window=5, moving=True, params={}, occluded="right"),
+]
+
+
+def fusion_case_inputs(c):
+    """(left BGR, right BGR, MiDaS-like f32, flow-depth f32) of a FUSION_CASES entry, from its seed."""
+    from stereovision_b200.synth import make_pair, make_aux_depths, to_bgr
+    l, r, gt = make_pair(c["H"], c["W"], max(c["num_disp"], 16), seed=c["seed"])
+    if c.get("occluded") == "right":
+        r = np.full_like(r, 22) + (r // 64)
+    midas, flow = make_aux_depths(gt, c["seed"])
+    return to_bgr(l), to_bgr(r), midas, flow

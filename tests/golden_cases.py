@@ -73,3 +73,8 @@ def fusion_case_inputs(c):
         r = np.full_like(r, 22) + (r // 64)
     midas, flow = make_aux_depths(gt, c["seed"])
     return to_bgr(l), to_bgr(r), midas, flow
+
+
+# depth_map.py drop-in (apply_stereo_rectification + create_depth_map with the script's own
+# MIN_DISP=0 / NUM_DISP=320 / WINDOW_SIZE=7 / 3WAY): W must exceed 320.
+DROPIN_CASE = dict(H=150, W=520, seed=51)

@@ -23,13 +23,14 @@
 // NP*l .. NP*l+NP-1 in registers.
 //
 // k_sweep is a persistent wavefront kernel: a CTA takes a band of SW_R consecutive rows (one
-// warp per row, skewed by SW_SK columns so that the diagonal predecessors are ready), the
+// warp per row, each row at least two columns behind the row above so that its diagonal predecessors are ready), the
 // L_r vectors of the row above travel through shared-memory rings, and the last row of a band
 // hands its L_r to the next band (another CTA) through an L2-resident carry buffer guarded by
 // per-band progress counters (release/acquire).  Bands are handed out by an atomic ticket in
 // dependency order, so a waiting CTA only ever waits on a CTA that is already running.
 #include "svb_common.cuh"
 #include <algorithm>
+#include <type_traits>
 #include <new>
 #include <vector>
 #include <string.h>
@@ -40,34 +41,31 @@
 
 // rows (= warps) per band
 __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 5 ? 16 : 8; }
-#define SW_SK 2                // minimum column lag between consecutive rows of a band
-// ring slots per path between two rows (>= 4; every extra slot is a column of slack between rows)
-#ifndef SW_LOCKSTEP
-#define SW_LOCKSTEP 0          // 1: one block barrier per column step instead of per-row progress flags
+#ifndef SW_SLEEP_NS
+#define SW_SLEEP_NS 40         // back-off while a row waits for its neighbour's progress counter
 #endif
+// ring slots per path between two rows (>= 4; every extra slot is a column of slack between rows)
 #ifndef SW_RING_FIRST
 #define SW_RING_FIRST 6
 #define SW_RING_LAST 5
-#define SW_STAGE 4
 #endif
 __host__ __device__ constexpr int sw_ring(int NP, bool last) { return NP <= 4 ? (last ? SW_RING_LAST : SW_RING_FIRST) : 4; }
 // slots of the per-row cp.async staging ring for C (and S1 in the last sweep); prefetch distance = slots - 1
-__host__ __device__ constexpr int sw_stage(int NP, bool last) { return NP <= 4 ? SW_STAGE : 4; }
+__host__ __device__ constexpr int sw_stage(int NP, bool last) { return NP <= 4 ? 4 : (last ? 3 : 4); }
+__host__ __device__ constexpr int sw_roww(int NP) { return NP * 32 + 4; }     // ring row: the vector, its minimum, pad to 16 B
 __host__ __device__ constexpr size_t sw_smem_words(int NP, bool last)
 {
-    return (size_t)(sw_rows(NP) + 1) * 3 * sw_ring(NP, last) * NP * 32 + (((sw_rows(NP) + 1) * 3 * sw_ring(NP, last) + 3) & ~3) +
-           (size_t)sw_rows(NP) * NP * 32 + (size_t)sw_rows(NP) * sw_stage(NP, last) * NP * 32 * (last ? 2 : 1);
+    return (size_t)(sw_rows(NP) + 1) * 3 * sw_ring(NP, last) * sw_roww(NP) +
+           (size_t)sw_rows(NP) * sw_stage(NP, last) * NP * 32 * (last ? 2 : 1) + (last ? (size_t)sw_rows(NP) * NP * 32 : 0);
 }
 #define SW_FLAG_EVERY 8        // carry progress is published every this many columns
 #define SW_SPIN_LIMIT (1 << 24)
-#ifndef SW_EXPERIMENT
-#define SW_EXPERIMENT 0        // timing experiments only (results are wrong): 1 = no intra-band waits, 2 = also no inter-band waits/fences
-#endif
 
 struct SgbmGeo {
     int H, W, D, Dp, NP, HALF, minD, minX1, width1, bs, r, ftzero;
     int P1, P2, uniq, d12, INV, mode, nstripes, rowsMax;
     int Wp;                    // words per plane row of the right descriptors
+    unsigned thMul;            // floor(2^32 / (100 - uniq)) + 1: exact division of the uniqueness threshold (0: divisor <= 1)
 };
 
 __host__ __device__ inline void job_rows(const SgbmGeo& g, int n, int& ys, int& ye, int& keep)
@@ -449,7 +447,8 @@ __device__ __forceinline__ uint32_t sgm_step(uint32_t (&Lq)[NP], const uint32_t 
         Lq[k] = L;
         mloc = pk_min(mloc, L);
     }
-    return pk_dup(__reduce_min_sync(FULLMASK, pk_hmin(mloc)));
+    // min of the two halves in both halves; a packed pair of equal halves is monotone in its value
+    return __reduce_min_sync(FULLMASK, pk_min(mloc, __byte_perm(mloc, 0, 0x1032)));
 }
 
 __device__ __forceinline__ int ld_acquire_gpu(const int* p)
@@ -474,8 +473,40 @@ __device__ __forceinline__ void sts_release_cta(int* p, int v)
     asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
 }
 
-__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
-#define SW_PF 12               // columns of C (and S1) requested into L2 ahead of use
+
+// one lane's NP-word slice, destination given as a shared-space address
+template <int NP>
+__device__ __forceinline__ void cp_async_vec_s(uint32_t sdst, const uint32_t* gsrc)
+{
+    if constexpr (NP % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < NP / 4; ++i)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst + 16 * i), "l"(gsrc + 4 * i));
+    } else {
+#pragma unroll
+        for (int i = 0; i < NP; ++i)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst + 4 * i), "l"(gsrc + i));
+    }
+}
+
+// Uniqueness threshold of A.4: a disparity d counts against the winner iff S[d] < th.
+__device__ __forceinline__ int wta_threshold(const SgbmGeo& g, int minS)
+{
+    const int f = 100 - g.uniq;
+    int th;
+    if (g.mode == SVB_MODE_SGBM_3WAY) {
+        // cv2's 3WAY vector loop: Sp[d] < (short)(100*minS/(100-u) + 1) (oracle/sgbm_oracle.c)
+        const unsigned x = 100u * (unsigned)minS;
+        th = g.uniq > 0 ? (int)(int16_t)((g.thMul ? __umulhi(x, g.thMul) : x) + 1u) : 0;
+        th = max(th, 0);
+    } else if (f <= 0) {
+        th = minS > 0 ? 0x8000 : 0;                          // S*0 < minS*100
+    } else {
+        const unsigned x = (unsigned)minS * 100u + (unsigned)f - 1u;   // S*f < minS*100  <=>  S < ceil(minS*100/f)
+        th = (int)(g.thMul ? __umulhi(x, g.thMul) : x);
+    }
+    return min(th, 0x8000);
+}
 
 struct SweepArgs {
     const uint32_t* C;        // [job][rowsMax][w1][VW]
@@ -495,37 +526,47 @@ struct SweepArgs {
 // VAR 0: D < Dp (pad disparities), saturating sums; 1: D == Dp, saturating sums;
 // 2: D == Dp and the per-sweep sum of L_r cannot reach 32768 -> plain adds.
 // MASK: paths of this sweep: 1 horizontal, 2 diagonal from behind, 4 vertical, 8 diagonal from ahead.
+//
+// Shared memory: every row (warp) of a band owns an INPUT ring per inter-row path: RING slots of
+// ROWW = VW + 4 words (the L_r vector of one column of the previous row, then its minimum in both
+// halves).  The row above writes it, the progress counters s_done[] order the accesses: row k may
+// start column i once row k-1 has published i + 2 (column i + 1 is the diagonal-from-ahead
+// predecessor) and row k-1 may overwrite a slot once row k has published the column that last read it.
+// Virtual columns -1 and w1 (predecessors outside the image, A.3) are zero rows of the ring.
 template <int NP, int VAR, int MASK, bool LAST>
 __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a, const SgbmGeo g)
 {
     constexpr bool FULL = VAR != 0, FAST = VAR == 2;
     constexpr bool VERT = (MASK & 14) != 0;                  // any path that crosses rows
-    constexpr int VW = NP * 32;
-    constexpr int SW_R = sw_rows(NP), SW_RING = sw_ring(NP, LAST), NS = sw_stage(NP, LAST), PFD = NS - 1;
-    extern __shared__ uint32_t smem[];
-    uint32_t* ring = smem;                                   // [SW_R + 1][3][SW_RING][VW]: INPUT ring of each warp (+ a dump)
-    uint32_t* rmin = ring + (SW_R + 1) * 3 * SW_RING * VW;   // [SW_R + 1][3][SW_RING]
-    uint32_t* wsc = rmin + (((SW_R + 1) * 3 * SW_RING + 3) & ~3);   // [SW_R][VW] (sweep 2: S vector for the subpixel taps)
-    uint32_t* cstage = wsc + SW_R * VW;                      // [SW_R][NS][VW] cp.async ring of C columns
-    uint32_t* sstage = cstage + SW_R * NS * VW;              // [SW_R][NS][VW] (sweep 2) ... and of S1 columns
+    constexpr int VW = NP * 32, ROWW = sw_roww(NP);
+    constexpr int SW_R = sw_rows(NP), RING = sw_ring(NP, LAST), NS = sw_stage(NP, LAST), PFD = NS - 1;
+    constexpr int PATHW = RING * ROWW, RINGW = 3 * PATHW;
+    extern __shared__ __align__(16) uint32_t smem[];
+    uint32_t* ring = smem;                                   // [SW_R + 1][3][RING][ROWW] (+1: where the last row dumps)
+    uint32_t* cstage = ring + (SW_R + 1) * RINGW;            // [SW_R][NS][VW] cp.async ring of C columns
+    uint32_t* sstage = cstage + SW_R * NS * VW;              // [SW_R][NS][VW] (last sweep) ... and of S1 columns
+    uint32_t* wsc = sstage + (LAST ? SW_R * NS * VW : 0);    // [SW_R][VW] (last sweep) S of the current column for the subpixel taps
     __shared__ int s_ticket;
-    __shared__ int s_done[SW_R + 1];                         // columns completed by each warp in this band
+    __shared__ int s_done[SW_R + 1];                         // columns published by each row of the band
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int w1 = g.width1;
     const uint32_t P1P1 = pk_dup(g.P1), P2P2 = pk_dup(g.P2);
     const int dir = a.dir;
-    uint32_t padm[NP];
+    uint32_t padm[NP], dpk[NP];
 #pragma unroll
     for (int k = 0; k < NP; ++k) {
         const int w = NP * lane + k;
         padm[k] = (w >= g.D ? 0xffffu : 0u) | (w + g.HALF >= g.D ? 0xffff0000u : 0u);
+        dpk[k] = ((uint32_t)(w + g.HALF) << 16) | (uint32_t)w;    // the two disparities of word k
     }
-    uint32_t* ring_in = ring + (size_t)warp * 3 * SW_RING * VW;
-    uint32_t* rmin_in = rmin + warp * 3 * SW_RING;
-    uint32_t* ring_out = ring_in + 3 * SW_RING * VW;         // input ring of warp + 1 (warp SW_R-1: the dump)
-    uint32_t* rmin_out = rmin_in + 3 * SW_RING;
+    uint32_t* ring_in = ring + (size_t)warp * RINGW;
+    uint32_t* ring_out = ring_in + RINGW;                    // input ring of warp + 1
     uint32_t* mysc = wsc + warp * VW;
+    const uint32_t cst_s = smem_u32(cstage + (size_t)warp * NS * VW + NP * lane);   // this lane's slice, slot 0
+    const uint32_t sst_s = smem_u32(sstage + (size_t)warp * NS * VW + NP * lane);
+    const uint32_t* cst = cstage + (size_t)warp * NS * VW;
+    const uint32_t* sst = sstage + (size_t)warp * NS * VW;
 
     for (;;) {
         __syncthreads();
@@ -557,12 +598,13 @@ __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a
         int* prog_mine = a.prog + (size_t)job * a.bandsPerJob + band;
         const int b = job / g.nstripes;
 
-        // ---- warp 0 of a non-first band: columns 0,1 of the carry into the ring, column 2 in flight
+        // ---- warp 0 of a non-first band copies the carry (last row of the previous band) into its own ring,
+        // two columns ahead of use, a third one in flight in registers
         uint32_t pre[3][NP];
         uint32_t premin = 0;
         int seen = 0;
         auto wait_cols = [&](int need) {     // all lanes of warp 0
-            if (SW_EXPERIMENT < 2 && seen < need) {
+            if (seen < need) {
                 if (lane == 0) {
                     int spins = 0;
                     while ((seen = ld_acquire_gpu(prog_pred)) < need) {
@@ -580,15 +622,21 @@ __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a
             if (lane < 3) premin = __ldcg(cmin_in + (size_t)c * 4 + lane);
         };
         auto stash_col = [&](int c) {
-            const int slot = c % SW_RING;
+            const int so = (c % RING) * ROWW;
 #pragma unroll
-            for (int p = 0; p < 3; ++p) vec_st<NP>(ring_in + (p * SW_RING + slot) * VW, lane, pre[p]);
-            if (lane < 3) rmin_in[lane * SW_RING + slot] = premin;
+            for (int p = 0; p < 3; ++p) vec_st<NP>(ring_in + p * PATHW + so, lane, pre[p]);
+            if (lane < 3) ring_in[lane * PATHW + so + VW] = premin;
+        };
+        auto zero_row = [&](uint32_t* rowp) {                // one ring row: vector + minimum
+            const uint32_t z[NP] = {};
+            vec_st<NP>(rowp, lane, z);
+            if (lane == 0) rowp[VW] = 0;
         };
         if (feed) {
             wait_cols(min(3, w1));
             fetch_col(0); stash_col(0);
             if (w1 > 1) { fetch_col(1); stash_col(1); }
+            else zero_row(ring_in + 2 * PATHW + (1 % RING) * ROWW);
             if (w1 > 2) fetch_col(2);
         }
 
@@ -598,222 +646,204 @@ __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a
         uint32_t minh2 = 0;                                  // min of the horizontal L_r, in both halves
         if (lane == 0) s_done[warp] = 0;
         if (VERT && active) {
-            // Virtual columns -1 and w1 of the previous row read as zero vectors ("outside" predecessors,
-            // A.3); a first row has no previous row at all.  Column -1 lives in slot RING-1.
-            const uint32_t z[NP] = {};
-            if (!havePred) {
-                for (int q = 0; q < 3 * SW_RING; ++q) vec_st<NP>(ring_in + q * VW, lane, z);
-                if (lane < 3 * SW_RING) rmin_in[lane] = 0;
+            if (!havePred) {                                 // first row of the job: no previous row at all
+                for (int q = lane; q < RINGW; q += 32) ring_in[q] = 0;
             } else {
-                vec_st<NP>(ring_in + (0 * SW_RING + SW_RING - 1) * VW, lane, z);
-                if (lane == 0) rmin_in[0 * SW_RING + SW_RING - 1] = 0;
+                zero_row(ring_in + (RING - 1) * ROWW);       // virtual column -1 of the diagonal-from-behind path
             }
         }
         __syncthreads();
-        // Rows of a band run decoupled: warp k may start column i once warp k-1 has finished
-        // column i+1 (diagonal-from-ahead predecessor), and may not lap the ring of warp k+1.
-        const bool waitPred = !SW_LOCKSTEP && SW_EXPERIMENT == 0 && VERT && warp > 0;
-        const bool waitSucc = !SW_LOCKSTEP && SW_EXPERIMENT == 0 && VERT && (warp + 1 < nact);
-        int seenP = 0, seenS = 0;
 
-        // running addresses (words): this lane's slice of the current column of C / S, ring slots of the
-        // previous row's columns i-1, i, i+1, and the L2 prefetch SW_PF columns ahead
+        const bool waitPred = VERT && warp > 0;
+        const bool waitSucc = VERT && (warp + 1 < nact);
         const int x0 = dir > 0 ? 0 : w1 - 1;
         const ptrdiff_t cstep = (ptrdiff_t)dir * VW;
         const uint32_t* pC0 = a.C + rowbase + (size_t)x0 * VW + NP * lane;
         const uint32_t* pS0 = a.S + rowbase + (size_t)x0 * VW + NP * lane;
-        uint32_t* pS = a.S + rowbase + (size_t)x0 * VW + NP * lane;
-        int sm1 = SW_RING - 1, s0 = 0, sp1 = 1;              // slots of columns i-1, i, i+1
         const int nloop = active && !rowSkip ? w1 : 0;
 
-        // C (and S1) columns are staged PFD columns ahead through a per-row cp.async ring: every lane
-        // copies and later reads back only its own slice, so a per-thread wait_group is all it takes
-        uint32_t* cst = cstage + (size_t)warp * NS * VW + NP * lane;
-        uint32_t* sst = sstage + (size_t)warp * NS * VW + NP * lane;
-        auto issue = [&](int col) {
-            if (SW_EXPERIMENT != 3 && col < nloop) {
-                const int slot = col % NS;
-                cp_async_vec<NP>(cst + slot * VW, pC0 + (ptrdiff_t)col * cstep);
-                if (LAST) cp_async_vec<NP>(sst + slot * VW, pS0 + (ptrdiff_t)col * cstep);
-            }
-            asm volatile("cp.async.commit_group;");
-        };
+        // C (and S1) columns are staged PFD columns ahead through a per-row cp.async ring: every lane copies
+        // and later reads back only its own slice, so a per-thread wait_group is all it takes.  The last PFD
+        // requests of a row run past its end into the neighbouring row (valid memory, never read back).
+        if (nloop) {
 #pragma unroll
-        for (int c = 0; c < PFD; ++c) issue(c);
-        int cslot = 0;
-#if SW_LOCKSTEP
-        const int nsteps = VERT ? w1 + SW_SK * (nact - 1) : w1;
-        for (int st = 0; st < nsteps; ++st) {
-            const int i = VERT ? st - SW_SK * warp : st;
-            if (i < 0 || i >= nloop) { if (VERT) __syncthreads(); continue; }
-#else
-        for (int i = 0; i < nloop; ++i) {
-#endif
-            if (waitPred) {
-                const int need = min(i + SW_SK, w1);
-                if (seenP < need) {
-                    if (lane == 0) { while ((seenP = lds_acquire_cta(&s_done[warp - 1])) < need) __nanosleep(20); }
-                    seenP = __shfl_sync(FULLMASK, seenP, 0);
+            for (int c = 0; c < PFD; ++c) {
+                cp_async_vec_s<NP>(cst_s + c * VW * 4, pC0 + (ptrdiff_t)c * cstep);
+                if (LAST) cp_async_vec_s<NP>(sst_s + c * VW * 4, pS0 + (ptrdiff_t)c * cstep);
+                asm volatile("cp.async.commit_group;");
+            }
+        }
+
+        auto run = [&](auto mid_c) {
+            // MIDW: a row with a row above and below in the same band, nothing to do with the carry
+            constexpr bool MIDW = decltype(mid_c)::value;
+            const bool wPred = MIDW ? true : waitPred, wSucc = MIDW ? true : waitSucc;
+            const bool doFeed = MIDW ? false : feed, doGlob = MIDW ? false : succGlob;
+            int seenP = 0, seenS = 0;
+            uint32_t o_m1 = (RING - 1) * ROWW, o_0 = 0, o_p1 = ROWW;   // ring offsets (words) of columns i-1, i, i+1
+            uint32_t cs_cur = 0, cs_prev = (NS - 1) * VW;              // stage offsets (words) of columns i, i-1
+            const uint32_t* gC = pC0 + (ptrdiff_t)PFD * cstep;         // this lane's slice of column i + PFD
+            const uint32_t* gS = pS0 + (ptrdiff_t)PFD * cstep;
+            uint32_t* pS = a.S + rowbase + (size_t)x0 * VW + NP * lane;
+            uint32_t rkey = 0, rcnt = 0, rtap = 0;                     // WTA record of column (i & ~31) + lane
+            const int* done_pred = &s_done[warp > 0 ? warp - 1 : 0];
+            const int* done_succ = &s_done[warp + 1];
+
+            for (int i = 0; i < nloop; ++i) {
+                if (VERT && wPred && seenP < i + 2) {
+                    while ((seenP = lds_acquire_cta(done_pred)) < i + 2) __nanosleep(SW_SLEEP_NS);
                 }
-            }
-            if (waitSucc && i >= SW_RING - SW_SK) {
-                const int need = i - SW_RING + SW_SK;
-                if (seenS < need) {
-                    if (lane == 0) { while ((seenS = lds_acquire_cta(&s_done[warp + 1])) < need) __nanosleep(20); }
-                    seenS = __shfl_sync(FULLMASK, seenS, 0);
+                if (VERT && wSucc && seenS < i - RING + 2) {
+                    while ((seenS = lds_acquire_cta(done_succ)) < i - RING + 2) __nanosleep(SW_SLEEP_NS);
                 }
-            }
-            if (VERT && i == w1 - 1) {                       // virtual column w1 of the diagonal-from-ahead path
-                const uint32_t z[NP] = {};
-                vec_st<NP>(ring_in + (2 * SW_RING + sp1) * VW, lane, z);
-                if (lane == 0) rmin_in[2 * SW_RING + sp1] = 0;
-                __syncwarp();
-            }
-            issue(i + PFD);
-            asm volatile("cp.async.wait_group %0;" ::"n"(PFD) : "memory");
-            uint32_t C[NP], S[NP];
-            vec_ld<NP>(cst + cslot * VW - NP * lane, lane, C, LdPlain());
-            if (LAST) vec_ld<NP>(sst + cslot * VW - NP * lane, lane, S, LdPlain());
-            else {
+                // column i + PFD -> the stage slot column i - 1 has just left
+                cp_async_vec_s<NP>(cst_s + cs_prev * 4, gC);
+                if (LAST) cp_async_vec_s<NP>(sst_s + cs_prev * 4, gS);
+                asm volatile("cp.async.commit_group;");
+                asm volatile("cp.async.wait_group %0;" ::"n"(PFD) : "memory");
+                uint32_t C[NP], S[NP];
+                vec_ld<NP>(cst + cs_cur, lane, C, LdPlain());
+                if (LAST) vec_ld<NP>(sst + cs_cur, lane, S, LdPlain());
+                else {
 #pragma unroll
-                for (int k = 0; k < NP; ++k) S[k] = 0u;
-            }
-            // predecessors on the previous row of the sweep
-            uint32_t Lt[3][NP], mq2[3];
-            if (VERT) {
-#pragma unroll
-                for (int p = 0; p < 3; ++p) {
-                    if (!(MASK & (2 << p))) continue;
-                    const int slot = p == 0 ? sm1 : (p == 1 ? s0 : sp1);
-                    vec_ld<NP>(ring_in + (p * SW_RING + slot) * VW, lane, Lt[p], LdPlain());
-                    mq2[p] = rmin_in[p * SW_RING + slot];
+                    for (int k = 0; k < NP; ++k) S[k] = 0u;
                 }
-            }
-            uint32_t sum[NP];                                // FAST: plain sum of this sweep's L_r
+                // predecessors on the previous row of the sweep
+                uint32_t Lt[3][NP], mq2[3];
+                if (VERT) {
 #pragma unroll
-            for (int k = 0; k < NP; ++k) sum[k] = 0;
-            if (MASK & 1) {                                  // horizontal: predecessor is the previous column
-                minh2 = sgm_step<NP, FULL>(Lh, C, minh2, P1P1, P2P2, lane, padm);
-#pragma unroll
-                for (int k = 0; k < NP; ++k) {
-                    if (FAST) sum[k] += Lh[k];
-                    else S[k] = pk_addmin(S[k], Lh[k], WALL2);
+                    for (int p = 0; p < 3; ++p) {
+                        if (!(MASK & (2 << p))) continue;
+                        const uint32_t* rp = ring_in + p * PATHW + (p == 0 ? o_m1 : (p == 1 ? o_0 : o_p1));
+                        vec_ld<NP>(rp, lane, Lt[p], LdPlain());
+                        mq2[p] = rp[VW];
+                    }
                 }
-            }
-            if (VERT) {
+                uint32_t sum[NP];                            // FAST: plain sum of this sweep's L_r
 #pragma unroll
-                for (int p = 0; p < 3; ++p) {
-                    if (!(MASK & (2 << p))) continue;
-                    const uint32_t m2 = sgm_step<NP, FULL>(Lt[p], C, mq2[p], P1P1, P2P2, lane, padm);
+                for (int k = 0; k < NP; ++k) sum[k] = 0;
+                if (MASK & 1) {                              // horizontal: predecessor is the previous column
+                    minh2 = sgm_step<NP, FULL>(Lh, C, minh2, P1P1, P2P2, lane, padm);
 #pragma unroll
                     for (int k = 0; k < NP; ++k) {
-                        if (FAST) sum[k] += Lt[p][k];
-                        else S[k] = pk_addmin(S[k], Lt[p][k], WALL2);
+                        if (FAST) sum[k] += Lh[k];
+                        else S[k] = pk_addmin(S[k], Lh[k], WALL2);
                     }
-                    vec_st<NP>(ring_out + (p * SW_RING + s0) * VW, lane, Lt[p]);
-                    rmin_out[p * SW_RING + s0] = m2;         // same value from every lane
                 }
-            }
-            if (FAST) {
+                if (VERT) {
 #pragma unroll
-                for (int k = 0; k < NP; ++k) S[k] = LAST ? pk_addmin(S[k], sum[k], WALL2) : sum[k];
-            }
-            if (!LAST && SW_EXPERIMENT != 4) vec_st<NP>(pS - NP * lane, lane, S);
-            if (succGlob) {
-                // last row of the band: hand L_r to the next band through the carry
+                    for (int p = 0; p < 3; ++p) {
+                        if (!(MASK & (2 << p))) continue;
+                        const uint32_t m2 = sgm_step<NP, FULL>(Lt[p], C, mq2[p], P1P1, P2P2, lane, padm);
 #pragma unroll
-                for (int p = 0; p < 3; ++p) {
-                    if (!(MASK & (2 << p))) continue;
-                    vec_st<NP>(carry_out + ((size_t)i * 3 + p) * VW, lane, Lt[p]);
+                        for (int k = 0; k < NP; ++k) {
+                            if (FAST) sum[k] += Lt[p][k];
+                            else S[k] = pk_addmin(S[k], Lt[p][k], WALL2);
+                        }
+                        uint32_t* wp = ring_out + p * PATHW + o_0;
+                        vec_st<NP>(wp, lane, Lt[p]);
+                        if (lane == 0) wp[VW] = m2;
+                        if (doGlob) {                        // last row of the band: hand L_r to the next band through the carry
+                            vec_st<NP>(carry_out + ((size_t)i * 3 + p) * VW, lane, Lt[p]);
+                            if (lane == 0) cmin_out[(size_t)i * 4 + p] = m2;
+                        }
+                    }
                 }
-                if (lane < 3) cmin_out[(size_t)i * 4 + lane] = rmin_out[lane * SW_RING + s0];
-                if (((i & (SW_FLAG_EVERY - 1)) == SW_FLAG_EVERY - 1) || i == w1 - 1) {
+                if (FAST) {
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) S[k] = LAST ? pk_addmin(S[k], sum[k], WALL2) : sum[k];
+                }
+                if (!LAST) vec_st<NP>(pS - NP * lane, lane, S);
+                if (doGlob && (((i & (SW_FLAG_EVERY - 1)) == SW_FLAG_EVERY - 1) || i == w1 - 1)) {
                     __syncwarp();
-                    if (SW_EXPERIMENT < 2 && lane == 0) st_release_gpu(prog_mine, i + 1);
+                    if (lane == 0) st_release_gpu(prog_mine, i + 1);
                 }
-            }
-            if (LAST) {
-                if (a.storeS) vec_st<NP>(pS - NP * lane, lane, S);
-                if (y >= keep) {
-                    const int xc = dir > 0 ? i : w1 - 1 - i;
-                    // ---- WTA (A.4): argmin with lowest-d tie break via keys (S << 16 | d)
-                    uint32_t kmin = 0xffffffffu;
-                    const uint32_t dlo = NP * lane, dhi = NP * lane + g.HALF;
+                if (LAST) {
+                    if (a.storeS) vec_st<NP>(pS - NP * lane, lane, S);
+                    if (y >= keep) {
+                        // ---- WTA (A.4): argmin with lowest-d tie break via keys (S << 16 | d)
+                        uint32_t kmin = 0xffffffffu;
 #pragma unroll
-                    for (int k = 0; k < NP; ++k) {
-                        const uint32_t klo = (S[k] << 16) | (dlo + k);
-                        const uint32_t khi = __byte_perm(S[k], dhi + k, 0x3254);
-                        kmin = min(kmin, min(klo, khi));
-                    }
-                    kmin = __reduce_min_sync(FULLMASK, kmin);
-                    const int minS = (int)(kmin >> 16), best = (int)(kmin & 0xffffu);
-                    // uniqueness: count disparities with S < th; the ones at best-1..best+1 do not count
-                    int th;
-                    if (g.mode == SVB_MODE_SGBM_3WAY) {
-                        // cv2's 3WAY vector loop: Sp[d] < (short)(100*minS/(100-u) + 1) (oracle/sgbm_oracle.c)
-                        th = g.uniq > 0 ? (int)(int16_t)((100 * minS) / (100 - g.uniq) + 1) : 0;
-                        th = max(th, 0);
-                    } else {
-                        const int f = 100 - g.uniq;
-                        th = (minS * 100 + f - 1) / f;       // S*f < minS*100  <=>  S < ceil(minS*100/f)
-                    }
-                    th = min(th, 0x8000);
-                    const uint32_t th2 = pk_dup((uint32_t)th);
-                    uint32_t cnt2 = 0;
+                        for (int k = 0; k < NP; ++k) {
+                            const uint32_t klo = __byte_perm(S[k], dpk[k], 0x1054);
+                            const uint32_t khi = __byte_perm(S[k], dpk[k], 0x3276);
+                            kmin = min(kmin, min(klo, khi));
+                        }
+                        kmin = __reduce_min_sync(FULLMASK, kmin);
+                        const int th = wta_threshold(g, (int)(kmin >> 16));
+                        // uniqueness: count disparities with S < th; the ones at best-1..best+1 are taken out later
+                        const uint32_t th2 = pk_dup((uint32_t)th);
+                        uint32_t bits = 0;
 #pragma unroll
-                    for (int k = 0; k < NP; ++k) {
-                        uint32_t lt = (__vsub2(S[k], th2) >> 15) & 0x00010001u;   // S, th in [0, 0x8000]
-                        if (!FULL) lt &= ~padm[k];
-                        cnt2 += lt;
-                    }
-                    const int cnt = (int)__reduce_add_sync(FULLMASK, (cnt2 & 0xffffu) + (cnt2 >> 16));
-                    vec_st<NP>(mysc, lane, S);
-                    __syncwarp();
-                    if (lane == 0) {
-                        const size_t pix = ((size_t)b * g.H + y) * g.W + (xc + g.minX1);
-                        int out = g.INV;
-                        if (minS < (int)WALL) {
-                            const uint16_t* sv = reinterpret_cast<const uint16_t*>(mysc);
-                            auto tap = [&](int d) { return (int)sv[d < g.HALF ? 2 * d : 2 * (d - g.HALF) + 1]; };
-                            const int sm1v = best > 0 ? tap(best - 1) : 0;
-                            const int sp1v = best < g.D - 1 ? tap(best + 1) : 0;
-                            const int excl = (minS < th) + (best > 0 && sm1v < th) + (best < g.D - 1 && sp1v < th);
-                            if (cnt <= excl) {
-                                int dsub = best * 16;
-                                if (best > 0 && best < g.D - 1) {
-                                    const int den = max(sm1v + sp1v - 2 * minS, 1);
-                                    dsub += ((sm1v - sp1v) * 16 + den) / (2 * den);   // C division: truncates toward zero
-                                }
-                                out = dsub + g.minD * 16;
+                        for (int k = 0; k < NP; ++k) {
+                            uint32_t lt = __vsub2(S[k], th2);                 // S, th in [0, 0x8000]: bit 15 = (S < th)
+                            if (!FULL) lt &= ~padm[k];
+                            bits |= (lt >> k) & (0x80008000u >> k);
+                        }
+                        const uint32_t cnt = __reduce_add_sync(FULLMASK, (uint32_t)__popc(bits));
+                        vec_st<NP>(mysc, lane, S);
+                        __syncwarp();
+                        const uint16_t* sv = reinterpret_cast<const uint16_t*>(mysc);
+                        const int best = (int)(kmin & 0xffffu);
+                        auto tap = [&](int d) { return (uint32_t)sv[d < g.HALF ? 2 * d : 2 * (d - g.HALF) + 1]; };
+                        const uint32_t sm1v = best > 0 ? tap(best - 1) : 0u;
+                        const uint32_t sp1v = best < g.D - 1 ? tap(best + 1) : 0u;
+                        if (lane == (i & 31)) { rkey = kmin; rcnt = cnt; rtap = sm1v | (sp1v << 16); }
+                        if ((i & 31) == 31 || i == w1 - 1) {
+                            // 32 columns decided at once: lane j finishes column (i & ~31) + j
+                            const int ci = (i & ~31) + lane;
+                            if (ci <= i) {
+                                const int xc = dir > 0 ? ci : w1 - 1 - ci;
                                 const int x = xc + g.minX1;
-                                const int x2 = x - best - g.minD;
-                                // smallest cost wins, then the largest x: the pixel cv2's right-to-left loop keeps
-                                atomicMin(a.key + ((size_t)b * g.H + y) * g.W + x2,
-                                          ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+                                const size_t rowpix = ((size_t)b * g.H + y) * g.W;
+                                const int minS = (int)(rkey >> 16), bst = (int)(rkey & 0xffffu);
+                                const int thr = wta_threshold(g, minS);
+                                const int s1 = (int)(rtap & 0xffffu), s2 = (int)(rtap >> 16);
+                                int out = g.INV;
+                                if (minS < (int)WALL) {
+                                    const int excl = (minS < thr) + (bst > 0 && s1 < thr) + (bst < g.D - 1 && s2 < thr);
+                                    if ((int)rcnt <= excl) {
+                                        int dsub = bst * 16;
+                                        if (bst > 0 && bst < g.D - 1) {
+                                            const int den = max(s1 + s2 - 2 * minS, 1);
+                                            dsub += ((s1 - s2) * 16 + den) / (2 * den);   // C division: truncates toward zero
+                                        }
+                                        out = dsub + g.minD * 16;
+                                        const int x2 = x - bst - g.minD;
+                                        // smallest cost wins, then the largest x: the pixel cv2's right-to-left loop keeps
+                                        atomicMin(a.key + rowpix + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+                                    }
+                                }
+                                a.raw[rowpix + x] = (int16_t)out;
                             }
                         }
-                        a.raw[pix] = (int16_t)out;
                     }
-                    __syncwarp();
                 }
+                if (doFeed) {
+                    const int cs = i + 2, cf = i + 3;
+                    if (cs < w1) stash_col(cs);
+                    else if (cs == w1) zero_row(ring_in + 2 * PATHW + (w1 % RING) * ROWW);   // virtual column w1
+                    if (cf < w1) { wait_cols(cf + 1); fetch_col(cf); }
+                }
+                if (VERT || LAST) __syncwarp();
+                if (VERT && lane == 0) sts_release_cta(&s_done[warp], i + 1);
+                gC += cstep; gS += cstep; pS += cstep;
+                o_m1 = o_0; o_0 = o_p1; o_p1 = o_p1 + ROWW == PATHW ? 0u : o_p1 + ROWW;
+                cs_prev = cs_cur; cs_cur = cs_cur + VW == NS * VW ? 0u : cs_cur + VW;
             }
-            if (feed) {
-                const int cs = i + 2, cf = i + 3;
-                if (cs < w1) stash_col(cs);
-                if (cf < w1) { wait_cols(cf + 1); fetch_col(cf); }
-            }
-#if SW_LOCKSTEP
-            if (VERT) __syncthreads();
-#else
-            if (VERT) {
+            if (VERT && nloop) {
+                // virtual column w1 for the row below (its diagonal-from-ahead predecessor at the last column),
+                // then a final count no column index reaches
+                if (wSucc) {
+                    while (seenS < w1 - RING + 2) { seenS = lds_acquire_cta(done_succ); if (seenS < w1 - RING + 2) __nanosleep(SW_SLEEP_NS); }
+                    zero_row(ring_out + 2 * PATHW + o_0);
+                }
                 __syncwarp();
-                if (SW_EXPERIMENT == 0 && lane == 0) sts_release_cta(&s_done[warp], i + 1);
+                if (lane == 0) sts_release_cta(&s_done[warp], w1 + 8);
             }
-#endif
-            pS += cstep;
-            sm1 = s0; s0 = sp1; sp1 = sp1 + 1 == SW_RING ? 0 : sp1 + 1;
-            cslot = cslot + 1 == NS ? 0 : cslot + 1;
-        }
+        };
+        if (VERT && warp > 0 && warp < nact - 1) run(std::true_type{});
+        else run(std::false_type{});
         asm volatile("cp.async.wait_all;" ::: "memory");
     }
 }
@@ -901,6 +931,7 @@ static int make_geo(const svb_sgbm_params& p, int H, int W, SgbmGeo& g)
     g.P2 = std::max(p.P2 > 0 ? p.P2 : 5, g.P1 + 1);
     g.uniq = p.uniquenessRatio >= 0 ? p.uniquenessRatio : 10;
     g.d12 = p.disp12MaxDiff > 0 ? p.disp12MaxDiff : 1;
+    g.thMul = (100 - g.uniq) > 1 ? 0xffffffffu / (unsigned)(100 - g.uniq) + 1u : 0u;
     g.INV = (g.minD - 1) * 16;
     g.mode = p.mode;
     g.nstripes = p.mode == SVB_MODE_SGBM_3WAY ? 4 : 1;

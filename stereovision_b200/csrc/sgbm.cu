@@ -41,6 +41,12 @@
 
 // rows (= warps) per band
 __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 5 ? 16 : 8; }
+#ifndef SW_EXPERIMENT
+#define SW_EXPERIMENT 0        // timing experiments only (results are wrong): 3 = no C/S1 loads, 4 = no S1 stores, 5 = both, 6 = no row hand-off waits
+#endif
+#ifndef SW_FMA_ADDS
+#define SW_FMA_ADDS 1          // P1 and sum additions of the recurrence as IMADs (FMA pipe) instead of ALU-pipe adds
+#endif
 #ifndef SW_SLEEP_NS
 #define SW_SLEEP_NS 40         // back-off while a row waits for its neighbour's progress counter
 #endif
@@ -421,9 +427,18 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
 // One step of the SGM recurrence (A.3) for a whole disparity vector held by a warp.
 //   L(d) = C(d) + min(Lq(d), Lq(d-1)+P1, Lq(d+1)+P1, minLq+P2) - minLq
 // Lq is updated in place; returns the warp-wide min of the new L (minLq for the next step).
+// a + b on the FMA pipe (IMAD with a run-time 1) -- the integer ALU pipe is the busy one in the sweeps
+__device__ __forceinline__ uint32_t add_fma(uint32_t a, uint32_t one, uint32_t b)
+{
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(one), "r"(b));
+    return r;
+}
+
 template <int NP, bool FULL>
 __device__ __forceinline__ uint32_t sgm_step(uint32_t (&Lq)[NP], const uint32_t (&C)[NP], uint32_t mq2,
-                                             uint32_t P1P1, uint32_t P2P2, int lane, const uint32_t (&padm)[NP])
+                                             uint32_t P1P1, uint32_t P2P2, int lane, const uint32_t (&padm)[NP],
+                                             uint32_t one)
 {
     // mq2 = minLq in both halves; returns the warp-wide min of the new L, again in both halves.
     // neighbours across lane boundaries; both halves of a word move together, except at the
@@ -438,9 +453,14 @@ __device__ __forceinline__ uint32_t sgm_step(uint32_t (&Lq)[NP], const uint32_t 
 #pragma unroll
     for (int k = 0; k < NP; ++k) {
         const uint32_t dn = (k + 1 < NP) ? Lq[k + 1] : next;
+#if SW_FMA_ADDS
+        uint32_t t = add_fma(pk_min(up, dn), one, P1P1);     // halves stay below 65536 (wall + P1)
+        t = pk_min(pk_min(t, Lq[k]), mqP2);
+#else
         uint32_t t = pk_min(up, dn);
         t = pk_addmin(t, P1P1, Lq[k]);
         t = pk_min(t, mqP2);
+#endif
         uint32_t L = C[k] + t - mq2;                         // halves stay in [0, 65535]: no carries
         if (!FULL) L = (L & ~padm[k]) | (WALL2 & padm[k]);   // pad disparities keep the wall
         up = Lq[k];
@@ -528,13 +548,19 @@ struct SweepArgs {
 // MASK: paths of this sweep: 1 horizontal, 2 diagonal from behind, 4 vertical, 8 diagonal from ahead.
 //
 // Shared memory: every row (warp) of a band owns an INPUT ring per inter-row path: RING slots of
-// ROWW = VW + 4 words (the L_r vector of one column of the previous row, then its minimum in both
-// halves).  The row above writes it, the progress counters s_done[] order the accesses: row k may
-// start column i once row k-1 has published i + 2 (column i + 1 is the diagonal-from-ahead
-// predecessor) and row k-1 may overwrite a slot once row k has published the column that last read it.
-// Virtual columns -1 and w1 (predecessors outside the image, A.3) are zero rows of the ring.
+// ROWW = VW + 4 words: the L_r vector of one column of the previous row; the four tail words of the
+// path-0 row of a slot hold that column's three path minima (both halves).  The row above writes it,
+// the progress counters s_done[] order the accesses: row k may start column i once row k-1 has
+// published i + 2 (column i + 1 is the diagonal-from-ahead predecessor) and row k-1 may overwrite a
+// slot once row k has published the column that last read it.  Virtual columns -1 and w1
+// (predecessors outside the image, A.3) are zero rows of the ring.
+// All rows run the same lean loop: two helper warps play "the row above" for row 0 (the loader
+// streams the carry of the previous band from L2 into row 0's ring with cp.async) and "the row
+// below" for the last row (the drain copies that row's output ring into the carry for the next
+// band and publishes the band's progress).  The pace of the whole wavefront is one warp's latency per column,
+// so nothing but the recurrence itself may sit in the rows' loop.
 template <int NP, int VAR, int MASK, bool LAST>
-__global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a, const SgbmGeo g)
+__global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const SweepArgs a, const SgbmGeo g)
 {
     constexpr bool FULL = VAR != 0, FAST = VAR == 2;
     constexpr bool VERT = (MASK & 14) != 0;                  // any path that crosses rows
@@ -542,17 +568,20 @@ __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a
     constexpr int SW_R = sw_rows(NP), RING = sw_ring(NP, LAST), NS = sw_stage(NP, LAST), PFD = NS - 1;
     constexpr int PATHW = RING * ROWW, RINGW = 3 * PATHW;
     extern __shared__ __align__(16) uint32_t smem[];
-    uint32_t* ring = smem;                                   // [SW_R + 1][3][RING][ROWW] (+1: where the last row dumps)
+    uint32_t* ring = smem;                                   // [SW_R + 1][3][RING][ROWW] (+1: what the last row writes)
     uint32_t* cstage = ring + (SW_R + 1) * RINGW;            // [SW_R][NS][VW] cp.async ring of C columns
     uint32_t* sstage = cstage + SW_R * NS * VW;              // [SW_R][NS][VW] (last sweep) ... and of S1 columns
     uint32_t* wsc = sstage + (LAST ? SW_R * NS * VW : 0);    // [SW_R][VW] (last sweep) S of the current column for the subpixel taps
     __shared__ int s_ticket;
-    __shared__ int s_done[SW_R + 1];                         // columns published by each row of the band
+    __shared__ int s_done[SW_R + 2];                         // [k]: columns published by row k (or by the drain for k = nact); [SW_R + 1]: by the loader
+    int* const s_load = &s_done[SW_R + 1];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool helper = warp >= SW_R;                        // SW_R: carry loader, SW_R + 1: carry drain
     const int w1 = g.width1;
     const uint32_t P1P1 = pk_dup(g.P1), P2P2 = pk_dup(g.P2);
     const int dir = a.dir;
+    const uint32_t one = a.njobs > 0;                        // 1, opaque to the compiler (add_fma)
     uint32_t padm[NP], dpk[NP];
 #pragma unroll
     for (int k = 0; k < NP; ++k) {
@@ -560,13 +589,20 @@ __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a
         padm[k] = (w >= g.D ? 0xffffu : 0u) | (w + g.HALF >= g.D ? 0xffff0000u : 0u);
         dpk[k] = ((uint32_t)(w + g.HALF) << 16) | (uint32_t)w;    // the two disparities of word k
     }
-    uint32_t* ring_in = ring + (size_t)warp * RINGW;
+    const int rw = helper ? 0 : warp;
+    uint32_t* ring_in = ring + (size_t)rw * RINGW;
     uint32_t* ring_out = ring_in + RINGW;                    // input ring of warp + 1
-    uint32_t* mysc = wsc + warp * VW;
-    const uint32_t cst_s = smem_u32(cstage + (size_t)warp * NS * VW + NP * lane);   // this lane's slice, slot 0
-    const uint32_t sst_s = smem_u32(sstage + (size_t)warp * NS * VW + NP * lane);
-    const uint32_t* cst = cstage + (size_t)warp * NS * VW;
-    const uint32_t* sst = sstage + (size_t)warp * NS * VW;
+    uint32_t* mysc = wsc + rw * VW;
+    const uint32_t cst_s = smem_u32(cstage + (size_t)rw * NS * VW + NP * lane);   // this lane's slice, slot 0
+    const uint32_t sst_s = smem_u32(sstage + (size_t)rw * NS * VW + NP * lane);
+    const uint32_t* cst = cstage + (size_t)rw * NS * VW;
+    const uint32_t* sst = sstage + (size_t)rw * NS * VW;
+
+    auto zero_col = [&](uint32_t* rbase, int p, uint32_t slotoff) {   // one column of one path: vector + its minimum
+        const uint32_t z[NP] = {};
+        vec_st<NP>(rbase + p * PATHW + slotoff, lane, z);
+        if (lane == 0) rbase[slotoff + VW + p] = 0;
+    };
 
     for (;;) {
         __syncthreads();
@@ -581,81 +617,128 @@ __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a
         const int nact = min(SW_R, nrows - r0);
         if (nact <= 0) continue;
 
-        const bool active = warp < nact;
-        const int sr = r0 + warp;                            // row index in sweep order
+        const bool active = !helper && warp < nact;
+        const int sr = r0 + rw;                              // row index in sweep order
         const int row = dir > 0 ? sr : nrows - 1 - sr;       // storage row within the job
         const int y = ys + row;
-        const bool havePred = sr > 0;
-        const bool feed = VERT && (warp == 0) && band > 0;   // warp 0 feeds its ring from the carry
-        const bool succGlob = VERT && active && (warp == nact - 1) && (r0 + nact < nrows);
         const bool rowSkip = LAST && !VERT && y < keep;      // 3WAY overlap rows: nothing depends on them
         const size_t rowbase = (((size_t)job * g.rowsMax + row) * w1) * VW;
-        const uint32_t* carry_in = a.carry + (((size_t)job * 2 + ((band + 1) & 1)) * w1) * 3 * VW;
-        const uint32_t* cmin_in = a.cmin + (((size_t)job * 2 + ((band + 1) & 1)) * w1) * 4;
-        uint32_t* carry_out = a.carry + (((size_t)job * 2 + (band & 1)) * w1) * 3 * VW;
-        uint32_t* cmin_out = a.cmin + (((size_t)job * 2 + (band & 1)) * w1) * 4;
-        const int* prog_pred = a.prog + (size_t)job * a.bandsPerJob + band - 1;
-        int* prog_mine = a.prog + (size_t)job * a.bandsPerJob + band;
         const int b = job / g.nstripes;
+        const int nL = VERT && band > 0 ? w1 : 0;            // carry columns the loader brings in
+        const int nD = VERT && (r0 + nact < nrows) ? w1 : 0; // carry columns the drain takes out
 
-        // ---- warp 0 of a non-first band copies the carry (last row of the previous band) into its own ring,
-        // two columns ahead of use, a third one in flight in registers
-        uint32_t pre[3][NP];
-        uint32_t premin = 0;
-        int seen = 0;
-        auto wait_cols = [&](int need) {     // all lanes of warp 0
-            if (seen < need) {
-                if (lane == 0) {
-                    int spins = 0;
-                    while ((seen = ld_acquire_gpu(prog_pred)) < need) {
-                        if (++spins > SW_SPIN_LIMIT) { atomicExch(a.err, 1); break; }
-                        __nanosleep(40);
+        if (active) {
+            if (lane == 0) s_done[warp] = 0;
+            if (VERT) {
+                if (warp == 0 && band == 0) {                // first row of the job: no previous row at all
+                    for (int q = lane; q < RINGW; q += 32) ring_in[q] = 0;
+                } else {
+                    zero_col(ring_in, 0, (RING - 1) * ROWW); // virtual column -1 of the diagonal-from-behind path
+                }
+            }
+        } else if (warp == SW_R && lane == 0) {
+            *s_load = nL ? 0 : w1 + 8;                       // no carry to wait for: row 0 runs free
+            s_done[nact] = nD ? 0 : w1 + 64;                 // nobody below the last row: it never waits
+        }
+        __syncthreads();
+
+        if (helper) {
+            const int* prog_pred = a.prog + (size_t)job * a.bandsPerJob + band - 1;
+            int* prog_mine = a.prog + (size_t)job * a.bandsPerJob + band;
+            if (warp == SW_R && nL) {
+                // ---- loader: the previous band's carry -> row 0's ring, DEPTH columns between request and publication
+                const uint32_t* carry_in = a.carry + (((size_t)job * 2 + ((band + 1) & 1)) * w1) * 3 * VW;
+                const uint32_t* cmin_in = a.cmin + (((size_t)job * 2 + ((band + 1) & 1)) * w1) * 4;
+                uint32_t* ring0 = ring;
+                const uint32_t ring0_s = smem_u32(ring0);
+                constexpr int DEPTH = RING - 2;
+                int seen0 = 0, seenG = 0;
+                bool dead = false;
+                for (int cl = 0; cl < nL + DEPTH - 1; ++cl) {
+                    if (cl < nL) {
+                        while (seen0 < cl - RING + 2) {
+                            seen0 = lds_acquire_cta(&s_done[0]);
+                            if (seen0 < cl - RING + 2) __nanosleep(SW_SLEEP_NS);
+                        }
+                        for (int spins = 0; seenG < cl + 1; ++spins) {
+                            seenG = ld_acquire_gpu(prog_pred);
+                            if (seenG >= cl + 1) break;
+                            if (spins > SW_SPIN_LIMIT) { dead = true; break; }
+                            __nanosleep(100);
+                        }
+                        if (dead) break;
+                        const uint32_t so = (uint32_t)(cl % RING) * ROWW;
+#pragma unroll
+                        for (int p = 0; p < 3; ++p) {
+                            if (!(MASK & (2 << p))) continue;
+                            const uint32_t* src = carry_in + ((size_t)cl * 3 + p) * VW;
+                            if constexpr (NP % 4 == 0) {
+                                cp_async_vec_s<NP>(ring0_s + (p * PATHW + so + NP * lane) * 4, src + NP * lane);
+                            } else {                         // 4-byte cp.async would go through L1: copy through registers
+                                uint32_t v[NP];
+                                vec_ld<NP>(src, lane, v, LdCg());
+                                vec_st<NP>(ring0 + p * PATHW + so, lane, v);
+                            }
+                        }
+                        if (lane == 0)
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring0_s + (so + VW) * 4),
+                                         "l"(cmin_in + (size_t)cl * 4));
+                    }
+                    asm volatile("cp.async.commit_group;");  // (empty groups while the pipeline runs out)
+                    if (cl >= DEPTH - 1) {
+                        asm volatile("cp.async.wait_group %0;" ::"n"(DEPTH - 1) : "memory");
+                        __syncwarp();
+                        if (lane == 0) sts_release_cta(s_load, cl - DEPTH + 2);
                     }
                 }
-                seen = __shfl_sync(FULLMASK, seen, 0);
-                __syncwarp();
+                if (dead) {
+                    if (lane == 0) { atomicExch(a.err, 1); sts_release_cta(s_load, w1 + 8); }   // let the rows run out
+                } else {
+                    // virtual column w1 for row 0, then the final count
+                    while (seen0 < w1 - RING + 2) {
+                        seen0 = lds_acquire_cta(&s_done[0]);
+                        if (seen0 < w1 - RING + 2) __nanosleep(SW_SLEEP_NS);
+                    }
+                    zero_col(ring0, 2, (uint32_t)(w1 % RING) * ROWW);
+                    __syncwarp();
+                    if (lane == 0) sts_release_cta(s_load, w1 + 8);
+                }
+                asm volatile("cp.async.wait_all;" ::: "memory");
             }
-        };
-        auto fetch_col = [&](int c) {
+            if (warp == SW_R + 1 && nD) {
+                // ---- drain: the last row's output ring -> the carry for the next band, progress every SW_FLAG_EVERY columns
+                uint32_t* carry_out = a.carry + (((size_t)job * 2 + (band & 1)) * w1) * 3 * VW;
+                uint32_t* cmin_out = a.cmin + (((size_t)job * 2 + (band & 1)) * w1) * 4;
+                const uint32_t* ringD = ring + (size_t)nact * RINGW;
+                int seenL = 0;
+                for (int cd = 0; cd < nD; ++cd) {
+                    while (seenL < cd + 1) {
+                        seenL = lds_acquire_cta(&s_done[nact - 1]);
+                        if (seenL < cd + 1) __nanosleep(SW_SLEEP_NS);
+                    }
+                    const uint32_t so = (uint32_t)(cd % RING) * ROWW;
 #pragma unroll
-            for (int p = 0; p < 3; ++p) vec_ld<NP>(carry_in + ((size_t)c * 3 + p) * VW, lane, pre[p], LdCg());
-            if (lane < 3) premin = __ldcg(cmin_in + (size_t)c * 4 + lane);
-        };
-        auto stash_col = [&](int c) {
-            const int so = (c % RING) * ROWW;
-#pragma unroll
-            for (int p = 0; p < 3; ++p) vec_st<NP>(ring_in + p * PATHW + so, lane, pre[p]);
-            if (lane < 3) ring_in[lane * PATHW + so + VW] = premin;
-        };
-        auto zero_row = [&](uint32_t* rowp) {                // one ring row: vector + minimum
-            const uint32_t z[NP] = {};
-            vec_st<NP>(rowp, lane, z);
-            if (lane == 0) rowp[VW] = 0;
-        };
-        if (feed) {
-            wait_cols(min(3, w1));
-            fetch_col(0); stash_col(0);
-            if (w1 > 1) { fetch_col(1); stash_col(1); }
-            else zero_row(ring_in + 2 * PATHW + (1 % RING) * ROWW);
-            if (w1 > 2) fetch_col(2);
+                    for (int p = 0; p < 3; ++p) {
+                        if (!(MASK & (2 << p))) continue;
+                        uint32_t v[NP];
+                        vec_ld<NP>(ringD + p * PATHW + so, lane, v, LdPlain());
+                        vec_st<NP>(carry_out + ((size_t)cd * 3 + p) * VW, lane, v);
+                    }
+                    if (lane < 4) cmin_out[(size_t)cd * 4 + lane] = ringD[so + VW + lane];
+                    __syncwarp();
+                    if (lane == 0) {
+                        sts_release_cta(&s_done[nact], cd + 2);          // the slot of column cd is free again
+                        if ((cd & (SW_FLAG_EVERY - 1)) == SW_FLAG_EVERY - 1 || cd == w1 - 1) st_release_gpu(prog_mine, cd + 1);
+                    }
+                }
+            }
+            continue;
         }
 
         uint32_t Lh[NP];
 #pragma unroll
         for (int k = 0; k < NP; ++k) Lh[k] = 0;
         uint32_t minh2 = 0;                                  // min of the horizontal L_r, in both halves
-        if (lane == 0) s_done[warp] = 0;
-        if (VERT && active) {
-            if (!havePred) {                                 // first row of the job: no previous row at all
-                for (int q = lane; q < RINGW; q += 32) ring_in[q] = 0;
-            } else {
-                zero_row(ring_in + (RING - 1) * ROWW);       // virtual column -1 of the diagonal-from-behind path
-            }
-        }
-        __syncthreads();
-
-        const bool waitPred = VERT && warp > 0;
-        const bool waitSucc = VERT && (warp + 1 < nact);
         const int x0 = dir > 0 ? 0 : w1 - 1;
         const ptrdiff_t cstep = (ptrdiff_t)dir * VW;
         const uint32_t* pC0 = a.C + rowbase + (size_t)x0 * VW + NP * lane;
@@ -673,177 +756,156 @@ __global__ void __launch_bounds__(sw_rows(NP) * 32, 1) k_sweep(const SweepArgs a
                 asm volatile("cp.async.commit_group;");
             }
         }
+        int seenP = 0, seenS = 0;
+        uint32_t o_m1 = (RING - 1) * ROWW, o_0 = 0, o_p1 = ROWW;   // ring offsets (words) of columns i-1, i, i+1
+        uint32_t cs_cur = 0, cs_prev = (NS - 1) * VW;              // stage offsets (words) of columns i, i-1
+        const uint32_t* gC = pC0 + (ptrdiff_t)PFD * cstep;         // this lane's slice of column i + PFD
+        const uint32_t* gS = pS0 + (ptrdiff_t)PFD * cstep;
+        uint32_t* pS = a.S + rowbase + (size_t)x0 * VW + NP * lane;
+        uint32_t rkey = 0, rcnt = 0, rtap = 0;                     // WTA record of column (i & ~31) + lane
+        const int* done_pred = warp > 0 ? &s_done[warp - 1] : s_load;
+        const int* done_succ = &s_done[warp + 1];
 
-        auto run = [&](auto mid_c) {
-            // MIDW: a row with a row above and below in the same band, nothing to do with the carry
-            constexpr bool MIDW = decltype(mid_c)::value;
-            const bool wPred = MIDW ? true : waitPred, wSucc = MIDW ? true : waitSucc;
-            const bool doFeed = MIDW ? false : feed, doGlob = MIDW ? false : succGlob;
-            int seenP = 0, seenS = 0;
-            uint32_t o_m1 = (RING - 1) * ROWW, o_0 = 0, o_p1 = ROWW;   // ring offsets (words) of columns i-1, i, i+1
-            uint32_t cs_cur = 0, cs_prev = (NS - 1) * VW;              // stage offsets (words) of columns i, i-1
-            const uint32_t* gC = pC0 + (ptrdiff_t)PFD * cstep;         // this lane's slice of column i + PFD
-            const uint32_t* gS = pS0 + (ptrdiff_t)PFD * cstep;
-            uint32_t* pS = a.S + rowbase + (size_t)x0 * VW + NP * lane;
-            uint32_t rkey = 0, rcnt = 0, rtap = 0;                     // WTA record of column (i & ~31) + lane
-            const int* done_pred = &s_done[warp > 0 ? warp - 1 : 0];
-            const int* done_succ = &s_done[warp + 1];
-
-            for (int i = 0; i < nloop; ++i) {
-                if (VERT && wPred && seenP < i + 2) {
-                    while ((seenP = lds_acquire_cta(done_pred)) < i + 2) __nanosleep(SW_SLEEP_NS);
-                }
-                if (VERT && wSucc && seenS < i - RING + 2) {
-                    while ((seenS = lds_acquire_cta(done_succ)) < i - RING + 2) __nanosleep(SW_SLEEP_NS);
-                }
-                // column i + PFD -> the stage slot column i - 1 has just left
+        for (int i = 0; i < nloop; ++i) {
+            if (SW_EXPERIMENT != 6 && VERT && seenP < i + 2) {
+                while ((seenP = lds_acquire_cta(done_pred)) < i + 2) __nanosleep(SW_SLEEP_NS);
+            }
+            if (SW_EXPERIMENT != 6 && VERT && seenS < i - RING + 2) {
+                while ((seenS = lds_acquire_cta(done_succ)) < i - RING + 2) __nanosleep(SW_SLEEP_NS);
+            }
+            // column i + PFD -> the stage slot column i - 1 has just left
+            if (SW_EXPERIMENT != 3 && SW_EXPERIMENT != 5) {
                 cp_async_vec_s<NP>(cst_s + cs_prev * 4, gC);
                 if (LAST) cp_async_vec_s<NP>(sst_s + cs_prev * 4, gS);
-                asm volatile("cp.async.commit_group;");
-                asm volatile("cp.async.wait_group %0;" ::"n"(PFD) : "memory");
-                uint32_t C[NP], S[NP];
-                vec_ld<NP>(cst + cs_cur, lane, C, LdPlain());
-                if (LAST) vec_ld<NP>(sst + cs_cur, lane, S, LdPlain());
-                else {
+            }
+            asm volatile("cp.async.commit_group;");
+            asm volatile("cp.async.wait_group %0;" ::"n"(PFD) : "memory");
+            uint32_t C[NP], S[NP];
+            vec_ld<NP>(cst + cs_cur, lane, C, LdPlain());
+            if (LAST) vec_ld<NP>(sst + cs_cur, lane, S, LdPlain());
+            else {
 #pragma unroll
-                    for (int k = 0; k < NP; ++k) S[k] = 0u;
+                for (int k = 0; k < NP; ++k) S[k] = 0u;
+            }
+            // predecessors on the previous row of the sweep
+            uint32_t Lt[3][NP], mq2[3];
+            if (VERT) {
+#pragma unroll
+                for (int p = 0; p < 3; ++p) {
+                    if (!(MASK & (2 << p))) continue;
+                    const uint32_t so = p == 0 ? o_m1 : (p == 1 ? o_0 : o_p1);
+                    vec_ld<NP>(ring_in + p * PATHW + so, lane, Lt[p], LdPlain());
+                    mq2[p] = ring_in[so + VW + p];
                 }
-                // predecessors on the previous row of the sweep
-                uint32_t Lt[3][NP], mq2[3];
-                if (VERT) {
+            }
+            uint32_t sum[NP];                                // FAST: plain sum of this sweep's L_r
 #pragma unroll
-                    for (int p = 0; p < 3; ++p) {
-                        if (!(MASK & (2 << p))) continue;
-                        const uint32_t* rp = ring_in + p * PATHW + (p == 0 ? o_m1 : (p == 1 ? o_0 : o_p1));
-                        vec_ld<NP>(rp, lane, Lt[p], LdPlain());
-                        mq2[p] = rp[VW];
-                    }
+            for (int k = 0; k < NP; ++k) sum[k] = 0;
+            if (MASK & 1) {                                  // horizontal: predecessor is the previous column
+                minh2 = sgm_step<NP, FULL>(Lh, C, minh2, P1P1, P2P2, lane, padm, one);
+#pragma unroll
+                for (int k = 0; k < NP; ++k) {
+                    if (FAST) sum[k] = SW_FMA_ADDS ? add_fma(Lh[k], one, sum[k]) : sum[k] + Lh[k];
+                    else S[k] = pk_addmin(S[k], Lh[k], WALL2);
                 }
-                uint32_t sum[NP];                            // FAST: plain sum of this sweep's L_r
+            }
+            if (VERT) {
 #pragma unroll
-                for (int k = 0; k < NP; ++k) sum[k] = 0;
-                if (MASK & 1) {                              // horizontal: predecessor is the previous column
-                    minh2 = sgm_step<NP, FULL>(Lh, C, minh2, P1P1, P2P2, lane, padm);
+                for (int p = 0; p < 3; ++p) {
+                    if (!(MASK & (2 << p))) continue;
+                    const uint32_t m2 = sgm_step<NP, FULL>(Lt[p], C, mq2[p], P1P1, P2P2, lane, padm, one);
 #pragma unroll
                     for (int k = 0; k < NP; ++k) {
-                        if (FAST) sum[k] += Lh[k];
-                        else S[k] = pk_addmin(S[k], Lh[k], WALL2);
+                        if (FAST) sum[k] = SW_FMA_ADDS ? add_fma(Lt[p][k], one, sum[k]) : sum[k] + Lt[p][k];
+                        else S[k] = pk_addmin(S[k], Lt[p][k], WALL2);
                     }
+                    vec_st<NP>(ring_out + p * PATHW + o_0, lane, Lt[p]);
+                    if (lane == 0) ring_out[o_0 + VW + p] = m2;
                 }
-                if (VERT) {
+            }
+            if (FAST) {
 #pragma unroll
-                    for (int p = 0; p < 3; ++p) {
-                        if (!(MASK & (2 << p))) continue;
-                        const uint32_t m2 = sgm_step<NP, FULL>(Lt[p], C, mq2[p], P1P1, P2P2, lane, padm);
+                for (int k = 0; k < NP; ++k) S[k] = LAST ? pk_addmin(S[k], sum[k], WALL2) : sum[k];
+            }
+            if (!LAST && SW_EXPERIMENT != 4 && SW_EXPERIMENT != 5) vec_st<NP>(pS - NP * lane, lane, S);
+            if (LAST) {
+                if (a.storeS) vec_st<NP>(pS - NP * lane, lane, S);
+                if (y >= keep) {
+                    // ---- WTA (A.4): argmin with lowest-d tie break via keys (S << 16 | d)
+                    uint32_t kmin = 0xffffffffu;
 #pragma unroll
-                        for (int k = 0; k < NP; ++k) {
-                            if (FAST) sum[k] += Lt[p][k];
-                            else S[k] = pk_addmin(S[k], Lt[p][k], WALL2);
-                        }
-                        uint32_t* wp = ring_out + p * PATHW + o_0;
-                        vec_st<NP>(wp, lane, Lt[p]);
-                        if (lane == 0) wp[VW] = m2;
-                        if (doGlob) {                        // last row of the band: hand L_r to the next band through the carry
-                            vec_st<NP>(carry_out + ((size_t)i * 3 + p) * VW, lane, Lt[p]);
-                            if (lane == 0) cmin_out[(size_t)i * 4 + p] = m2;
-                        }
+                    for (int k = 0; k < NP; ++k) {
+                        const uint32_t klo = __byte_perm(S[k], dpk[k], 0x1054);
+                        const uint32_t khi = __byte_perm(S[k], dpk[k], 0x3276);
+                        kmin = min(kmin, min(klo, khi));
                     }
-                }
-                if (FAST) {
+                    kmin = __reduce_min_sync(FULLMASK, kmin);
+                    const int th = wta_threshold(g, (int)(kmin >> 16));
+                    // uniqueness: count disparities with S < th; the ones at best-1..best+1 are taken out later
+                    const uint32_t th2 = pk_dup((uint32_t)th);
+                    uint32_t bits = 0;
 #pragma unroll
-                    for (int k = 0; k < NP; ++k) S[k] = LAST ? pk_addmin(S[k], sum[k], WALL2) : sum[k];
-                }
-                if (!LAST) vec_st<NP>(pS - NP * lane, lane, S);
-                if (doGlob && (((i & (SW_FLAG_EVERY - 1)) == SW_FLAG_EVERY - 1) || i == w1 - 1)) {
+                    for (int k = 0; k < NP; ++k) {
+                        uint32_t lt = __vsub2(S[k], th2);                 // S, th in [0, 0x8000]: bit 15 = (S < th)
+                        if (!FULL) lt &= ~padm[k];
+                        bits |= (lt >> k) & (0x80008000u >> k);
+                    }
+                    const uint32_t cnt = __reduce_add_sync(FULLMASK, (uint32_t)__popc(bits));
+                    vec_st<NP>(mysc, lane, S);
                     __syncwarp();
-                    if (lane == 0) st_release_gpu(prog_mine, i + 1);
-                }
-                if (LAST) {
-                    if (a.storeS) vec_st<NP>(pS - NP * lane, lane, S);
-                    if (y >= keep) {
-                        // ---- WTA (A.4): argmin with lowest-d tie break via keys (S << 16 | d)
-                        uint32_t kmin = 0xffffffffu;
-#pragma unroll
-                        for (int k = 0; k < NP; ++k) {
-                            const uint32_t klo = __byte_perm(S[k], dpk[k], 0x1054);
-                            const uint32_t khi = __byte_perm(S[k], dpk[k], 0x3276);
-                            kmin = min(kmin, min(klo, khi));
-                        }
-                        kmin = __reduce_min_sync(FULLMASK, kmin);
-                        const int th = wta_threshold(g, (int)(kmin >> 16));
-                        // uniqueness: count disparities with S < th; the ones at best-1..best+1 are taken out later
-                        const uint32_t th2 = pk_dup((uint32_t)th);
-                        uint32_t bits = 0;
-#pragma unroll
-                        for (int k = 0; k < NP; ++k) {
-                            uint32_t lt = __vsub2(S[k], th2);                 // S, th in [0, 0x8000]: bit 15 = (S < th)
-                            if (!FULL) lt &= ~padm[k];
-                            bits |= (lt >> k) & (0x80008000u >> k);
-                        }
-                        const uint32_t cnt = __reduce_add_sync(FULLMASK, (uint32_t)__popc(bits));
-                        vec_st<NP>(mysc, lane, S);
-                        __syncwarp();
-                        const uint16_t* sv = reinterpret_cast<const uint16_t*>(mysc);
-                        const int best = (int)(kmin & 0xffffu);
-                        auto tap = [&](int d) { return (uint32_t)sv[d < g.HALF ? 2 * d : 2 * (d - g.HALF) + 1]; };
-                        const uint32_t sm1v = best > 0 ? tap(best - 1) : 0u;
-                        const uint32_t sp1v = best < g.D - 1 ? tap(best + 1) : 0u;
-                        if (lane == (i & 31)) { rkey = kmin; rcnt = cnt; rtap = sm1v | (sp1v << 16); }
-                        if ((i & 31) == 31 || i == w1 - 1) {
-                            // 32 columns decided at once: lane j finishes column (i & ~31) + j
-                            const int ci = (i & ~31) + lane;
-                            if (ci <= i) {
-                                const int xc = dir > 0 ? ci : w1 - 1 - ci;
-                                const int x = xc + g.minX1;
-                                const size_t rowpix = ((size_t)b * g.H + y) * g.W;
-                                const int minS = (int)(rkey >> 16), bst = (int)(rkey & 0xffffu);
-                                const int thr = wta_threshold(g, minS);
-                                const int s1 = (int)(rtap & 0xffffu), s2 = (int)(rtap >> 16);
-                                int out = g.INV;
-                                if (minS < (int)WALL) {
-                                    const int excl = (minS < thr) + (bst > 0 && s1 < thr) + (bst < g.D - 1 && s2 < thr);
-                                    if ((int)rcnt <= excl) {
-                                        int dsub = bst * 16;
-                                        if (bst > 0 && bst < g.D - 1) {
-                                            const int den = max(s1 + s2 - 2 * minS, 1);
-                                            dsub += ((s1 - s2) * 16 + den) / (2 * den);   // C division: truncates toward zero
-                                        }
-                                        out = dsub + g.minD * 16;
-                                        const int x2 = x - bst - g.minD;
-                                        // smallest cost wins, then the largest x: the pixel cv2's right-to-left loop keeps
-                                        atomicMin(a.key + rowpix + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+                    const uint16_t* sv = reinterpret_cast<const uint16_t*>(mysc);
+                    const int best = (int)(kmin & 0xffffu);
+                    auto tap = [&](int d) { return (uint32_t)sv[d < g.HALF ? 2 * d : 2 * (d - g.HALF) + 1]; };
+                    const uint32_t sm1v = best > 0 ? tap(best - 1) : 0u;
+                    const uint32_t sp1v = best < g.D - 1 ? tap(best + 1) : 0u;
+                    if (lane == (i & 31)) { rkey = kmin; rcnt = cnt; rtap = sm1v | (sp1v << 16); }
+                    if ((i & 31) == 31 || i == w1 - 1) {
+                        // 32 columns decided at once: lane j finishes column (i & ~31) + j
+                        const int ci = (i & ~31) + lane;
+                        if (ci <= i) {
+                            const int xc = dir > 0 ? ci : w1 - 1 - ci;
+                            const int x = xc + g.minX1;
+                            const size_t rowpix = ((size_t)b * g.H + y) * g.W;
+                            const int minS = (int)(rkey >> 16), bst = (int)(rkey & 0xffffu);
+                            const int thr = wta_threshold(g, minS);
+                            const int s1 = (int)(rtap & 0xffffu), s2 = (int)(rtap >> 16);
+                            int out = g.INV;
+                            if (minS < (int)WALL) {
+                                const int excl = (minS < thr) + (bst > 0 && s1 < thr) + (bst < g.D - 1 && s2 < thr);
+                                if ((int)rcnt <= excl) {
+                                    int dsub = bst * 16;
+                                    if (bst > 0 && bst < g.D - 1) {
+                                        const int den = max(s1 + s2 - 2 * minS, 1);
+                                        dsub += ((s1 - s2) * 16 + den) / (2 * den);   // C division: truncates toward zero
                                     }
+                                    out = dsub + g.minD * 16;
+                                    const int x2 = x - bst - g.minD;
+                                    // smallest cost wins, then the largest x: the pixel cv2's right-to-left loop keeps
+                                    atomicMin(a.key + rowpix + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
                                 }
-                                a.raw[rowpix + x] = (int16_t)out;
                             }
+                            a.raw[rowpix + x] = (int16_t)out;
                         }
                     }
                 }
-                if (doFeed) {
-                    const int cs = i + 2, cf = i + 3;
-                    if (cs < w1) stash_col(cs);
-                    else if (cs == w1) zero_row(ring_in + 2 * PATHW + (w1 % RING) * ROWW);   // virtual column w1
-                    if (cf < w1) { wait_cols(cf + 1); fetch_col(cf); }
-                }
-                if (VERT || LAST) __syncwarp();
-                if (VERT && lane == 0) sts_release_cta(&s_done[warp], i + 1);
-                gC += cstep; gS += cstep; pS += cstep;
-                o_m1 = o_0; o_0 = o_p1; o_p1 = o_p1 + ROWW == PATHW ? 0u : o_p1 + ROWW;
-                cs_prev = cs_cur; cs_cur = cs_cur + VW == NS * VW ? 0u : cs_cur + VW;
             }
-            if (VERT && nloop) {
-                // virtual column w1 for the row below (its diagonal-from-ahead predecessor at the last column),
-                // then a final count no column index reaches
-                if (wSucc) {
-                    while (seenS < w1 - RING + 2) { seenS = lds_acquire_cta(done_succ); if (seenS < w1 - RING + 2) __nanosleep(SW_SLEEP_NS); }
-                    zero_row(ring_out + 2 * PATHW + o_0);
-                }
-                __syncwarp();
-                if (lane == 0) sts_release_cta(&s_done[warp], w1 + 8);
+            if (VERT || LAST) __syncwarp();
+            if (VERT && lane == 0) sts_release_cta(&s_done[warp], i + 1);
+            gC += cstep; gS += cstep; pS += cstep;
+            o_m1 = o_0; o_0 = o_p1; o_p1 = o_p1 + ROWW == PATHW ? 0u : o_p1 + ROWW;
+            cs_prev = cs_cur; cs_cur = cs_cur + VW == NS * VW ? 0u : cs_cur + VW;
+        }
+        if (VERT && nloop) {
+            // virtual column w1 for the row below (its diagonal-from-ahead predecessor at the last column),
+            // then a final count no column index reaches
+            while (seenS < w1 - RING + 2) {
+                seenS = lds_acquire_cta(done_succ);
+                if (seenS < w1 - RING + 2) __nanosleep(SW_SLEEP_NS);
             }
-        };
-        if (VERT && warp > 0 && warp < nact - 1) run(std::true_type{});
-        else run(std::false_type{});
+            zero_col(ring_out, 2, o_0);
+            __syncwarp();
+            if (lane == 0) sts_release_cta(&s_done[warp], w1 + 8);
+        }
         asm volatile("cp.async.wait_all;" ::: "memory");
     }
 }
@@ -1054,14 +1116,14 @@ static int launch_sweep(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, cudaS
     auto kfn = k_sweep<NP, VAR, MASK, LAST>;
     SVB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, SW_R * 32, smem));
+    SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, (SW_R + 2) * 32, smem));
     if (per_sm < 1) { svb_set_error("k_sweep does not fit on an SM (smem %zu)", smem); return SVB_ERR_UNSUPPORTED; }
     const long long tickets = (long long)a.njobs * a.bandsPerJob;
     const int grid = (int)std::min<long long>(tickets, (long long)h->num_sms * per_sm);
     // ticket = 0, err untouched, prog = 0
     SVB_CUDA(cudaMemsetAsync(a.ticket, 0, 4, st));
     SVB_CUDA(cudaMemsetAsync(a.prog, 0, (size_t)tickets * 4, st));
-    kfn<<<grid, SW_R * 32, smem, st>>>(a, g);
+    kfn<<<grid, (SW_R + 2) * 32, smem, st>>>(a, g);   // SW_R rows + the two carry helper warps
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

@@ -652,21 +652,15 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                 uint32_t* ring0 = ring;
                 const uint32_t ring0_s = smem_u32(ring0);
                 constexpr int DEPTH = RING - 2;
-                int seen0 = 0, seenG = 0;
+                int seen0 = 0, seenG = 0, cl = 0, cp = 0;    // next column to request / to publish
                 bool dead = false;
-                for (int cl = 0; cl < nL + DEPTH - 1; ++cl) {
-                    if (cl < nL) {
-                        while (seen0 < cl - RING + 2) {
-                            seen0 = lds_acquire_cta(&s_done[0]);
-                            if (seen0 < cl - RING + 2) __nanosleep(SW_SLEEP_NS);
-                        }
-                        for (int spins = 0; seenG < cl + 1; ++spins) {
-                            seenG = ld_acquire_gpu(prog_pred);
-                            if (seenG >= cl + 1) break;
-                            if (spins > SW_SPIN_LIMIT) { dead = true; break; }
-                            __nanosleep(100);
-                        }
-                        if (dead) break;
+                long long spins = 0;
+                while (cp < nL) {
+                    // request as far ahead as row 0's ring allows ...
+                    bool can = cl < nL && cl - cp < DEPTH;
+                    if (can && seen0 < cl - RING + 2) { seen0 = lds_acquire_cta(&s_done[0]); can = seen0 >= cl - RING + 2; }
+                    if (can && seenG < cl + 1) { seenG = ld_acquire_gpu(prog_pred); can = seenG >= cl + 1; }
+                    if (can) {
                         const uint32_t so = (uint32_t)(cl % RING) * ROWW;
 #pragma unroll
                         for (int p = 0; p < 3; ++p) {
@@ -683,12 +677,24 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                         if (lane == 0)
                             asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring0_s + (so + VW) * 4),
                                          "l"(cmin_in + (size_t)cl * 4));
-                    }
-                    asm volatile("cp.async.commit_group;");  // (empty groups while the pipeline runs out)
-                    if (cl >= DEPTH - 1) {
-                        asm volatile("cp.async.wait_group %0;" ::"n"(DEPTH - 1) : "memory");
+                        asm volatile("cp.async.commit_group;");
+                        ++cl;
+                        spins = 0;
+                    } else if (cp < cl) {
+                        // ... and whenever that is not possible, hand over the oldest requested column once it has landed
+                        switch (cl - cp - 1) {
+                            case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
+                            case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
+                            case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
+                            default: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
+                        }
                         __syncwarp();
-                        if (lane == 0) sts_release_cta(s_load, cl - DEPTH + 2);
+                        ++cp;
+                        if (lane == 0) sts_release_cta(s_load, cp);
+                        spins = 0;
+                    } else {
+                        if (++spins > SW_SPIN_LIMIT) { dead = true; break; }
+                        __nanosleep(SW_SLEEP_NS);
                     }
                 }
                 if (dead) {

@@ -39,8 +39,11 @@
 #define WALL2 0x7fff7fffu
 #define FULLMASK 0xffffffffu
 
+#ifndef SW_ROWS4
+#define SW_ROWS4 18
+#endif
 // rows (= warps) per band
-__host__ __device__ constexpr int sw_rows(int NP) { return NP <= 5 ? 16 : 8; }
+__host__ __device__ constexpr int sw_rows(int NP) { return NP <= 4 ? SW_ROWS4 : (NP <= 5 ? 16 : 8); }
 #ifndef SW_EXPERIMENT
 #define SW_EXPERIMENT 0        // timing experiments only (results are wrong): 3 = no C/S1 loads, 4 = no S1 stores, 5 = both, 6 = no row hand-off waits
 #endif
@@ -53,7 +56,7 @@ __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 5 ? 16 : 8; }
 // ring slots per path between two rows (>= 4; every extra slot is a column of slack between rows)
 #ifndef SW_RING_FIRST
 #define SW_RING_FIRST 6
-#define SW_RING_LAST 5
+#define SW_RING_LAST 4
 #endif
 __host__ __device__ constexpr int sw_ring(int NP, bool last) { return NP <= 4 ? (last ? SW_RING_LAST : SW_RING_FIRST) : 4; }
 // slots of the per-row cp.async staging ring for C (and S1 in the last sweep); prefetch distance = slots - 1
@@ -833,7 +836,6 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
 #pragma unroll
                 for (int k = 0; k < NP; ++k) S[k] = LAST ? pk_addmin(S[k], sum[k], WALL2) : sum[k];
             }
-            if (!LAST && SW_EXPERIMENT != 4 && SW_EXPERIMENT != 5) vec_st<NP>(pS - NP * lane, lane, S);
             if (LAST) {
                 if (a.storeS) vec_st<NP>(pS - NP * lane, lane, S);
                 if (y >= keep) {
@@ -897,6 +899,8 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
             }
             if (VERT || LAST) __syncwarp();
             if (VERT && lane == 0) sts_release_cta(&s_done[warp], i + 1);
+            // (after the publication: its fence then has no global store of this column to wait for)
+            if (!LAST && SW_EXPERIMENT != 4 && SW_EXPERIMENT != 5) vec_st<NP>(pS - NP * lane, lane, S);
             gC += cstep; gS += cstep; pS += cstep;
             o_m1 = o_0; o_0 = o_p1; o_p1 = o_p1 + ROWW == PATHW ? 0u : o_p1 + ROWW;
             cs_prev = cs_cur; cs_cur = cs_cur + VW == NS * VW ? 0u : cs_cur + VW;

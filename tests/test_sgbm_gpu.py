@@ -151,3 +151,25 @@ def test_sgbm_full_size_properties(cfg):
     assert valid.mean() > 0.5
     err = np.abs(a[0][valid] / 16.0 - gt0[valid])
     assert np.mean(err <= 1.0) > 0.95
+
+
+@pytest.mark.parametrize("cfg", [
+    dict(H=64, W=200, D=64, mode=1, B=600),     # more bands than CTAs: every CTA takes several bands in turn
+    dict(H=100, W=500, D=256, mode=1, B=100),   # the headline vector width (4 words per lane), carry across bands
+    dict(H=64, W=200, D=64, mode=0, B=600),
+    dict(H=70, W=420, D=320, mode=2, B=80),     # 3WAY stripes at the reference's own numDisparities
+])
+def test_sgbm_many_pairs_persistent_ctas_bit_exact(cfg):
+    """The sweep kernels are persistent: with more (pair, band) tickets than resident CTAs each CTA
+    re-initialises its rings and counters between bands.  Every copy of the pair must equal the oracle."""
+    torch = _torch()
+    H, W, D, B = cfg["H"], cfg["W"], cfg["D"], cfg["B"]
+    l, r, _ = make_pair(H, W, D, seed=3)
+    bs = 5
+    prm = dict(minDisparity=0, numDisparities=D, blockSize=bs, P1=8 * bs * bs, P2=32 * bs * bs, disp12MaxDiff=1,
+               preFilterCap=63, uniquenessRatio=10, speckleWindowSize=100, speckleRange=32, mode=cfg["mode"])
+    ref = torch.from_numpy(oracle.sgbm_compute(l, r, **prm)).cuda()
+    L = torch.from_numpy(l).cuda().unsqueeze(0).repeat(B, 1, 1).contiguous()
+    R = torch.from_numpy(r).cuda().unsqueeze(0).repeat(B, 1, 1).contiguous()
+    out = svb.StereoSGBM_create(**prm).compute(L, R)
+    assert int((out != ref.unsqueeze(0)).sum()) == 0

@@ -92,9 +92,9 @@ __host__ __device__ inline void job_rows(const SgbmGeo& g, int n, int& ys, int& 
 // ------------------------------------------------------------------------------------------
 // k_prefilter: per image row, the two BT channels (A.1 step 1-2) and their half-pixel
 // interval bounds (A.1 step 3).
-// Left: one 32-byte record per pixel {u, -u, u0, -u1} x 2 channels, each duplicated into both
+// Left: one 32-byte record per pixel {u, -u, u0, 1 - u1} x 2 channels, each duplicated into both
 // halves of a u32.
-// Right: 6 planes per row {v1, v0, -v} x 2 channels; entry(xr) = a[xr] | a[xr - HALF] << 16,
+// Right: 6 planes per row {-v1, v0, -v} x 2 channels; entry(xr) = a[xr] | a[xr - HALF] << 16,
 // i.e. the operands of disparity index w (low) and w + HALF (high) for left pixel x = xr + w.
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ void bt_channels(const uint8_t* img, int H, int W, int y, int x, int ftzero,
@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
             rec[c * 4 + 0] = pk_dup((uint32_t)u);
             rec[c * 4 + 1] = pk_dup((uint32_t)(-u));
             rec[c * 4 + 2] = pk_dup((uint32_t)u0);
-            rec[c * 4 + 3] = pk_dup((uint32_t)(-u1));
+            rec[c * 4 + 3] = pk_dup((uint32_t)(1 - u1));     // v - u1 = ~(-v) + (1 - u1)
         }
     }
     {
@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
             int va = x < W - 1 ? (v + p[2]) / 2 : v;
             int vb = x > 0 ? (v + p[0]) / 2 : v;
             int v0 = min(min(va, vb), v), v1 = max(max(va, vb), v);
-            const uint16_t ops[3] = {(uint16_t)v1, (uint16_t)v0, (uint16_t)(-v)};
+            const uint16_t ops[3] = {(uint16_t)(-v1), (uint16_t)v0, (uint16_t)(-v)};
 #pragma unroll
             for (int o = 0; o < 3; ++o) {
                 uint16_t* plane = base + (size_t)(c * 3 + o) * 2 * g.Wp;
@@ -356,15 +356,17 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
                     const uint32_t v1a = sp[0 * BW + e], v0a = sp[1 * BW + e], nva = sp[2 * BW + e];
                     const uint32_t v1b = sp[3 * BW + e], v0b = sp[4 * BW + e], nvb = sp[5 * BW + e];
                     // channel 0: c0 = max(0, u - v1, v0 - u); c1 = max(0, v - u1, u0 - v)
-                    uint32_t a = __vsub2(l0.x, v1a);
+                    // (operands are stored negated where that saves the subtraction: planes {-v1, v0, -v},
+                    //  records {u, -u, u0, 1 - u1}; a packed negation would cost two more instructions)
+                    uint32_t a = __vadd2(l0.x, v1a);                         // u - v1
                     uint32_t c0 = __viaddmax_s16x2_relu(v0a, l0.y, a);
-                    uint32_t bb = __vsub2(l0.w, nva);
+                    uint32_t bb = __vadd2(~nva, l0.w);                       // v - u1
                     uint32_t c1 = __viaddmax_s16x2_relu(l0.z, nva, bb);
                     uint32_t pix = __vminu2(c0, c1);
                     // channel 1 (raw intensity), cost >> 2
-                    a = __vsub2(l1.x, v1b);
+                    a = __vadd2(l1.x, v1b);
                     c0 = __viaddmax_s16x2_relu(v0b, l1.y, a);
-                    bb = __vsub2(l1.w, nvb);
+                    bb = __vadd2(~nvb, l1.w);
                     c1 = __viaddmax_s16x2_relu(l1.z, nvb, bb);
                     pix += (__vminu2(c0, c1) >> 2) & 0x3fff3fffu;
                     pb[c * VW + 32 * k + lane] = pix;

@@ -43,7 +43,7 @@
 #define SW_ROWS4 18
 #endif
 // rows (= warps) per band
-__host__ __device__ constexpr int sw_rows(int NP) { return NP <= 4 ? SW_ROWS4 : (NP <= 5 ? 16 : 8); }
+__host__ __device__ constexpr int sw_rows(int NP) { return NP <= 2 ? 24 : (NP == 3 ? 22 : (NP == 4 ? SW_ROWS4 : (NP == 5 ? 16 : 8))); }
 #ifndef SW_EXPERIMENT
 #define SW_EXPERIMENT 0        // timing experiments only (results are wrong): 3 = no C/S1 loads, 4 = no S1 stores, 5 = both, 6 = no row hand-off waits
 #endif
@@ -197,6 +197,12 @@ __device__ __forceinline__ void vec_ld(const uint32_t* p, int lane, uint32_t (&v
             uint4 t = ld4(reinterpret_cast<const uint4*>(w) + i);
             v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
         }
+    } else if constexpr (NP % 2 == 0) {
+#pragma unroll
+        for (int i = 0; i < NP / 2; ++i) {
+            uint2 t = ld4(reinterpret_cast<const uint2*>(w) + i);
+            v[2 * i] = t.x; v[2 * i + 1] = t.y;
+        }
     } else {
 #pragma unroll
         for (int i = 0; i < NP; ++i) v[i] = ld4(w + i);
@@ -204,14 +210,17 @@ __device__ __forceinline__ void vec_ld(const uint32_t* p, int lane, uint32_t (&v
 }
 struct LdPlain {
     __device__ __forceinline__ uint4 operator()(const uint4* p) const { return *p; }
+    __device__ __forceinline__ uint2 operator()(const uint2* p) const { return *p; }
     __device__ __forceinline__ uint32_t operator()(const uint32_t* p) const { return *p; }
 };
 struct LdNc {     // read-only data written by an earlier kernel
     __device__ __forceinline__ uint4 operator()(const uint4* p) const { return __ldg(p); }
+    __device__ __forceinline__ uint2 operator()(const uint2* p) const { return __ldg(p); }
     __device__ __forceinline__ uint32_t operator()(const uint32_t* p) const { return __ldg(p); }
 };
 struct LdCg {     // data written by another CTA of this kernel: bypass L1
     __device__ __forceinline__ uint4 operator()(const uint4* p) const { return __ldcg(p); }
+    __device__ __forceinline__ uint2 operator()(const uint2* p) const { return __ldcg(p); }
     __device__ __forceinline__ uint32_t operator()(const uint32_t* p) const { return __ldcg(p); }
 };
 template <int NP>
@@ -222,6 +231,9 @@ __device__ __forceinline__ void vec_st(uint32_t* p, int lane, const uint32_t (&v
 #pragma unroll
         for (int i = 0; i < NP / 4; ++i)
             reinterpret_cast<uint4*>(w)[i] = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    } else if constexpr (NP % 2 == 0) {
+#pragma unroll
+        for (int i = 0; i < NP / 2; ++i) reinterpret_cast<uint2*>(w)[i] = make_uint2(v[2 * i], v[2 * i + 1]);
     } else {
 #pragma unroll
         for (int i = 0; i < NP; ++i) w[i] = v[i];
@@ -507,6 +519,10 @@ __device__ __forceinline__ void cp_async_vec_s(uint32_t sdst, const uint32_t* gs
 #pragma unroll
         for (int i = 0; i < NP / 4; ++i)
             asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst + 16 * i), "l"(gsrc + 4 * i));
+    } else if constexpr (NP % 2 == 0) {
+#pragma unroll
+        for (int i = 0; i < NP / 2; ++i)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sdst + 8 * i), "l"(gsrc + 2 * i));
     } else {
 #pragma unroll
         for (int i = 0; i < NP; ++i)

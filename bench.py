@@ -46,6 +46,21 @@ def b_alg_bytes(wl):
     return 4 * wl["W"] * wl["H"] + 4 * wl["W"] * wl["H"] * wl["D"]
 
 
+# DRAM bytes per pair and launch (dram__bytes_read.sum + dram__bytes_write.sum) from the committed
+# ncu --set full capture profiles/r01_v4_ncu_top3_summary_b8.txt (8 pairs per launch).
+NCU_TRAFFIC_PER_PAIR = {
+    "sgbm_1080p_d256_hh": {"k_cost": (0.871314 + 7.301723) / 8 * 1e9,
+                           "k_sweep<first>": (7.457215 + 8.518117) / 8 * 1e9,
+                           "k_sweep<last+wta>": (14.904629 + 1.291582) / 8 * 1e9},
+}
+
+
+def kernel_alg_bytes(wl, name):
+    """Algorithmic bytes per pair of one kernel: volumes it must read / write once."""
+    n2 = 2 * wl["W"] * wl["H"] * wl["D"]            # one int16 volume (upper bound: full width)
+    return {"k_cost": n2, "k_sweep<first>": 2 * n2, "k_sweep<last+wta>": 2 * n2}.get(name)
+
+
 def make_inputs(wl, B, seed0):
     """Synthetic pairs: a few distinct seeded scenes, tiled to the batch (generation is slow)."""
     from stereovision_b200.synth import make_pair
@@ -273,8 +288,14 @@ def main():
             dms, dl = stages[dom]
             # the hot path as one unit: B_alg x pairs over the summed device time of its kernels
             ach = balg * B * args.steps / (sgbm_ms / 1e3) / 1e9
+            tr = NCU_TRAFFIC_PER_PAIR.get(args.workload, {}).get(dom)
+            kalg = kernel_alg_bytes(wl, dom)
             roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                    "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                    "traffic": tr * B if tr else None,
+                    "traffic_source": "ncu dram bytes of the dominant kernel per launch (profiles/r01_v4_ncu_top3_summary_b8.txt, scaled to this batch)" if tr else None,
+                    "dominant_kernel_alg_bytes_per_launch": kalg * B if kalg else None,
+                    "dominant_kernel_achieved": (kalg * B / (dms / max(dl, 1) / 1e3) / 1e9) if kalg else None,
+                    "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                     "kernel": "sgbm chain (all stages)", "dominant_kernel": dom,
                     "dominant_share": dms / sgbm_ms if sgbm_ms else None,
                     "dominant_ms_per_launch": dms / max(dl, 1),

@@ -47,6 +47,14 @@ __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 2 ? 24 : (NP ==
 #ifndef SW_EXPERIMENT
 #define SW_EXPERIMENT 0        // timing experiments only (results are wrong): 3 = no C/S1 loads, 4 = no S1 stores, 5 = both, 6 = no row hand-off waits
 #endif
+#ifndef SW_PLAIN_FLAG
+// 1: a row publishes its progress counter with a plain volatile shared store after __syncwarp() instead of
+// st.release.cta.  The data it guards are shared-memory stores of the same warp, issued earlier in program
+// order; an SM performs a warp's shared-memory instructions in issue order, and the reader uses ld.acquire.
+// The release fence also waited for the row's outstanding cp.async / global stores (15.3 -> 14.4 ms per 32
+// pairs in the first sweep).  0 restores the fence.
+#define SW_PLAIN_FLAG 1
+#endif
 #ifndef SW_FMA_ADDS
 #define SW_FMA_ADDS 1          // P1 and sum additions of the recurrence as IMADs (FMA pipe) instead of ALU-pipe adds
 #endif
@@ -916,7 +924,11 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                 }
             }
             if (VERT || LAST) __syncwarp();
+#if SW_PLAIN_FLAG
+            if (VERT && lane == 0) asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(&s_done[warp])), "r"(i + 1) : "memory");
+#else
             if (VERT && lane == 0) sts_release_cta(&s_done[warp], i + 1);
+#endif
             // (after the publication: its fence then has no global store of this column to wait for)
             if (!LAST && SW_EXPERIMENT != 4 && SW_EXPERIMENT != 5) vec_st<NP>(pS - NP * lane, lane, S);
             gC += cstep; gS += cstep; pS += cstep;

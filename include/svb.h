@@ -124,6 +124,14 @@ int svb_disp_to_depth_dev(const int16_t* disp16_dev, int B, int H, int W, double
 int svb_reproject3d_dev(const void* disp_dev, int is_s16, int B, int H, int W, const double* Q_host16,
                         int handleMissingValues, float* minscratch_dev, float* out_dev, void* stream);
 
+/* ---- cv2.initUndistortRectifyMap(K, dist, R, P, size, CV_16SC2) (depth_map.py:633-638,
+ *      fused_depth_map.py:404-409).  Host pointers to row-major doubles: K9 3x3, dist ndist
+ *      (0, 4, 5, 8, 12 or 14 with zero tilt) coefficients, R9 3x3 or NULL (identity), P 3 x pcols
+ *      (pcols 3 or 4: cv2 uses its left 3x3 block).  Device outputs: map1 s16 [H,W,2], map2 u16 [H,W]. */
+int svb_init_undistort_rectify_map_dev(const double* K9, const double* dist, int ndist, const double* R9,
+                                       const double* P, int pcols, int W, int H, int16_t* map1_dev,
+                                       uint16_t* map2_dev, void* stream);
+
 /* ==== Fusion chain of fused_depth_map.py.  All maps are f32 [B,H,W] on the
  *      device; no call synchronises the stream.  Scratch is caller-owned (sizes from the *_scratch_bytes
  *      functions). */

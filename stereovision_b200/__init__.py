@@ -10,6 +10,7 @@ from .cv_api import (  # noqa: F401
     INTER_LINEAR, COLOR_BGR2GRAY,
     StereoSGBM, StereoBM, StereoSGBM_create, StereoBM_create,
     remap, cvtColor, medianBlur, filterSpeckles, reprojectImageTo3D, disparity_to_depth,
+    initUndistortRectifyMap, CV_16SC2,
     release_workspaces,
 )
 

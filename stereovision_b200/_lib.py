@@ -66,6 +66,9 @@ SIGNATURES = {
                                       c_double, c_void_p, c_void_p, c_void_p]),
     "svb_reproject3d_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, ctypes.POINTER(c_double), c_int,
                                     c_void_p, c_void_p, c_void_p]),
+    "svb_init_undistort_rectify_map_dev": (c_int, [ctypes.POINTER(c_double), ctypes.POINTER(c_double), c_int,
+                                                   ctypes.POINTER(c_double), ctypes.POINTER(c_double), c_int, c_int,
+                                                   c_int, c_void_p, c_void_p, c_void_p]),
     "svb_normalize_disparity_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "svb_range_scratch_bytes": (c_size_t, [c_int]),
     "svb_calibrate_midas_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p,

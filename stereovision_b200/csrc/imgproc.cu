@@ -416,3 +416,97 @@ extern "C" int svb_reproject3d_dev(const void* disp, int is_s16, int B, int H, i
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// cv2.initUndistortRectifyMap(K, dist, R, P, size, CV_16SC2)  (depth_map.py:633-638,
+// fused_depth_map.py:404-409).  One thread per destination pixel, float64 like
+// OpenCV: back-project through ir = inv(P[:, :3] * R) (inverted on the host), rational +
+// tangential + thin-prism distortion, project with K, then the fixed-point form cv2.remap
+// consumes: map1 = (iu >> 5, iv >> 5) as s16, map2 = (iv & 31) * 32 + (iu & 31).
+// ------------------------------------------------------------------------------------------
+struct MapArgs {
+    double ir[9];
+    double k[12];             // k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4
+    double fx, fy, u0, v0;
+};
+
+__device__ __forceinline__ int cv_round_sat(double v)
+{
+    // cvRound = round half to even (lrint); saturate_cast<int>
+    if (!(v > -2147483648.0)) return INT_MIN;
+    if (v >= 2147483647.0) return INT_MAX;
+    return __double2int_rn(v);
+}
+
+__global__ void __launch_bounds__(256) k_init_undistort_rectify_map(MapArgs a, int H, int W, short2* __restrict__ map1,
+                                                                     unsigned short* __restrict__ map2)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= W) return;
+    // explicit _rn operations: no FMA contraction, the same roundings as the scalar C++ expression
+    const double _x = __dadd_rn(__dmul_rn((double)j, a.ir[0]), __dadd_rn(__dmul_rn((double)i, a.ir[1]), a.ir[2]));
+    const double _y = __dadd_rn(__dmul_rn((double)j, a.ir[3]), __dadd_rn(__dmul_rn((double)i, a.ir[4]), a.ir[5]));
+    const double _w = __dadd_rn(__dmul_rn((double)j, a.ir[6]), __dadd_rn(__dmul_rn((double)i, a.ir[7]), a.ir[8]));
+    const double w = __ddiv_rn(1.0, _w);
+    const double x = __dmul_rn(_x, w), y = __dmul_rn(_y, w);
+    const double x2 = __dmul_rn(x, x), y2 = __dmul_rn(y, y);
+    const double r2 = __dadd_rn(x2, y2), _2xy = __dmul_rn(__dmul_rn(2.0, x), y);
+    const double k1 = a.k[0], k2 = a.k[1], p1 = a.k[2], p2 = a.k[3], k3 = a.k[4], k4 = a.k[5], k5 = a.k[6], k6 = a.k[7];
+    const double s1 = a.k[8], s2 = a.k[9], s3 = a.k[10], s4 = a.k[11];
+    const double num = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(k3, r2), k2), r2), k1), r2));
+    const double den = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(k6, r2), k5), r2), k4), r2));
+    const double kr = __ddiv_rn(num, den);
+    const double r4 = __dmul_rn(r2, r2);
+    double xd = __dadd_rn(__dmul_rn(x, kr), __dmul_rn(p1, _2xy));
+    xd = __dadd_rn(xd, __dmul_rn(p2, __dadd_rn(r2, __dmul_rn(2.0, x2))));
+    xd = __dadd_rn(__dadd_rn(xd, __dmul_rn(s1, r2)), __dmul_rn(s2, r4));
+    double yd = __dadd_rn(__dmul_rn(y, kr), __dmul_rn(p1, __dadd_rn(r2, __dmul_rn(2.0, y2))));
+    yd = __dadd_rn(yd, __dmul_rn(p2, _2xy));
+    yd = __dadd_rn(__dadd_rn(yd, __dmul_rn(s3, r2)), __dmul_rn(s4, r4));
+    const double u = __dadd_rn(__dmul_rn(a.fx, xd), a.u0), v = __dadd_rn(__dmul_rn(a.fy, yd), a.v0);
+    const int iu = cv_round_sat(__dmul_rn(u, 32.0)), iv = cv_round_sat(__dmul_rn(v, 32.0));
+    const size_t o = (size_t)i * W + j;
+    map1[o] = make_short2((short)(iu >> 5), (short)(iv >> 5));
+    map2[o] = (unsigned short)((iv & 31) * 32 + (iu & 31));
+}
+
+extern "C" int svb_init_undistort_rectify_map_dev(const double* K9, const double* dist, int ndist, const double* R9,
+                                                  const double* P, int pcols, int W, int H, int16_t* map1_dev,
+                                                  uint16_t* map2_dev, void* stream)
+{
+    if (!K9 || !P || !map1_dev || !map2_dev || W < 1 || H < 1 || (pcols != 3 && pcols != 4) || ndist < 0 ||
+        (ndist && !dist)) {
+        svb_set_error("svb_init_undistort_rectify_map_dev: bad argument");
+        return SVB_ERR_PARAM;
+    }
+    if (ndist != 0 && ndist != 4 && ndist != 5 && ndist != 8 && ndist != 12 && ndist != 14) {
+        svb_set_error("distCoeffs must have 4, 5, 8, 12 or 14 elements (got %d)", ndist);   // cv2's own check
+        return SVB_ERR_PARAM;
+    }
+    if (ndist == 14 && (dist[12] != 0.0 || dist[13] != 0.0)) {
+        svb_set_error("tilted sensor model (tauX, tauY) is not implemented");
+        return SVB_ERR_UNSUPPORTED;
+    }
+    MapArgs a;
+    for (int q = 0; q < 12; ++q) a.k[q] = q < ndist ? dist[q] : 0.0;
+    a.fx = K9[0]; a.fy = K9[4]; a.u0 = K9[2]; a.v0 = K9[5];
+    // M = P[:, :3] * R, ir = M^-1 (adjugate / determinant in double)
+    double M[9];
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) {
+            double s = 0;
+            for (int q = 0; q < 3; ++q) s += P[r * pcols + q] * (R9 ? R9[q * 3 + c] : (q == c ? 1.0 : 0.0));
+            M[r * 3 + c] = s;
+        }
+    const double det = M[0] * (M[4] * M[8] - M[5] * M[7]) - M[1] * (M[3] * M[8] - M[5] * M[6]) +
+                       M[2] * (M[3] * M[7] - M[4] * M[6]);
+    if (det == 0.0) { svb_set_error("newCameraMatrix * R is singular"); return SVB_ERR_PARAM; }
+    const double id = 1.0 / det;
+    a.ir[0] = (M[4] * M[8] - M[5] * M[7]) * id; a.ir[1] = (M[2] * M[7] - M[1] * M[8]) * id; a.ir[2] = (M[1] * M[5] - M[2] * M[4]) * id;
+    a.ir[3] = (M[5] * M[6] - M[3] * M[8]) * id; a.ir[4] = (M[0] * M[8] - M[2] * M[6]) * id; a.ir[5] = (M[2] * M[3] - M[0] * M[5]) * id;
+    a.ir[6] = (M[3] * M[7] - M[4] * M[6]) * id; a.ir[7] = (M[1] * M[6] - M[0] * M[7]) * id; a.ir[8] = (M[0] * M[4] - M[1] * M[3]) * id;
+    k_init_undistort_rectify_map<<<dim3(svb_ceil_div(W, 256), H), 256, 0, (cudaStream_t)stream>>>(
+        a, H, W, (short2*)map1_dev, map2_dev);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}

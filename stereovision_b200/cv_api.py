@@ -382,3 +382,39 @@ def disparity_to_depth(disp16, fx=700.0, baseline=0.08, min_disp=0.0, min_depth=
                                                 float(min_depth), float(max_depth), disparity.data_ptr(),
                                                 depth.data_ptr(), _stream_ptr()))
     return _ret(depth, was), _ret(disparity, was)
+
+
+CV_16SC2 = 11
+
+
+def initUndistortRectifyMap(cameraMatrix, distCoeffs, R, newCameraMatrix, size, m1type=CV_16SC2, device=None,
+                            as_tensor=False):
+    """cv2.initUndistortRectifyMap(K, dist, R, P, (W, H), cv2.CV_16SC2) -> (map1 s16 [H,W,2], map2 u16 [H,W])
+    (depth_map.py:633-638, fused_depth_map.py:404-409).  Computed on the device in float64 like OpenCV;
+    as_tensor=True leaves the maps on the device for svb.remap."""
+    if m1type != CV_16SC2:
+        raise NotImplementedError("only CV_16SC2 maps are on the reference's path")
+    torch = _torch()
+    K = np.ascontiguousarray(cameraMatrix, dtype=np.float64)
+    P = np.ascontiguousarray(newCameraMatrix, dtype=np.float64)
+    if K.shape != (3, 3) or P.ndim != 2 or P.shape[0] != 3 or P.shape[1] not in (3, 4):
+        raise ValueError("cameraMatrix must be 3x3 and newCameraMatrix 3x3 or 3x4")
+    D = None if distCoeffs is None else np.ascontiguousarray(distCoeffs, dtype=np.float64).ravel()
+    Rm = None if R is None else np.ascontiguousarray(R, dtype=np.float64)
+    if Rm is not None and Rm.shape != (3, 3):
+        raise ValueError("R must be 3x3")
+    W, H = int(size[0]), int(size[1])
+    if not torch.cuda.is_available():
+        raise _lib.SvbError("no CUDA device available; stereovision_b200 has no CPU fallback")
+    dev = _ensure_device(device)
+    tdev = torch.device("cuda", dev)
+    m1 = torch.empty((H, W, 2), dtype=torch.int16, device=tdev)
+    m2 = torch.empty((H, W), dtype=torch.uint16, device=tdev)
+    dp = ctypes.POINTER(ctypes.c_double)
+    _lib.check(_lib.lib().svb_init_undistort_rectify_map_dev(
+        K.ctypes.data_as(dp), D.ctypes.data_as(dp) if D is not None and D.size else None, 0 if D is None else int(D.size),
+        Rm.ctypes.data_as(dp) if Rm is not None else None, P.ctypes.data_as(dp), int(P.shape[1]), W, H,
+        m1.data_ptr(), m2.data_ptr(), _stream_ptr()))
+    if as_tensor:
+        return m1, m2
+    return m1.cpu().numpy(), m2.cpu().numpy()

@@ -54,6 +54,22 @@ def main():
     out["Q2"] = Q
     out["reproj_s16"] = cv2.reprojectImageTo3D(d16, Q)
     out["reproj_f32"] = cv2.reprojectImageTo3D(f, Q, handleMissingValues=True)
+    # initUndistortRectifyMap (depth_map.py:633-638): the reference's own recipe on the synthetic calibration,
+    # plus the 8- and 12-coefficient distortion models
+    Wm, Hm = 200, 140
+    cal = synth_calibration(Wm, Hm)
+    R1, R2, P1, P2, _, _, _ = cv2.stereoRectify(cal["mtx_left"], cal["dist_left"], cal["mtx_right"], cal["dist_right"],
+                                                (Wm, Hm), cal["R"], cal["T"], alpha=0)
+    d8 = np.array([-0.3, 0.1, 2e-3, -1e-3, 0.02, 0.01, -0.02, 0.005])
+    d12 = np.concatenate([d8, [1e-3, -2e-3, 5e-4, 1e-4]])
+    out["maps_K"], out["maps_R1"], out["maps_P1"], out["maps_R2"], out["maps_P2"] = cal["mtx_left"], R1, P1, R2, P2
+    for tag, (K, D, R, P) in {"l5": (cal["mtx_left"], cal["dist_left"], R1, P1),
+                              "r5": (cal["mtx_right"], cal["dist_right"], R2, P2),
+                              "l8": (cal["mtx_left"], d8, R1, P1), "l12": (cal["mtx_left"], d12, R1, P1),
+                              "l0": (cal["mtx_left"], None, None, cal["mtx_left"])}.items():
+        m1, m2 = cv2.initUndistortRectifyMap(K, D, R, P, (Wm, Hm), cv2.CV_16SC2)
+        out[f"maps_{tag}_m1"], out[f"maps_{tag}_m2"] = m1, m2
+        out[f"maps_{tag}_dist"] = np.zeros(0) if D is None else np.asarray(D, np.float64)
     np.savez_compressed(os.path.join(HERE, "golden.npz"), **out)
     print("wrote", os.path.join(HERE, "golden.npz"), os.path.getsize(os.path.join(HERE, "golden.npz")), "bytes")
 

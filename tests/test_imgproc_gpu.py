@@ -78,3 +78,37 @@ def test_depth_tail_matches_numpy_restatement(golden):
     ref = np.where(valid, zc, 0)
     assert ref.dtype == np.float32
     np.testing.assert_allclose(depth, ref, rtol=1e-6, atol=0)
+
+
+@pytest.mark.parametrize("tag", ["l5", "r5", "l8", "l12", "l0"])
+def test_init_undistort_rectify_map_bit_exact(golden, tag):
+    """cv2.initUndistortRectifyMap(..., CV_16SC2) on the device: 5-, 8-, 12-coefficient models,
+    no distortion / no rotation; and the maps feed svb.remap without leaving the device."""
+    from oracle.maps import init_undistort_rectify_map
+    from tests.test_oracle_golden import map_case
+    K, dist, R, P, size = map_case(golden, tag)
+    m1, m2 = svb.initUndistortRectifyMap(K, dist, R, P, size, svb.CV_16SC2)
+    assert m1.dtype == np.int16 and m1.shape == (size[1], size[0], 2) and m2.dtype == np.uint16
+    assert np.array_equal(m1, golden[f"maps_{tag}_m1"]) and np.array_equal(m2, golden[f"maps_{tag}_m2"])
+    o1, o2 = init_undistort_rectify_map(K, dist, R, P, size)
+    assert np.array_equal(m1, o1) and np.array_equal(m2, o2)
+    t1, t2 = svb.initUndistortRectifyMap(K, dist, R, P, size, as_tensor=True)
+    l, _, _ = make_pair(size[1], size[0], 16, seed=9)
+    assert np.array_equal(svb.remap(to_bgr(l), t1, t2, svb.INTER_LINEAR), oracle.remap(to_bgr(l), m1, m2))
+
+
+def test_init_undistort_rectify_map_full_size_and_errors(golden):
+    from oracle.maps import init_undistort_rectify_map
+    K, dist, R, P, _ = None, None, None, None, None
+    from tests.test_oracle_golden import map_case
+    K, dist, R, P, _ = map_case(golden, "l5")
+    s = 1920 / 200.0
+    Kb = K.copy(); Kb[:2] *= s
+    Pb = P.copy(); Pb[:2] *= s
+    m1, m2 = svb.initUndistortRectifyMap(Kb, dist, R, Pb, (1920, 1344))
+    o1, o2 = init_undistort_rectify_map(Kb, dist, R, Pb, (1920, 1344))
+    assert np.array_equal(m1, o1) and np.array_equal(m2, o2)
+    with pytest.raises(ValueError):
+        svb.initUndistortRectifyMap(K, np.zeros(6), R, P, (64, 48))          # cv2 rejects 6 coefficients too
+    with pytest.raises(NotImplementedError):
+        svb.initUndistortRectifyMap(K, np.r_[np.zeros(12), 0.01, 0.0], R, P, (64, 48))

@@ -79,3 +79,23 @@ def test_bm_oracle_matches_golden(golden):
         l, r, _ = make_pair(c["H"], c["W"], max(c["numDisparities"], 16), seed=c["seed"])
         got = oracle.bm_compute(l, r, **_bm_kwargs(c))
         assert np.array_equal(got, golden[f"bm_{i}"]), i
+
+
+MAP_TAGS = {"l5": ("maps_R1", "maps_P1"), "r5": ("maps_R2", "maps_P2"), "l8": ("maps_R1", "maps_P1"),
+            "l12": ("maps_R1", "maps_P1"), "l0": (None, "maps_K")}
+
+
+def map_case(golden, tag):
+    """(K, dist, R, P, size) of a golden initUndistortRectifyMap case; K of the right camera equals the left one
+    in the synthetic calibration (tests/golden_cases.synth_calibration)."""
+    rk, pk = MAP_TAGS[tag]
+    dist = golden[f"maps_{tag}_dist"]
+    return (golden["maps_K"], dist if dist.size else None, None if rk is None else golden[rk], golden[pk], (200, 140))
+
+
+@pytest.mark.parametrize("tag", sorted(MAP_TAGS))
+def test_undistort_rectify_map_oracle_matches_golden(golden, tag):
+    from oracle.maps import init_undistort_rectify_map
+    m1, m2 = init_undistort_rectify_map(*map_case(golden, tag))
+    assert m1.dtype == np.int16 and m2.dtype == np.uint16
+    assert np.array_equal(m1, golden[f"maps_{tag}_m1"]) and np.array_equal(m2, golden[f"maps_{tag}_m2"])

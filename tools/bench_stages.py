@@ -61,7 +61,10 @@ def main():
         f_ = svb.normalize_to_stereo_range(flow_d, dispf)
         return svb.fuse_depth_maps(n_, c_, m_, None, f_, True)
 
+    Kc = np.array([[0.78 * W, 0, W / 2 + 3], [0, 0.78 * W, H / 2 - 2], [0, 0, 1]], np.float64)
+    dc = np.array([-0.10, 0.02, 1e-3, -1e-3, 0], np.float64)
     rows = [
+        ("initUndistortRectifyMap (N1, per map pair)", lambda: svb.initUndistortRectifyMap(Kc, dc, None, Kc, (W, H), as_tensor=True), 6 * px / B),
         ("remap BGR + gray (a1,a2)", lambda: svb.remap(bgr, m1, m2, svb.INTER_LINEAR, to_gray=True), (3 + 1) * px),
         ("remap BGR (a1)", lambda: svb.remap(bgr, m1, m2, svb.INTER_LINEAR), 6 * px),
         ("s16->f32 + median5 + depth (a10,a11)", lambda: svb.disparity_to_depth(disp16), 10 * px),

@@ -191,6 +191,11 @@ def main():
         run_reference_arm(args, wl, rank, world)
         return
 
+    # Libraries (NCCL's version banner) write to fd 1; the contract is ONE JSON line on stdout, so
+    # everything before that line goes to stderr.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     if not torch.cuda.is_available():
@@ -309,9 +314,9 @@ def main():
             "config": {"workload": args.workload, "H": H, "W": W, "numDisparities": D, "mode": wl["mode"],
                        "blockSize": 5, "pairs_per_gpu_per_step": B, "l2_policy": "inputs+volumes >> L2 (126 MB)",
                        "gdisp_evals_per_s": value * H * W * D / 1e9},
-            "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": 2 * B * H * W,
-                    "d2h_bytes_per_step": 2 * B * H * W},
-            "gpu_launches": launches,
+            "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": 2 * B * H * W * world,
+                    "d2h_bytes_per_step": 2 * B * H * W * world},
+            "gpu_launches": launches * world,
             "clocks": sampler.summary(),
             "roofline": roof,
         }
@@ -320,6 +325,8 @@ def main():
             dt, kind, used = cpu_reference_run(wl, cores, cores)
             line["cpu_baseline"] = {"value": cores / dt, "unit": "pairs/s", "cores": used, "kind": kind,
                                     "sample": f"{cores} distinct pairs once, one pair per thread (cv2.setNumThreads(1))"}
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
         print(json.dumps(line), flush=True)
     L.svb_sgbm_destroy(h)
     if world > 1:

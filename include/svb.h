@@ -180,6 +180,36 @@ size_t svb_occlusion_scratch_bytes(int B, int H, int W, int block);
 int svb_occlusion_stats_u8_dev(const uint8_t* gray_dev, int B, int H, int W, int block, double* stats_dev,
                                void* scratch_dev, size_t scratch_bytes, void* stream);
 
+/* ==== SURVEY 8(f) N3: the data-parallel code around the mono estimators of fused_depth_map.py.
+ *      Maps are [B,H,W] on the device; scratch from the *_scratch_bytes functions; nothing synchronises. */
+
+/* cv2.bilateralFilter(src f32, d, sigmaColor, sigmaSpace), BORDER_REFLECT_101 (fused_depth_map.py:1400,
+ * 1409, 1690); d odd, <= 15. */
+size_t svb_bilateral_scratch_bytes(int B);
+int svb_bilateral_f32_dev(const float* src_dev, int B, int H, int W, int d, double sigma_color,
+                          double sigma_space, float* dst_dev, void* scratch_dev, size_t scratch_bytes,
+                          void* stream);
+
+/* MiDaS post-processing, fused_depth_map.py:1134-1145: torch.nn.functional.interpolate(pred [B,Hi,Wi],
+ * size=(Ho,Wo), mode="bicubic", align_corners=False), then (x - min) / (max - min + 1e-8) * 255 per image
+ * (zeros when max - min < 1e-6). */
+size_t svb_midas_scratch_bytes(int B);
+int svb_midas_upsample_normalize_dev(const float* pred_dev, int B, int Hi, int Wi, float* out_dev, int Ho,
+                                     int Wo, void* scratch_dev, size_t scratch_bytes, void* stream);
+
+/* Contrast confidence, fused_depth_map.py:1150-1156: cv2.normalize(cv2.absdiff(gray, cv2.GaussianBlur(gray,
+ * (5,5), 0)), None, 0, 1, cv2.NORM_MINMAX) on u8 gray [B,H,W] -> u8.  Scratch: svb_midas_scratch_bytes. */
+int svb_contrast_confidence_u8_dev(const uint8_t* gray_dev, int B, int H, int W, uint8_t* conf_dev,
+                                   void* scratch_dev, size_t scratch_bytes, void* stream);
+
+/* Flow depth, fused_depth_map.py:1386-1398 + 1491-1497: expected flow = cv2.perspectiveTransform(pixel grid,
+ * H) - grid, residual = flow - expected, current = 1 / (hypot(residual) + 0.5); when stable_dev is given it
+ * becomes alpha * stable + (1 - alpha) * current (or a copy of current when stable_valid == 0).
+ * flow_dev f32 [B,H,W,2]; homography9 HOST doubles [B][9]. */
+int svb_flow_residual_depth_dev(const float* flow_dev, int B, int H, int W, const double* homography9,
+                                float* current_dev, float* stable_dev, int stable_valid, double alpha,
+                                void* stream);
+
 #ifdef __cplusplus
 }
 #endif

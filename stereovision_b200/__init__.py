@@ -19,4 +19,10 @@ from .fusion import (  # noqa: F401
     detect_camera_occlusion, occlusion_stats, percentiles,
 )
 
+from .mono import (  # noqa: F401
+    bilateralFilter, midas_postprocess, upsample_normalize, contrast_confidence, flow_residual_depth,
+)
+
+from ._lib import SvbError  # noqa: F401
+
 __version__ = "0.1.0"

@@ -83,6 +83,15 @@ SIGNATURES = {
     "svb_occlusion_scratch_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "svb_occlusion_stats_u8_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t,
                                            c_void_p]),
+    "svb_bilateral_scratch_bytes": (c_size_t, [c_int]),
+    "svb_bilateral_f32_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_double, c_double, c_void_p, c_void_p,
+                                      c_size_t, c_void_p]),
+    "svb_midas_scratch_bytes": (c_size_t, [c_int]),
+    "svb_midas_upsample_normalize_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p,
+                                                 c_size_t, c_void_p]),
+    "svb_contrast_confidence_u8_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "svb_flow_residual_depth_dev": (c_int, [c_void_p, c_int, c_int, c_int, ctypes.POINTER(c_double), c_void_p,
+                                            c_void_p, c_int, c_double, c_void_p]),
 }
 
 

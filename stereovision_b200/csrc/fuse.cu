@@ -521,12 +521,12 @@ __global__ void k_fuse_init(FuseState* fs, int B)
     if (b < B) { fs[b].kmin = 0xffffffffu; fs[b].kmax = 0; }
 }
 
-__global__ void k_bilat_lut(FuseState* __restrict__ fs, float gc)
+__global__ void k_bilat_lut(FuseState* __restrict__ fs, float gc, float min_max /* filter only when max > this */)
 {
     FuseState* s = fs + blockIdx.x;
     const float mn = key2f(s->kmin), mx = key2f(s->kmax);
     const float len = __fsub_rn(mx, mn);
-    const bool filter = mx > 10.0f && len > FLT_EPSILON;
+    const bool filter = mx > min_max && len > FLT_EPSILON;
     const float scale = filter ? __fdiv_rn((float)LUT_BINS, len) : 0.f;
     __syncthreads();
     if (threadIdx.x == 0) { s->filter = filter; s->scale = scale; }
@@ -543,7 +543,7 @@ __global__ void k_bilat_lut(FuseState* __restrict__ fs, float gc)
 #define BT_Y 8
 __global__ void __launch_bounds__(BT_X * BT_Y) k_bilateral(const float* __restrict__ fused, int H, int W, BilatTaps bt,
                                                           const FuseState* __restrict__ fs, unsigned char* __restrict__ out8,
-                                                          float* __restrict__ outf)
+                                                          float* __restrict__ outf, int clip255)
 {
     __shared__ float tile[BT_Y + FUSE_MAXD - 1][BT_X + FUSE_MAXD - 1];
     __shared__ float lut[LUT_BINS + 2];
@@ -586,9 +586,9 @@ __global__ void __launch_bounds__(BT_X * BT_Y) k_bilateral(const float* __restri
     } else {
         res = img[(size_t)y * W + x];
     }
-    res = fminf(fmaxf(res, 0.0f), 255.0f);
+    if (clip255) res = fminf(fmaxf(res, 0.0f), 255.0f);
     const size_t o = ((size_t)b * H + y) * W + x;
-    out8[o] = (unsigned char)(int)res;
+    if (out8) out8[o] = (unsigned char)(int)res;
     if (outf) outf[o] = res;
 }
 
@@ -664,9 +664,9 @@ extern "C" int svb_fuse_depth_maps_dev(const float* stereo_dev, const float* con
         else SVB_CUDA(cudaMemsetAsync(tmp, 0, n * sizeof(float), s));      // conf == 1 everywhere -> weight 0
     }
     k_blend<<<grid, 128, 0, s>>>(a, H, W, g, fused, fs);
-    k_bilat_lut<<<B, 256, 0, s>>>(fs, bt.gc);
+    k_bilat_lut<<<B, 256, 0, s>>>(fs, bt.gc, 10.0f);
     dim3 bgrid(svb_ceil_div(W, BT_X), svb_ceil_div(H, BT_Y), B);
-    k_bilateral<<<bgrid, dim3(BT_X, BT_Y), 0, s>>>(fused, H, W, bt, fs, out_u8_dev, out_f32_dev);
+    k_bilateral<<<bgrid, dim3(BT_X, BT_Y), 0, s>>>(fused, H, W, bt, fs, out_u8_dev, out_f32_dev, 1);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
@@ -789,6 +789,282 @@ extern "C" int svb_occlusion_stats_u8_dev(const uint8_t* gray_dev, int B, int H,
     const int nb = (int)min((size_t)svb_ceil_div(148 * 8, B), (n + 4095) / 4096);
     k_occ_hist<<<dim3(max(nb, 1), B), 256, 0, s>>>(gray_dev, n, hist);
     k_occ_final<<<B, 256, 0, s>>>(stds, bh * bw, hist, (double)n, stats_dev);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// the data-parallel parts around the mono estimators.
+//   MiDaS post-processing (fused_depth_map.py:1126-1158): bicubic upsample of the network output
+//   (torch.nn.functional.interpolate, mode="bicubic", align_corners=False), min-max normalisation to
+//   0..255, contrast confidence = cv2.normalize(absdiff(gray, GaussianBlur(gray, 5x5)), 0, 1, MINMAX)
+//   flow depth (fused_depth_map.py:1386-1403, 1492-1498): expected flow of the ego-motion homography,
+//   residual magnitude, 1 / (r + 0.5), exponential average, bilateral 9/75/75
+// ------------------------------------------------------------------------------------------
+static void make_bilat_taps(BilatTaps& bt, int d, double sigma_color, double sigma_space)
+{
+    bt.d = d;
+    const double sc = sigma_color > 0 ? sigma_color : 1.0, ss = sigma_space > 0 ? sigma_space : 1.0;
+    bt.gc = (float)(-0.5 / (sc * sc));
+    const double gs = -0.5 / (ss * ss);
+    const int r = d / 2;
+    for (int i = -r; i <= r; ++i)
+        for (int j = -r; j <= r; ++j) {
+            const double rr = sqrt((double)i * i + (double)j * j);
+            bt.sw[(i + r) * d + (j + r)] = rr > r ? -1.f : (float)exp(rr * rr * gs);
+        }
+}
+
+__global__ void k_minmax_f32(const float* __restrict__ src, size_t n, FuseState* __restrict__ fs)
+{
+    const int b = blockIdx.y;
+    const float* p = src + (size_t)b * n;
+    unsigned kmin = 0xffffffffu, kmax = 0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const unsigned k = f2key(p[i]);
+        kmin = min(kmin, k);
+        kmax = max(kmax, k);
+    }
+    kmin = __reduce_min_sync(0xffffffffu, kmin);
+    kmax = __reduce_max_sync(0xffffffffu, kmax);
+    if ((threadIdx.x & 31) == 0) {
+        if (kmin != 0xffffffffu) atomicMin(&fs[b].kmin, kmin);
+        if (kmax) atomicMax(&fs[b].kmax, kmax);
+    }
+}
+
+extern "C" size_t svb_bilateral_scratch_bytes(int B) { return (size_t)B * sizeof(FuseState) + 256; }
+
+/* cv2.bilateralFilter(src f32, d, sigmaColor, sigmaSpace) (fused_depth_map.py:1400, 1690) */
+extern "C" int svb_bilateral_f32_dev(const float* src_dev, int B, int H, int W, int d, double sigma_color,
+                                     double sigma_space, float* dst_dev, void* scratch_dev, size_t scratch_bytes,
+                                     void* stream)
+{
+    if (!src_dev || !dst_dev || !scratch_dev || B < 1 || H < 1 || W < 1) {
+        svb_set_error("svb_bilateral_f32_dev: bad argument");
+        return SVB_ERR_PARAM;
+    }
+    if (d < 1 || d > FUSE_MAXD || !(d & 1)) {
+        svb_set_error("svb_bilateral_f32_dev: d must be odd and <= %d", FUSE_MAXD);
+        return SVB_ERR_UNSUPPORTED;
+    }
+    if (scratch_bytes < svb_bilateral_scratch_bytes(B)) { svb_set_error("svb_bilateral_f32_dev: scratch too small"); return SVB_ERR_PARAM; }
+    cudaStream_t s = (cudaStream_t)stream;
+    FuseState* fs = (FuseState*)(((uintptr_t)scratch_dev + 127) & ~(uintptr_t)127);
+    BilatTaps bt;
+    make_bilat_taps(bt, d, sigma_color, sigma_space);
+    const size_t n = (size_t)H * W;
+    k_fuse_init<<<svb_ceil_div(B, 128), 128, 0, s>>>(fs, B);
+    const int nb = (int)min((size_t)svb_ceil_div(148 * 8, B), (n + 1023) / 1024);
+    k_minmax_f32<<<dim3(max(nb, 1), B), 256, 0, s>>>(src_dev, n, fs);
+    k_bilat_lut<<<B, 256, 0, s>>>(fs, bt.gc, -FLT_MAX);
+    k_bilateral<<<dim3(svb_ceil_div(W, BT_X), svb_ceil_div(H, BT_Y), B), dim3(BT_X, BT_Y), 0, s>>>(
+        src_dev, H, W, bt, fs, nullptr, dst_dev, 0);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// torch's upsample_bicubic2d (A = -0.75, align_corners = False): source index (dst + 0.5) * scale - 0.5,
+// taps clamped to the image, x taps accumulated first, then y
+__device__ __forceinline__ void cubic_coeffs(float t, float (&w)[4])
+{
+    const float A = -0.75f;
+    float x = t + 1.0f;
+    w[0] = ((A * x - 5.0f * A) * x + 8.0f * A) * x - 4.0f * A;
+    w[1] = ((A + 2.0f) * t - (A + 3.0f)) * t * t + 1.0f;
+    x = 1.0f - t;
+    w[2] = ((A + 2.0f) * x - (A + 3.0f)) * x * x + 1.0f;
+    x = 2.0f - t;
+    w[3] = ((A * x - 5.0f * A) * x + 8.0f * A) * x - 4.0f * A;
+}
+
+__global__ void __launch_bounds__(256) k_resize_bicubic(const float* __restrict__ src, int Hi, int Wi, float* __restrict__ dst,
+                                                        int Ho, int Wo, float sy, float sx, FuseState* __restrict__ fs)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+    unsigned kmin = 0xffffffffu, kmax = 0;
+    if (x < Wo) {
+        const float fy = __fsub_rn(__fmul_rn((float)y + 0.5f, sy), 0.5f), fx = __fsub_rn(__fmul_rn((float)x + 0.5f, sx), 0.5f);
+        const float fly = floorf(fy), flx = floorf(fx);
+        const int iy = (int)fly, ix = (int)flx;
+        float wy[4], wx[4];
+        cubic_coeffs(fy - fly, wy);
+        cubic_coeffs(fx - flx, wx);
+        const float* img = src + (size_t)b * Hi * Wi;
+        float acc = 0.f;
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const float* row = img + (size_t)min(max(iy - 1 + a, 0), Hi - 1) * Wi;
+            float r = 0.f;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) r += row[min(max(ix - 1 + c, 0), Wi - 1)] * wx[c];
+            acc += r * wy[a];
+        }
+        dst[((size_t)b * Ho + y) * Wo + x] = acc;
+        kmin = kmax = f2key(acc);
+    }
+    if (fs) {
+        kmin = __reduce_min_sync(0xffffffffu, kmin);
+        kmax = __reduce_max_sync(0xffffffffu, kmax);
+        if ((threadIdx.x & 31) == 0) {
+            if (kmin != 0xffffffffu) atomicMin(&fs[b].kmin, kmin);
+            if (kmax) atomicMax(&fs[b].kmax, kmax);
+        }
+    }
+}
+
+// (x - min) / (max - min + 1e-8) * 255 in float32, zeros when max - min < 1e-6 (fused_depth_map.py:1138-1145)
+__global__ void k_minmax_scale255(float* __restrict__ data, size_t n, const FuseState* __restrict__ fs)
+{
+    const int b = blockIdx.y;
+    const float mn = key2f(fs[b].kmin), mx = key2f(fs[b].kmax);
+    const float len = __fsub_rn(mx, mn);
+    const bool flat = len < 1e-6f;
+    const float den = __fadd_rn(len, 1e-8f);
+    float* p = data + (size_t)b * n;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        p[i] = flat ? 0.0f : __fmul_rn(__fdiv_rn(__fsub_rn(p[i], mn), den), 255.0f);
+}
+
+extern "C" size_t svb_midas_scratch_bytes(int B) { return (size_t)B * sizeof(FuseState) + 256; }
+
+extern "C" int svb_midas_upsample_normalize_dev(const float* pred_dev, int B, int Hi, int Wi, float* out_dev, int Ho, int Wo,
+                                                void* scratch_dev, size_t scratch_bytes, void* stream)
+{
+    if (!pred_dev || !out_dev || !scratch_dev || B < 1 || Hi < 1 || Wi < 1 || Ho < 1 || Wo < 1) {
+        svb_set_error("svb_midas_upsample_normalize_dev: bad argument");
+        return SVB_ERR_PARAM;
+    }
+    if (scratch_bytes < svb_midas_scratch_bytes(B)) { svb_set_error("svb_midas_upsample_normalize_dev: scratch too small"); return SVB_ERR_PARAM; }
+    cudaStream_t s = (cudaStream_t)stream;
+    FuseState* fs = (FuseState*)(((uintptr_t)scratch_dev + 127) & ~(uintptr_t)127);
+    k_fuse_init<<<svb_ceil_div(B, 128), 128, 0, s>>>(fs, B);
+    k_resize_bicubic<<<dim3(svb_ceil_div(Wo, 256), Ho, B), 256, 0, s>>>(pred_dev, Hi, Wi, out_dev, Ho, Wo,
+                                                                        (float)Hi / (float)Ho, (float)Wi / (float)Wo, fs);
+    const size_t n = (size_t)Ho * Wo;
+    const int nb = (int)min((size_t)svb_ceil_div(148 * 8, B), (n + 1023) / 1024);
+    k_minmax_scale255<<<dim3(max(nb, 1), B), 256, 0, s>>>(out_dev, n, fs);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// contrast confidence (fused_depth_map.py:1150-1156): cv2.GaussianBlur(u8, 5x5, sigma 0) is the fixed-point
+// binomial filter (sum w_i w_j p + 128) >> 8 with w = {1,4,6,4,1} and BORDER_REFLECT_101
+constexpr int CC_X = 64, CC_Y = 8;
+__global__ void __launch_bounds__(CC_X* CC_Y) k_contrast_u8(const unsigned char* __restrict__ gray, int H, int W,
+                                                             unsigned char* __restrict__ contrast, FuseState* __restrict__ fs)
+{
+    __shared__ unsigned char tile[CC_Y + 4][CC_X + 4];
+    const int b = blockIdx.z, x0 = blockIdx.x * CC_X, y0 = blockIdx.y * CC_Y;
+    const unsigned char* img = gray + (size_t)b * H * W;
+    const int tid = threadIdx.y * CC_X + threadIdx.x;
+    for (int i = tid; i < (CC_Y + 4) * (CC_X + 4); i += CC_X * CC_Y) {
+        const int ty = i / (CC_X + 4), tx = i - ty * (CC_X + 4);
+        tile[ty][tx] = img[(size_t)reflect101(y0 + ty - 2, H) * W + reflect101(x0 + tx - 2, W)];
+    }
+    __syncthreads();
+    const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+    unsigned c = 0, cmin = 255, cmax = 0;
+    if (x < W && y < H) {
+        unsigned s = 0;
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            const unsigned char* t = &tile[threadIdx.y + i][threadIdx.x];
+            const unsigned r = t[0] + 4u * t[1] + 6u * t[2] + 4u * t[3] + t[4];
+            s += r * (i == 0 || i == 4 ? 1u : i == 2 ? 6u : 4u);
+        }
+        const int blur = (int)((s + 128u) >> 8), g = tile[threadIdx.y + 2][threadIdx.x + 2];
+        c = (unsigned)abs(g - blur);
+        contrast[((size_t)b * H + y) * W + x] = (unsigned char)c;
+        cmin = cmax = c;
+    }
+    cmin = __reduce_min_sync(0xffffffffu, cmin);
+    cmax = __reduce_max_sync(0xffffffffu, cmax);
+    if ((tid & 31) == 0) {
+        atomicMin(&fs[b].kmin, cmin);
+        atomicMax(&fs[b].kmax, cmax);
+    }
+}
+
+// cv2.normalize(c, None, 0, 1, NORM_MINMAX) on CV_8U: scale = 1 / (max - min) (0 for a flat image),
+// shift = -min * scale, result = saturate_u8(rint(c * scale + shift)) evaluated in float32
+__global__ void k_contrast_norm(unsigned char* __restrict__ data, size_t n, const FuseState* __restrict__ fs)
+{
+    const int b = blockIdx.y;
+    const int mn = (int)fs[b].kmin, mx = (int)fs[b].kmax;
+    const double scale = mx > mn ? 1.0 / (double)(mx - mn) : 0.0;
+    const float fsc = (float)scale, fsh = (float)(0.0 - (double)mn * scale);
+    __shared__ unsigned char lut[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x)
+        lut[i] = (unsigned char)min(max(__float2int_rn(__fadd_rn(__fmul_rn((float)i, fsc), fsh)), 0), 255);
+    __syncthreads();
+    unsigned char* p = data + (size_t)b * n;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = lut[p[i]];
+}
+
+extern "C" int svb_contrast_confidence_u8_dev(const uint8_t* gray_dev, int B, int H, int W, uint8_t* conf_dev, void* scratch_dev,
+                                              size_t scratch_bytes, void* stream)
+{
+    if (!gray_dev || !conf_dev || !scratch_dev || B < 1 || H < 1 || W < 1) {
+        svb_set_error("svb_contrast_confidence_u8_dev: bad argument");
+        return SVB_ERR_PARAM;
+    }
+    if (scratch_bytes < svb_midas_scratch_bytes(B)) { svb_set_error("svb_contrast_confidence_u8_dev: scratch too small"); return SVB_ERR_PARAM; }
+    cudaStream_t s = (cudaStream_t)stream;
+    FuseState* fs = (FuseState*)(((uintptr_t)scratch_dev + 127) & ~(uintptr_t)127);
+    k_fuse_init<<<svb_ceil_div(B, 128), 128, 0, s>>>(fs, B);
+    k_contrast_u8<<<dim3(svb_ceil_div(W, CC_X), svb_ceil_div(H, CC_Y), B), dim3(CC_X, CC_Y), 0, s>>>(gray_dev, H, W, conf_dev, fs);
+    const size_t n = (size_t)H * W;
+    const int nb = (int)min((size_t)svb_ceil_div(148 * 8, B), (n + 1023) / 1024);
+    k_contrast_norm<<<dim3(max(nb, 1), B), 256, 0, s>>>(conf_dev, n, fs);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// flow depth (fused_depth_map.py:1386-1398 with the expected flow of :1491-1497): cv2.perspectiveTransform
+// evaluates the homography in double on float32 coordinates and rounds the warped point to float32
+struct Homography { double m[9]; };
+__global__ void k_flow_residual_depth(const float2* __restrict__ flow, int H, int W, Homography hm, float* __restrict__ current,
+                                      float* __restrict__ stable, int stable_valid, float a_keep, float a_new)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= W) return;
+    const double dx = (double)x, dy = (double)y;
+    const double* m = hm.m;
+    double w = __dadd_rn(__dadd_rn(__dmul_rn(dx, m[6]), __dmul_rn(dy, m[7])), m[8]);
+    float ex = 0.f, ey = 0.f;
+    if (fabs(w) > 2.220446049250313e-16) {
+        w = __ddiv_rn(1.0, w);
+        ex = (float)__dmul_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, m[0]), __dmul_rn(dy, m[1])), m[2]), w);
+        ey = (float)__dmul_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, m[3]), __dmul_rn(dy, m[4])), m[5]), w);
+    }
+    ex = __fsub_rn(ex, (float)x);
+    ey = __fsub_rn(ey, (float)y);
+    const size_t o = (size_t)y * W + x;
+    const float2 f = flow[o];
+    const float rx = __fsub_rn(f.x, ex), ry = __fsub_rn(f.y, ey);
+    const float mag = (float)__dsqrt_rn(__dadd_rn(__dmul_rn((double)rx, (double)rx), __dmul_rn((double)ry, (double)ry)));
+    const float cur = __fdiv_rn(1.0f, __fadd_rn(mag, 0.5f));
+    current[o] = cur;
+    if (stable) stable[o] = stable_valid ? __fadd_rn(__fmul_rn(a_keep, stable[o]), __fmul_rn(a_new, cur)) : cur;
+}
+
+extern "C" int svb_flow_residual_depth_dev(const float* flow_dev, int B, int H, int W, const double* homography9, float* current_dev,
+                                           float* stable_dev, int stable_valid, double alpha, void* stream)
+{
+    if (!flow_dev || !homography9 || !current_dev || B < 1 || H < 1 || W < 1) {
+        svb_set_error("svb_flow_residual_depth_dev: bad argument");
+        return SVB_ERR_PARAM;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t n = (size_t)H * W;
+    for (int b = 0; b < B; ++b) {
+        Homography hm;
+        for (int i = 0; i < 9; ++i) hm.m[i] = homography9[b * 9 + i];
+        k_flow_residual_depth<<<dim3(svb_ceil_div(W, 256), H), 256, 0, s>>>(
+            (const float2*)flow_dev + b * n, H, W, hm, current_dev + b * n, stable_dev ? stable_dev + b * n : nullptr, stable_valid,
+            (float)alpha, (float)(1.0 - alpha));
+    }
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

@@ -78,3 +78,40 @@ def fusion_case_inputs(c):
 # depth_map.py drop-in (apply_stereo_rectification + create_depth_map with the script's own
 # MIN_DISP=0 / NUM_DISP=320 / WINDOW_SIZE=7 / 3WAY): W must exceed 320.
 DROPIN_CASE = dict(H=150, W=520, seed=51)
+
+
+# the code around the mono estimators (fused_depth_map.py:1134-1158, 1386-1403).
+# pred: shape of the network output that is upsampled to the frame; flat: constant prediction / frame.
+MONO_CASES = [
+    dict(H=120, W=176, seed=61, pred=(48, 64)),
+    dict(H=97, W=131, seed=62, pred=(24, 32)),
+    dict(H=64, W=80, seed=63, pred=(96, 128), flat=True),          # the degenerate ranges
+    dict(H=104, W=136, seed=64, pred=(150, 200)),                    # prediction larger than the frame
+]
+
+
+def mono_case_inputs(c):
+    """(frame BGR u8, network prediction f32 [h,w]) of a MONO_CASES entry, from its seed."""
+    from stereovision_b200.synth import make_pair, to_bgr
+    l, _, _ = make_pair(c["H"], c["W"], 16, seed=c["seed"])
+    rng = np.random.default_rng(2000 + c["seed"])
+    h, w = c["pred"]
+    if c.get("flat"):
+        return to_bgr(np.full_like(l, 77)), np.full((h, w), 0.5, np.float32)
+    yy, xx = np.mgrid[0:h, 0:w]
+    pred = 400.0 + 300.0 * np.sin(xx / 9.0 + rng.uniform(0, 3)) * np.cos(yy / 7.0) + rng.normal(0, 25.0, (h, w))
+    return to_bgr(l), pred.astype(np.float32)
+
+
+def mono_flow_frames(c, n=4):
+    """n BGR frames of a camera panning over the textured image of a MONO_CASES entry (integer shifts plus
+    a little noise), for OpticalFlowDepthEstimator."""
+    from stereovision_b200.synth import make_pair, to_bgr
+    l, _, _ = make_pair(c["H"] + 16, c["W"] + 32, 16, seed=c["seed"])
+    rng = np.random.default_rng(3000 + c["seed"])
+    frames = []
+    for k in range(n):
+        crop = l[2 * k:2 * k + c["H"], 3 * k:3 * k + c["W"]].astype(np.int16)
+        crop[c["H"] // 3:c["H"] // 3 + 20, c["W"] // 2:c["W"] // 2 + 30] = l[8:28, 40 + 6 * k:70 + 6 * k]   # a nearer object
+        frames.append(to_bgr(np.clip(crop + rng.integers(-2, 3, crop.shape), 0, 255).astype(np.uint8)))
+    return frames

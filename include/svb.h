@@ -210,6 +210,34 @@ int svb_flow_residual_depth_dev(const float* flow_dev, int B, int H, int W, cons
                                 float* current_dev, float* stable_dev, int stable_valid, double alpha,
                                 void* stream);
 
+/* ==== SURVEY 8(f) N4: display-side reductions, written to a headless device buffer (no window system). */
+
+/* create_depth_map's depth in float64 -- what NumPy computes when fx is read from a float64 camera matrix
+ * (depth_map.py:915-933).  Same as svb_disp_to_depth_dev otherwise. */
+int svb_disp_to_depth_f64_dev(const int16_t* disp16_dev, int B, int H, int W, double fx, double baseline,
+                              double min_disp, double min_depth, double max_depth, float* disparity_dev,
+                              double* depth_dev, void* stream);
+
+/* Normalise to an 8-bit index and look it up in cv2.COLORMAP_JET (2) / cv2.COLORMAP_TURBO (20)
+ * (cv2.applyColorMap).  src_kind selects the reference expression that produces the index:
+ *   0  u8 source as is                                    fused_depth_map.py:1016, 1700
+ *   1  np.clip(f32, 0, 255).astype(u8)                    fused_depth_map.py:3026, 3052
+ *   2  f32 disparity -> depth_clipped -> ((z - min) / (max - min) * 255).astype(u8)   depth_map.py:926-937
+ *   3  the same in float64 (float64 fx)
+ *   4  f32 depth, zeros where depth <= 0, clipped, same scaling   depth_map.py:1187-1192
+ *   5  the same on f64 depth
+ *   6  cv2.normalize(f32, None, lo, hi, NORM_MINMAX).astype(u8) per image   depth_map.py:1207-1208
+ * params5 (host) = {fx * baseline, min_depth, max_depth, lo, hi}; kinds 0/1 accept NULL.  Outputs (either may be
+ * NULL): index u8 [B,npix], bgr u8 [B,npix,3].  Scratch (kind 6 only): svb_display_scratch_bytes. */
+size_t svb_display_scratch_bytes(int B);
+int svb_colormap_dev(const void* src_dev, int src_kind, int B, size_t npix, int colormap, const double* params5,
+                     uint8_t* index_dev, uint8_t* bgr_dev, void* scratch_dev, size_t scratch_bytes, void* stream);
+
+/* Legend range of the fused map (fused_depth_map.py:1997-2004): per image {min, max} over the non-zero pixels of
+ * u8 [B,npix] as int32 [B][2]; {0, 0} when every pixel is zero. */
+int svb_range_nonzero_u8_dev(const uint8_t* src_dev, int B, size_t npix, int* minmax_dev, void* scratch_dev,
+                             size_t scratch_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,9 +11,20 @@ tests/golden/make_golden_mono.py produced with torch and cv2 themselves in the b
 """
 import numpy as np
 
-from .fusion import _reflect101, bilateral_filter
+from .fusion import bilateral_filter
 
 f32 = np.float32
+
+
+def _reflect101(i, n):
+    """cv2.borderInterpolate(i, n, BORDER_REFLECT_101), repeated reflection for images smaller than the kernel."""
+    i = np.asarray(i).copy()
+    if n == 1:
+        return np.zeros_like(i)
+    while ((i < 0) | (i >= n)).any():
+        i = np.where(i < 0, -i, i)
+        i = np.where(i >= n, 2 * (n - 1) - i, i)
+    return i
 
 
 def _cubic_weights(t, A=f32(-0.75)):

@@ -23,6 +23,10 @@ from .mono import (  # noqa: F401
     bilateralFilter, midas_postprocess, upsample_normalize, contrast_confidence, flow_residual_depth,
 )
 
+from .display import (  # noqa: F401
+    COLORMAP_JET, COLORMAP_TURBO, applyColorMap, clip_colormap, depth_colormap, depth_display_colormap,
+    disparity_colormap, legend_range, legend_depth_range,
+)
 from ._lib import SvbError  # noqa: F401
 
 __version__ = "0.1.0"

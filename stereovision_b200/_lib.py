@@ -92,6 +92,12 @@ SIGNATURES = {
     "svb_contrast_confidence_u8_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
     "svb_flow_residual_depth_dev": (c_int, [c_void_p, c_int, c_int, c_int, ctypes.POINTER(c_double), c_void_p,
                                             c_void_p, c_int, c_double, c_void_p]),
+    "svb_disp_to_depth_f64_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_double, c_double, c_double, c_double,
+                                          c_double, c_void_p, c_void_p, c_void_p]),
+    "svb_display_scratch_bytes": (c_size_t, [c_int]),
+    "svb_colormap_dev": (c_int, [c_void_p, c_int, c_int, c_size_t, c_int, ctypes.POINTER(c_double), c_void_p,
+                                 c_void_p, c_void_p, c_size_t, c_void_p]),
+    "svb_range_nonzero_u8_dev": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_void_p, c_size_t, c_void_p]),
 }
 
 

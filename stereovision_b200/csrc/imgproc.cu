@@ -61,10 +61,11 @@ __global__ void __launch_bounds__(256) k_median3_s16(const int16_t* __restrict__
 // 5x5 median on f32.  FROM_S16: the source is the s16 x16 disparity and is scaled by 1/16
 // on load (exact), fusing depth_map.py:909 with :912.  DEPTH: also emit
 // depth_map.py:926-933 (depth = fxB / (d + 1e-6), clip, validity mask) in the epilogue.
-template <bool FROM_S16, bool DEPTH>
+// DEPTH 2: the same in float64, which is what NumPy computes when fx comes from a float64 camera matrix (:917).
+template <bool FROM_S16, int DEPTH>
 __global__ void __launch_bounds__(256) k_median5_f32(const void* __restrict__ src_, int H, int W,
-                                                     float* __restrict__ dst, float* __restrict__ depth,
-                                                     float fxB, float min_disp, float min_depth, float max_depth)
+                                                     float* __restrict__ dst, void* __restrict__ depth_,
+                                                     double fxB64, float min_disp, double min_depth64, double max_depth64)
 {
     const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
     if (x >= W) return;
@@ -98,12 +99,19 @@ __global__ void __launch_bounds__(256) k_median5_f32(const void* __restrict__ sr
     const float d = v[1];
     const size_t o = img + (size_t)y * W + x;
     dst[o] = d;
-    if (DEPTH) {
+    if (DEPTH == 1) {
         // NumPy float32 semantics of depth_map.py:926-933
+        float* depth = (float*)depth_;
+        const float fxB = (float)fxB64, min_depth = (float)min_depth64, max_depth = (float)max_depth64;
         const float z = __fdiv_rn(fxB, __fadd_rn(d, 1e-6f));
         const float zc = fminf(fmaxf(z, min_depth), max_depth);
         const bool valid = (d > min_disp) && (zc >= min_depth) && (zc <= max_depth);
         depth[o] = valid ? zc : 0.f;
+    }
+    if (DEPTH == 2) {
+        const double z = __ddiv_rn(fxB64, (double)__fadd_rn(d, 1e-6f));
+        const double zc = fmin(fmax(z, min_depth64), max_depth64);
+        ((double*)depth_)[o] = (d > min_disp) ? zc : 0.0;
     }
 }
 
@@ -118,8 +126,8 @@ extern "C" int svb_median3_s16_dev(const int16_t* src, int B, int H, int W, int1
 extern "C" int svb_median5_f32_dev(const float* src, int B, int H, int W, float* dst, void* stream)
 {
     if (!src || !dst || B <= 0 || H <= 0 || W <= 0) { svb_set_error("median5: bad argument"); return SVB_ERR_PARAM; }
-    k_median5_f32<false, false><<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(
-        src, H, W, dst, nullptr, 0.f, 0.f, 0.f, 0.f);
+    k_median5_f32<false, 0><<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(
+        src, H, W, dst, nullptr, 0.0, 0.f, 0.0, 0.0);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
@@ -132,8 +140,21 @@ extern "C" int svb_disp_to_depth_dev(const int16_t* disp16, int B, int H, int W,
         svb_set_error("disp_to_depth: bad argument"); return SVB_ERR_PARAM;
     }
     // Python computes fx*BASELINE in double, NumPy then casts the scalar to float32
-    k_median5_f32<true, true><<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(
-        disp16, H, W, disparity, depth, (float)(fx * baseline), (float)min_disp, (float)min_depth, (float)max_depth);
+    k_median5_f32<true, 1><<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(
+        disp16, H, W, disparity, depth, fx * baseline, (float)min_disp, min_depth, max_depth);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+extern "C" int svb_disp_to_depth_f64_dev(const int16_t* disp16, int B, int H, int W, double fx, double baseline,
+                                         double min_disp, double min_depth, double max_depth,
+                                         float* disparity, double* depth, void* stream)
+{
+    if (!disp16 || !disparity || !depth || B <= 0 || H <= 0 || W <= 0) {
+        svb_set_error("disp_to_depth_f64: bad argument"); return SVB_ERR_PARAM;
+    }
+    k_median5_f32<true, 2><<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(
+        disp16, H, W, disparity, depth, fx * baseline, (float)min_disp, min_depth, max_depth);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

@@ -368,8 +368,10 @@ def reprojectImageTo3D(disparity, Q, handleMissingValues=False):
 def disparity_to_depth(disp16, fx=700.0, baseline=0.08, min_disp=0.0, min_depth=0.3, max_depth=2.0):
     """The tail of depth_map.create_depth_map (depth_map.py:909-933) in one kernel:
     disparity = disp16/16 -> medianBlur 5 -> depth = fx*B/(d+1e-6), clip, validity mask.
-    Returns (depth_final f32, disparity f32)."""
+    Returns (depth_final, disparity f32).  depth_final is float32 for a Python-number fx and float64 for a NumPy
+    float64 fx (camera_matrix[0, 0], depth_map.py:917) -- NumPy's promotion in the reference."""
     torch = _torch()
+    f64 = isinstance(fx, np.floating) and not isinstance(fx, (np.float32, np.float16))
     d, was = _to_dev(disp16)
     if d.dtype != torch.int16 or d.ndim not in (2, 3):
         raise ValueError("disp16 must be int16 [H,W] or [B,H,W]")
@@ -377,10 +379,10 @@ def disparity_to_depth(disp16, fx=700.0, baseline=0.08, min_disp=0.0, min_depth=
     H, W = int(d.shape[-2]), int(d.shape[-1])
     _ensure_device(d.device.index)
     disparity = torch.empty(d.shape, dtype=torch.float32, device=d.device)
-    depth = torch.empty(d.shape, dtype=torch.float32, device=d.device)
-    _lib.check(_lib.lib().svb_disp_to_depth_dev(d.data_ptr(), B, H, W, float(fx), float(baseline), float(min_disp),
-                                                float(min_depth), float(max_depth), disparity.data_ptr(),
-                                                depth.data_ptr(), _stream_ptr()))
+    depth = torch.empty(d.shape, dtype=torch.float64 if f64 else torch.float32, device=d.device)
+    fn = _lib.lib().svb_disp_to_depth_f64_dev if f64 else _lib.lib().svb_disp_to_depth_dev
+    _lib.check(fn(d.data_ptr(), B, H, W, float(fx), float(baseline), float(min_disp),
+                  float(min_depth), float(max_depth), disparity.data_ptr(), depth.data_ptr(), _stream_ptr()))
     return _ret(depth, was), _ret(disparity, was)
 
 

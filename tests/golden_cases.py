@@ -115,3 +115,26 @@ def mono_flow_frames(c, n=4):
         crop[c["H"] // 3:c["H"] // 3 + 20, c["W"] // 2:c["W"] // 2 + 30] = l[8:28, 40 + 6 * k:70 + 6 * k]   # a nearer object
         frames.append(to_bgr(np.clip(crop + rng.integers(-2, 3, crop.shape), 0, 255).astype(np.uint8)))
     return frames
+
+
+# SURVEY 8(f) N4 (display-side reductions): W must exceed depth_map.py's NUM_DISP = 320.
+DISPLAY_CASE = dict(H=120, W=480, seed=71, fx=374.4, min_depth=0.2, max_depth=40.0)
+
+
+def display_case_inputs():
+    """(MiDaS-like f32 map stretched beyond 0..255, u8 map for the legend) of DISPLAY_CASE."""
+    from stereovision_b200.synth import make_pair, make_aux_depths
+    c = DISPLAY_CASE
+    _, _, gt = make_pair(c["H"], c["W"], 64, seed=c["seed"])
+    midas, flow = make_aux_depths(gt, c["seed"])
+    wide = (midas.astype(np.float32) - np.float32(midas.mean())) * np.float32(1.7) + np.float32(120.0)
+    return wide, np.where(flow > 0, np.clip(flow, 90, 255), 0).astype(np.uint8)
+
+
+def dense_disparity(c=None):
+    """A float32 disparity field covering the multiples of 1/16 in [-1, 320) (what compute()/16 can hold)."""
+    c = c or DISPLAY_CASE
+    rng = np.random.default_rng(4000 + c["seed"])
+    d = rng.integers(-16, 320 * 16, (c["H"], c["W"])).astype(np.float32) / np.float32(16.0)
+    d[:, :40] = rng.integers(1, 16 * 16, (c["H"], 40)).astype(np.float32) / np.float32(16.0)     # plenty of near range
+    return d

@@ -63,6 +63,11 @@ def main():
 
     Kc = np.array([[0.78 * W, 0, W / 2 + 3], [0, 0.78 * W, H / 2 - 2], [0, 0, 1]], np.float64)
     dc = np.array([-0.10, 0.02, 1e-3, -1e-3, 0], np.float64)
+    gen = torch.Generator(device=dev).manual_seed(1)
+    pred_d = torch.randn((B, 384, 384), device=dev, generator=gen) * 200 + 500
+    flow2_d = torch.randn((B, H, W, 2), device=dev, generator=gen) * 3
+    stab_d = torch.rand((B, H, W), device=dev, generator=gen) + 0.1
+    Hm = np.array([[1.01, 0.002, 1.5], [-0.003, 0.99, -2.0], [1e-6, -2e-6, 1.0]])
     rows = [
         ("initUndistortRectifyMap (N1, per map pair)", lambda: svb.initUndistortRectifyMap(Kc, dc, None, Kc, (W, H), as_tensor=True), 6 * px / B),
         ("remap BGR + gray (a1,a2)", lambda: svb.remap(bgr, m1, m2, svb.INTER_LINEAR, to_gray=True), (3 + 1) * px),
@@ -75,6 +80,10 @@ def main():
         ("fuse_depth_maps (a16)", lambda: svb.fuse_depth_maps(norm, conf, cal_d, None, flow_n, True), 17 * px),
         ("fusion chain a13-a16 (C5)", chain, 17 * px),
         ("occlusion statistics (a17)", lambda: svb.occlusion_stats(gray_l), px),
+        ("MiDaS upsample 384x384 -> frame + normalise (N3)", lambda: svb.upsample_normalize(pred_d, (H, W)), 12 * px),
+        ("contrast confidence u8 (N3)", lambda: svb.contrast_confidence(gray_l), 4 * px),
+        ("flow residual depth + bilateral (N3)", lambda: svb.flow_residual_depth(flow2_d, Hm, stab_d, True), 36 * px),
+        ("bilateralFilter f32 9/75/75 (N3)", lambda: svb.bilateralFilter(flow_d, 9, 75, 75), 12 * px),
         ("StereoBM 64/15 (a18)", lambda: bm.compute(gray_l, gray_r), 4 * px),
     ]
     for name, fn, bytes_per_item in rows:

@@ -96,7 +96,7 @@ static void pixel_cost_row(const uint8_t* L, const uint8_t* R, int H, int W, int
  * "+P2 per path" has the sign backwards, cv2's S is the textbook sum.) */
 static void box_cost_volume(const uint8_t* L, const uint8_t* R, int H, int W,
                             int minD, int D, int ftzero, int bs, int P2,
-                            int minX1, int maxX1, int ylo, int y0, int y1,
+                            int minX1, int maxX1, int ylo, int y0, int y1, int hh4,
                             int16_t* C /* rows y0..y1-1 stored at (y-y0) */)
 {
     int width1 = maxX1 - minX1, r = bs / 2;
@@ -121,6 +121,10 @@ static void box_cost_volume(const uint8_t* L, const uint8_t* R, int H, int W,
         for (size_t i = 0; i < rowsz; ++i) {
             int s = 0;
             for (int k = -r; k <= r; ++k) s += hs[(size_t)iclamp(y + k, ylo, H - 1) * rowsz + i];
+            /* MODE_HH4 (probed on cv2 4.13, 60/60 random cases bit-exact): rows whose box window
+             * reaches below the image (y + r > H-1, y > 0) carry cost 0 for every disparity --
+             * cv2's HH4 cost pass only updates C while the incoming row k = y + r exists. */
+            if (hh4 && y + r > H - 1 && y > 0) s = 0;
             c[i] = (int16_t)s;
         }
     }
@@ -234,7 +238,6 @@ int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
 {
     int minD = p->minDisparity, D = p->numDisparities, bs = p->blockSize;
     if (D <= 0 || bs < 1) return -1;
-    if (p->mode == ORC_MODE_HH4) return -3; /* not restated */
     int maxD = minD + D;
     int minX1 = imax(maxD, 0), maxX1 = W + imin(minD, 0), width1 = maxX1 - minX1;
     int INV = (minD - 1) * 16;
@@ -258,7 +261,7 @@ int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
             if (ye <= ys) continue;
             int16_t* C = (int16_t*)malloc(sizeof(int16_t) * (size_t)(ye - ys) * rowsz);
             uint16_t* S = (uint16_t*)calloc((size_t)(ye - ys) * rowsz, sizeof(uint16_t));
-            box_cost_volume(left, right, H, W, minD, D, ftzero, bs, P2, minX1, maxX1, ys, ys, ye, C);
+            box_cost_volume(left, right, H, W, minD, D, ftzero, bs, P2, minX1, maxX1, ys, ys, ye, 0, C);
             aggregate_path(C, S, ys, ye, width1, D, P1, P2, 1, 0);
             aggregate_path(C, S, ys, ye, width1, D, P1, P2, 0, 1);
             aggregate_path(C, S, ys, ye, width1, D, P1, P2, -1, 0);
@@ -274,10 +277,12 @@ int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
     } else {
         int16_t* C = (int16_t*)malloc(sizeof(int16_t) * (size_t)H * rowsz);
         uint16_t* S = (uint16_t*)calloc((size_t)H * rowsz, sizeof(uint16_t));
-        box_cost_volume(left, right, H, W, minD, D, ftzero, bs, P2, minX1, maxX1, 0, 0, H, C);
+        box_cost_volume(left, right, H, W, minD, D, ftzero, bs, P2, minX1, maxX1, 0, 0, H, p->mode == ORC_MODE_HH4, C);
         static const int dirs[8][2] = {{1,0},{1,1},{0,1},{-1,1},{-1,0},{-1,-1},{0,-1},{1,-1}};
-        int npaths = p->mode == ORC_MODE_HH ? 8 : 5;
-        for (int k = 0; k < npaths; ++k)
+        int npaths = p->mode == ORC_MODE_SGBM ? 5 : 8;
+        /* MODE_HH4 (cv2 computeDisparitySGBM_HH4): the four axis-aligned paths only. */
+        int step = p->mode == ORC_MODE_HH4 ? 2 : 1;
+        for (int k = 0; k < npaths; k += step)
             aggregate_path(C, S, 0, H, width1, D, P1, P2, dirs[k][0], dirs[k][1]);
         for (int y = 0; y < H; ++y)
             wta_row(S + (size_t)y * rowsz, W, width1, D, minD, minX1, uniq, d12, 0,

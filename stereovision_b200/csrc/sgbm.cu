@@ -439,8 +439,13 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
                 if (emit && xc < w1) {
                     uint32_t* dst = vol + (((size_t)job * g.rowsMax + (y - ys)) * w1 + xc) * VW;
                     uint32_t o[NP];
+                    // MODE_HH4: cv2 leaves the rows whose window reaches below the image at cost 0 (oracle/sgbm_oracle.c)
+                    const bool zrow = g.mode == SVB_MODE_HH4 && y + r > g.H - 1 && y > 0;
 #pragma unroll
-                    for (int k = 0; k < NP; ++k) o[k] = FULL ? acc[cc][k] : ((acc[cc][k] & ~padm[k]) | (WALL2 & padm[k]));
+                    for (int k = 0; k < NP; ++k) {
+                        const uint32_t cv = zrow ? 0u : acc[cc][k];
+                        o[k] = FULL ? cv : ((cv & ~padm[k]) | (WALL2 & padm[k]));
+                    }
                     vec_st<NP>(dst, lane, o);
                 }
             }
@@ -1012,7 +1017,6 @@ static int make_geo(const svb_sgbm_params& p, int H, int W, SgbmGeo& g)
         svb_set_error("numDisparities=%d: this engine requires a multiple of 16", p.numDisparities);
         return SVB_ERR_UNSUPPORTED;
     }
-    if (p.mode == SVB_MODE_HH4) { svb_set_error("MODE_HH4 is not implemented"); return SVB_ERR_UNSUPPORTED; }
     if (p.mode < 0 || p.mode > 3) { svb_set_error("bad mode %d", p.mode); return SVB_ERR_PARAM; }
     g.H = H; g.W = W; g.D = p.numDisparities; g.minD = p.minDisparity;
     g.NP = (g.D + 63) / 64; g.Dp = 64 * g.NP; g.HALF = 32 * g.NP;
@@ -1242,7 +1246,8 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     SVB_LAUNCH_CHECK(); h->launches++;
     SVB_CUDA(cudaMemsetAsync(key, 0xff, npix * 4, st));
 
-    // path sets (A.3): 3WAY {->, down | <-}; SGBM {->, \, |, / | <-}; HH {->, \, |, / | <-, \, |, /}
+    // path sets (A.3): 3WAY {->, down | <-}; SGBM {->, \, |, / | <-}; HH {->, \, |, / | <-, \, |, /};
+    // HH4 {->, down | <-, up}
     SweepArgs a;
     a.C = Cv; a.S = Sv;
     a.carry = (uint32_t*)(ws + L.carry); a.cmin = (uint32_t*)(ws + L.cmin);
@@ -1258,16 +1263,17 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     {
         ProfScope ps(h, CAT_SWEEP1, st);
         a.dir = 1;
-        rc = g.mode == SVB_MODE_SGBM_3WAY ? launch_sweep_var<NP, 5, false>(h, a, g, var, st)
-                                          : launch_sweep_var<NP, 15, false>(h, a, g, var, st);
+        rc = (g.mode == SVB_MODE_SGBM_3WAY || g.mode == SVB_MODE_HH4) ? launch_sweep_var<NP, 5, false>(h, a, g, var, st)
+                                                                      : launch_sweep_var<NP, 15, false>(h, a, g, var, st);
         if (rc != SVB_OK) return rc;
         h->launches++;
     }
     {
         ProfScope ps(h, CAT_SWEEP2, st);
         a.dir = -1;
-        rc = g.mode == SVB_MODE_HH ? launch_sweep_var<NP, 15, true>(h, a, g, var, st)
-                                   : launch_sweep_var<NP, 1, true>(h, a, g, var, st);
+        rc = g.mode == SVB_MODE_HH    ? launch_sweep_var<NP, 15, true>(h, a, g, var, st)
+             : g.mode == SVB_MODE_HH4 ? launch_sweep_var<NP, 5, true>(h, a, g, var, st)
+                                      : launch_sweep_var<NP, 1, true>(h, a, g, var, st);
         if (rc != SVB_OK) return rc;
         h->launches++;
     }

@@ -2,7 +2,7 @@
 must not need cv2 or /root/reference)."""
 import numpy as np
 
-MODE_SGBM, MODE_HH, MODE_3WAY = 0, 1, 2
+MODE_SGBM, MODE_HH, MODE_3WAY, MODE_HH4 = 0, 1, 2, 3
 
 
 def _p(minD, D, bs, mode, uniq=10, spw=100, spr=32, d12=1, cap=63, p1=None, p2=None):
@@ -23,6 +23,10 @@ SGBM_CASES = [
     dict(H=48, W=120, seed=18, prm=_p(0, 80, 7, MODE_3WAY, uniq=0, spw=0)),     # D not a power of two
     dict(H=64, W=100, seed=19, prm=_p(0, 32, 9, MODE_SGBM, p1=1944, p2=7776)),   # S saturates at 32767
     dict(H=40, W=400, seed=20, prm=_p(0, 320, 7, MODE_3WAY)),                    # the reference's own D / bs
+    # MODE_HH4 (4 axis-aligned paths; the rows within blockSize/2 of the bottom edge cost 0)
+    dict(H=64, W=141, seed=21, prm=_p(0, 64, 5, MODE_HH4)),
+    dict(H=70, W=120, seed=22, prm=_p(-8, 32, 9, MODE_HH4, uniq=5, d12=2, cap=31, spw=0)),
+    dict(H=33, W=230, seed=23, prm=_p(4, 144, 3, MODE_HH4, uniq=15)),
 ]
 
 BM_CASES = [

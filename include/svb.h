@@ -65,6 +65,13 @@ int svb_sgbm_compute_dev(svb_sgbm_t* h, const uint8_t* left_dev, const uint8_t* 
                          int B, int H, int W, int16_t* disp_dev, void* stream);
 int svb_sgbm_compute_host(svb_sgbm_t* h, const uint8_t* left_host, const uint8_t* right_host,
                           int B, int H, int W, int16_t* disp_host);
+/* The same with cn = 1 (u8 [B,H,W]) or cn = 3 (interleaved u8 [B,H,W,3]: cv2.StereoSGBM accepts colour
+ * images and sums the Birchfield-Tomasi cost over the channels; the reference converts to gray first,
+ * depth_map.py:871-879, so this is SURVEY 8(f) N2 surface completeness). */
+int svb_sgbm_compute_cn_dev(svb_sgbm_t* h, const uint8_t* left_dev, const uint8_t* right_dev,
+                            int B, int H, int W, int cn, int16_t* disp_dev, void* stream);
+int svb_sgbm_compute_cn_host(svb_sgbm_t* h, const uint8_t* left_host, const uint8_t* right_host,
+                             int B, int H, int W, int cn, int16_t* disp_host);
 /* Test hook: copy internal stages of the LAST compute (chunk 0, image 0) to host buffers
  * (any may be NULL).  C,S: u16 [rows,width1,D] (3WAY: kept rows only are meaningful),
  * raw: s16 [H,W] disparity before median/speckle.  The aggregated volume S only exists in

@@ -60,8 +60,9 @@ def sgbm_compute(left, right, minDisparity=0, numDisparities=16, blockSize=3, P1
     S (uint16) and the raw disparity before median/speckle."""
     left = np.ascontiguousarray(left, np.uint8)
     right = np.ascontiguousarray(right, np.uint8)
-    assert left.shape == right.shape and left.ndim == 2
-    H, W = left.shape
+    assert left.shape == right.shape and (left.ndim == 2 or (left.ndim == 3 and left.shape[2] == 3))
+    H, W = left.shape[:2]
+    cn = 1 if left.ndim == 2 else 3
     prm = _SgbmParams(minDisparity, numDisparities, blockSize, P1, P2, disp12MaxDiff,
                       preFilterCap, uniquenessRatio, speckleWindowSize, speckleRange, mode)
     disp = np.empty((H, W), np.int16)
@@ -72,8 +73,8 @@ def sgbm_compute(left, right, minDisparity=0, numDisparities=16, blockSize=3, P1
     if stages and width1 > 0:
         C = np.empty((H, width1, numDisparities), np.int16)
         S = np.empty((H, width1, numDisparities), np.uint16)
-    rc = lib().orc_sgbm_compute(
-        _p(left, ctypes.c_uint8), _p(right, ctypes.c_uint8), H, W, ctypes.byref(prm),
+    rc = lib().orc_sgbm_compute_cn(
+        _p(left, ctypes.c_uint8), _p(right, ctypes.c_uint8), H, W, cn, ctypes.byref(prm),
         _p(disp, ctypes.c_int16),
         _p(C, ctypes.c_int16) if C is not None else None,
         _p(S, ctypes.c_uint16) if S is not None else None,

@@ -34,15 +34,17 @@ static inline int iclamp(int v, int lo, int hi) { return v < lo ? lo : (v > hi ?
 
 /* x-Sobel prefiltered channel (p0) and raw channel (p1) of
  * one image row.  Columns 0 and W-1 of BOTH channels are ftzero. */
-static void prefilter_row(const uint8_t* img, int H, int W, int y, int ftzero,
+static void prefilter_row(const uint8_t* img, int H, int W, int cn, int ch, int y, int ftzero,
                           int* p0, int* p1)
 {
     int yn = y > 0 ? y - 1 : y, ys = y < H - 1 ? y + 1 : y;
-    const uint8_t *r = img + (size_t)y * W, *rn = img + (size_t)yn * W, *rs = img + (size_t)ys * W;
+    const uint8_t *r = img + (size_t)y * W * cn + ch, *rn = img + (size_t)yn * W * cn + ch,
+                  *rs = img + (size_t)ys * W * cn + ch;
     for (int x = 1; x < W - 1; ++x) {
-        int g = 2 * (r[x + 1] - r[x - 1]) + (rn[x + 1] - rn[x - 1]) + (rs[x + 1] - rs[x - 1]);
+        int e = (x + 1) * cn, w = (x - 1) * cn;
+        int g = 2 * (r[e] - r[w]) + (rn[e] - rn[w]) + (rs[e] - rs[w]);
         p0[x] = iclamp(g, -ftzero, ftzero) + ftzero;
-        p1[x] = r[x];
+        p1[x] = r[x * cn];
     }
     p0[0] = p1[0] = ftzero;
     if (W > 1) p0[W - 1] = p1[W - 1] = ftzero;
@@ -50,16 +52,19 @@ static void prefilter_row(const uint8_t* img, int H, int W, int y, int ftzero,
 
 /* Birchfield-Tomasi cost of one row into pix[xc*D + d]
  * (accumulated over the two channels; channel 1 is >>2). */
-static void pixel_cost_row(const uint8_t* L, const uint8_t* R, int H, int W, int y,
+static void pixel_cost_row(const uint8_t* L, const uint8_t* R, int H, int W, int cn, int y,
                            int minD, int D, int ftzero, int minX1, int maxX1,
                            int* scratch /* 10*W ints */, int* pix)
 {
     int *l0 = scratch, *l1 = l0 + W, *r0 = l1 + W, *r1 = r0 + W;
     int *v0 = r1 + W, *v1 = v0 + W, *u0 = v1 + W, *u1 = u0 + W;
     int width1 = maxX1 - minX1;
-    prefilter_row(L, H, W, y, ftzero, l0, l1);
-    prefilter_row(R, H, W, y, ftzero, r0, r1);
     memset(pix, 0, sizeof(int) * (size_t)width1 * D);
+    /* 3-channel input (cv2 calcPixelCostBT, cn = 3): every colour channel contributes its own
+     * gradient channel (unscaled) and raw channel (>>2); the costs add. */
+    for (int ch = 0; ch < cn; ++ch) {
+    prefilter_row(L, H, W, cn, ch, y, ftzero, l0, l1);
+    prefilter_row(R, H, W, cn, ch, y, ftzero, r0, r1);
     for (int c = 0; c < 2; ++c) {
         const int* pl = c ? l1 : l0;
         const int* pr = c ? r1 : r0;
@@ -88,13 +93,14 @@ static void pixel_cost_row(const uint8_t* L, const uint8_t* R, int H, int W, int
             }
         }
     }
+    }
 }
 
 /* C[y,xc,d] = box(blockSize) over pix, replicate borders in the cost
  * domain; rows clamp to [ylo, H-1].  (cv2 stores C+P2 and subtracts minLr+P2 in
  * the recurrence; the two cancel, so plain C is kept here -- probed: SURVEY A.3's
  * "+P2 per path" has the sign backwards, cv2's S is the textbook sum.) */
-static void box_cost_volume(const uint8_t* L, const uint8_t* R, int H, int W,
+static void box_cost_volume(const uint8_t* L, const uint8_t* R, int H, int W, int cn,
                             int minD, int D, int ftzero, int bs, int P2,
                             int minX1, int maxX1, int ylo, int y0, int y1, int hh4,
                             int16_t* C /* rows y0..y1-1 stored at (y-y0) */)
@@ -108,7 +114,7 @@ static void box_cost_volume(const uint8_t* L, const uint8_t* R, int H, int W,
     /* horizontal sums for every row that any window can touch */
     int ya = imax(ylo, y0 - r), yb = imin(H - 1, y1 - 1 + r);
     for (int y = ya; y <= yb; ++y) {
-        pixel_cost_row(L, R, H, W, y, minD, D, ftzero, minX1, maxX1, scratch, pix);
+        pixel_cost_row(L, R, H, W, cn, y, minD, D, ftzero, minX1, maxX1, scratch, pix);
         int32_t* h = hs + (size_t)y * rowsz;
         for (int xc = 0; xc < width1; ++xc)
             for (int k = -r; k <= r; ++k) {
@@ -232,10 +238,22 @@ void orc_filter_speckles_s16(int16_t* img, int H, int W, int newVal, int maxSpec
 /* Returns 0 on success, <0 on parameter errors (the checks cv2 4.13 makes).
  * Optional stage outputs (may be NULL): C_out/S_out [H*width1*D] (3WAY: kept rows of each stripe),
  * raw_out [H*W] = disparity before median3/speckle. */
+int orc_sgbm_compute_cn(const uint8_t* left, const uint8_t* right, int H, int W, int cn,
+                        const orc_sgbm_params* p, int16_t* disp,
+                        int16_t* C_out, uint16_t* S_out, int16_t* raw_out);
 int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
                      const orc_sgbm_params* p, int16_t* disp,
                      int16_t* C_out, uint16_t* S_out, int16_t* raw_out)
 {
+    return orc_sgbm_compute_cn(left, right, H, W, 1, p, disp, C_out, S_out, raw_out);
+}
+
+/* left/right: u8 [H,W] (cn = 1) or interleaved [H,W,3] (cn = 3). */
+int orc_sgbm_compute_cn(const uint8_t* left, const uint8_t* right, int H, int W, int cn,
+                        const orc_sgbm_params* p, int16_t* disp,
+                        int16_t* C_out, uint16_t* S_out, int16_t* raw_out)
+{
+    if (cn != 1 && cn != 3) return -4;
     int minD = p->minDisparity, D = p->numDisparities, bs = p->blockSize;
     if (D <= 0 || bs < 1) return -1;
     int maxD = minD + D;
@@ -261,7 +279,7 @@ int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
             if (ye <= ys) continue;
             int16_t* C = (int16_t*)malloc(sizeof(int16_t) * (size_t)(ye - ys) * rowsz);
             uint16_t* S = (uint16_t*)calloc((size_t)(ye - ys) * rowsz, sizeof(uint16_t));
-            box_cost_volume(left, right, H, W, minD, D, ftzero, bs, P2, minX1, maxX1, ys, ys, ye, 0, C);
+            box_cost_volume(left, right, H, W, cn, minD, D, ftzero, bs, P2, minX1, maxX1, ys, ys, ye, 0, C);
             aggregate_path(C, S, ys, ye, width1, D, P1, P2, 1, 0);
             aggregate_path(C, S, ys, ye, width1, D, P1, P2, 0, 1);
             aggregate_path(C, S, ys, ye, width1, D, P1, P2, -1, 0);
@@ -277,7 +295,7 @@ int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
     } else {
         int16_t* C = (int16_t*)malloc(sizeof(int16_t) * (size_t)H * rowsz);
         uint16_t* S = (uint16_t*)calloc((size_t)H * rowsz, sizeof(uint16_t));
-        box_cost_volume(left, right, H, W, minD, D, ftzero, bs, P2, minX1, maxX1, 0, 0, H, p->mode == ORC_MODE_HH4, C);
+        box_cost_volume(left, right, H, W, cn, minD, D, ftzero, bs, P2, minX1, maxX1, 0, 0, H, p->mode == ORC_MODE_HH4, C);
         static const int dirs[8][2] = {{1,0},{1,1},{0,1},{-1,1},{-1,0},{-1,-1},{0,-1},{1,-1}};
         int npaths = p->mode == ORC_MODE_SGBM ? 5 : 8;
         /* MODE_HH4 (cv2 computeDisparitySGBM_HH4): the four axis-aligned paths only. */

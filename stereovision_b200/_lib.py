@@ -46,6 +46,8 @@ SIGNATURES = {
     "svb_sgbm_set_workspace_limit": (c_int, [c_void_p, c_size_t]),
     "svb_sgbm_compute_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "svb_sgbm_compute_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "svb_sgbm_compute_cn_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "svb_sgbm_compute_cn_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "svb_sgbm_set_debug": (c_int, [c_void_p, c_int]),
     "svb_sgbm_debug_stages": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "svb_sgbm_last_launches": (c_int, [c_void_p]),

@@ -81,6 +81,7 @@ __host__ __device__ constexpr size_t sw_smem_words(int NP, bool last)
 struct SgbmGeo {
     int H, W, D, Dp, NP, HALF, minD, minX1, width1, bs, r, ftzero;
     int P1, P2, uniq, d12, INV, mode, nstripes, rowsMax;
+    int cn;                    // image channels (1, or 3: interleaved colour -- cv2 sums the BT cost of every channel)
     int Wp;                    // words per plane row of the right descriptors
     unsigned thMul;            // floor(2^32 / (100 - uniq)) + 1: exact division of the uniqueness threshold (0: divisor <= 1)
 };
@@ -105,19 +106,21 @@ __host__ __device__ inline void job_rows(const SgbmGeo& g, int n, int& ys, int& 
 // Right: 6 planes per row {-v1, v0, -v} x 2 channels; entry(xr) = a[xr] | a[xr - HALF] << 16,
 // i.e. the operands of disparity index w (low) and w + HALF (high) for left pixel x = xr + w.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void bt_channels(const uint8_t* img, int H, int W, int y, int x, int ftzero,
+// img points at channel ch of pixel (0,0); cn = pixel stride in bytes
+__device__ __forceinline__ void bt_channels(const uint8_t* img, int H, int W, int cn, int y, int x, int ftzero,
                                             int& p0, int& p1)
 {
     if (x <= 0 || x >= W - 1) { p0 = p1 = ftzero; return; }
     int yn = y > 0 ? y - 1 : y, ys = y < H - 1 ? y + 1 : y;
-    const uint8_t *r = img + (size_t)y * W, *rn = img + (size_t)yn * W, *rs = img + (size_t)ys * W;
-    int g = 2 * ((int)r[x + 1] - r[x - 1]) + ((int)rn[x + 1] - rn[x - 1]) + ((int)rs[x + 1] - rs[x - 1]);
+    const uint8_t *r = img + (size_t)y * W * cn, *rn = img + (size_t)yn * W * cn, *rs = img + (size_t)ys * W * cn;
+    const int e = (x + 1) * cn, w = (x - 1) * cn;
+    int g = 2 * ((int)r[e] - r[w]) + ((int)rn[e] - rn[w]) + ((int)rs[e] - rs[w]);
     g = max(-ftzero, min(ftzero, g));
-    p0 = g + ftzero; p1 = r[x];
+    p0 = g + ftzero; p1 = r[x * cn];
 }
 
 __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ left, const uint8_t* __restrict__ right,
-                                                   int nimg, SgbmGeo g, uint32_t* __restrict__ ldesc,
+                                                   int nimg, int ch, SgbmGeo g, uint32_t* __restrict__ ldesc,
                                                    uint32_t* __restrict__ rdesc)
 {
     int x = blockIdx.x * blockDim.x + threadIdx.x;
@@ -125,10 +128,10 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
     if (x >= g.W) return;
     const int H = g.H, W = g.W;
     {
-        const uint8_t* img = left + (size_t)b * H * W;
+        const uint8_t* img = left + (size_t)b * H * W * g.cn + ch;
         int c0[3], c1[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) bt_channels(img, H, W, y, min(max(x + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
+        for (int k = 0; k < 3; ++k) bt_channels(img, H, W, g.cn, y, min(max(x + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
         uint32_t* rec = ldesc + ((size_t)(b * H + y) * W + x) * 8;
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
@@ -144,10 +147,10 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
         }
     }
     {
-        const uint8_t* img = right + (size_t)b * H * W;
+        const uint8_t* img = right + (size_t)b * H * W * g.cn + ch;
         int c0[3], c1[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) bt_channels(img, H, W, y, min(max(x + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
+        for (int k = 0; k < 3; ++k) bt_channels(img, H, W, g.cn, y, min(max(x + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
         uint16_t* base = reinterpret_cast<uint16_t*>(rdesc + (size_t)(b * H + y) * 6 * g.Wp);
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
@@ -273,6 +276,7 @@ __host__ __device__ constexpr int ck_blkw(int NP) { return (6 * (ck_se(NP) / ck_
 struct CostArgs {
     int OC;                    // output columns per strip = CK_PC - 2r (or less when the ring is large)
     int nstrips, rseg, nsegs;  // strips per row, rows per segment, segments per job
+    int accum;                 // add to the stored C (colour input: one pass per channel)
 };
 
 template <int NP, bool FULL>
@@ -442,8 +446,10 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
                     // MODE_HH4: cv2 leaves the rows whose window reaches below the image at cost 0 (oracle/sgbm_oracle.c)
                     const bool zrow = g.mode == SVB_MODE_HH4 && y + r > g.H - 1 && y > 0;
 #pragma unroll
+                    if (ca.accum) vec_ld<NP>(dst, lane, t, LdPlain());
+#pragma unroll
                     for (int k = 0; k < NP; ++k) {
-                        const uint32_t cv = zrow ? 0u : acc[cc][k];
+                        const uint32_t cv = zrow ? 0u : (ca.accum ? acc[cc][k] + t[k] : acc[cc][k]);
                         o[k] = FULL ? cv : ((cv & ~padm[k]) | (WALL2 & padm[k]));
                     }
                     vec_st<NP>(dst, lane, o);
@@ -1008,7 +1014,7 @@ struct svb_sgbm {
     bool have_last = false;
 };
 
-static int make_geo(const svb_sgbm_params& p, int H, int W, SgbmGeo& g)
+static int make_geo(const svb_sgbm_params& p, int H, int W, int cn, SgbmGeo& g)
 {
     if (H <= 0 || W <= 0) { svb_set_error("empty image (%dx%d)", W, H); return SVB_ERR_PARAM; }
     if (p.numDisparities <= 0) { svb_set_error("numDisparities must be > 0"); return SVB_ERR_PARAM; }
@@ -1018,7 +1024,8 @@ static int make_geo(const svb_sgbm_params& p, int H, int W, SgbmGeo& g)
         return SVB_ERR_UNSUPPORTED;
     }
     if (p.mode < 0 || p.mode > 3) { svb_set_error("bad mode %d", p.mode); return SVB_ERR_PARAM; }
-    g.H = H; g.W = W; g.D = p.numDisparities; g.minD = p.minDisparity;
+    if (cn != 1 && cn != 3) { svb_set_error("images must have 1 or 3 channels (got %d)", cn); return SVB_ERR_PARAM; }
+    g.H = H; g.W = W; g.cn = cn; g.D = p.numDisparities; g.minD = p.minDisparity;
     g.NP = (g.D + 63) / 64; g.Dp = 64 * g.NP; g.HALF = 32 * g.NP;
     if (g.NP > 8) { svb_set_error("numDisparities=%d > 512 unsupported", g.D); return SVB_ERR_UNSUPPORTED; }
     const int maxD = g.minD + g.D;
@@ -1042,7 +1049,7 @@ static int make_geo(const svb_sgbm_params& p, int H, int W, SgbmGeo& g)
     g.mode = p.mode;
     g.nstripes = p.mode == SVB_MODE_SGBM_3WAY ? 4 : 1;
     const int win = 2 * g.r + 1;
-    const long long cmax = (long long)win * win * (2 * g.ftzero + 63);
+    const long long cmax = (long long)cn * win * win * (2 * g.ftzero + 63);
     // L <= C + P2 must stay below cv2's MAX_COST (its int16 C+P2 buffer has the same limit)
     if (g.ftzero > 127 || cmax + g.P2 > 32766 || g.P1 > 32767) {
         svb_set_error("blockSize/preFilterCap/P2 overflow the 16-bit cost range "
@@ -1101,7 +1108,7 @@ extern "C" int svb_sgbm_create(const svb_sgbm_params* p, svb_sgbm_t** out)
     if (!p || !out) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
     SgbmGeo g;
     // validate what does not depend on the image size with a generously wide dummy image
-    int rc = make_geo(*p, 16, 65535, g);
+    int rc = make_geo(*p, 16, 65535, 1, g);
     if (rc != SVB_OK) return rc;
     svb_sgbm* h = new (std::nothrow) svb_sgbm();
     if (!h) return SVB_ERR_NOMEM;
@@ -1119,7 +1126,7 @@ extern "C" void svb_sgbm_destroy(svb_sgbm_t* h)
 extern "C" size_t svb_sgbm_workspace_bytes(const svb_sgbm_t* h, int B, int H, int W)
 {
     SgbmGeo g;
-    if (!h || make_geo(h->prm, H, W, g) != SVB_OK) return 0;
+    if (!h || make_geo(h->prm, H, W, 1, g) != SVB_OK) return 0;
     return make_layout(g, pick_chunk(h, g, B)).total;
 }
 extern "C" int svb_sgbm_set_workspace_limit(svb_sgbm_t* h, size_t bytes)
@@ -1196,9 +1203,12 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     int32_t* scratch = (int32_t*)(ws + L.scratch);
     const int njobs = nb * g.nstripes;
 
+    // colour input: one prefilter + cost pass per channel, the box sums add up in C (A.1: cv2 sums the BT cost
+    // of all 2*cn channels before the box filter, and the box filter is linear)
+    for (int ch = 0; ch < g.cn; ++ch) {
     {
         ProfScope ps(h, CAT_PREFILTER, st);
-        k_prefilter<<<dim3(svb_ceil_div(g.W, 256), g.H, nb), 256, 0, st>>>(left, right, nb, g, ldesc, rdesc);
+        k_prefilter<<<dim3(svb_ceil_div(g.W, 256), g.H, nb), 256, 0, st>>>(left, right, nb, ch, g, ldesc, rdesc);
     }
     SVB_LAUNCH_CHECK(); h->launches++;
 
@@ -1206,6 +1216,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         // k_cost tiling: ring of bs rows per output column in shared memory
         const int bs = 2 * g.r + 1, VW = NP * 32;
         CostArgs ca;
+        ca.accum = ch > 0;
         const size_t fixed = ((size_t)2 * ck_nblk(NP) * ck_blkw(NP) + 2 * CK_PC * 8 + (size_t)2 * CK_PC * VW) * 4;
         const size_t budget = 200 * 1024;
         int OC = CK_PC - 2 * g.r;
@@ -1240,6 +1251,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         }
         SVB_LAUNCH_CHECK(); h->launches++;
     }
+    }
 
     const size_t npix = (size_t)nb * g.H * g.W;
     k_fill_s16<<<svb_ceil_div(npix, 256), 256, 0, st>>>(raw, npix, (int16_t)g.INV);
@@ -1256,7 +1268,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     a.njobs = njobs; a.bandsPerJob = L.bands;
     a.storeS = h->debug ? 1 : 0;
     const int win = 2 * g.r + 1;
-    const long long lmax = (long long)win * win * (2 * g.ftzero + 63) + g.P2;
+    const long long lmax = (long long)g.cn * win * win * (2 * g.ftzero + 63) + g.P2;
     int var = g.D == g.Dp ? 1 : 0;
     if (var == 1 && 4 * lmax <= 32767) var = 2;
     int rc;
@@ -1302,10 +1314,16 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
 extern "C" int svb_sgbm_compute_dev(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
                                     int B, int H, int W, int16_t* disp, void* stream)
 {
+    return svb_sgbm_compute_cn_dev(h, left, right, B, H, W, 1, disp, stream);
+}
+
+extern "C" int svb_sgbm_compute_cn_dev(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
+                                       int B, int H, int W, int cn, int16_t* disp, void* stream)
+{
     if (!h || !left || !right || !disp) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
     if (B <= 0) { svb_set_error("batch must be >= 1"); return SVB_ERR_PARAM; }
     SgbmGeo g;
-    int rc = make_geo(h->prm, H, W, g);
+    int rc = make_geo(h->prm, H, W, cn, g);
     if (rc != SVB_OK) return rc;
     if (!h->num_sms) {
         int dev = 0;
@@ -1328,7 +1346,7 @@ extern "C" int svb_sgbm_compute_dev(svb_sgbm_t* h, const uint8_t* left, const ui
         const int n = std::min(nb, B - b0);
         const size_t off = (size_t)b0 * H * W;
         switch (g.NP) {
-#define CASE(N) case N: rc = run_chunk<N>(h, g, L, left + off, right + off, n, disp + off, st); break;
+#define CASE(N) case N: rc = run_chunk<N>(h, g, L, left + off * cn, right + off * cn, n, disp + off, st); break;
             CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
 #undef CASE
             default: svb_set_error("bad NP"); rc = SVB_ERR_UNSUPPORTED;
@@ -1352,18 +1370,24 @@ static int check_sweep_err(svb_sgbm* h)
 extern "C" int svb_sgbm_compute_host(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
                                      int B, int H, int W, int16_t* disp)
 {
+    return svb_sgbm_compute_cn_host(h, left, right, B, H, W, 1, disp);
+}
+
+extern "C" int svb_sgbm_compute_cn_host(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
+                                        int B, int H, int W, int cn, int16_t* disp)
+{
     if (!h || !left || !right || !disp) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
-    if (B <= 0 || H <= 0 || W <= 0) { svb_set_error("bad shape"); return SVB_ERR_PARAM; }
-    const size_t n = (size_t)B * H * W;
-    int rc = h->stage_in.reserve(2 * n);
+    if (B <= 0 || H <= 0 || W <= 0 || (cn != 1 && cn != 3)) { svb_set_error("bad shape"); return SVB_ERR_PARAM; }
+    const size_t n = (size_t)B * H * W, nin = n * cn;
+    int rc = h->stage_in.reserve(2 * nin);
     if (rc != SVB_OK) return rc;
     rc = h->stage_out.reserve(2 * n);
     if (rc != SVB_OK) return rc;
     uint8_t* dl = (uint8_t*)h->stage_in.p;
-    uint8_t* dr = dl + n;
-    SVB_CUDA(cudaMemcpyAsync(dl, left, n, cudaMemcpyHostToDevice, 0));
-    SVB_CUDA(cudaMemcpyAsync(dr, right, n, cudaMemcpyHostToDevice, 0));
-    rc = svb_sgbm_compute_dev(h, dl, dr, B, H, W, (int16_t*)h->stage_out.p, 0);
+    uint8_t* dr = dl + nin;
+    SVB_CUDA(cudaMemcpyAsync(dl, left, nin, cudaMemcpyHostToDevice, 0));
+    SVB_CUDA(cudaMemcpyAsync(dr, right, nin, cudaMemcpyHostToDevice, 0));
+    rc = svb_sgbm_compute_cn_dev(h, dl, dr, B, H, W, cn, (int16_t*)h->stage_out.p, 0);
     if (rc != SVB_OK) return rc;
     SVB_CUDA(cudaMemcpyAsync(disp, h->stage_out.p, 2 * n, cudaMemcpyDeviceToHost, 0));
     SVB_CUDA(cudaStreamSynchronize(0));

@@ -91,8 +91,8 @@ def _check_pair(left, right):
         raise ValueError("left and right must both be NumPy arrays or both torch tensors")
     if tuple(left.shape) != tuple(right.shape):
         raise ValueError(f"left and right must have the same size: {tuple(left.shape)} vs {tuple(right.shape)}")
-    if left.ndim not in (2, 3):
-        raise ValueError("expected [H,W] or [B,H,W] single-channel 8-bit images")
+    if left.ndim not in (2, 3, 4) or (left.ndim == 4 and left.shape[-1] != 3):
+        raise ValueError("expected [H,W] / [B,H,W] single-channel or [H,W,3] / [B,H,W,3] colour 8-bit images")
     if _is_tensor(left):
         torch = _torch()
         if left.dtype != torch.uint8 or right.dtype != torch.uint8:
@@ -114,18 +114,25 @@ class _Matcher:
         """disparity = matcher.compute(left, right) -> int16 (x16 fixed point), same shape."""
         _check_pair(left, right)
         L = _lib.lib()
-        batched = left.ndim == 3
-        B = left.shape[0] if batched else 1
-        H, W = left.shape[-2], left.shape[-1]
-        host_fn = L.svb_sgbm_compute_host if self._kind == "sgbm" else L.svb_bm_compute_host
-        dev_fn = L.svb_sgbm_compute_dev if self._kind == "sgbm" else L.svb_bm_compute_dev
+        # cv2 reads a 3-dim array as H x W x channels: a trailing dimension of 3 is colour (no image is 3 wide)
+        cn = 3 if left.ndim >= 3 and left.shape[-1] == 3 else 1
+        oshape = tuple(left.shape[:-1]) if cn == 3 else tuple(left.shape)
+        B = oshape[0] if len(oshape) == 3 else 1
+        H, W = oshape[-2], oshape[-1]
+        if self._kind == "sgbm":
+            host_fn = lambda h, l, r, B, H, W, o: L.svb_sgbm_compute_cn_host(h, l, r, B, H, W, cn, o)
+            dev_fn = lambda h, l, r, B, H, W, o, st: L.svb_sgbm_compute_cn_dev(h, l, r, B, H, W, cn, o, st)
+        else:
+            if cn != 1:
+                raise ValueError("StereoBM needs single-channel 8-bit images (cv2: CV_8UC1)")
+            host_fn, dev_fn = L.svb_bm_compute_host, L.svb_bm_compute_dev
         if _is_tensor(left):
             torch = _torch()
             dev = _ensure_device(left.device.index)
             h = _handle(self._kind, self._params(), dev)
             self._pre_compute(h)
             l, r = left.contiguous(), right.contiguous()
-            out = torch.empty(left.shape, dtype=torch.int16, device=left.device)
+            out = torch.empty(oshape, dtype=torch.int16, device=left.device)
             _lib.check(dev_fn(h, l.data_ptr(), r.data_ptr(), B, H, W, out.data_ptr(), _stream_ptr()))
             self._last = h
             return out
@@ -134,7 +141,7 @@ class _Matcher:
         self._pre_compute(h)
         l = np.ascontiguousarray(left)
         r = np.ascontiguousarray(right)
-        out = np.empty(left.shape, np.int16)
+        out = np.empty(oshape, np.int16)
         _lib.check(host_fn(h, l.ctypes.data, r.ctypes.data, B, H, W, out.ctypes.data))
         self._last = h
         return out

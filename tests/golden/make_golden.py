@@ -12,7 +12,7 @@ import numpy as np
 
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", ".."))
 from stereovision_b200.synth import make_pair, to_bgr  # noqa: E402
-from tests.golden_cases import SGBM_CASES, BM_CASES, synth_calibration  # noqa: E402
+from tests.golden_cases import SGBM_CASES, SGBM_COLOR_CASES, BM_CASES, color_pair, synth_calibration  # noqa: E402
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -22,6 +22,9 @@ def main():
     for i, c in enumerate(SGBM_CASES):
         l, r, _ = make_pair(c["H"], c["W"], max(c["prm"]["numDisparities"], 16), seed=c["seed"])
         out[f"sgbm_{i}"] = cv2.StereoSGBM_create(**c["prm"]).compute(l, r)
+    for i, c in enumerate(SGBM_COLOR_CASES):
+        l, r = color_pair(c)
+        out[f"sgbm_color_{i}"] = cv2.StereoSGBM_create(**c["prm"]).compute(l, r)
     for i, c in enumerate(BM_CASES):
         l, r, _ = make_pair(c["H"], c["W"], max(c["numDisparities"], 16), seed=c["seed"])
         bm = cv2.StereoBM_create(c["numDisparities"], c["blockSize"])

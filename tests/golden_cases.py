@@ -29,6 +29,28 @@ SGBM_CASES = [
     dict(H=33, W=230, seed=23, prm=_p(4, 144, 3, MODE_HH4, uniq=15)),
 ]
 
+# 3-channel input (cv2 sums the BT cost over the colour channels); P1/P2 as the reference's
+# 8*3*bs^2 / 32*3*bs^2 (depth_map.py:898-899)
+SGBM_COLOR_CASES = [
+    dict(H=60, W=120, seed=24, prm=_p(0, 32, 5, MODE_SGBM, p1=600, p2=2400)),
+    dict(H=52, W=150, seed=25, prm=_p(0, 64, 3, MODE_HH, p1=216, p2=864, uniq=5)),
+    dict(H=64, W=140, seed=26, prm=_p(0, 48, 7, MODE_3WAY, p1=1176, p2=4704)),
+    dict(H=40, W=100, seed=27, prm=_p(-8, 16, 5, MODE_HH4, p1=600, p2=2400, cap=31)),
+]
+
+
+def color_pair(c):
+    """Interleaved BGR pair of a SGBM_COLOR_CASES entry: per-channel gains plus independent seeded noise."""
+    from stereovision_b200.synth import make_pair, to_bgr
+    l, r, _ = make_pair(c["H"], c["W"], max(c["prm"]["numDisparities"], 16), seed=c["seed"])
+    rng = np.random.default_rng(5000 + c["seed"])
+    out = []
+    for g in (l, r):
+        bgr = to_bgr(g).astype(np.int16) + rng.integers(-12, 13, g.shape + (3,))
+        out.append(np.clip(bgr, 0, 255).astype(np.uint8))
+    return out[0], out[1]
+
+
 BM_CASES = [
     dict(H=60, W=120, seed=31, numDisparities=16, blockSize=9),
     dict(H=72, W=150, seed=32, numDisparities=64, blockSize=15),

@@ -5,7 +5,7 @@ import pytest
 
 import oracle
 from stereovision_b200.synth import make_pair, to_bgr
-from tests.golden_cases import SGBM_CASES
+from tests.golden_cases import SGBM_CASES, SGBM_COLOR_CASES, color_pair
 
 
 @pytest.mark.parametrize("i", range(len(SGBM_CASES)))
@@ -16,6 +16,14 @@ def test_sgbm_oracle_matches_golden(golden, i):
     ref = golden[f"sgbm_{i}"]
     assert got.dtype == np.int16 and got.shape == ref.shape
     assert int((got != ref).sum()) == 0          # bit-exact
+
+
+@pytest.mark.parametrize("i", range(len(SGBM_COLOR_CASES)))
+def test_sgbm_color_oracle_matches_golden(golden, i):
+    c = SGBM_COLOR_CASES[i]
+    l, r = color_pair(c)
+    got = oracle.sgbm_compute(l, r, **c["prm"])
+    assert got.shape == l.shape[:2] and int((got != golden[f"sgbm_color_{i}"]).sum()) == 0
 
 
 def test_remap_gray_oracle_matches_golden(golden):
@@ -53,7 +61,7 @@ def test_sgbm_oracle_vs_live_cv2_random(have_cv2):
     for it in range(12):
         D = int(rng.choice([16, 32, 48]))
         bs = int(rng.choice([3, 5, 7]))
-        mode = int(rng.choice([0, 1, 2]))
+        mode = int(rng.choice([0, 1, 2, 3]))
         minD = 0 if mode == 2 else int(rng.choice([0, -8, 4]))
         H, W = int(rng.integers(40, 80)), int(rng.integers(D + 40, D + 120))
         prm = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=8 * bs * bs, P2=32 * bs * bs,

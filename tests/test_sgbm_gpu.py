@@ -7,7 +7,7 @@ import pytest
 import oracle
 import stereovision_b200 as svb
 from stereovision_b200.synth import make_pair, make_batch
-from tests.golden_cases import SGBM_CASES
+from tests.golden_cases import SGBM_CASES, SGBM_COLOR_CASES, color_pair
 
 pytestmark = pytest.mark.gpu
 
@@ -35,6 +35,25 @@ def test_sgbm_matches_golden_and_oracle(golden, i):
                f"raw mismatches {int((raw != st['raw']).sum())}, final {int((got != ref).sum())}")
         raise AssertionError(msg)
     assert np.array_equal(got, golden[f"sgbm_{i}"])
+
+
+@pytest.mark.parametrize("i", range(len(SGBM_COLOR_CASES)))
+def test_sgbm_color_matches_golden_and_oracle(golden, i):
+    """3-channel input: [H,W,3] like cv2, [B,H,W,3] batched, host and device paths."""
+    torch = _torch()
+    c = SGBM_COLOR_CASES[i]
+    l, r = color_pair(c)
+    m = svb.StereoSGBM_create(**c["prm"])
+    got = m.compute(l, r)
+    assert got.dtype == np.int16 and got.shape == l.shape[:2]
+    assert np.array_equal(got, oracle.sgbm_compute(l, r, **c["prm"]))
+    assert np.array_equal(got, golden[f"sgbm_color_{i}"])
+    L2, R2 = np.stack([l, l[::-1].copy()]), np.stack([r, r[::-1].copy()])
+    dev = m.compute(torch.from_numpy(L2).cuda(), torch.from_numpy(R2).cuda()).cpu().numpy()
+    assert dev.shape == L2.shape[:3] and np.array_equal(dev[0], got)
+    assert np.array_equal(dev[1], oracle.sgbm_compute(L2[1], R2[1], **c["prm"]))
+    with pytest.raises(ValueError):
+        svb.StereoBM_create(16, 9).compute(l, r)
 
 
 @pytest.mark.parametrize("mode", [0, 1, 2, 3])

@@ -100,6 +100,12 @@ int svb_bm_compute_dev(svb_bm_t* h, const uint8_t* left_dev, const uint8_t* righ
 int svb_bm_compute_host(svb_bm_t* h, const uint8_t* left_host, const uint8_t* right_host,
                         int B, int H, int W, int16_t* disp_host);
 int svb_bm_last_launches(const svb_bm_t* h);
+/* cv2.validateDisparity(disparity, cost, minDisparity, numberOfDisparities, disp12MaxDiff) (calib3d; what
+ * StereoBM runs when disp12MaxDiff >= 0).  disp s16 [B,H,W] x16 fixed point, modified in place; cost s16
+ * (cost_is_s32 == 0) or s32 [B,H,W]; scratch: B*H*W*10 bytes of device memory. */
+int svb_validate_disparity_dev(int16_t* disp_dev, const void* cost_dev, int cost_is_s32, int B, int H, int W,
+                               int minDisparity, int numberOfDisparities, int disp12MaxDiff,
+                               void* scratch_dev, void* stream);
 
 /* ---- cv2.remap(src, map1 CV_16SC2, map2 CV_16UC1, INTER_LINEAR), BORDER_CONSTANT 0
  *      (depth_map.py:815-826, fused_depth_map.py:480-491); to_gray!=0 fuses

@@ -156,3 +156,13 @@ def bm_compute(left, right, numDisparities=64, blockSize=21, minDisparity=0, pre
     if rc != 0:
         raise ValueError(f"orc_bm_compute rejected the parameters (code {rc})")
     return disp
+
+
+def validate_disparity(disp, cost, minDisparity, numberOfDisparities, disp12MaxDiff=1):
+    """cv2.validateDisparity restated (returns a validated copy)."""
+    out = np.ascontiguousarray(disp, np.int16).copy()
+    c = np.ascontiguousarray(cost, np.int32)
+    assert out.ndim == 2 and c.shape == out.shape
+    lib().orc_validate_disparity(_p(out, ctypes.c_int16), _p(c, ctypes.c_int32), out.shape[0], out.shape[1],
+                                 int(minDisparity), int(numberOfDisparities), int(disp12MaxDiff))
+    return out

@@ -39,6 +39,39 @@ void orc_bm_prefilter_xsobel(const uint8_t* src, int H, int W, int cap, uint8_t*
     }
 }
 
+/* cv2.validateDisparity (calib3d; StereoBM runs it when disp12MaxDiff >= 0): right-view map by scatter-min
+ * of the cost at x - round(d/16) (first x wins ties), then a pixel is dropped iff BOTH roundings of its
+ * disparity land on right-view entries that disagree by more than disp12MaxDiff*16.  Pinned bit-exact
+ * against the public cv2.validateDisparity. */
+void orc_validate_disparity(int16_t* disp, const int* cost, int H, int W, int minD, int D, int disp12MaxDiff)
+{
+    const int FILTERED = (minD - 1) * 16;
+    const int maxD = minD + D, minX1 = maxD > 0 ? maxD : 0, maxX1 = W + (minD < 0 ? minD : 0);
+    const int d12 = disp12MaxDiff * 16;
+    int* d2 = (int*)malloc(sizeof(int) * 2 * (size_t)W);
+    int* c2 = d2 + W;
+    for (int y = 0; y < H; ++y) {
+        int16_t* dp = disp + (size_t)y * W;
+        for (int x = 0; x < W; ++x) { d2[x] = FILTERED; c2[x] = 0x7fffffff; }
+        for (int x = minX1; x < maxX1; ++x) {
+            const int d = dp[x], c = cost[(size_t)y * W + x];
+            if (d == FILTERED) continue;
+            const int x2 = x - ((d + 8) >> 4);
+            if (x2 < 0 || x2 >= W) continue;
+            if (c2[x2] > c) { c2[x2] = c; d2[x2] = d; }
+        }
+        for (int x = minX1; x < maxX1; ++x) {
+            const int d = dp[x];
+            if (d == FILTERED) continue;
+            const int x0 = x - (d >> 4), x1 = x - ((d + 15) >> 4);
+            if (0 <= x0 && x0 < W && d2[x0] > FILTERED && abs(d2[x0] - d) > d12 &&
+                0 <= x1 && x1 < W && d2[x1] > FILTERED && abs(d2[x1] - d) > d12)
+                dp[x] = (int16_t)FILTERED;
+        }
+    }
+    free(d2);
+}
+
 /* returns 0, or <0 for what cv2 rejects */
 int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W, const orc_bm_params* p, int16_t* disp)
 {
@@ -60,11 +93,16 @@ int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W, cons
     orc_bm_prefilter_xsobel(left, H, W, cap, L);
     orc_bm_prefilter_xsobel(right, H, W, cap, R);
     int* sad = (int*)malloc(sizeof(int) * (D + 2));
+    int* cost = (int*)calloc((size_t)H * W, sizeof(int));
     const int x_lo = lofs + r, x_hi = W - r;              /* valid ROI columns */
     for (int y = r; y < H - r; ++y)
         for (int xp = 0; xp < width1; ++xp) {
             const int x = xp + lofs;
-            if (x < x_lo || x >= x_hi) continue;
+            /* cv2 evaluates every column of the width1 domain (windows clamp at the image sides); the
+             * columns outside the valid ROI only matter as candidates of validateDisparity below and
+             * are blanked afterwards */
+            if ((x < x_lo || x >= x_hi) && p->disp12MaxDiff < 0) continue;
+            if (x >= W) continue;                          /* minDisparity > 0: cv2 runs past the row end there */
             int ts = 0;
             for (int k = 0; k < D; ++k) sad[k + 1] = 0;
             for (int j = -r; j <= r; ++j) {
@@ -89,11 +127,21 @@ int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W, cons
                 if (k < D) continue;
             }
             sad[0] = sad[2]; sad[D + 1] = sad[D - 1];
+            cost[(size_t)y * W + x] = sad[mind + 1];
             const int pp = sad[mind + 2], n = sad[mind], dd = pp + n - 2 * sad[mind + 1] + abs(pp - n);
             disp[(size_t)y * W + x] =
                 (int16_t)((((D - mind - 1 + minD) * 256 + (dd != 0 ? (pp - n) * 256 / dd : 0) + 15) >> 4));
         }
-    free(L); free(R); free(sad);
+    /* stereobm.cpp `if (disp12MaxDiff >= 0) validateDisparity(...)` with the winning SAD as cost; the
+     * columns outside the valid ROI took part as candidates (probed, 40/40 random cv2 cases) and are blanked
+     * afterwards. */
+    if (p->disp12MaxDiff >= 0) {
+        orc_validate_disparity(disp, cost, H, W, minD, D, p->disp12MaxDiff);
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x)
+                if (x < x_lo || x >= x_hi) disp[(size_t)y * W + x] = (int16_t)FILTERED;
+    }
+    free(L); free(R); free(sad); free(cost);
     if (p->speckleWindowSize > 0)
         orc_filter_speckles_s16(disp, H, W, FILTERED, p->speckleWindowSize, p->speckleRange);
     return 0;

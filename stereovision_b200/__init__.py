@@ -9,7 +9,7 @@ from .cv_api import (  # noqa: F401
     StereoSGBM_MODE_SGBM, StereoSGBM_MODE_HH, StereoSGBM_MODE_SGBM_3WAY, StereoSGBM_MODE_HH4,
     INTER_LINEAR, COLOR_BGR2GRAY,
     StereoSGBM, StereoBM, StereoSGBM_create, StereoBM_create,
-    remap, cvtColor, medianBlur, filterSpeckles, reprojectImageTo3D, disparity_to_depth,
+    remap, cvtColor, medianBlur, filterSpeckles, validateDisparity, reprojectImageTo3D, disparity_to_depth,
     initUndistortRectifyMap, CV_16SC2,
     release_workspaces,
 )

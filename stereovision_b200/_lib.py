@@ -58,6 +58,8 @@ SIGNATURES = {
     "svb_bm_compute_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "svb_bm_compute_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "svb_bm_last_launches": (c_int, [c_void_p]),
+    "svb_validate_disparity_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                           c_void_p, c_void_p]),
     "svb_remap_u8_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
                                  c_void_p, c_int, c_void_p]),
     "svb_bgr2gray_dev": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p]),

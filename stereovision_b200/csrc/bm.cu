@@ -46,7 +46,8 @@ __device__ __forceinline__ uint32_t bm_absdiff(uint32_t U2, uint32_t nU2, uint32
 
 template <int NP>
 __global__ void __launch_bounds__(1024) k_bm(const uint8_t* __restrict__ lp, const uint32_t* __restrict__ rdesc,
-                                             BmGeo g, int TY, int XSEG, int16_t* __restrict__ disp)
+                                             BmGeo g, int TY, int XSEG, int16_t* __restrict__ disp,
+                                             int16_t* __restrict__ cost)
 {
     extern __shared__ uint32_t smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, NW = blockDim.x >> 5;
@@ -113,7 +114,9 @@ __global__ void __launch_bounds__(1024) k_bm(const uint8_t* __restrict__ lp, con
                 for (int k = 0; k < NP; ++k) s[k] += hsb[((warp + t2) * NP + k) * 32 + lane];
                 ts += (int)tsb[warp + t2];
             }
-            const bool roi = row_ok && x >= g.lofs + r && x < W - r;
+            // with a cost map (disp12MaxDiff >= 0) every column of the width1 domain is evaluated: cv2 lets the
+            // columns outside the valid ROI vote in validateDisparity and blanks them afterwards
+            const bool roi = row_ok && x < W && (cost != nullptr || (x >= g.lofs + r && x < W - r));
             if (roi && ts >= g.tex) {
                 // argmin over BM index kk = D-1-d' (lowest kk = largest disparity wins ties)
                 uint32_t key = 0xffffffffu;
@@ -150,6 +153,7 @@ __global__ void __launch_bounds__(1024) k_bm(const uint8_t* __restrict__ lp, con
                         const int dd = p + n - 2 * minsad + abs(p - n);
                         const int v = ((D - mind - 1 + g.minD) * 256 + (dd != 0 ? (p - n) * 256 / dd : 0) + 15) >> 4;
                         disp[((size_t)b * g.H + y) * W + x] = (int16_t)v;
+                        if (cost) cost[((size_t)b * g.H + y) * W + x] = (int16_t)minsad;
                     }
                     __syncwarp();
                 }
@@ -157,6 +161,82 @@ __global__ void __launch_bounds__(1024) k_bm(const uint8_t* __restrict__ lp, con
         }
         __syncthreads();
     }
+}
+
+// ------------------------------------------------------------------------------------------
+// cv2.validateDisparity (calib3d; StereoBM calls it when disp12MaxDiff >= 0): per row, the right-view map
+// is a scatter-min of the cost at x2 = x - round(d/16) (lowest x wins ties: key = cost | x | d), then a
+// pixel is dropped iff BOTH roundings of its disparity hit right-view entries that differ by more than
+// disp12MaxDiff*16.  Afterwards the columns outside [keep_lo, keep_hi) are blanked (StereoBM's ROI).
+// ------------------------------------------------------------------------------------------
+template <typename CT>
+__global__ void __launch_bounds__(256) k_validate_scatter(const int16_t* __restrict__ disp, const CT* __restrict__ cost,
+                                                          int H, int W, int minX1, int maxX1, int inv,
+                                                          unsigned long long* __restrict__ keys)
+{
+    const int x = minX1 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= maxX1) return;
+    const size_t row = ((size_t)blockIdx.z * H + blockIdx.y) * W;
+    const int d = disp[row + x];
+    if (d == inv) return;
+    const int x2 = x - ((d + 8) >> 4);
+    if (x2 < 0 || x2 >= W) return;                           // cannot happen for d inside [minD, maxD)
+    const unsigned long long key = ((unsigned long long)((uint32_t)(int)cost[row + x] ^ 0x80000000u) << 32) |
+                                   ((unsigned long long)(uint32_t)x << 16) | (uint16_t)d;
+    atomicMin(keys + row + x2, key);
+}
+
+__global__ void __launch_bounds__(256) k_validate_check(const int16_t* __restrict__ src, int16_t* __restrict__ dst,
+                                                        int H, int W, int minX1, int maxX1, int inv, int d12,
+                                                        int keep_lo, int keep_hi,
+                                                        const unsigned long long* __restrict__ keys)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= W) return;
+    const size_t row = ((size_t)blockIdx.z * H + blockIdx.y) * W;
+    int d = src[row + x];
+    if (x >= minX1 && x < maxX1 && d != inv) {
+        const int x0 = x - (d >> 4), x1 = x - ((d + 15) >> 4);
+        auto bad = [&](int xx) {
+            if (xx < 0 || xx >= W) return false;
+            const unsigned long long k = keys[row + xx];
+            if (k == ~0ull) return false;                    // nothing landed there
+            const int d2 = (int16_t)(uint16_t)k;
+            return d2 > inv && abs(d2 - d) > d12;
+        };
+        if (bad(x0) && bad(x1)) d = inv;
+    }
+    if (x < keep_lo || x >= keep_hi) d = inv;
+    dst[row + x] = (int16_t)d;
+}
+
+// disp s16 [B,H,W] in place; cost s16 (cost_is_s32 == 0) or s32 [B,H,W]; scratch: B*H*W*8 bytes (keys) + B*H*W*2
+// bytes (a copy of the input, so that the check does not read what it overwrites).
+extern "C" int svb_validate_disparity_dev(int16_t* disp, const void* cost, int cost_is_s32, int B, int H, int W,
+                                          int minDisparity, int numberOfDisparities, int disp12MaxDiff,
+                                          void* scratch, void* stream)
+{
+    if (!disp || !cost || !scratch) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
+    if (B <= 0 || H <= 0 || W <= 0 || W > 65535) { svb_set_error("bad shape"); return SVB_ERR_PARAM; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int maxD = minDisparity + numberOfDisparities;
+    const int minX1 = std::max(maxD, 0), maxX1 = W + std::min(minDisparity, 0);
+    const int inv = (minDisparity - 1) * 16;
+    const size_t npix = (size_t)B * H * W;
+    unsigned long long* keys = (unsigned long long*)scratch;
+    int16_t* copy = (int16_t*)(keys + npix);
+    SVB_CUDA(cudaMemsetAsync(keys, 0xff, npix * 8, st));
+    SVB_CUDA(cudaMemcpyAsync(copy, disp, npix * 2, cudaMemcpyDeviceToDevice, st));
+    if (maxX1 > minX1) {
+        dim3 grid(svb_ceil_div(maxX1 - minX1, 256), H, B);
+        if (cost_is_s32) k_validate_scatter<int><<<grid, 256, 0, st>>>(copy, (const int*)cost, H, W, minX1, maxX1, inv, keys);
+        else k_validate_scatter<int16_t><<<grid, 256, 0, st>>>(copy, (const int16_t*)cost, H, W, minX1, maxX1, inv, keys);
+        SVB_LAUNCH_CHECK();
+    }
+    k_validate_check<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(copy, disp, H, W, minX1, maxX1, inv,
+                                                                       disp12MaxDiff * 16, 0, W, keys);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
 }
 
 __global__ void k_bm_fill(int16_t* p, size_t n, int16_t v)
@@ -187,11 +267,14 @@ static int bm_geo(const svb_bm_params& p, int H, int W, BmGeo& g, bool& trivial)
     if (p.preFilterCap < 1 || p.preFilterCap > 63) { svb_set_error("preFilterCap must be within 1..63"); return SVB_ERR_PARAM; }
     if (p.textureThreshold < 0) { svb_set_error("texture threshold must be non-negative"); return SVB_ERR_PARAM; }
     if (p.uniquenessRatio < 0) { svb_set_error("uniqueness ratio must be non-negative"); return SVB_ERR_PARAM; }
-    if (p.disp12MaxDiff >= 0) { svb_set_error("StereoBM disp12MaxDiff >= 0 (validateDisparity) is not implemented"); return SVB_ERR_UNSUPPORTED; }
     if (p.blockSize > 31) { svb_set_error("blockSize %d > 31 unsupported by the BM kernel", p.blockSize); return SVB_ERR_UNSUPPORTED; }
     if (p.numDisparities > 512) { svb_set_error("numDisparities > 512 unsupported"); return SVB_ERR_UNSUPPORTED; }
     if ((long long)p.blockSize * p.blockSize * 2 * p.preFilterCap > 65535) {
         svb_set_error("blockSize^2 * 2*preFilterCap exceeds the 16-bit SAD range of the BM kernel"); return SVB_ERR_UNSUPPORTED;
+    }
+    if (p.disp12MaxDiff >= 0 && (long long)p.blockSize * p.blockSize * 2 * p.preFilterCap > 32767) {
+        svb_set_error("disp12MaxDiff >= 0: blockSize^2 * 2*preFilterCap exceeds the int16 cost map cv2 validates with");
+        return SVB_ERR_UNSUPPORTED;
     }
     g.H = H; g.W = W; g.D = p.numDisparities; g.NP = (g.D + 63) / 64; g.minD = p.minDisparity;
     g.bs = p.blockSize; g.r = p.blockSize / 2; g.cap = p.preFilterCap; g.tex = p.textureThreshold;
@@ -225,7 +308,8 @@ extern "C" void svb_bm_destroy(svb_bm_t* h)
 extern "C" int svb_bm_last_launches(const svb_bm_t* h) { return h ? h->launches : 0; }
 
 template <int NP>
-static int bm_launch(const BmGeo& g, const uint8_t* lp, const uint32_t* rdesc, int nb, int16_t* disp, cudaStream_t st)
+static int bm_launch(const BmGeo& g, const uint8_t* lp, const uint32_t* rdesc, int nb, int16_t* disp, int16_t* cost,
+                     cudaStream_t st)
 {
     int TY = std::min(16, 32 - 2 * g.r);
     const int NW = TY + 2 * g.r;
@@ -233,7 +317,7 @@ static int bm_launch(const BmGeo& g, const uint8_t* lp, const uint32_t* rdesc, i
     const int XSEG = 160;
     SVB_CUDA(cudaFuncSetAttribute(k_bm<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(svb_ceil_div(g.width1, XSEG), svb_ceil_div(g.H, TY), nb);
-    k_bm<NP><<<grid, 32 * NW, smem, st>>>(lp, rdesc, g, TY, XSEG, disp);
+    k_bm<NP><<<grid, 32 * NW, smem, st>>>(lp, rdesc, g, TY, XSEG, disp, cost);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
@@ -254,25 +338,45 @@ extern "C" int svb_bm_compute_dev(svb_bm_t* h, const uint8_t* left, const uint8_
     if (trivial) return SVB_OK;
     const size_t lp_bytes = (npix + 255) & ~(size_t)255;
     const size_t rd_bytes = ((size_t)B * H * 4 * g.Wh * 4 + 255) & ~(size_t)255;
-    const size_t sc_bytes = h->prm.speckleWindowSize > 0 ? npix * 8 : 0;
+    const bool validate = h->prm.disp12MaxDiff >= 0;
+    // scratch shared by validateDisparity (keys u64 + input copy s16 + cost s16) and the speckle filter (2 x s32)
+    const size_t sc_bytes = validate ? npix * 12 : (h->prm.speckleWindowSize > 0 ? npix * 8 : 0);
     rc = h->ws.reserve(lp_bytes + rd_bytes + sc_bytes);
     if (rc != SVB_OK) return rc;
     uint8_t* lp = (uint8_t*)h->ws.p;
     uint32_t* rdesc = (uint32_t*)((char*)h->ws.p + lp_bytes);
     k_bm_prefilter<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(left, right, g, lp, rdesc);
     SVB_LAUNCH_CHECK(); h->launches++;
+    char* scratch = (char*)h->ws.p + lp_bytes + rd_bytes;
+    int16_t* cost = validate ? (int16_t*)(scratch + npix * 10) : nullptr;
     switch (g.NP) {
-#define CASE(N) case N: rc = bm_launch<N>(g, lp, rdesc, B, disp, st); break;
+#define CASE(N) case N: rc = bm_launch<N>(g, lp, rdesc, B, disp, cost, st); break;
         CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
 #undef CASE
         default: svb_set_error("bad NP"); rc = SVB_ERR_UNSUPPORTED;
     }
     if (rc != SVB_OK) return rc;
     h->launches++;
+    if (validate) {
+        // the winning SAD fits int16 (checked in bm_geo); columns outside the valid ROI are blanked by the check
+        unsigned long long* keys = (unsigned long long*)scratch;
+        int16_t* copy = (int16_t*)(keys + npix);
+        const int maxD = g.minD + g.D, minX1 = std::max(maxD, 0), maxX1 = W + std::min(g.minD, 0);
+        SVB_CUDA(cudaMemsetAsync(keys, 0xff, npix * 8, st));
+        SVB_CUDA(cudaMemcpyAsync(copy, disp, npix * 2, cudaMemcpyDeviceToDevice, st));
+        if (maxX1 > minX1) {
+            k_validate_scatter<int16_t><<<dim3(svb_ceil_div(maxX1 - minX1, 256), H, B), 256, 0, st>>>(
+                copy, cost, H, W, minX1, maxX1, g.FILTERED, keys);
+            SVB_LAUNCH_CHECK(); h->launches++;
+        }
+        k_validate_check<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(
+            copy, disp, H, W, minX1, maxX1, g.FILTERED, h->prm.disp12MaxDiff * 16, g.lofs + g.r, W - g.r, keys);
+        SVB_LAUNCH_CHECK(); h->launches++;
+    }
     if (h->prm.speckleWindowSize > 0) {
         // stereobm.cpp passes speckleRange unscaled (SGBM scales it by 16) -- probed on cv2 4.13
         rc = svb_filter_speckles_s16_dev(disp, B, H, W, g.FILTERED, h->prm.speckleWindowSize, h->prm.speckleRange,
-                                         (int32_t*)((char*)h->ws.p + lp_bytes + rd_bytes), st);
+                                         (int32_t*)scratch, st);
         if (rc != SVB_OK) return rc;
         h->launches += 4;
     }

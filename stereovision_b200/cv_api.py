@@ -352,6 +352,30 @@ def filterSpeckles(img, newVal, maxSpeckleSize, maxDiff):
     return img
 
 
+def validateDisparity(disparity, cost, minDisparity, numberOfDisparities, disp12MaxDiff=1):
+    """cv2.validateDisparity(disparity, cost, minDisparity, numberOfDisparities[, disp12MaxDiff]): the
+    left-right check StereoBM runs when disp12MaxDiff >= 0.  disparity int16 (x16), cost int16 or int32,
+    [H,W] or [B,H,W]; modified in place like cv2 and returned."""
+    torch = _torch()
+    d, was = _to_dev(disparity)
+    c, _ = _to_dev(cost)
+    if d.dtype != torch.int16 or d.ndim not in (2, 3):
+        raise ValueError("disparity: expected int16 [H,W] or [B,H,W]")
+    if c.dtype not in (torch.int16, torch.int32) or tuple(c.shape) != tuple(d.shape):
+        raise ValueError("cost: expected int16 or int32 of the disparity's shape")
+    B = 1 if d.ndim == 2 else int(d.shape[0])
+    H, W = int(d.shape[-2]), int(d.shape[-1])
+    _ensure_device(d.device.index)
+    scratch = torch.empty(10 * d.numel() + 16, dtype=torch.uint8, device=d.device)
+    _lib.check(_lib.lib().svb_validate_disparity_dev(d.data_ptr(), c.data_ptr(), int(c.dtype == torch.int32), B, H, W,
+                                                     int(minDisparity), int(numberOfDisparities), int(disp12MaxDiff),
+                                                     scratch.data_ptr(), _stream_ptr()))
+    if was:
+        return d
+    disparity[...] = d.cpu().numpy()
+    return disparity
+
+
 def reprojectImageTo3D(disparity, Q, handleMissingValues=False):
     """cv2.reprojectImageTo3D(disparity, Q): int16 input is NOT divided by 16."""
     torch = _torch()

@@ -26,11 +26,24 @@ def main():
         l, r = color_pair(c)
         out[f"sgbm_color_{i}"] = cv2.StereoSGBM_create(**c["prm"]).compute(l, r)
     for i, c in enumerate(BM_CASES):
-        l, r, _ = make_pair(c["H"], c["W"], max(c["numDisparities"], 16), seed=c["seed"])
+        l, r, _ = make_pair(c["H"], c["W"], max(c["numDisparities"], 16), seed=c["seed"], noise=c.get("noise", 6))
         bm = cv2.StereoBM_create(c["numDisparities"], c["blockSize"])
         for k, v in c.get("set", {}).items():
             getattr(bm, "set" + k)(v)
         out[f"bm_{i}"] = bm.compute(l, r)
+    # cv2.validateDisparity on a BM disparity with seeded int16 / int32 cost maps
+    c = BM_CASES[0]
+    l, r, _ = make_pair(c["H"], c["W"], 16, seed=c["seed"], noise=25)
+    bm = cv2.StereoBM_create(c["numDisparities"], c["blockSize"]); bm.setUniquenessRatio(0); bm.setTextureThreshold(0)
+    d = bm.compute(l, r)
+    rng = np.random.default_rng(77)
+    out["validate_in"] = d
+    out["validate_cost16"] = rng.integers(0, 40, d.shape).astype(np.int16)      # many ties: lowest x must win
+    out["validate_cost32"] = rng.integers(-100000, 100000, d.shape).astype(np.int32)
+    for k, (cost, d12) in enumerate(((out["validate_cost16"], 1), (out["validate_cost32"], 0), (out["validate_cost16"], 4))):
+        v = d.copy()
+        cv2.validateDisparity(v, cost, 0, c["numDisparities"], d12)
+        out[f"validate_out_{k}"] = v
     # remap + gray with maps from the reference's own recipe (depth_map.py:625-638)
     H, W = 120, 160
     calib = synth_calibration(W, H)

@@ -58,6 +58,12 @@ BM_CASES = [
     dict(H=64, W=128, seed=34, numDisparities=32, blockSize=7, set={"MinDisparity": -4, "UniquenessRatio": 0}),
     dict(H=64, W=140, seed=35, numDisparities=48, blockSize=11,
          set={"TextureThreshold": 50, "SpeckleWindowSize": 30, "SpeckleRange": 4}),
+    # disp12MaxDiff >= 0 (cv2.validateDisparity inside StereoBM)
+    dict(H=81, W=98, seed=36, numDisparities=32, blockSize=9, noise=25,
+         set={"Disp12MaxDiff": 1, "UniquenessRatio": 0, "TextureThreshold": 0}),
+    dict(H=70, W=160, seed=37, numDisparities=64, blockSize=15, noise=20,
+         set={"Disp12MaxDiff": 0, "MinDisparity": -16, "SpeckleWindowSize": 30, "SpeckleRange": 4}),
+    dict(H=64, W=141, seed=38, numDisparities=48, blockSize=7, noise=12, set={"Disp12MaxDiff": 3}),
 ]
 
 

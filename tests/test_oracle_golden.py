@@ -75,7 +75,7 @@ def test_sgbm_oracle_vs_live_cv2_random(have_cv2):
 def _bm_kwargs(c):
     kw = dict(numDisparities=c["numDisparities"], blockSize=c["blockSize"])
     m = {"MinDisparity": "minDisparity", "UniquenessRatio": "uniquenessRatio", "TextureThreshold": "textureThreshold",
-         "SpeckleWindowSize": "speckleWindowSize", "SpeckleRange": "speckleRange", "PreFilterCap": "preFilterCap"}
+         "SpeckleWindowSize": "speckleWindowSize", "SpeckleRange": "speckleRange", "PreFilterCap": "preFilterCap", "Disp12MaxDiff": "disp12MaxDiff"}
     for k, v in c.get("set", {}).items():
         kw[m[k]] = v
     return kw
@@ -84,9 +84,16 @@ def _bm_kwargs(c):
 def test_bm_oracle_matches_golden(golden):
     from tests.golden_cases import BM_CASES
     for i, c in enumerate(BM_CASES):
-        l, r, _ = make_pair(c["H"], c["W"], max(c["numDisparities"], 16), seed=c["seed"])
+        l, r, _ = make_pair(c["H"], c["W"], max(c["numDisparities"], 16), seed=c["seed"], noise=c.get("noise", 6))
         got = oracle.bm_compute(l, r, **_bm_kwargs(c))
         assert np.array_equal(got, golden[f"bm_{i}"]), i
+
+
+def test_validate_disparity_oracle_matches_golden(golden):
+    d = golden["validate_in"]
+    for k, (cost, d12) in enumerate(((golden["validate_cost16"], 1), (golden["validate_cost32"], 0),
+                                     (golden["validate_cost16"], 4))):
+        assert np.array_equal(oracle.validate_disparity(d, cost, 0, 16, d12), golden[f"validate_out_{k}"]), k
 
 
 MAP_TAGS = {"l5": ("maps_R1", "maps_P1"), "r5": ("maps_R2", "maps_P2"), "l8": ("maps_R1", "maps_P1"),

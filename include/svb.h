@@ -91,6 +91,8 @@ int svb_sgbm_get_profile(svb_sgbm_t* h, int max_stages, char* names, float* ms, 
 typedef struct {
     int minDisparity, numDisparities, blockSize, preFilterCap, textureThreshold;
     int uniquenessRatio, speckleWindowSize, speckleRange, disp12MaxDiff;
+    int preFilterType;   /* cv2.STEREO_BM_PREFILTER_NORMALIZED_RESPONSE = 0, _XSOBEL = 1 (cv2's default) */
+    int preFilterSize;   /* window of the normalized-response prefilter: odd, 5..255 (cv2's default 9) */
 } svb_bm_params;
 typedef struct svb_bm svb_bm_t;
 int svb_bm_create(const svb_bm_params* p, svb_bm_t** out);

@@ -28,7 +28,7 @@ class _SgbmParams(ctypes.Structure):
 class _BmParams(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int) for n in (
         "minDisparity", "numDisparities", "blockSize", "preFilterCap", "textureThreshold",
-        "uniquenessRatio", "speckleWindowSize", "speckleRange", "disp12MaxDiff")]
+        "uniquenessRatio", "speckleWindowSize", "speckleRange", "disp12MaxDiff", "preFilterType", "preFilterSize")]
 
 
 def build(force=False):
@@ -142,14 +142,15 @@ def reproject_image_to_3d(disp, Q, handleMissingValues=False):
 
 
 def bm_compute(left, right, numDisparities=64, blockSize=21, minDisparity=0, preFilterCap=31,
-               textureThreshold=10, uniquenessRatio=15, speckleWindowSize=0, speckleRange=0, disp12MaxDiff=-1):
+               textureThreshold=10, uniquenessRatio=15, speckleWindowSize=0, speckleRange=0, disp12MaxDiff=-1,
+               preFilterType=1, preFilterSize=9):
     """cv2.StereoBM_create(numDisparities, blockSize).compute(left, right) restated."""
     left = np.ascontiguousarray(left, np.uint8)
     right = np.ascontiguousarray(right, np.uint8)
     assert left.shape == right.shape and left.ndim == 2
     H, W = left.shape
     prm = _BmParams(minDisparity, numDisparities, blockSize, preFilterCap, textureThreshold,
-                    uniquenessRatio, speckleWindowSize, speckleRange, disp12MaxDiff)
+                    uniquenessRatio, speckleWindowSize, speckleRange, disp12MaxDiff, preFilterType, preFilterSize)
     disp = np.empty((H, W), np.int16)
     rc = lib().orc_bm_compute(_p(left, ctypes.c_uint8), _p(right, ctypes.c_uint8), H, W, ctypes.byref(prm),
                               _p(disp, ctypes.c_int16))

@@ -13,6 +13,7 @@
 typedef struct {
     int minDisparity, numDisparities, blockSize, preFilterCap, textureThreshold;
     int uniquenessRatio, speckleWindowSize, speckleRange, disp12MaxDiff;
+    int preFilterType, preFilterSize;   /* cv2.STEREO_BM_PREFILTER_NORMALIZED_RESPONSE = 0, _XSOBEL = 1 (default) */
 } orc_bm_params;
 
 void orc_filter_speckles_s16(int16_t* img, int H, int W, int newVal, int maxSpeckleSize, int maxDiff);
@@ -35,6 +36,31 @@ void orc_bm_prefilter_xsobel(const uint8_t* src, int H, int W, int cap, uint8_t*
         for (int x = 1; x < W - 1; ++x) {
             int g = (r0[x + 1] - r0[x - 1]) + 2 * (r1[x + 1] - r1[x - 1]) + (r2[x + 1] - r2[x - 1]);
             d[x] = (uint8_t)(bclamp(g, -cap, cap) + cap);
+        }
+    }
+}
+
+/* stereobm.cpp prefilterNorm (PREFILTER_NORMALIZED_RESPONSE): centre-weighted cross minus the mean of a
+ * preFilterSize^2 box (replicate borders in both), in 10-bit fixed point, clipped to [0, 2*cap]. */
+void orc_bm_prefilter_norm(const uint8_t* src, int H, int W, int winsize, int cap, uint8_t* dst)
+{
+    const int w2 = winsize / 2;
+    int scale_g = winsize * winsize / 8;
+    const int scale_s = (1024 + scale_g) / (scale_g * 2);
+    scale_g *= scale_s;
+    for (int y = 0; y < H; ++y) {
+        const uint8_t* prev = src + (size_t)(y > 0 ? y - 1 : 0) * W;
+        const uint8_t* curr = src + (size_t)y * W;
+        const uint8_t* next = src + (size_t)(y < H - 1 ? y + 1 : H - 1) * W;
+        for (int x = 0; x < W; ++x) {
+            int sum = 0;
+            for (int j = -w2; j <= w2; ++j) {
+                const uint8_t* row = src + (size_t)bclamp(y + j, 0, H - 1) * W;
+                for (int i = -w2; i <= w2; ++i) sum += row[bclamp(x + i, 0, W - 1)];
+            }
+            const int l = curr[x > 0 ? x - 1 : x], r = curr[x < W - 1 ? x + 1 : x];
+            const int val = ((curr[x] * 4 + l + r + prev[x] + next[x]) * scale_g - sum * scale_s) >> 10;
+            dst[(size_t)y * W + x] = (uint8_t)(val < -cap ? 0 : val > cap ? 2 * cap : val + cap);
         }
     }
 }
@@ -80,6 +106,8 @@ int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W, cons
     if (D <= 0 || D % 16 != 0) return -1;
     if (bs < 5 || bs > 255 || bs % 2 == 0 || bs >= W || bs >= H) return -1;
     if (cap < 1 || cap > 63) return -1;
+    if (p->preFilterType != 0 && p->preFilterType != 1) return -1;
+    if (p->preFilterType == 0 && (p->preFilterSize < 5 || p->preFilterSize > 255 || p->preFilterSize % 2 == 0)) return -1;
     if (p->textureThreshold < 0 || p->uniquenessRatio < 0) return -1;
     const int FILTERED = (minD - 1) * 16;
     for (size_t i = 0; i < (size_t)H * W; ++i) disp[i] = (int16_t)FILTERED;
@@ -90,8 +118,13 @@ int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W, cons
 
     uint8_t* L = (uint8_t*)malloc((size_t)H * W);
     uint8_t* R = (uint8_t*)malloc((size_t)H * W);
-    orc_bm_prefilter_xsobel(left, H, W, cap, L);
-    orc_bm_prefilter_xsobel(right, H, W, cap, R);
+    if (p->preFilterType == 0) {
+        orc_bm_prefilter_norm(left, H, W, p->preFilterSize, cap, L);
+        orc_bm_prefilter_norm(right, H, W, p->preFilterSize, cap, R);
+    } else {
+        orc_bm_prefilter_xsobel(left, H, W, cap, L);
+        orc_bm_prefilter_xsobel(right, H, W, cap, R);
+    }
     int* sad = (int*)malloc(sizeof(int) * (D + 2));
     int* cost = (int*)calloc((size_t)H * W, sizeof(int));
     const int x_lo = lofs + r, x_hi = W - r;              /* valid ROI columns */

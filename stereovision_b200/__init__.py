@@ -7,6 +7,7 @@ No CPU fallback: without the built library or a CUDA device, calls raise.
 from .cv_api import (  # noqa: F401
     STEREO_SGBM_MODE_SGBM, STEREO_SGBM_MODE_HH, STEREO_SGBM_MODE_SGBM_3WAY, STEREO_SGBM_MODE_HH4,
     StereoSGBM_MODE_SGBM, StereoSGBM_MODE_HH, StereoSGBM_MODE_SGBM_3WAY, StereoSGBM_MODE_HH4,
+    STEREO_BM_PREFILTER_NORMALIZED_RESPONSE, STEREO_BM_PREFILTER_XSOBEL,
     INTER_LINEAR, COLOR_BGR2GRAY,
     StereoSGBM, StereoBM, StereoSGBM_create, StereoBM_create,
     remap, cvtColor, medianBlur, filterSpeckles, validateDisparity, reprojectImageTo3D, disparity_to_depth,

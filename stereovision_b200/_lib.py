@@ -24,7 +24,7 @@ class SgbmParams(ctypes.Structure):
 class BmParams(ctypes.Structure):
     _fields_ = [(n, c_int) for n in (
         "minDisparity", "numDisparities", "blockSize", "preFilterCap", "textureThreshold",
-        "uniquenessRatio", "speckleWindowSize", "speckleRange", "disp12MaxDiff")]
+        "uniquenessRatio", "speckleWindowSize", "speckleRange", "disp12MaxDiff", "preFilterType", "preFilterSize")]
 
 
 class FuseParams(ctypes.Structure):

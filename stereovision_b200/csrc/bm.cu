@@ -14,15 +14,47 @@
 struct BmGeo {
     int H, W, D, NP, minD, bs, r, cap, tex, uniq, FILTERED;
     int lofs, rofs, width1, Wh;
+    int pft, pfs;              // prefilter type (0 normalized response, 1 x-Sobel) and window
 };
 
+// PREFILTER_NORMALIZED_RESPONSE, pass 1: vertical sums of preFilterSize rows (replicate borders) of both images
+__global__ void __launch_bounds__(256) k_bm_vsum(const uint8_t* __restrict__ left, const uint8_t* __restrict__ right,
+                                                 BmGeo g, uint16_t* __restrict__ vs)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    const int b = blockIdx.z >> 1, side = blockIdx.z & 1;
+    if (x >= g.W) return;
+    const size_t io = (size_t)b * g.H * g.W;
+    const uint8_t* img = (side ? right : left) + io;
+    const int w2 = g.pfs / 2;
+    int s = 0;
+    for (int j = -w2; j <= w2; ++j) s += img[(size_t)min(max(y + j, 0), g.H - 1) * g.W + x];
+    vs[((size_t)side * gridDim.z / 2) * g.H * g.W + io + (size_t)y * g.W + x] = (uint16_t)s;   // <= 255 * 255
+}
+
 __global__ void __launch_bounds__(256) k_bm_prefilter(const uint8_t* __restrict__ left, const uint8_t* __restrict__ right,
-                                                      BmGeo g, uint8_t* __restrict__ lp, uint32_t* __restrict__ rdesc)
+                                                      BmGeo g, uint8_t* __restrict__ lp, uint32_t* __restrict__ rdesc,
+                                                      const uint16_t* __restrict__ vs)
 {
     const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
     const int H = g.H, W = g.W, cap = g.cap;
     if (x >= W) return;
+    // stereobm.cpp prefilterNorm: ((4c + l + r + u + d) * scale_g - boxsum * scale_s) >> 10, clipped to [0, 2 cap]
+    int scale_g = g.pfs * g.pfs / 8;
+    const int scale_s = (1024 + scale_g) / (scale_g * 2);
+    scale_g *= scale_s;
+    const size_t io = (size_t)b * H * W;
     auto pf = [&](const uint8_t* img, int xx) -> int {
+        if (g.pft == 0) {
+            const uint16_t* v = vs + (img == left + io ? 0 : (size_t)gridDim.z * H * W) + io + (size_t)y * W;
+            const int w2 = g.pfs / 2;
+            int sum = 0;
+            for (int i = -w2; i <= w2; ++i) sum += v[min(max(xx + i, 0), W - 1)];
+            const uint8_t* cr = img + (size_t)y * W;
+            const int up = img[(size_t)max(y - 1, 0) * W + xx], dn = img[(size_t)min(y + 1, H - 1) * W + xx];
+            const int val = ((cr[xx] * 4 + cr[max(xx - 1, 0)] + cr[min(xx + 1, W - 1)] + up + dn) * scale_g - sum * scale_s) >> 10;
+            return val < -cap ? 0 : (val > cap ? 2 * cap : val + cap);
+        }
         if (xx <= 0 || xx >= W - 1) return cap;
         if ((H & 1) && y == H - 1) return cap;
         const int ya = y > 0 ? y - 1 : (H > 1 ? 1 : 0), yb = y < H - 1 ? y + 1 : (H > 1 ? H - 2 : 0);
@@ -30,7 +62,6 @@ __global__ void __launch_bounds__(256) k_bm_prefilter(const uint8_t* __restrict_
         const int gx = ((int)r0[xx + 1] - r0[xx - 1]) + 2 * ((int)r1[xx + 1] - r1[xx - 1]) + ((int)r2[xx + 1] - r2[xx - 1]);
         return max(-cap, min(cap, gx)) + cap;
     };
-    const size_t io = (size_t)b * H * W;
     lp[io + (size_t)y * W + x] = (uint8_t)pf(left + io, x);
     const int v0 = pf(right + io, x), v1 = pf(right + io, max(x - 1, 0));
     uint32_t* base = rdesc + (size_t)(b * H + y) * 4 * g.Wh + (size_t)(x & 1) * g.Wh + (x >> 1);
@@ -264,6 +295,12 @@ static int bm_geo(const svb_bm_params& p, int H, int W, BmGeo& g, bool& trivial)
     if (H > 0 && W > 0 && (p.blockSize >= W || p.blockSize >= H)) {
         svb_set_error("SADWindowSize must not be larger than image width or height"); return SVB_ERR_PARAM;
     }
+    if (p.preFilterType != 0 && p.preFilterType != 1) {
+        svb_set_error("preFilterType must be PREFILTER_XSOBEL or PREFILTER_NORMALIZED_RESPONSE"); return SVB_ERR_PARAM;
+    }
+    if (p.preFilterSize < 5 || p.preFilterSize > 255 || p.preFilterSize % 2 == 0) {
+        svb_set_error("preFilterSize must be odd and be within 5..255"); return SVB_ERR_PARAM;
+    }
     if (p.preFilterCap < 1 || p.preFilterCap > 63) { svb_set_error("preFilterCap must be within 1..63"); return SVB_ERR_PARAM; }
     if (p.textureThreshold < 0) { svb_set_error("texture threshold must be non-negative"); return SVB_ERR_PARAM; }
     if (p.uniquenessRatio < 0) { svb_set_error("uniqueness ratio must be non-negative"); return SVB_ERR_PARAM; }
@@ -279,6 +316,7 @@ static int bm_geo(const svb_bm_params& p, int H, int W, BmGeo& g, bool& trivial)
     g.H = H; g.W = W; g.D = p.numDisparities; g.NP = (g.D + 63) / 64; g.minD = p.minDisparity;
     g.bs = p.blockSize; g.r = p.blockSize / 2; g.cap = p.preFilterCap; g.tex = p.textureThreshold;
     g.uniq = p.uniquenessRatio; g.FILTERED = (g.minD - 1) * 16;
+    g.pft = p.preFilterType; g.pfs = p.preFilterSize;
     const int s = g.D - 1 + g.minD;
     g.lofs = std::max(s, 0); g.rofs = -std::min(s, 0);
     g.width1 = W - g.rofs - g.D + 1;
@@ -341,11 +379,18 @@ extern "C" int svb_bm_compute_dev(svb_bm_t* h, const uint8_t* left, const uint8_
     const bool validate = h->prm.disp12MaxDiff >= 0;
     // scratch shared by validateDisparity (keys u64 + input copy s16 + cost s16) and the speckle filter (2 x s32)
     const size_t sc_bytes = validate ? npix * 12 : (h->prm.speckleWindowSize > 0 ? npix * 8 : 0);
-    rc = h->ws.reserve(lp_bytes + rd_bytes + sc_bytes);
+    const size_t vs_bytes = g.pft == 0 ? npix * 4 : 0;       // vertical sums of both images (u16), dead after the prefilter
+    rc = h->ws.reserve(lp_bytes + rd_bytes + std::max(sc_bytes, vs_bytes));
     if (rc != SVB_OK) return rc;
     uint8_t* lp = (uint8_t*)h->ws.p;
     uint32_t* rdesc = (uint32_t*)((char*)h->ws.p + lp_bytes);
-    k_bm_prefilter<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(left, right, g, lp, rdesc);
+    uint16_t* vs = nullptr;
+    if (g.pft == 0) {
+        vs = (uint16_t*)((char*)h->ws.p + lp_bytes + rd_bytes);
+        k_bm_vsum<<<dim3(svb_ceil_div(W, 256), H, 2 * B), 256, 0, st>>>(left, right, g, vs);
+        SVB_LAUNCH_CHECK(); h->launches++;
+    }
+    k_bm_prefilter<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(left, right, g, lp, rdesc, vs);
     SVB_LAUNCH_CHECK(); h->launches++;
     char* scratch = (char*)h->ws.p + lp_bytes + rd_bytes;
     int16_t* cost = validate ? (int16_t*)(scratch + npix * 10) : nullptr;

@@ -22,6 +22,7 @@ STEREO_SGBM_MODE_SGBM = 0
 STEREO_SGBM_MODE_HH = 1
 STEREO_SGBM_MODE_SGBM_3WAY = 2
 STEREO_SGBM_MODE_HH4 = 3
+STEREO_BM_PREFILTER_NORMALIZED_RESPONSE, STEREO_BM_PREFILTER_XSOBEL = 0, 1
 StereoSGBM_MODE_SGBM, StereoSGBM_MODE_HH = 0, 1
 StereoSGBM_MODE_SGBM_3WAY, StereoSGBM_MODE_HH4 = 2, 3
 INTER_LINEAR = 1
@@ -217,7 +218,8 @@ class StereoBM(_Matcher):
     (preFilterCap 31, textureThreshold 10, uniquenessRatio 15, X-Sobel prefilter)."""
     _kind = "bm"
     _names = ("minDisparity", "numDisparities", "blockSize", "preFilterCap", "textureThreshold",
-              "uniquenessRatio", "speckleWindowSize", "speckleRange", "disp12MaxDiff")
+              "uniquenessRatio", "speckleWindowSize", "speckleRange", "disp12MaxDiff", "preFilterType",
+              "preFilterSize")
 
     def __init__(self, numDisparities=0, blockSize=21):
         self._minDisparity = 0
@@ -229,6 +231,8 @@ class StereoBM(_Matcher):
         self._speckleWindowSize = 0
         self._speckleRange = 0
         self._disp12MaxDiff = -1
+        self._preFilterType = STEREO_BM_PREFILTER_XSOBEL
+        self._preFilterSize = 9
 
     def _params(self):
         return tuple(getattr(self, "_" + n) for n in self._names)

@@ -64,6 +64,12 @@ BM_CASES = [
     dict(H=70, W=160, seed=37, numDisparities=64, blockSize=15, noise=20,
          set={"Disp12MaxDiff": 0, "MinDisparity": -16, "SpeckleWindowSize": 30, "SpeckleRange": 4}),
     dict(H=64, W=141, seed=38, numDisparities=48, blockSize=7, noise=12, set={"Disp12MaxDiff": 3}),
+    # PREFILTER_NORMALIZED_RESPONSE (type 0), default window 9 and others
+    dict(H=70, W=150, seed=39, numDisparities=32, blockSize=9, set={"PreFilterType": 0}),
+    dict(H=61, W=133, seed=40, numDisparities=48, blockSize=15,
+         set={"PreFilterType": 0, "PreFilterSize": 5, "PreFilterCap": 63, "MinDisparity": -4}),
+    dict(H=66, W=120, seed=41, numDisparities=16, blockSize=7, noise=20,
+         set={"PreFilterType": 0, "PreFilterSize": 31, "PreFilterCap": 10, "Disp12MaxDiff": 1}),
 ]
 
 

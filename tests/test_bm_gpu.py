@@ -39,7 +39,8 @@ def test_bm_random_params_vs_oracle():
         kw = dict(numDisparities=D, blockSize=bs, minDisparity=minD, preFilterCap=int(rng.choice([5, 31, 63])),
                   textureThreshold=int(rng.choice([0, 10, 200])), uniquenessRatio=int(rng.choice([0, 5, 15])),
                   speckleWindowSize=int(rng.choice([0, 30])), speckleRange=int(rng.choice([1, 4])),
-                  disp12MaxDiff=int(rng.choice([-1, -1, 0, 1, 4])))
+                  disp12MaxDiff=int(rng.choice([-1, -1, 0, 1, 4])), preFilterType=int(rng.choice([1, 1, 0])),
+                  preFilterSize=int(rng.choice([5, 9, 21])))
         if kw["disp12MaxDiff"] >= 0 and bs * bs * 2 * kw["preFilterCap"] > 32767:
             kw["preFilterCap"] = 31
         l, r, _ = make_pair(H, W, max(D, 16), seed=700 + it, noise=int(rng.choice([0, 6, 25])))

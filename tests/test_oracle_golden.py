@@ -75,7 +75,8 @@ def test_sgbm_oracle_vs_live_cv2_random(have_cv2):
 def _bm_kwargs(c):
     kw = dict(numDisparities=c["numDisparities"], blockSize=c["blockSize"])
     m = {"MinDisparity": "minDisparity", "UniquenessRatio": "uniquenessRatio", "TextureThreshold": "textureThreshold",
-         "SpeckleWindowSize": "speckleWindowSize", "SpeckleRange": "speckleRange", "PreFilterCap": "preFilterCap", "Disp12MaxDiff": "disp12MaxDiff"}
+         "SpeckleWindowSize": "speckleWindowSize", "SpeckleRange": "speckleRange", "PreFilterCap": "preFilterCap", "Disp12MaxDiff": "disp12MaxDiff",
+         "PreFilterType": "preFilterType", "PreFilterSize": "preFilterSize"}
     for k, v in c.get("set", {}).items():
         kw[m[k]] = v
     return kw

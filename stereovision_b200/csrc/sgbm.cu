@@ -77,6 +77,7 @@ __host__ __device__ constexpr size_t sw_smem_words(int NP, bool last)
 }
 #define SW_FLAG_EVERY 8        // carry progress is published every this many columns
 #define SW_SPIN_LIMIT (1 << 24)
+#define SVB_HOST_PIPE 4        // sub-ranges per chunk in the *_host entry points (upload / per-image kernels / download overlap)
 
 struct SgbmGeo {
     int H, W, D, Dp, NP, HALF, minD, minX1, width1, bs, r, ftzero;
@@ -277,9 +278,12 @@ struct CostArgs {
     int OC;                    // output columns per strip = CK_PC - 2r (or less when the ring is large)
     int nstrips, rseg, nsegs;  // strips per row, rows per segment, segments per job
     int accum;                 // add to the stored C (colour input: one pass per channel)
+    int job0;                  // first job of this launch (the per-image kernels run on sub-ranges of a chunk)
 };
 
-template <int NP, bool FULL>
+// XTRA: the rare variants (colour accumulation passes, MODE_HH4's zero rows) live in their own instance so that
+// the plain kernel keeps its code and register allocation (13.8 vs 14.5 ms per 32 pairs at 1080p/D256 otherwise)
+template <int NP, bool FULL, bool XTRA>
 __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ CUtensorMap tmR,
                                                         const __grid_constant__ CUtensorMap tmL,
                                                         SgbmGeo g, CostArgs ca, uint32_t* __restrict__ vol)
@@ -295,7 +299,7 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
     uint32_t* ring = pixbuf + 2 * CK_PC * VW;                // [OC][bs][VW]
 
     const int strip = blockIdx.x % ca.nstrips, seg = blockIdx.x / ca.nstrips;
-    const int job = blockIdx.y, b = job / g.nstripes, n = job % g.nstripes;
+    const int job = blockIdx.y + ca.job0, b = job / g.nstripes, n = job % g.nstripes;
     int ys, ye, keep;
     job_rows(g, n, ys, ye, keep);
     const int ya = ys + seg * ca.rseg, yb = min(ya + ca.rseg, ye);   // output rows of this CTA
@@ -443,14 +447,18 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
                 if (emit && xc < w1) {
                     uint32_t* dst = vol + (((size_t)job * g.rowsMax + (y - ys)) * w1 + xc) * VW;
                     uint32_t o[NP];
-                    // MODE_HH4: cv2 leaves the rows whose window reaches below the image at cost 0 (oracle/sgbm_oracle.c)
-                    const bool zrow = g.mode == SVB_MODE_HH4 && y + r > g.H - 1 && y > 0;
+                    if constexpr (XTRA) {
+                        // MODE_HH4: cv2 leaves the rows whose window reaches below the image at cost 0 (oracle/sgbm_oracle.c)
+                        const bool zrow = g.mode == SVB_MODE_HH4 && y + r > g.H - 1 && y > 0;
+                        if (ca.accum) vec_ld<NP>(dst, lane, t, LdPlain());
 #pragma unroll
-                    if (ca.accum) vec_ld<NP>(dst, lane, t, LdPlain());
+                        for (int k = 0; k < NP; ++k) {
+                            const uint32_t cv = zrow ? 0u : (ca.accum ? acc[cc][k] + t[k] : acc[cc][k]);
+                            o[k] = FULL ? cv : ((cv & ~padm[k]) | (WALL2 & padm[k]));
+                        }
+                    } else {
 #pragma unroll
-                    for (int k = 0; k < NP; ++k) {
-                        const uint32_t cv = zrow ? 0u : (ca.accum ? acc[cc][k] + t[k] : acc[cc][k]);
-                        o[k] = FULL ? cv : ((cv & ~padm[k]) | (WALL2 & padm[k]));
+                        for (int k = 0; k < NP; ++k) o[k] = FULL ? acc[cc][k] : ((acc[cc][k] & ~padm[k]) | (WALL2 & padm[k]));
                     }
                     vec_st<NP>(dst, lane, o);
                 }
@@ -1001,6 +1009,9 @@ struct svb_sgbm {
     size_t ws_limit = 0;            // 0: 60 % of the free device memory at first use
     SvbBuf ws;
     SvbBuf stage_in, stage_out;     // device staging for the *_host entry point
+    // *_host pipeline: H2D of sub-batch i+1 and D2H of sub-batch i-1 overlap the kernels of sub-batch i
+    cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
+    std::vector<cudaEvent_t> ev_in, ev_done;
     int launches = 0;
     int num_sms = 0;
     bool debug = false;             // keep the final S volume (debug_stages)
@@ -1120,6 +1131,11 @@ extern "C" void svb_sgbm_destroy(svb_sgbm_t* h)
 {
     if (!h) return;
     for (auto& e : h->evs) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    for (auto& e : h->ev_in) cudaEventDestroy(e);
+    for (auto& e : h->ev_done) cudaEventDestroy(e);
+    if (h->s_in) cudaStreamDestroy(h->s_in);
+    if (h->s_run) cudaStreamDestroy(h->s_run);
+    if (h->s_out) cudaStreamDestroy(h->s_out);
     h->ws.release(); h->stage_in.release(); h->stage_out.release();
     delete h;
 }
@@ -1188,9 +1204,20 @@ static int launch_sweep_var(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, i
     }
 }
 
+// The *_host entry points hand run_chunk their host buffers: the per-image stages in front of the sweeps
+// (prefilter, cost) and behind them (LR check, median, speckle) run on sub-ranges of the chunk, so that the
+// upload of sub-range i+1 and the download of sub-range i-1 overlap them.  The wavefront sweeps always see the
+// whole chunk (their ramp-up/-down is what makes small launches slow).
+struct HostPipe {
+    const uint8_t *hl, *hr;            // host images of the whole batch
+    int16_t* hout;                     // host disparities of the whole batch
+    size_t pin, pout;                  // bytes per image in, elements per image out
+    int nsub;                          // sub-ranges per chunk
+};
+
 template <int NP>
 static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const uint8_t* left, const uint8_t* right,
-                     int nb, int16_t* disp, cudaStream_t st)
+                     int nb, int16_t* disp, cudaStream_t st, const HostPipe* hp, int base)
 {
     char* ws = (char*)h->ws.p;
     uint32_t* ldesc = (uint32_t*)(ws + L.ldesc);
@@ -1203,12 +1230,28 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     int32_t* scratch = (int32_t*)(ws + L.scratch);
     const int njobs = nb * g.nstripes;
 
+    const size_t hw = (size_t)g.H * g.W;
+    const int nsub = hp ? std::min(hp->nsub, nb) : 1, per = (nb + nsub - 1) / nsub;
+    int evi = 0;
+    for (int s0 = 0; s0 < nb; s0 += per) {
+    const int ns = std::min(per, nb - s0);
+    if (hp) {                                               // upload this sub-range while the previous one computes
+        uint8_t* dl = const_cast<uint8_t*>(left) + s0 * hp->pin;
+        uint8_t* dr = const_cast<uint8_t*>(right) + s0 * hp->pin;
+        SVB_CUDA(cudaMemcpyAsync(dl, hp->hl + (base + s0) * hp->pin, ns * hp->pin, cudaMemcpyHostToDevice, h->s_in));
+        SVB_CUDA(cudaMemcpyAsync(dr, hp->hr + (base + s0) * hp->pin, ns * hp->pin, cudaMemcpyHostToDevice, h->s_in));
+        SVB_CUDA(cudaEventRecord(h->ev_in[evi], h->s_in));
+        SVB_CUDA(cudaStreamWaitEvent(st, h->ev_in[evi], 0));
+        ++evi;
+    }
     // colour input: one prefilter + cost pass per channel, the box sums add up in C (A.1: cv2 sums the BT cost
     // of all 2*cn channels before the box filter, and the box filter is linear)
     for (int ch = 0; ch < g.cn; ++ch) {
     {
         ProfScope ps(h, CAT_PREFILTER, st);
-        k_prefilter<<<dim3(svb_ceil_div(g.W, 256), g.H, nb), 256, 0, st>>>(left, right, nb, ch, g, ldesc, rdesc);
+        k_prefilter<<<dim3(svb_ceil_div(g.W, 256), g.H, ns), 256, 0, st>>>(
+            left + s0 * hw * g.cn, right + s0 * hw * g.cn, ns, ch, g, ldesc + s0 * hw * 8,
+            rdesc + (size_t)s0 * g.H * 6 * g.Wp);
     }
     SVB_LAUNCH_CHECK(); h->launches++;
 
@@ -1217,6 +1260,8 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         const int bs = 2 * g.r + 1, VW = NP * 32;
         CostArgs ca;
         ca.accum = ch > 0;
+        ca.job0 = s0 * g.nstripes;
+        const int njobs = ns * g.nstripes;                   // jobs of this launch
         const size_t fixed = ((size_t)2 * ck_nblk(NP) * ck_blkw(NP) + 2 * CK_PC * 8 + (size_t)2 * CK_PC * VW) * 4;
         const size_t budget = 200 * 1024;
         int OC = CK_PC - 2 * g.r;
@@ -1242,14 +1287,15 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         if (rc != SVB_OK) return rc;
         dim3 grid(ca.nstrips * ca.nsegs, njobs);
         ProfScope ps(h, CAT_COST, st);
-        if (g.D == g.Dp) {
-            SVB_CUDA(cudaFuncSetAttribute(k_cost<NP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            k_cost<NP, true><<<grid, CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv);
-        } else {
-            SVB_CUDA(cudaFuncSetAttribute(k_cost<NP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            k_cost<NP, false><<<grid, CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv);
-        }
+        const bool xtra = ca.accum || g.mode == SVB_MODE_HH4;
+#define LAUNCH_COST(F, X) do { \
+            SVB_CUDA(cudaFuncSetAttribute(k_cost<NP, F, X>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            k_cost<NP, F, X><<<grid, CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv); } while (0)
+        if (g.D == g.Dp) { if (xtra) LAUNCH_COST(true, true); else LAUNCH_COST(true, false); }
+        else             { if (xtra) LAUNCH_COST(false, true); else LAUNCH_COST(false, false); }
+#undef LAUNCH_COST
         SVB_LAUNCH_CHECK(); h->launches++;
+    }
     }
     }
 
@@ -1289,24 +1335,34 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         if (rc != SVB_OK) return rc;
         h->launches++;
     }
-    {
-        ProfScope ps(h, CAT_LR, st);
-        k_lrcheck<<<dim3(svb_ceil_div(g.width1, 256), g.H, nb), 256, 0, st>>>(raw, key, g, nb);
-    }
-    SVB_LAUNCH_CHECK(); h->launches++;
-
-    {
-        ProfScope ps(h, CAT_MEDIAN, st);
-        rc = svb_median3_s16_dev(raw, nb, g.H, g.W, disp, st);
-    }
-    if (rc != SVB_OK) return rc;
-    h->launches++;
-    if (h->prm.speckleWindowSize > 0) {
-        ProfScope ps(h, CAT_SPECKLE, st);
-        rc = svb_filter_speckles_s16_dev(disp, nb, g.H, g.W, g.INV, h->prm.speckleWindowSize,
-                                         16 * h->prm.speckleRange, scratch, st);
+    evi = 0;
+    for (int s0 = 0; s0 < nb; s0 += per) {
+        const int ns = std::min(per, nb - s0);
+        {
+            ProfScope ps(h, CAT_LR, st);
+            k_lrcheck<<<dim3(svb_ceil_div(g.width1, 256), g.H, ns), 256, 0, st>>>(raw + s0 * hw, key + s0 * hw, g, ns);
+        }
+        SVB_LAUNCH_CHECK(); h->launches++;
+        {
+            ProfScope ps(h, CAT_MEDIAN, st);
+            rc = svb_median3_s16_dev(raw + s0 * hw, ns, g.H, g.W, disp + s0 * hw, st);
+        }
         if (rc != SVB_OK) return rc;
-        h->launches += 4;
+        h->launches++;
+        if (h->prm.speckleWindowSize > 0) {
+            ProfScope ps(h, CAT_SPECKLE, st);
+            rc = svb_filter_speckles_s16_dev(disp + s0 * hw, ns, g.H, g.W, g.INV, h->prm.speckleWindowSize,
+                                             16 * h->prm.speckleRange, scratch + 2 * s0 * hw, st);
+            if (rc != SVB_OK) return rc;
+            h->launches += 4;
+        }
+        if (hp) {                                           // download this sub-range while the next one finishes
+            SVB_CUDA(cudaEventRecord(h->ev_done[evi], st));
+            SVB_CUDA(cudaStreamWaitEvent(h->s_out, h->ev_done[evi], 0));
+            SVB_CUDA(cudaMemcpyAsync(hp->hout + (base + s0) * hp->pout, disp + s0 * hw, ns * hw * 2,
+                                     cudaMemcpyDeviceToHost, h->s_out));
+            ++evi;
+        }
     }
     return SVB_OK;
 }
@@ -1317,8 +1373,17 @@ extern "C" int svb_sgbm_compute_dev(svb_sgbm_t* h, const uint8_t* left, const ui
     return svb_sgbm_compute_cn_dev(h, left, right, B, H, W, 1, disp, stream);
 }
 
+static int sgbm_compute_impl(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
+                             int B, int H, int W, int cn, int16_t* disp, void* stream, const HostPipe* hp);
+
 extern "C" int svb_sgbm_compute_cn_dev(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
                                        int B, int H, int W, int cn, int16_t* disp, void* stream)
+{
+    return sgbm_compute_impl(h, left, right, B, H, W, cn, disp, stream, nullptr);
+}
+
+static int sgbm_compute_impl(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
+                             int B, int H, int W, int cn, int16_t* disp, void* stream, const HostPipe* hp)
 {
     if (!h || !left || !right || !disp) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
     if (B <= 0) { svb_set_error("batch must be >= 1"); return SVB_ERR_PARAM; }
@@ -1346,7 +1411,7 @@ extern "C" int svb_sgbm_compute_cn_dev(svb_sgbm_t* h, const uint8_t* left, const
         const int n = std::min(nb, B - b0);
         const size_t off = (size_t)b0 * H * W;
         switch (g.NP) {
-#define CASE(N) case N: rc = run_chunk<N>(h, g, L, left + off * cn, right + off * cn, n, disp + off, st); break;
+#define CASE(N) case N: rc = run_chunk<N>(h, g, L, left + off * cn, right + off * cn, n, disp + off, st, hp, b0); break;
             CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
 #undef CASE
             default: svb_set_error("bad NP"); rc = SVB_ERR_UNSUPPORTED;
@@ -1385,12 +1450,28 @@ extern "C" int svb_sgbm_compute_cn_host(svb_sgbm_t* h, const uint8_t* left, cons
     if (rc != SVB_OK) return rc;
     uint8_t* dl = (uint8_t*)h->stage_in.p;
     uint8_t* dr = dl + nin;
-    SVB_CUDA(cudaMemcpyAsync(dl, left, nin, cudaMemcpyHostToDevice, 0));
-    SVB_CUDA(cudaMemcpyAsync(dr, right, nin, cudaMemcpyHostToDevice, 0));
-    rc = svb_sgbm_compute_cn_dev(h, dl, dr, B, H, W, cn, (int16_t*)h->stage_out.p, 0);
-    if (rc != SVB_OK) return rc;
-    SVB_CUDA(cudaMemcpyAsync(disp, h->stage_out.p, 2 * n, cudaMemcpyDeviceToHost, 0));
-    SVB_CUDA(cudaStreamSynchronize(0));
+    int16_t* dout = (int16_t*)h->stage_out.p;
+    if (!h->s_in) {
+        SVB_CUDA(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
+        SVB_CUDA(cudaStreamCreateWithFlags(&h->s_run, cudaStreamNonBlocking));
+        SVB_CUDA(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+    }
+    // SVB_HOST_PIPE sub-ranges per chunk: only the first upload and the last download are exposed
+    const size_t need = (size_t)SVB_HOST_PIPE;
+    while (h->ev_in.size() < need) {
+        cudaEvent_t e1, e2;
+        SVB_CUDA(cudaEventCreateWithFlags(&e1, cudaEventDisableTiming));
+        SVB_CUDA(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+        h->ev_in.push_back(e1); h->ev_done.push_back(e2);
+    }
+    HostPipe hp;
+    hp.hl = left; hp.hr = right; hp.hout = disp;
+    hp.pin = (size_t)H * W * cn; hp.pout = (size_t)H * W;
+    hp.nsub = SVB_HOST_PIPE;
+    rc = sgbm_compute_impl(h, dl, dr, B, H, W, cn, dout, h->s_run, &hp);
+    if (rc != SVB_OK) { cudaDeviceSynchronize(); return rc; }
+    SVB_CUDA(cudaStreamSynchronize(h->s_out));
+    SVB_CUDA(cudaStreamSynchronize(h->s_run));
     return check_sweep_err(h);
 }
 

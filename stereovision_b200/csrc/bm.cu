@@ -281,6 +281,10 @@ struct svb_bm {
     svb_bm_params prm;
     SvbBuf ws, stage_in, stage_out;
     int launches = 0;
+    // *_host pipeline: upload of sub-batch i+1 and download of sub-batch i-1 overlap the kernels of sub-batch i
+    // (every BM kernel is per image, so sub-batches cost nothing on the device)
+    cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[4] = {}, ev_done[4] = {};
 };
 
 static int bm_geo(const svb_bm_params& p, int H, int W, BmGeo& g, bool& trivial)
@@ -340,6 +344,13 @@ extern "C" int svb_bm_create(const svb_bm_params* p, svb_bm_t** out)
 extern "C" void svb_bm_destroy(svb_bm_t* h)
 {
     if (!h) return;
+    for (int i = 0; i < 4; ++i) {
+        if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]);
+        if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
+    }
+    if (h->s_in) cudaStreamDestroy(h->s_in);
+    if (h->s_run) cudaStreamDestroy(h->s_run);
+    if (h->s_out) cudaStreamDestroy(h->s_out);
     h->ws.release(); h->stage_in.release(); h->stage_out.release();
     delete h;
 }
@@ -440,11 +451,34 @@ extern "C" int svb_bm_compute_host(svb_bm_t* h, const uint8_t* left, const uint8
     if (rc != SVB_OK) return rc;
     uint8_t* dl = (uint8_t*)h->stage_in.p;
     uint8_t* dr = dl + n;
-    SVB_CUDA(cudaMemcpyAsync(dl, left, n, cudaMemcpyHostToDevice, 0));
-    SVB_CUDA(cudaMemcpyAsync(dr, right, n, cudaMemcpyHostToDevice, 0));
-    rc = svb_bm_compute_dev(h, dl, dr, B, H, W, (int16_t*)h->stage_out.p, 0);
-    if (rc != SVB_OK) return rc;
-    SVB_CUDA(cudaMemcpyAsync(disp, h->stage_out.p, 2 * n, cudaMemcpyDeviceToHost, 0));
-    SVB_CUDA(cudaStreamSynchronize(0));
+    int16_t* dout = (int16_t*)h->stage_out.p;
+    if (!h->s_in) {
+        SVB_CUDA(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
+        SVB_CUDA(cudaStreamCreateWithFlags(&h->s_run, cudaStreamNonBlocking));
+        SVB_CUDA(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+        for (int i = 0; i < 4; ++i) {
+            SVB_CUDA(cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming));
+            SVB_CUDA(cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+        }
+    }
+    const int nsub = std::min(B, 4), per = (B + nsub - 1) / nsub;
+    const size_t hw = (size_t)H * W;
+    int launches = 0, i = 0;
+    for (int b0 = 0; b0 < B; b0 += per, ++i) {
+        const int nb = std::min(per, B - b0);
+        SVB_CUDA(cudaMemcpyAsync(dl + b0 * hw, left + b0 * hw, nb * hw, cudaMemcpyHostToDevice, h->s_in));
+        SVB_CUDA(cudaMemcpyAsync(dr + b0 * hw, right + b0 * hw, nb * hw, cudaMemcpyHostToDevice, h->s_in));
+        SVB_CUDA(cudaEventRecord(h->ev_in[i], h->s_in));
+        SVB_CUDA(cudaStreamWaitEvent(h->s_run, h->ev_in[i], 0));
+        rc = svb_bm_compute_dev(h, dl + b0 * hw, dr + b0 * hw, nb, H, W, dout + b0 * hw, h->s_run);
+        if (rc != SVB_OK) { cudaDeviceSynchronize(); return rc; }
+        launches += h->launches;
+        SVB_CUDA(cudaEventRecord(h->ev_done[i], h->s_run));
+        SVB_CUDA(cudaStreamWaitEvent(h->s_out, h->ev_done[i], 0));
+        SVB_CUDA(cudaMemcpyAsync(disp + b0 * hw, dout + b0 * hw, nb * hw * 2, cudaMemcpyDeviceToHost, h->s_out));
+    }
+    h->launches = launches;
+    SVB_CUDA(cudaStreamSynchronize(h->s_out));
+    SVB_CUDA(cudaStreamSynchronize(h->s_run));
     return SVB_OK;
 }

@@ -2,10 +2,13 @@
 // config 2) for sm_100a, bit-exact on int16 output.
 //
 //   k_bm_prefilter  X-Sobel prefilter (cap-clipped), right image also as paired u16x2 planes
-//   k_bm<NP>        one warp per image row slides along x keeping the horizontal SAD box sum
-//                   for all disparities in registers; rows meet in shared memory, the first TY
-//                   warps add blockSize rows and finish the pixel in place: texture test, argmin,
-//                   uniqueness, subpixel.  The SAD volume never exists in HBM.
+//   k_bm_tex_h/_v   texture test + ROI as a byte mask of the pixels that need a decision
+//   k_bm2<NP>       a CTA walks down a strip of 64 window columns: vertical SAD sums in registers (entering row
+//                   added, leaving row recomputed and subtracted), one barrier per row, horizontal box by
+//                   sliding along each warp's run of output columns, argmin / uniqueness in place, subpixel
+//                   division batched 32 pixels at a time.  The SAD volume never exists in HBM.
+//                   (k_bm v1 -- one warp per row sliding along x, two block barriers per column -- ran at
+//                   5 968 pairs/s on BASELINE config 2; this one at 12 492.)
 //   speckle filter  (imgproc.cu) when speckleWindowSize > 0
 #include "svb_common.cuh"
 #include <algorithm>
@@ -75,123 +78,207 @@ __device__ __forceinline__ uint32_t bm_absdiff(uint32_t U2, uint32_t nU2, uint32
     return __vmaxs2(__vadd2(U2, nV2), __vadd2(V2, nU2));
 }
 
-template <int NP>
-__global__ void __launch_bounds__(1024) k_bm(const uint8_t* __restrict__ lp, const uint32_t* __restrict__ rdesc,
-                                             BmGeo g, int TY, int XSEG, int16_t* __restrict__ disp,
-                                             int16_t* __restrict__ cost)
+// ------------------------------------------------------------------------------------------
+// k_bm_texture: T(y, x) = sum over the bs x bs window of |L - cap| (A.6 texture test), columns clamped like
+// the SAD window's left columns.  Two tiny passes (horizontal box -> u16, vertical box -> s32).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_bm_tex_h(const uint8_t* __restrict__ lp, BmGeo g, uint16_t* __restrict__ th)
 {
-    extern __shared__ uint32_t smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, NW = blockDim.x >> 5;
-    const int b = blockIdx.z;
-    const int y0 = blockIdx.y * TY;
-    const int xs = blockIdx.x * XSEG, xe = min(xs + XSEG, g.width1);
-    const int r = g.r, bs = 2 * r + 1, D = g.D, W = g.W;
-    uint32_t* hsb = smem;                                  // [NW][NP][32] horizontal sums
-    uint32_t* tsb = smem + (size_t)NW * NP * 32;           // [NW] horizontal texture sums
-    uint32_t* svb = tsb + NW;                              // [TY][NP*32] final SAD vectors (pairs)
-    const int yy = min(max(y0 - r + warp, 0), g.H - 1);
-    const uint8_t* lrow = lp + ((size_t)b * g.H + yy) * W;
-    const uint32_t* rrow = rdesc + (size_t)(b * g.H + yy) * 4 * g.Wh;
-    uint32_t hs[NP];
-#pragma unroll
-    for (int k = 0; k < NP; ++k) hs[k] = 0;
-    int hts = 0;
-    const int y = y0 + warp;
-    const bool out_warp = warp < TY && y < g.H;
-    const bool row_ok = y >= r && y < g.H - r;
-
-    // cost vector of window column j (A.6: left column and right start column clamp separately)
-    auto column = [&](int j, uint32_t (&c)[NP], int& t) {
-        const int lc = min(max(j + g.lofs, 0), W - 1);
-        const int rs = min(max(j + g.rofs, 0), W - D);
-        const int u = lrow[lc];
-        t = abs(u - g.cap);
-        const uint32_t U2 = pk_dup((uint32_t)u), nU2 = pk_dup((uint32_t)(-u));
-        const int xr0 = rs + D - 1;                        // right column of disparity index d' = 0
-        const uint32_t* rp = rrow + (size_t)(xr0 & 1) * g.Wh;
-#pragma unroll
-        for (int k = 0; k < NP; ++k) {
-            const int m = max((xr0 >> 1) - (32 * k + lane), 0);
-            c[k] = bm_absdiff(U2, nU2, __ldg(rp + m), __ldg(rp + 2 * g.Wh + m));
-        }
-    };
-
-    for (int j = xs - r; j < xe + r; ++j) {
-        uint32_t c[NP]; int t;
-        column(j, c, t);
-#pragma unroll
-        for (int k = 0; k < NP; ++k) hs[k] += c[k];
-        hts += t;
-        if (j - bs >= xs - r) {                            // column leaving the window
-            column(j - bs, c, t);
-#pragma unroll
-            for (int k = 0; k < NP; ++k) hs[k] -= c[k];
-            hts -= t;
-        }
-        if (j - r < xs) continue;
-        const int xp = j - r;
-#pragma unroll
-        for (int k = 0; k < NP; ++k) hsb[(warp * NP + k) * 32 + lane] = hs[k];
-        if (lane == 0) tsb[warp] = (uint32_t)hts;
-        __syncthreads();
-        if (out_warp) {
-            const int x = xp + g.lofs;
-            uint32_t s[NP];
-            int ts = 0;
-#pragma unroll
-            for (int k = 0; k < NP; ++k) s[k] = 0;
-            for (int t2 = 0; t2 < bs; ++t2) {
-#pragma unroll
-                for (int k = 0; k < NP; ++k) s[k] += hsb[((warp + t2) * NP + k) * 32 + lane];
-                ts += (int)tsb[warp + t2];
-            }
-            // with a cost map (disp12MaxDiff >= 0) every column of the width1 domain is evaluated: cv2 lets the
-            // columns outside the valid ROI vote in validateDisparity and blanks them afterwards
-            const bool roi = row_ok && x < W && (cost != nullptr || (x >= g.lofs + r && x < W - r));
-            if (roi && ts >= g.tex) {
-                // argmin over BM index kk = D-1-d' (lowest kk = largest disparity wins ties)
-                uint32_t key = 0xffffffffu;
-#pragma unroll
-                for (int k = 0; k < NP; ++k) {
-                    const int d0 = 2 * (32 * k + lane);
-                    if (d0 < D) key = min(key, ((s[k] & 0xffffu) << 16) | (uint32_t)(D - 1 - d0));
-                    if (d0 + 1 < D) key = min(key, ((s[k] >> 16) << 16) | (uint32_t)(D - 2 - d0));
-                }
-                key = __reduce_min_sync(0xffffffffu, key);
-                const int minsad = (int)(key >> 16), mind = (int)(key & 0xffffu);
-                bool rej = false;
-                if (g.uniq > 0) {
-                    const int thresh = minsad + (minsad * g.uniq / 100);
-#pragma unroll
-                    for (int k = 0; k < NP; ++k) {
-                        const int d0 = 2 * (32 * k + lane);
-                        const int k0 = D - 1 - d0, k1 = D - 2 - d0;
-                        rej |= d0 < D && (k0 < mind - 1 || k0 > mind + 1) && (int)(s[k] & 0xffffu) <= thresh;
-                        rej |= d0 + 1 < D && (k1 < mind - 1 || k1 > mind + 1) && (int)(s[k] >> 16) <= thresh;
-                    }
-                }
-                rej = __any_sync(0xffffffffu, rej);
-                if (!rej) {
-                    uint32_t* sv = svb + (size_t)warp * NP * 32;
-#pragma unroll
-                    for (int k = 0; k < NP; ++k) sv[32 * k + lane] = s[k];
-                    __syncwarp();
-                    if (lane == 0) {
-                        const uint16_t* sd = reinterpret_cast<const uint16_t*>(sv);     // indexed by d'
-                        auto sadk = [&](int kk) { return (int)sd[D - 1 - kk]; };
-                        const int p = mind + 1 < D ? sadk(mind + 1) : sadk(D - 2);
-                        const int n = mind - 1 >= 0 ? sadk(mind - 1) : sadk(1);
-                        const int dd = p + n - 2 * minsad + abs(p - n);
-                        const int v = ((D - mind - 1 + g.minD) * 256 + (dd != 0 ? (p - n) * 256 / dd : 0) + 15) >> 4;
-                        disp[((size_t)b * g.H + y) * W + x] = (int16_t)v;
-                        if (cost) cost[((size_t)b * g.H + y) * W + x] = (int16_t)minsad;
-                    }
-                    __syncwarp();
-                }
-            }
-        }
-        __syncthreads();
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+    if (x >= g.W) return;
+    const uint8_t* row = lp + ((size_t)b * g.H + y) * g.W;
+    int s = 0;
+    for (int j = -g.r; j <= g.r; ++j) s += abs((int)row[min(max(x + j, 0), g.W - 1)] - g.cap);
+    th[((size_t)b * g.H + y) * g.W + x] = (uint16_t)s;       // <= 31 * 63
+}
+// ok(y, x) = 1 where k_bm2 has to decide a pixel: inside the rows / columns cv2 evaluates and textured enough.
+// all_cols: disp12MaxDiff >= 0 -- every column of the width1 domain is evaluated (cv2 lets the columns outside
+// the valid ROI vote in validateDisparity and blanks them afterwards).
+__global__ void __launch_bounds__(256) k_bm_tex_v(const uint16_t* __restrict__ th, BmGeo g, int all_cols,
+                                                  uint8_t* __restrict__ ok)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+    if (x >= g.W) return;
+    bool o = y >= g.r && y < g.H - g.r && x >= g.lofs && x < g.lofs + g.width1;
+    if (!all_cols) o = o && x >= g.lofs + g.r && x < g.W - g.r;
+    if (o) {
+        int s = 0;
+        for (int i = -g.r; i <= g.r; ++i) s += th[((size_t)b * g.H + y + i) * g.W + x];
+        o = s >= g.tex;
     }
+    ok[((size_t)b * g.H + y) * g.W + x] = o ? 1 : 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// k_bm2<NP>: a CTA walks DOWN a strip of BM2_PC window columns of one image (a row segment of it).
+//   vertical phase: warp w owns 4 window columns; their vertical SAD sums V(c, d) over the last bs rows live in
+//     registers: per row  V += |L - R|(row v) - |L - R|(row v - bs)  (the leaving row is recomputed: three
+//     packed ops and two cached loads beat a 100 KB shared-memory ring), then V goes to a double-buffered
+//     shared row buffer;
+//   ONE block barrier per row;
+//   horizontal phase: warp w owns a run of output columns: S(oc) = sum of V over 2r+1 columns, slid along the
+//     run; texture test from k_bm_texture's map; argmin / uniqueness / subpixel in place.
+// The SAD volume never exists in HBM; no per-column barriers (the old k_bm had two per column step).
+// ------------------------------------------------------------------------------------------
+#define BM2_WARPS 16
+#define BM2_CPW 4                          // window columns per warp
+#define BM2_PC (BM2_WARPS * BM2_CPW)       // window columns per strip
+
+// subpixel disparity of one parked pixel (A.6), written by the lane that holds it
+__device__ __forceinline__ void bm2_finish(uint32_t key, uint32_t pn, uint32_t off, int D, int minD,
+                                           int16_t* __restrict__ disp, int16_t* __restrict__ cost)
+{
+    const int minsad = (int)(key >> 16), mind = (int)(key & 0xffffu);
+    const int p = (int)(pn & 0xffffu), n = (int)(pn >> 16);
+    const int dd = p + n - 2 * minsad + abs(p - n);
+    const int val = ((D - mind - 1 + minD) * 256 + (dd != 0 ? (p - n) * 256 / dd : 0) + 15) >> 4;
+    disp[off] = (int16_t)val;
+    if (cost) cost[off] = (int16_t)minsad;
+}
+
+template <int NP>
+__global__ void __launch_bounds__(BM2_WARPS * 32) k_bm2(const uint8_t* __restrict__ lp, const uint32_t* __restrict__ rdesc,
+                                                        const uint8_t* __restrict__ okmap, BmGeo g, int OC, int nstrips,
+                                                        int rseg, int16_t* __restrict__ disp, int16_t* __restrict__ cost)
+{
+    constexpr int VW = NP * 32;
+    extern __shared__ uint32_t smem[];
+    uint32_t* vbuf = smem;                                   // [2][BM2_PC][VW] vertical sums of the current row
+    uint32_t* scr = smem + 2 * BM2_PC * VW;                  // [BM2_WARPS][VW] per-warp scratch for the subpixel taps
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int strip = blockIdx.x % nstrips, seg = blockIdx.x / nstrips, b = blockIdx.z;
+    const int r = g.r, bs = 2 * r + 1, D = g.D, W = g.W, H = g.H;
+    const int ya = r + seg * rseg, yb = min(ya + rseg, H - r);   // output rows of this CTA
+    if (ya >= yb) return;
+    const int xs = strip * OC;                               // first output column (width1 domain)
+
+    // row-invariant addressing of this warp's window columns (A.6: left column and right start clamp separately)
+    int lc[BM2_CPW], pl[BM2_CPW], m[BM2_CPW][NP];
+#pragma unroll
+    for (int q = 0; q < BM2_CPW; ++q) {
+        const int j = xs - r + BM2_CPW * warp + q;
+        lc[q] = min(max(j + g.lofs, 0), W - 1);
+        const int rs = min(max(j + g.rofs, 0), W - D);
+        const int xr0 = rs + D - 1;                          // right column of disparity index d' = 0
+        pl[q] = (xr0 & 1) * g.Wh;
+#pragma unroll
+        for (int k = 0; k < NP; ++k) m[q][k] = max((xr0 >> 1) - (32 * k + lane), 0);
+    }
+    uint32_t V[BM2_CPW][NP];
+#pragma unroll
+    for (int q = 0; q < BM2_CPW; ++q)
+#pragma unroll
+        for (int k = 0; k < NP; ++k) V[q][k] = 0;
+
+    // per-lane constants of the decision: BM indices kk of this lane's two disparities, pad flags
+    uint32_t kkpk[NP], padlo[NP], padhi[NP];
+#pragma unroll
+    for (int k = 0; k < NP; ++k) {
+        const int d0 = 2 * (32 * k + lane);
+        kkpk[k] = (uint32_t)((D - 1 - d0) & 0xffff) | ((uint32_t)((D - 2 - d0) & 0xffff) << 16);
+        padlo[k] = d0 < D ? 0u : 0xffffffffu;
+        padhi[k] = d0 + 1 < D ? 0u : 0xffffffffu;
+    }
+    uint32_t rkey = 0, rpn = 0, roff = 0;                    // parked pixel of this lane
+    int nrec = 0;
+    const int R = (OC + BM2_WARPS - 1) / BM2_WARPS;          // output columns per warp (<= BM2_CPW)
+    const int oc_lo = warp * R, oc_hi = min(oc_lo + R, OC);
+    const uint8_t* limg = lp + (size_t)b * H * W;
+    const uint32_t* rimg = rdesc + (size_t)b * H * 4 * g.Wh;
+
+    const int v0 = ya - r, v1 = yb - 1 + r;                  // input rows: all inside the image
+    for (int v = v0; v <= v1; ++v) {
+        const int it = v - v0, buf = it & 1;
+        // ---- vertical phase
+        {
+            const uint8_t* lrow = limg + (size_t)v * W;
+            const uint32_t* rrow = rimg + (size_t)v * 4 * g.Wh;
+#pragma unroll
+            for (int q = 0; q < BM2_CPW; ++q) {
+                const int u = lrow[lc[q]];
+                const uint32_t U2 = pk_dup((uint32_t)u), nU2 = pk_dup((uint32_t)(-u));
+                const uint32_t* rp = rrow + pl[q];
+#pragma unroll
+                for (int k = 0; k < NP; ++k) V[q][k] += bm_absdiff(U2, nU2, __ldg(rp + m[q][k]), __ldg(rp + 2 * g.Wh + m[q][k]));
+            }
+            if (it >= bs) {
+                const uint8_t* lold = lrow - (size_t)bs * W;
+                const uint32_t* rold = rrow - (size_t)bs * 4 * g.Wh;
+#pragma unroll
+                for (int q = 0; q < BM2_CPW; ++q) {
+                    const int u = lold[lc[q]];
+                    const uint32_t U2 = pk_dup((uint32_t)u), nU2 = pk_dup((uint32_t)(-u));
+                    const uint32_t* rp = rold + pl[q];
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) V[q][k] -= bm_absdiff(U2, nU2, __ldg(rp + m[q][k]), __ldg(rp + 2 * g.Wh + m[q][k]));
+                }
+            }
+            uint32_t* vb = vbuf + ((size_t)buf * BM2_PC + BM2_CPW * warp) * VW;
+#pragma unroll
+            for (int q = 0; q < BM2_CPW; ++q)
+#pragma unroll
+                for (int k = 0; k < NP; ++k) vb[q * VW + 32 * k + lane] = V[q][k];
+        }
+        __syncthreads();
+        if (it < bs - 1) continue;                           // window not complete yet
+        // ---- horizontal phase: output row y, this warp's run of output columns
+        const int y = v - r;
+        const uint32_t* vb = vbuf + (size_t)buf * BM2_PC * VW;
+        const uint8_t* okrow = okmap + ((size_t)b * H + y) * W;
+        uint32_t s[NP];
+        for (int oc = oc_lo; oc < oc_hi; ++oc) {
+            if (oc == oc_lo) {
+#pragma unroll
+                for (int k = 0; k < NP; ++k) s[k] = 0;
+                for (int c = oc; c < oc + bs; ++c)
+#pragma unroll
+                    for (int k = 0; k < NP; ++k) s[k] += vb[c * VW + 32 * k + lane];
+            } else {
+#pragma unroll
+                for (int k = 0; k < NP; ++k) s[k] += vb[(oc + bs - 1) * VW + 32 * k + lane] - vb[(oc - 1) * VW + 32 * k + lane];
+            }
+            const int x = xs + oc + g.lofs;
+            if (x >= W) break;
+            if (!okrow[x]) continue;
+            // argmin over BM index kk = D-1-d' (lowest kk = largest disparity wins ties): keys (sad << 16 | kk)
+            uint32_t key = 0xffffffffu;
+#pragma unroll
+            for (int k = 0; k < NP; ++k) {
+                const uint32_t klo = __byte_perm(s[k], kkpk[k], 0x1054), khi = __byte_perm(s[k], kkpk[k], 0x3276);
+                key = min(key, min(klo | padlo[k], khi | padhi[k]));
+            }
+            key = __reduce_min_sync(0xffffffffu, key);
+            const int minsad = (int)(key >> 16), mind = (int)(key & 0xffffu);
+            // the SADs at mind-1 / mind+1 (replicated at the ends of the range): subpixel taps, and the two entries
+            // the uniqueness test leaves out
+            uint32_t* sv = scr + (size_t)warp * VW;
+#pragma unroll
+            for (int k = 0; k < NP; ++k) sv[32 * k + lane] = s[k];
+            __syncwarp();
+            const uint16_t* sd = reinterpret_cast<const uint16_t*>(sv);         // indexed by d' = D-1-kk
+            const bool hasp = mind + 1 < D, hasn = mind >= 1;
+            const int p = sd[hasp ? D - 2 - mind : 1], n = sd[hasn ? D - mind : D - 2];   // sad[mind+1], sad[mind-1]
+            __syncwarp();
+            if (g.uniq > 0) {
+                // cv2: reject iff some kk outside mind-1..mind+1 has sad <= thresh; count all sad <= thresh instead
+                const int thresh = minsad + (minsad * g.uniq / 100);
+                int cnt = 0;
+#pragma unroll
+                for (int k = 0; k < NP; ++k)
+                    cnt += ((int)(s[k] & 0xffffu) <= thresh && !padlo[k]) + ((int)(s[k] >> 16) <= thresh && !padhi[k]);
+                cnt = __reduce_add_sync(0xffffffffu, cnt);
+                if (cnt > 1 + (hasp && p <= thresh) + (hasn && n <= thresh)) continue;
+            }
+            // park the pixel in lane nrec; 32 parked pixels are finished together (one division per lane)
+            if (lane == nrec) { rkey = key; rpn = (uint32_t)p | ((uint32_t)n << 16); roff = (uint32_t)(y * W + x); }
+            if (++nrec == 32) {
+                bm2_finish(rkey, rpn, roff, D, g.minD, disp + (size_t)b * H * W, cost ? cost + (size_t)b * H * W : nullptr);
+                nrec = 0;
+            }
+        }
+    }
+    if (lane < nrec)
+        bm2_finish(rkey, rpn, roff, D, g.minD, disp + (size_t)b * H * W, cost ? cost + (size_t)b * H * W : nullptr);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -281,6 +368,7 @@ struct svb_bm {
     svb_bm_params prm;
     SvbBuf ws, stage_in, stage_out;
     int launches = 0;
+    int num_sms = 0;
     // *_host pipeline: upload of sub-batch i+1 and download of sub-batch i-1 overlap the kernels of sub-batch i
     // (every BM kernel is per image, so sub-batches cost nothing on the device)
     cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
@@ -357,16 +445,23 @@ extern "C" void svb_bm_destroy(svb_bm_t* h)
 extern "C" int svb_bm_last_launches(const svb_bm_t* h) { return h ? h->launches : 0; }
 
 template <int NP>
-static int bm_launch(const BmGeo& g, const uint8_t* lp, const uint32_t* rdesc, int nb, int16_t* disp, int16_t* cost,
-                     cudaStream_t st)
+static int bm2_launch(const BmGeo& g, const uint8_t* lp, const uint32_t* rdesc, const uint8_t* tex, int nb, int num_sms,
+                      int16_t* disp, int16_t* cost, cudaStream_t st)
 {
-    int TY = std::min(16, 32 - 2 * g.r);
-    const int NW = TY + 2 * g.r;
-    const size_t smem = ((size_t)NW * NP * 32 + NW + (size_t)TY * NP * 32) * 4;
-    const int XSEG = 160;
-    SVB_CUDA(cudaFuncSetAttribute(k_bm<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid(svb_ceil_div(g.width1, XSEG), svb_ceil_div(g.H, TY), nb);
-    k_bm<NP><<<grid, 32 * NW, smem, st>>>(lp, rdesc, g, TY, XSEG, disp, cost);
+    // output columns per strip: a multiple of the warp count when that costs little (every warp gets the same run)
+    // (phase 1 costs ~36 instructions per window column, phase 2 ~100 per output column of the longest run)
+    const int ocmax = BM2_PC - 2 * g.r, ocr = ocmax / BM2_WARPS * BM2_WARPS;
+    auto est = [](int oc) { return (36.0 * BM2_PC + 100.0 * BM2_WARPS * ((oc + BM2_WARPS - 1) / BM2_WARPS)) / oc; };
+    const int OC = ocr >= BM2_WARPS && est(ocr) < est(ocmax) ? ocr : ocmax;
+    const int bs = 2 * g.r + 1, nstrips = svb_ceil_div(g.width1, OC), rows = g.H - 2 * g.r;
+    // row segments: enough CTAs to fill the SMs, few enough to keep the bs-1 warm-up rows cheap
+    int nsegs = 1;
+    while ((long long)nstrips * nb * nsegs < 4LL * num_sms && rows / (nsegs * 2) >= 4 * bs) nsegs *= 2;
+    const int rseg = svb_ceil_div(rows, nsegs);
+    nsegs = svb_ceil_div(rows, rseg);
+    const size_t smem = ((size_t)2 * BM2_PC + BM2_WARPS) * NP * 32 * 4;
+    SVB_CUDA(cudaFuncSetAttribute(k_bm2<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_bm2<NP><<<dim3(nstrips * nsegs, 1, nb), BM2_WARPS * 32, smem, st>>>(lp, rdesc, tex, g, OC, nstrips, rseg, disp, cost);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
@@ -391,8 +486,15 @@ extern "C" int svb_bm_compute_dev(svb_bm_t* h, const uint8_t* left, const uint8_
     // scratch shared by validateDisparity (keys u64 + input copy s16 + cost s16) and the speckle filter (2 x s32)
     const size_t sc_bytes = validate ? npix * 12 : (h->prm.speckleWindowSize > 0 ? npix * 8 : 0);
     const size_t vs_bytes = g.pft == 0 ? npix * 4 : 0;       // vertical sums of both images (u16), dead after the prefilter
-    rc = h->ws.reserve(lp_bytes + rd_bytes + std::max(sc_bytes, vs_bytes));
+    const size_t sv_bytes = (std::max(sc_bytes, vs_bytes) + 255) & ~(size_t)255;
+    const size_t th_bytes = (npix * 2 + 255) & ~(size_t)255;     // texture map: horizontal pass u16, then s32
+    rc = h->ws.reserve(lp_bytes + rd_bytes + sv_bytes + th_bytes + npix * 4);
     if (rc != SVB_OK) return rc;
+    if (!h->num_sms) {
+        int dev = 0;
+        SVB_CUDA(cudaGetDevice(&dev));
+        SVB_CUDA(cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, dev));
+    }
     uint8_t* lp = (uint8_t*)h->ws.p;
     uint32_t* rdesc = (uint32_t*)((char*)h->ws.p + lp_bytes);
     uint16_t* vs = nullptr;
@@ -405,8 +507,14 @@ extern "C" int svb_bm_compute_dev(svb_bm_t* h, const uint8_t* left, const uint8_
     SVB_LAUNCH_CHECK(); h->launches++;
     char* scratch = (char*)h->ws.p + lp_bytes + rd_bytes;
     int16_t* cost = validate ? (int16_t*)(scratch + npix * 10) : nullptr;
+    uint16_t* th = (uint16_t*)(scratch + sv_bytes);
+    uint8_t* tex = (uint8_t*)(scratch + sv_bytes + th_bytes);
+    k_bm_tex_h<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(lp, g, th);
+    SVB_LAUNCH_CHECK(); h->launches++;
+    k_bm_tex_v<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(th, g, validate ? 1 : 0, tex);
+    SVB_LAUNCH_CHECK(); h->launches++;
     switch (g.NP) {
-#define CASE(N) case N: rc = bm_launch<N>(g, lp, rdesc, B, disp, cost, st); break;
+#define CASE(N) case N: rc = bm2_launch<N>(g, lp, rdesc, tex, B, h->num_sms, disp, cost, st); break;
         CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
 #undef CASE
         default: svb_set_error("bad NP"); rc = SVB_ERR_UNSUPPORTED;

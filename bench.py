@@ -105,6 +105,27 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.samples)}
 
 
+def bind_to_gpu_numa_node(torch, local):
+    """One process per GPU: run this rank (and first-touch its pinned staging buffers) on the host cores next to
+    its GPU, so that eight ranks do not pull their PCIe copies across the socket interconnect.  Returns the cpu
+    list used (None when sysfs does not say)."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bus = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        txt = open(f"/sys/bus/pci/devices/{bus}/local_cpulist").read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return txt
+    except Exception:
+        pass
+    return None
+
+
 def cpu_reference_run(wl, npairs, threads):
     """The reference's own CPU implementation of the path: cv2.StereoSGBM.compute
     (depth_map.py:894-909) over `npairs` distinct pairs, one pair per worker thread (cv2
@@ -202,6 +223,7 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the svb arm has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_numa_node(torch, local) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -312,7 +334,7 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16",
             "data": "synthetic",
             "config": {"workload": args.workload, "H": H, "W": W, "numDisparities": D, "mode": wl["mode"],
-                       "blockSize": 5, "pairs_per_gpu_per_step": B, "l2_policy": "inputs+volumes >> L2 (126 MB)",
+                       "blockSize": 5, "pairs_per_gpu_per_step": B, "l2_policy": "inputs+volumes >> L2 (126 MB)", "host_numa_cpus": numa,
                        "gdisp_evals_per_s": value * H * W * D / 1e9},
             "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": 2 * B * H * W * world,
                     "d2h_bytes_per_step": 2 * B * H * W * world},

@@ -47,11 +47,11 @@ def b_alg_bytes(wl):
 
 
 # DRAM bytes per pair and launch (dram__bytes_read.sum + dram__bytes_write.sum) from the committed
-# ncu --set full capture profiles/r01_v4_ncu_top3_summary_b8.txt (8 pairs per launch).
+# ncu --set full capture profiles/r01_v6_ncu_top3_summary_b8.txt (8 pairs per launch).
 NCU_TRAFFIC_PER_PAIR = {
-    "sgbm_1080p_d256_hh": {"k_cost": (0.871314 + 7.301723) / 8 * 1e9,
-                           "k_sweep<first>": (7.457215 + 8.518117) / 8 * 1e9,
-                           "k_sweep<last+wta>": (14.904629 + 1.291582) / 8 * 1e9},
+    "sgbm_1080p_d256_hh": {"k_cost": (0.873369 + 7.302557) / 8 * 1e9,
+                           "k_sweep<first>": (7.441713 + 8.516373) / 8 * 1e9,
+                           "k_sweep<last+wta>": (14.898929 + 1.292766) / 8 * 1e9},
 }
 
 
@@ -319,7 +319,7 @@ def main():
             kalg = kernel_alg_bytes(wl, dom)
             roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": tr * B if tr else None,
-                    "traffic_source": "ncu dram bytes of the dominant kernel per launch (profiles/r01_v4_ncu_top3_summary_b8.txt, scaled to this batch)" if tr else None,
+                    "traffic_source": "ncu dram bytes of the dominant kernel per launch (profiles/r01_v6_ncu_top3_summary_b8.txt, scaled to this batch)" if tr else None,
                     "dominant_kernel_alg_bytes_per_launch": kalg * B if kalg else None,
                     "dominant_kernel_achieved": (kalg * B / (dms / max(dl, 1) / 1e3) / 1e9) if kalg else None,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",

@@ -1,0 +1,59 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[0]: one live frame through the depth_map.py path (640x480 BGR pair, synthetic calibration):
+remap x2 -> BGR2GRAY x2 -> StereoSGBM -> /16 -> medianBlur 5 -> depth, and reprojectImageTo3D.
+Host arrays in, host arrays out, one frame at a time: the latency the reference's camera loop sees.  Times the
+engine (cv2-shaped Python surface, the INTEGRATION.md binding) and cv2 itself on the same frame; checks the
+int16 disparity bit for bit.  Not the headline bench (bench.py is)."""
+import json, os, sys, time
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import stereovision_b200 as svb
+from stereovision_b200.synth import make_pair, to_bgr
+from tests.golden_cases import synth_calibration
+
+H, W = 480, 640
+CASES = {"script": dict(D=320, bs=7, mode=2), "c1": dict(D=64, bs=5, mode=2), "c1_sgbm": dict(D=64, bs=5, mode=0)}
+
+
+def frame(api, lb, rb, cal, D, bs, mode):
+    lr = api.remap(lb, cal["left_map1"], cal["left_map2"], api.INTER_LINEAR)
+    rr = api.remap(rb, cal["right_map1"], cal["right_map2"], api.INTER_LINEAR)
+    gl, gr = api.cvtColor(lr, api.COLOR_BGR2GRAY), api.cvtColor(rr, api.COLOR_BGR2GRAY)
+    st = api.StereoSGBM_create(minDisparity=0, numDisparities=D, blockSize=bs, P1=8 * 3 * bs * bs, P2=32 * 3 * bs * bs,
+                               disp12MaxDiff=1, uniquenessRatio=10, speckleWindowSize=100, speckleRange=32,
+                               preFilterCap=63, mode=mode)
+    d16 = st.compute(gl, gr)
+    disp = api.medianBlur(d16.astype(np.float32) / 16.0, 5)
+    depth = (700 * 0.08) / (disp + 1e-6)
+    pts = api.reprojectImageTo3D(d16, cal["Q"])
+    return d16, depth, pts
+
+
+def timeit(fn, n):
+    fn()
+    t0 = time.perf_counter()
+    for _ in range(n):
+        fn()
+    return (time.perf_counter() - t0) / n * 1e3
+
+
+def main():
+    import cv2
+    cal = synth_calibration(W, H)
+    out = {}
+    for name, c in CASES.items():
+        l, r, _ = make_pair(H, W, min(c["D"], 128), seed=9)
+        lb, rb = to_bgr(l), to_bgr(r)
+        a = frame(svb, lb, rb, cal, **c)
+        b = frame(cv2, lb, rb, cal, **c)
+        assert np.array_equal(a[0], b[0]), name
+        fin = np.isfinite(b[2])
+        assert np.allclose(a[2][fin], b[2][fin], rtol=1e-4, atol=1e-5)
+        out[name] = {"svb_ms_per_frame": timeit(lambda: frame(svb, lb, rb, cal, **c), 20),
+                     "cv2_ms_per_frame": timeit(lambda: frame(cv2, lb, rb, cal, **c), 3), **c}
+    print(json.dumps({"workload": "depth_map.py frame path 640x480 (BASELINE configs[0])", "cv2_threads": cv2.getNumThreads(),
+                      "frames": out}))
+
+
+if __name__ == "__main__":
+    main()

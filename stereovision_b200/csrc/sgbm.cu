@@ -587,6 +587,7 @@ struct SweepArgs {
     int16_t* raw;             // [img][H][W]   (sweep 2)
     uint32_t* key;            // [img][H][W]   right-view scatter-min keys (sweep 2)
     int njobs, bandsPerJob;
+    int bandRows;             // rows per band of this launch (<= sw_rows(NP); fewer when there are not enough bands for the SMs)
     int dir;                  // +1: rows top-down, columns left-to-right; -1: the opposite
     int storeS;               // debug: sweep 2 writes the final S back
 };
@@ -661,8 +662,8 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
         const int job = t % a.njobs, band = t / a.njobs;
         int ys, ye, keep;
         job_rows(g, job % g.nstripes, ys, ye, keep);
-        const int nrows = ye - ys, r0 = band * SW_R;
-        const int nact = min(SW_R, nrows - r0);
+        const int nrows = ye - ys, r0 = band * a.bandRows;
+        const int nact = min(a.bandRows, nrows - r0);
         if (nact <= 0) continue;
 
         const bool active = !helper && warp < nact;
@@ -1091,7 +1092,7 @@ static SgbmLayout make_layout(const SgbmGeo& g, int nb)
     L.S = o; o += al256(vol);
     L.carry = o; o += al256(njobs * 2 * g.width1 * 3 * g.Dp * 2);
     L.cmin = o; o += al256(njobs * 2 * g.width1 * 4 * 4);
-    L.sync = o; o += al256((njobs * L.bands + 64) * 4);      // [0] ticket, [1] err, [16..] prog
+    L.sync = o; o += al256((njobs * g.rowsMax + 64) * 4);    // [0] ticket, [1] err, [16..] prog (one per band; bands <= rows)
     L.raw = o; o += al256((size_t)nb * g.H * g.W * 2);
     L.key = o; o += al256((size_t)nb * g.H * g.W * 4);
     L.scratch = o; o += al256((size_t)nb * g.H * g.W * 8);
@@ -1108,6 +1109,9 @@ static size_t ws_limit_of(const svb_sgbm* h)
 }
 static int pick_chunk(const svb_sgbm* h, const SgbmGeo& g, int B)
 {
+    // the workspace of an earlier call already holds the whole batch: no cudaMemGetInfo (it costs ~0.1 ms,
+    // which is most of a single 640x480 frame)
+    if (!h->ws_limit && h->ws.cap && make_layout(g, B).total <= h->ws.cap) return B;
     const size_t per = make_layout(g, 1).total;
     size_t nb = ws_limit_of(h) / per;
     if (nb < 1) nb = 1;
@@ -1311,7 +1315,19 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     a.carry = (uint32_t*)(ws + L.carry); a.cmin = (uint32_t*)(ws + L.cmin);
     a.ticket = sync; a.err = sync + 1; a.prog = sync + 16;
     a.raw = raw; a.key = key;
-    a.njobs = njobs; a.bandsPerJob = L.bands;
+    // Rows per band: sw_rows(NP).  A sweep WITHOUT inter-row paths (the last sweep of MODE_SGBM / 3WAY: <- only) has
+    // independent rows, so a small batch (a single live frame) gets shorter bands there and spreads over all SMs
+    // (640x480 frame: 0.32 -> 0.22 ms).  Sweeps with vertical paths keep full bands: their latency is the dependent
+    // chain (columns + 2 x rows) x one warp's column latency (~0.6 us), and every extra band boundary adds ~16 columns
+    // to it (measured for the first sweep of that frame: 18 / 12 / 9 / 6 / 4 rows per band -> 0.51 / 0.51 / 0.53 /
+    // 0.57 / 0.64 ms).
+    const int rows_full = sw_rows(NP);
+    int rows_free = rows_full;
+    if ((long long)njobs * L.bands < h->num_sms)
+        rows_free = std::min(rows_full, std::max(4, (int)(((long long)njobs * g.rowsMax + h->num_sms - 1) / h->num_sms)));
+    auto set_band_rows = [&](int br) { a.bandRows = br; a.bandsPerJob = (g.rowsMax + br - 1) / br; };
+    set_band_rows(rows_full);
+    a.njobs = njobs;
     a.storeS = h->debug ? 1 : 0;
     const int win = 2 * g.r + 1;
     const long long lmax = (long long)g.cn * win * win * (2 * g.ftzero + 63) + g.P2;
@@ -1329,6 +1345,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     {
         ProfScope ps(h, CAT_SWEEP2, st);
         a.dir = -1;
+        if (g.mode != SVB_MODE_HH && g.mode != SVB_MODE_HH4) set_band_rows(rows_free);
         rc = g.mode == SVB_MODE_HH    ? launch_sweep_var<NP, 15, true>(h, a, g, var, st)
              : g.mode == SVB_MODE_HH4 ? launch_sweep_var<NP, 5, true>(h, a, g, var, st)
                                       : launch_sweep_var<NP, 1, true>(h, a, g, var, st);

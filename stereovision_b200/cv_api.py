@@ -265,6 +265,44 @@ def _ret(t, was_tensor):
     return t if was_tensor else t.cpu().numpy()
 
 
+# Rectification maps are built once per calibration (depth_map.py:633-638) and passed to cv2.remap on every
+# frame: keep their device copies.  Keyed by the array object (dropped with it through a weakref); a strided
+# sample of the contents guards against in-place edits.
+_map_cache = {}
+_map_cache_lock = threading.Lock()
+
+
+def _map_sample(a):
+    flat = a.reshape(-1)
+    step = max(1, flat.size // 257)
+    return flat[::step].tobytes() + flat[-64:].tobytes()
+
+
+def _cached_map(a):
+    """Device copy of a NumPy map (cached); tensors pass through."""
+    if _is_tensor(a) or not isinstance(a, np.ndarray) or not a.flags.c_contiguous:
+        return _to_dev(a)[0]
+    import weakref
+    torch = _torch()
+    dev = torch.cuda.current_device() if torch.cuda.is_available() else -1
+    key = (id(a), dev)
+    sample = _map_sample(a)
+    with _map_cache_lock:
+        hit = _map_cache.get(key)
+    if hit is not None and hit[1] == (a.shape, a.dtype.str, a.ctypes.data) and hit[2] == sample:
+        return hit[0]
+    t = _to_dev(a)[0]
+    try:
+        ref = weakref.ref(a, lambda _r, k=key: _map_cache.pop(k, None))
+    except TypeError:
+        return t
+    with _map_cache_lock:
+        if len(_map_cache) > 64:
+            _map_cache.clear()
+        _map_cache[key] = (t, (a.shape, a.dtype.str, a.ctypes.data), sample, ref)
+    return t
+
+
 def remap(src, map1, map2, interpolation=INTER_LINEAR, to_gray=False):
     """cv2.remap(src, map1, map2, cv2.INTER_LINEAR) for the fixed-point maps the reference
     builds with initUndistortRectifyMap(..., CV_16SC2) (depth_map.py:633-638, 815-826).
@@ -273,8 +311,8 @@ def remap(src, map1, map2, interpolation=INTER_LINEAR, to_gray=False):
     if interpolation != INTER_LINEAR:
         raise NotImplementedError("only INTER_LINEAR is on the reference's path")
     torch = _torch()
-    m1, _ = _to_dev(map1)
-    m2, _ = _to_dev(map2)
+    m1 = _cached_map(map1)
+    m2 = _cached_map(map2)
     if m1.dtype != torch.int16 or m1.ndim != 3 or m1.shape[2] != 2 or m2.dtype not in (torch.uint16, torch.int16):
         raise ValueError("maps must be CV_16SC2 [H,W,2] int16 + CV_16UC1 [H,W] uint16")
     s, was = _to_dev(src)

@@ -30,6 +30,28 @@ def test_remap_and_gray_bit_exact(golden):
         assert np.array_equal(out[b], oracle.remap(src[b], mm1, mm2))
 
 
+def test_remap_map_cache_follows_the_arrays():
+    """The device copies of the maps are cached per array object: a second call reuses them, a new array (even at
+    the same address) or an edited one is uploaded again."""
+    from stereovision_b200 import cv_api
+    rng = np.random.default_rng(4)
+    src = rng.integers(0, 256, (50, 70), dtype=np.uint8)
+    mm1 = rng.integers(0, 45, (40, 60, 2)).astype(np.int16)
+    mm2 = rng.integers(0, 1024, (40, 60)).astype(np.uint16)
+    a = svb.remap(src, mm1, mm2, svb.INTER_LINEAR)
+    n = len(cv_api._map_cache)
+    assert np.array_equal(svb.remap(src, mm1, mm2, svb.INTER_LINEAR), a) and len(cv_api._map_cache) == n
+    mm1[...] = rng.integers(0, 45, mm1.shape)                 # edited in place: the sample changes
+    assert np.array_equal(svb.remap(src, mm1, mm2, svb.INTER_LINEAR), oracle.remap(src, mm1, mm2))
+    for _ in range(3):                                         # fresh arrays, possibly at a recycled address
+        mm1 = rng.integers(0, 45, (40, 60, 2)).astype(np.int16)
+        assert np.array_equal(svb.remap(src, mm1, mm2, svb.INTER_LINEAR), oracle.remap(src, mm1, mm2))
+    del mm1, mm2
+    import gc
+    gc.collect()
+    assert len(cv_api._map_cache) <= n                         # entries leave with their arrays
+
+
 def test_median_and_speckle_bit_exact(golden):
     d16 = golden["med3_in"]
     assert np.array_equal(svb.medianBlur(d16, 3), golden["med3"])

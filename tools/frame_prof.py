@@ -27,3 +27,29 @@ x = torch.from_numpy(lb)
 t("torch H2D 0.9MB pageable", lambda: x.cuda())
 y = x.cuda()
 t("torch D2H 0.9MB", lambda: y.cpu())
+# where a single-frame SGBM call spends its time: host-buffer call vs device call + sync vs device time (events)
+import ctypes
+from stereovision_b200 import _lib
+L = _lib.lib()
+for D, bs, mode in ((64, 5, 2), (320, 7, 2)):
+    h = ctypes.c_void_p()
+    _lib.check(L.svb_sgbm_create(ctypes.byref(_lib.SgbmParams(0, D, bs, 8*3*bs*bs, 32*3*bs*bs, 1, 63, 10, 100, 32, mode)), ctypes.byref(h)))
+    ld, rd = torch.from_numpy(l).cuda(), torch.from_numpy(r).cuda()
+    od = torch.empty((H, W), dtype=torch.int16, device="cuda")
+    oh = np.empty((H, W), np.int16)
+    sp = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    dev = lambda: _lib.check(L.svb_sgbm_compute_dev(h, ld.data_ptr(), rd.data_ptr(), 1, H, W, od.data_ptr(), sp))
+    t(f"C compute_host D={D}", lambda: _lib.check(L.svb_sgbm_compute_host(h, l.ctypes.data, r.ctypes.data, 1, H, W, oh.ctypes.data)))
+    t(f"C compute_dev+sync D={D}", lambda: (dev(), torch.cuda.synchronize()))
+    t(f"C compute_dev enqueue D={D}", dev); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dev(); torch.cuda.synchronize(); e0.record()
+    for _ in range(20): dev()
+    e1.record(); torch.cuda.synchronize()
+    print(f"device time per frame D={D}      {e0.elapsed_time(e1)/20:7.3f} ms")
+    L.svb_sgbm_set_profiling(h, 1)
+    for _ in range(10): dev()
+    names = ctypes.create_string_buffer(32 * 16); pms = (ctypes.c_float * 16)(); pln = (ctypes.c_int * 16)()
+    n = L.svb_sgbm_get_profile(h, 16, names, pms, pln)
+    print({names.raw[32*i:32*i+32].split(b"\0")[0].decode(): round(pms[i] / 10, 4) for i in range(n)})
+    L.svb_sgbm_set_profiling(h, 0)

@@ -66,9 +66,18 @@ __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 2 ? 24 : (NP ==
 #define SW_RING_FIRST 6
 #define SW_RING_LAST 4
 #endif
-__host__ __device__ constexpr int sw_ring(int NP, bool last) { return NP <= 4 ? (last ? SW_RING_LAST : SW_RING_FIRST) : 4; }
+// NP <= 2 (numDisparities <= 128) leaves most of the shared memory unused: deeper rings and staging there
+#ifndef SW_RING_SMALL
+#define SW_RING_SMALL 6
+#define SW_RING_SMALL_LAST 4
+#define SW_STAGE_SMALL 4
+#endif
+__host__ __device__ constexpr int sw_ring(int NP, bool last)
+{
+    return NP <= 2 ? (last ? SW_RING_SMALL_LAST : SW_RING_SMALL) : (NP <= 4 ? (last ? SW_RING_LAST : SW_RING_FIRST) : 4);
+}
 // slots of the per-row cp.async staging ring for C (and S1 in the last sweep); prefetch distance = slots - 1
-__host__ __device__ constexpr int sw_stage(int NP, bool last) { return NP <= 4 ? 4 : (last ? 3 : 4); }
+__host__ __device__ constexpr int sw_stage(int NP, bool last) { return NP <= 2 ? SW_STAGE_SMALL : (NP <= 4 ? 4 : (last ? 3 : 4)); }
 __host__ __device__ constexpr int sw_roww(int NP) { return NP * 32 + 4; }     // ring row: the vector, its minimum, pad to 16 B
 __host__ __device__ constexpr size_t sw_smem_words(int NP, bool last)
 {

@@ -291,23 +291,16 @@ extern "C" int svb_filter_speckles_s16_dev(int16_t* img, int B, int H, int W, in
 // source contribute 0.  One thread per output pixel; C = 1 or 3 interleaved channels; the
 // maps are shared by the whole batch (blockIdx.z) and stay L2-resident.
 // ---------------------------------------------------------------------------------------
-template <int C, bool GRAY>
-__global__ void __launch_bounds__(256) k_remap_u8(const uint8_t* __restrict__ src, int Hs, int Ws,
-                                                  const int16_t* __restrict__ map1, const uint16_t* __restrict__ map2,
-                                                  int Ho, int Wo, uint8_t* __restrict__ dst)
+// one destination pixel of cv2.remap (A.7): fixed-point bilinear tap of the 2x2 source block, BORDER_CONSTANT 0
+template <int C>
+__device__ __forceinline__ void remap_pixel(const uint8_t* __restrict__ img, int Hs, int Ws, int sx, int sy, int f,
+                                            int (&out)[C])
 {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
-    if (x >= Wo) return;
-    const size_t mo = (size_t)y * Wo + x;
-    const short2 m1 = reinterpret_cast<const short2*>(map1)[mo];
-    const int f = map2[mo] & 1023, fx = f & 31, fy = f >> 5;
-    const int sx = m1.x, sy = m1.y;
+    const int fx = f & 31, fy = f >> 5;
     const int w00 = (32 - fy) * (32 - fx) * 32, w01 = (32 - fy) * fx * 32;
     const int w10 = fy * (32 - fx) * 32, w11 = fy * fx * 32;
-    const uint8_t* img = src + (size_t)blockIdx.z * Hs * Ws * C;
     const bool x0 = sx >= 0 && sx < Ws, x1 = sx + 1 >= 0 && sx + 1 < Ws;
     const bool y0 = sy >= 0 && sy < Hs, y1 = sy + 1 >= 0 && sy + 1 < Hs;
-    int out[C];
 #pragma unroll
     for (int c = 0; c < C; ++c) {
         int acc = 16384;
@@ -323,13 +316,61 @@ __global__ void __launch_bounds__(256) k_remap_u8(const uint8_t* __restrict__ sr
         }
         out[c] = min(max(acc >> 15, 0), 255);
     }
+}
+__device__ __forceinline__ int gray_of(int b, int g, int r) { return (3735 * b + 19235 * g + 9798 * r + 16384) >> 15; }
+
+template <int C, bool GRAY>
+__global__ void __launch_bounds__(256) k_remap_u8(const uint8_t* __restrict__ src, int Hs, int Ws,
+                                                  const int16_t* __restrict__ map1, const uint16_t* __restrict__ map2,
+                                                  int Ho, int Wo, uint8_t* __restrict__ dst)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= Wo) return;
+    const size_t mo = (size_t)y * Wo + x;
+    const short2 m1 = reinterpret_cast<const short2*>(map1)[mo];
+    int out[C];
+    remap_pixel<C>(src + (size_t)blockIdx.z * Hs * Ws * C, Hs, Ws, m1.x, m1.y, map2[mo] & 1023, out);
     const size_t o = ((size_t)blockIdx.z * Ho + y) * Wo + x;
     if (GRAY) {
-        dst[o] = (uint8_t)((3735 * out[0] + 19235 * out[1] + 9798 * out[C - 1] + 16384) >> 15);
+        dst[o] = (uint8_t)gray_of(out[0], out[1], out[C - 1]);
     } else {
 #pragma unroll
         for (int c = 0; c < C; ++c) dst[o * C + c] = (uint8_t)out[c];
     }
+}
+
+// Four destination pixels per thread (Wo % 4 == 0, 16-byte aligned maps and destination): the maps come in as one
+// 128-bit and one 64-bit load, the result leaves as 32-bit words (3 for BGR, 1 for gray / single channel); the
+// source taps stay byte gathers through the read-only path (neighbouring pixels share their cache lines).
+template <int C, bool GRAY>
+__global__ void __launch_bounds__(256) k_remap_u8x4(const uint8_t* __restrict__ src, int Hs, int Ws,
+                                                    const int16_t* __restrict__ map1, const uint16_t* __restrict__ map2,
+                                                    int Ho, int Wo, uint8_t* __restrict__ dst)
+{
+    const int x = (blockIdx.x * blockDim.x + threadIdx.x) * 4, y = blockIdx.y;
+    if (x >= Wo) return;
+    const size_t mo = (size_t)y * Wo + x;
+    const int4 m1 = *reinterpret_cast<const int4*>(map1 + 2 * mo);          // 4 x (sx | sy << 16)
+    const uint2 m2 = *reinterpret_cast<const uint2*>(map2 + mo);            // 4 x u16
+    const uint8_t* img = src + (size_t)blockIdx.z * Hs * Ws * C;
+    const int mm[4] = {m1.x, m1.y, m1.z, m1.w};
+    const unsigned ff[4] = {m2.x & 0xffffu, m2.x >> 16, m2.y & 0xffffu, m2.y >> 16};
+    constexpr int CO = GRAY ? 1 : C;
+    uint8_t px[4 * CO];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        int out[C];
+        remap_pixel<C>(img, Hs, Ws, (int)(short)(mm[q] & 0xffff), mm[q] >> 16, (int)(ff[q] & 1023u), out);
+        if (GRAY) px[q] = (uint8_t)gray_of(out[0], out[1], out[C - 1]);
+        else {
+#pragma unroll
+            for (int c = 0; c < C; ++c) px[q * C + c] = (uint8_t)out[c];
+        }
+    }
+    uint32_t* o = reinterpret_cast<uint32_t*>(dst + (((size_t)blockIdx.z * Ho + y) * Wo + x) * CO);
+#pragma unroll
+    for (int w = 0; w < CO; ++w)
+        o[w] = (uint32_t)px[4 * w] | ((uint32_t)px[4 * w + 1] << 8) | ((uint32_t)px[4 * w + 2] << 16) | ((uint32_t)px[4 * w + 3] << 24);
 }
 
 extern "C" int svb_remap_u8_dev(const uint8_t* src, int B, int Hs, int Ws, int C, const int16_t* map1,
@@ -342,7 +383,13 @@ extern "C" int svb_remap_u8_dev(const uint8_t* src, int B, int Hs, int Ws, int C
     if (to_gray && C != 3) { svb_set_error("remap: to_gray needs 3 channels"); return SVB_ERR_PARAM; }
     dim3 grid(svb_ceil_div(Wo, 256), Ho, B);
     cudaStream_t st = (cudaStream_t)stream;
-    if (C == 1) k_remap_u8<1, false><<<grid, 256, 0, st>>>(src, Hs, Ws, map1, map2, Ho, Wo, dst);
+    const bool x4 = Wo % 4 == 0 && ((uintptr_t)map1 & 15) == 0 && ((uintptr_t)map2 & 7) == 0 && ((uintptr_t)dst & 3) == 0;
+    if (x4) {
+        dim3 g4(svb_ceil_div(Wo / 4, 128), Ho, B);
+        if (C == 1) k_remap_u8x4<1, false><<<g4, 128, 0, st>>>(src, Hs, Ws, map1, map2, Ho, Wo, dst);
+        else if (to_gray) k_remap_u8x4<3, true><<<g4, 128, 0, st>>>(src, Hs, Ws, map1, map2, Ho, Wo, dst);
+        else k_remap_u8x4<3, false><<<g4, 128, 0, st>>>(src, Hs, Ws, map1, map2, Ho, Wo, dst);
+    } else if (C == 1) k_remap_u8<1, false><<<grid, 256, 0, st>>>(src, Hs, Ws, map1, map2, Ho, Wo, dst);
     else if (to_gray) k_remap_u8<3, true><<<grid, 256, 0, st>>>(src, Hs, Ws, map1, map2, Ho, Wo, dst);
     else k_remap_u8<3, false><<<grid, 256, 0, st>>>(src, Hs, Ws, map1, map2, Ho, Wo, dst);
     SVB_LAUNCH_CHECK();

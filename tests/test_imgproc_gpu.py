@@ -28,6 +28,15 @@ def test_remap_and_gray_bit_exact(golden):
     out = svb.remap(src, mm1, mm2, svb.INTER_LINEAR)
     for b in range(3):
         assert np.array_equal(out[b], oracle.remap(src[b], mm1, mm2))
+    # widths that are not a multiple of 4 take the one-pixel-per-thread kernel
+    mm1 = rng.integers(-5, 75, (33, 57, 2)).astype(np.int16)
+    mm2 = rng.integers(0, 1024, (33, 57)).astype(np.uint16)
+    for im in (src, src[..., 1].copy()):
+        out = svb.remap(im, mm1, mm2, svb.INTER_LINEAR)
+        for b in range(3):
+            assert np.array_equal(out[b], oracle.remap(im[b], mm1, mm2))
+    g = svb.remap(src, mm1, mm2, svb.INTER_LINEAR, to_gray=True)
+    assert np.array_equal(g[1], oracle.bgr2gray(oracle.remap(src[1], mm1, mm2)))
 
 
 def test_remap_map_cache_follows_the_arrays():

@@ -831,8 +831,11 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
         const int* done_succ = &s_done[warp + 1];
 
         for (int i = 0; i < nloop; ++i) {
-            if (SW_EXPERIMENT != 6 && VERT && seenP < i + 2) {
-                while ((seenP = lds_acquire_cta(done_pred)) < i + 2) __nanosleep(SW_SLEEP_NS);
+            // column i + 1 of the row above is only needed by the diagonal-from-ahead path: without it (3WAY, HH4) a row
+            // follows the row above one column behind instead of two (a single frame's dependent chain gets shorter)
+            constexpr int NEED = (MASK & 8) ? 2 : 1;
+            if (SW_EXPERIMENT != 6 && VERT && seenP < i + NEED) {
+                while ((seenP = lds_acquire_cta(done_pred)) < i + NEED) __nanosleep(SW_SLEEP_NS);
             }
             if (SW_EXPERIMENT != 6 && VERT && seenS < i - RING + 2) {
                 while ((seenS = lds_acquire_cta(done_succ)) < i - RING + 2) __nanosleep(SW_SLEEP_NS);

@@ -206,3 +206,29 @@ def test_sgbm_single_live_frame_bit_exact(mode):
     prm = dict(minDisparity=0, numDisparities=D, blockSize=bs, P1=8 * bs * bs, P2=32 * bs * bs, disp12MaxDiff=1,
                preFilterCap=63, uniquenessRatio=10, speckleWindowSize=100, speckleRange=32, mode=mode)
     assert np.array_equal(svb.StereoSGBM_create(**prm).compute(l, r), oracle.sgbm_compute(l, r, **prm))
+
+
+def test_sgbm_color_random_params_vs_oracle():
+    """3-channel input over random parameters, modes and shapes (the oracle's colour path is pinned by live cv2
+    and by the sgbm_color_* goldens)."""
+    _torch()
+    rng = np.random.default_rng(321)
+    for it in range(12):
+        D = int(rng.choice([16, 32, 64, 96, 160]))
+        bs = int(rng.choice([1, 3, 5, 7]))
+        mode = int(rng.choice([0, 1, 2, 3]))
+        minD = 0 if mode == 2 else int(rng.choice([0, -8, 4]))
+        if mode == 2 and bs == 1:
+            bs = 3
+        H = int(rng.integers(20, 60))
+        W = int(rng.integers(D + abs(minD) + bs + 8, D + abs(minD) + 100))
+        prm = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=8 * 3 * bs * bs, P2=32 * 3 * bs * bs,
+                   disp12MaxDiff=int(rng.choice([1, 2])), preFilterCap=int(rng.choice([15, 31, 63])),
+                   uniquenessRatio=int(rng.choice([0, 10])), speckleWindowSize=int(rng.choice([0, 50])),
+                   speckleRange=2, mode=mode)
+        l = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+        r = np.roll(l, -int(rng.integers(1, 9)), axis=1)
+        r = np.clip(r.astype(np.int16) + rng.integers(-10, 11, r.shape), 0, 255).astype(np.uint8)
+        got = svb.StereoSGBM_create(**prm).compute(l, r)
+        ref = oracle.sgbm_compute(l, r, **prm)
+        assert np.array_equal(got, ref), (H, W, prm, int((got != ref).sum()))

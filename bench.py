@@ -61,6 +61,34 @@ def kernel_alg_bytes(wl, name):
     return {"k_cost": n2, "k_sweep<first>": 2 * n2, "k_sweep<last+wta>": 2 * n2}.get(name)
 
 
+def load_pinned_hashes():
+    """SHA-256 of cv2's own output for the seeds this bench feeds (tests/golden/fullsize_sha256.json, written by
+    tests/golden/make_golden_fullsize.py with cv2 4.13.0; only the hashes travel, never cv2)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "tests", "golden", "fullsize_sha256.json")))["bench"]
+    except Exception:
+        return {}
+
+
+def parity_check(workload, outs, seed0, nuniq):
+    """OUTSIDE the timed region: hash the first and the last pair of every output batch in `outs`
+    ({name: int16 [B,H,W] host array}) and compare with cv2's committed hash for that pair's seed."""
+    import hashlib
+    pinned = load_pinned_hashes()
+    checked, ok = [], True
+    for name, arr in outs.items():
+        B = arr.shape[0]
+        for i in sorted({0, B - 1}):
+            seed = seed0 + i % nuniq
+            want = pinned.get(f"{workload}/seed{seed}", {}).get("sha256")
+            got = hashlib.sha256(np.ascontiguousarray(arr[i]).tobytes()).hexdigest()
+            match = None if want is None else (got == want)
+            checked.append({"output": name, "pair": i, "seed": seed, "sha256": got[:16], "match": match})
+            ok = ok and bool(match)
+    return {"pairs_checked": len(checked), "sha256_match": ok, "against": "tests/golden/fullsize_sha256.json "
+            "(cv2 4.13.0 StereoSGBM.compute on the same seeded pairs)", "checked": checked}
+
+
 def make_inputs(wl, B, seed0):
     """Synthetic pairs: a few distinct seeded scenes, tiled to the batch (generation is slow)."""
     from stereovision_b200.synth import make_pair
@@ -291,10 +319,16 @@ def main():
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
-    tmax = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    # ---- parity of what was just timed (outside the timed region): first and last pair of the device-resident
+    # output and of the host-path output against cv2's committed hashes; the wavefront flag of the device path
+    _lib.check(L.svb_sgbm_check(h))
+    parity = parity_check(args.workload, {"value(dev)": Od.cpu().numpy(), "e2e(host)": Op.numpy()},
+                          seed0=1000 * rank, nuniq=min(B, 4))
+    tmax = torch.tensor([ms, e2e_s * 1e3, 0.0 if parity["sha256_match"] else 1.0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     ms, e2e_ms = float(tmax[0]), float(tmax[1])
+    parity["all_ranks_match"] = float(tmax[2]) == 0.0
 
     if rank == 0:
         pairs = B * world * args.steps
@@ -339,6 +373,7 @@ def main():
             "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": 2 * B * H * W * world,
                     "d2h_bytes_per_step": 2 * B * H * W * world},
             "gpu_launches": launches * world,
+            "parity": parity,
             "clocks": sampler.summary(),
             "roofline": roof,
         }

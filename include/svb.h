@@ -80,6 +80,16 @@ int svb_sgbm_set_debug(svb_sgbm_t* h, int enable);
 int svb_sgbm_debug_stages(svb_sgbm_t* h, uint16_t* C_host, uint16_t* S_host, int16_t* raw_host);
 /* Number of kernel launches issued by the last compute call (bench.py's gpu_launches). */
 int svb_sgbm_last_launches(const svb_sgbm_t* h);
+/* The aggregation kernels hand rows from CTA to CTA through device-side progress counters; a wait that runs into
+ * its spin limit (only a device reset or a foreign writer can cause that) raises a sticky flag instead of hanging.
+ * svb_sgbm_check waits for the handle's last compute and returns SVB_ERR_CUDA if the flag was raised since the
+ * previous check (those disparities are invalid).  The *_host entry points call it before they return; a *_dev
+ * caller calls it at its own synchronisation points -- and the NEXT *_dev compute on the handle reports a flag
+ * left by a finished predecessor without synchronising.  Successive computes of one handle are ordered on the
+ * device even when they arrive on different streams (they share one workspace). */
+int svb_sgbm_check(svb_sgbm_t* h);
+/* Test hook: raise that flag by hand. */
+int svb_sgbm_debug_trip_error(svb_sgbm_t* h);
 
 /* Per-stage device timing (CUDA events on the launching stream) for bench.py's roofline.
  * enable=1 starts/reset recording, 0 stops.  get_profile synchronises and returns the number

@@ -134,8 +134,16 @@ int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W, cons
             /* cv2 evaluates every column of the width1 domain (windows clamp at the image sides); the
              * columns outside the valid ROI only matter as candidates of validateDisparity below and
              * are blanked afterwards */
-            if ((x < x_lo || x >= x_hi) && p->disp12MaxDiff < 0) continue;
-            if (x >= W) continue;                          /* minDisparity > 0: cv2 runs past the row end there */
+            /* minDisparity > 0: the last minDisparity positions of the width1 domain lie past the row end
+             * (x >= W).  cv2 computes them all the same (windows clamp to the image) and its store lands in
+             * the first minDisparity columns of the NEXT row.  Inside the ROI rows the column blanking wipes
+             * that again; the spill of the last ROI row (y = H-1-r) into row H-r survives -- that row was
+             * blanked before the matcher ran (stereobm.cpp FindStereoCorrespInvoker).  Probed on cv2 4.13
+             * (single stripe; with several stripes cv2 races with itself at the stripe seams). */
+            const int spill = x >= W;
+            if (spill && y != H - 1 - r) continue;
+            if (!spill && (x < x_lo || x >= x_hi) && p->disp12MaxDiff < 0) continue;
+            int16_t* out = spill ? disp + (size_t)(y + 1) * W + (x - W) : disp + (size_t)y * W + x;
             int ts = 0;
             for (int k = 0; k < D; ++k) sad[k + 1] = 0;
             for (int j = -r; j <= r; ++j) {
@@ -160,10 +168,9 @@ int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W, cons
                 if (k < D) continue;
             }
             sad[0] = sad[2]; sad[D + 1] = sad[D - 1];
-            cost[(size_t)y * W + x] = sad[mind + 1];
+            if (!spill) cost[(size_t)y * W + x] = sad[mind + 1];
             const int pp = sad[mind + 2], n = sad[mind], dd = pp + n - 2 * sad[mind + 1] + abs(pp - n);
-            disp[(size_t)y * W + x] =
-                (int16_t)((((D - mind - 1 + minD) * 256 + (dd != 0 ? (pp - n) * 256 / dd : 0) + 15) >> 4));
+            *out = (int16_t)((((D - mind - 1 + minD) * 256 + (dd != 0 ? (pp - n) * 256 / dd : 0) + 15) >> 4));
         }
     /* stereobm.cpp `if (disp12MaxDiff >= 0) validateDisparity(...)` with the winning SAD as cost; the
      * columns outside the valid ROI took part as candidates (probed, 40/40 random cv2 cases) and are blanked
@@ -172,7 +179,7 @@ int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W, cons
         orc_validate_disparity(disp, cost, H, W, minD, D, p->disp12MaxDiff);
         for (int y = 0; y < H; ++y)
             for (int x = 0; x < W; ++x)
-                if (x < x_lo || x >= x_hi) disp[(size_t)y * W + x] = (int16_t)FILTERED;
+                if ((x < x_lo || x >= x_hi) && !(y == H - r && x < minD)) disp[(size_t)y * W + x] = (int16_t)FILTERED;
     }
     free(L); free(R); free(sad); free(cost);
     if (p->speckleWindowSize > 0)

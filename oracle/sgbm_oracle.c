@@ -198,6 +198,16 @@ static void wta_row(const uint16_t* Srow, int W, int width1, int D, int minD, in
         int best = -1, minS = MAXC;
         for (int d = 0; d < D; ++d) if (s[d] < minS) { minS = s[d]; best = d; }
         if (best < 0) continue;
+        if (three_way) {
+            /* cv2's 3WAY argmin runs 8 int16 lanes over d (lane = d mod 8): within a lane a later d with an
+             * EQUAL cost replaces the earlier one, across lanes the lowest recorded d wins.  Only visible with
+             * uniquenessRatio = 0 (any tie further than 1 apart is rejected otherwise).  Probed on cv2 4.13. */
+            int top[8];
+            for (int j = 0; j < 8; ++j) top[j] = -1;
+            for (int d = 0; d < D; ++d) if (s[d] == minS) top[d & 7] = d;
+            best = D;
+            for (int j = 0; j < 8; ++j) if (top[j] >= 0 && top[j] < best) best = top[j];
+        }
         int reject = 0;
         if (three_way) {
             /* cv2's 3WAY vector loop tests Sp[d] < (short)(thresh+1), thresh = 100*minS/(100-u)

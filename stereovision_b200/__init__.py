@@ -12,7 +12,7 @@ from .cv_api import (  # noqa: F401
     StereoSGBM, StereoBM, StereoSGBM_create, StereoBM_create,
     remap, cvtColor, medianBlur, filterSpeckles, validateDisparity, reprojectImageTo3D, disparity_to_depth,
     initUndistortRectifyMap, CV_16SC2,
-    release_workspaces,
+    release_workspaces, pool_size, invalidate_map_cache,
 )
 
 from .fusion import (  # noqa: F401

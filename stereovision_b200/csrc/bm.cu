@@ -357,6 +357,54 @@ extern "C" int svb_validate_disparity_dev(int16_t* disp, const void* cost, int c
     return SVB_OK;
 }
 
+// minDisparity > 0: the last minDisparity positions of cv2's width1 domain lie past the row end (left column
+// lofs + xp >= W).  cv2 evaluates them like any other position (window columns clamp to the image) and its store
+// lands in the first minDisparity columns of the NEXT row; inside the ROI rows the column blanking wipes that again,
+// but the spill of the last ROI row (y = H-1-r) into row H-r survives (oracle/bm_oracle.c; probed on cv2 4.13).
+// One warp per (image, spilled position): brute-force SAD over the window, lanes over the disparity index.
+__global__ void __launch_bounds__(32) k_bm_spill(const uint8_t* __restrict__ lp, const uint32_t* __restrict__ rdesc,
+                                                 BmGeo g, int16_t* __restrict__ disp)
+{
+    __shared__ int sad[512 + 2];
+    const int lane = threadIdx.x, b = blockIdx.y;
+    const int xp = g.W - g.lofs + blockIdx.x;                // lofs + xp = W + blockIdx.x
+    const int y = g.H - 1 - g.r, D = g.D, r = g.r;
+    const uint8_t* L = lp + (size_t)b * g.H * g.W;
+    auto rv = [&](int yy, int x) -> int {                    // prefiltered right pixel: low half of its paired plane entry
+        return (int)(rdesc[(size_t)(b * g.H + yy) * 4 * g.Wh + (size_t)(x & 1) * g.Wh + (x >> 1)] & 0xffffu);
+    };
+    int ts = 0;
+    for (int k = lane; k < D; k += 32) sad[k + 1] = 0;
+    for (int j = -r; j <= r; ++j) {
+        const int lc = min(max(xp + j + g.lofs, 0), g.W - 1);
+        const int rs = min(max(xp + j + g.rofs, 0), g.W - D);
+        for (int i = -r; i <= r; ++i) {
+            const int yy = min(max(y + i, 0), g.H - 1);
+            const int lv = L[(size_t)yy * g.W + lc];
+            ts += abs(lv - g.cap);
+            for (int k = lane; k < D; k += 32) sad[k + 1] += abs(lv - rv(yy, rs + k));
+        }
+    }
+    __syncwarp();
+    if (ts < g.tex) return;
+    uint32_t key = 0xffffffffu;
+    for (int k = lane; k < D; k += 32) key = min(key, ((uint32_t)sad[k + 1] << 16) | (uint32_t)k);
+    key = __reduce_min_sync(0xffffffffu, key);
+    const int minsad = (int)(key >> 16), mind = (int)(key & 0xffffu);
+    if (g.uniq > 0) {
+        const int thresh = minsad + minsad * g.uniq / 100;
+        bool rej = false;
+        for (int k = lane; k < D; k += 32) rej |= (k < mind - 1 || k > mind + 1) && sad[k + 1] <= thresh;
+        if (__any_sync(0xffffffffu, rej)) return;
+    }
+    if (lane == 0) {
+        sad[0] = sad[2]; sad[D + 1] = sad[D - 1];
+        const int pp = sad[mind + 2], n = sad[mind], dd = pp + n - 2 * minsad + abs(pp - n);
+        disp[(size_t)b * g.H * g.W + (size_t)(y + 1) * g.W + blockIdx.x] =
+            (int16_t)(((D - mind - 1 + g.minD) * 256 + (dd != 0 ? (pp - n) * 256 / dd : 0) + 15) >> 4);
+    }
+}
+
 __global__ void k_bm_fill(int16_t* p, size_t n, int16_t v)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -373,6 +421,8 @@ struct svb_bm {
     // (every BM kernel is per image, so sub-batches cost nothing on the device)
     cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
     cudaEvent_t ev_in[4] = {}, ev_done[4] = {};
+    // successive computes of one handle share its workspace: a compute that arrives on another stream waits here
+    cudaEvent_t ev_last = nullptr;
 };
 
 static int bm_geo(const svb_bm_params& p, int H, int W, BmGeo& g, bool& trivial)
@@ -439,6 +489,7 @@ extern "C" void svb_bm_destroy(svb_bm_t* h)
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_run) cudaStreamDestroy(h->s_run);
     if (h->s_out) cudaStreamDestroy(h->s_out);
+    if (h->ev_last) cudaEventDestroy(h->ev_last);
     h->ws.release(); h->stage_in.release(); h->stage_out.release();
     delete h;
 }
@@ -476,6 +527,12 @@ extern "C" int svb_bm_compute_dev(svb_bm_t* h, const uint8_t* left, const uint8_
     if (rc != SVB_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     h->launches = 0;
+    if (!h->ev_last) SVB_CUDA(cudaEventCreateWithFlags(&h->ev_last, cudaEventDisableTiming));
+    else SVB_CUDA(cudaStreamWaitEvent(st, h->ev_last, 0));
+    struct Rec {                                             // whatever path returns: the next compute waits for this one
+        svb_bm* h; cudaStream_t st;
+        ~Rec() { cudaEventRecord(h->ev_last, st); }
+    } rec{h, st};
     const size_t npix = (size_t)B * H * W;
     k_bm_fill<<<svb_ceil_div(npix, 256), 256, 0, st>>>(disp, npix, (int16_t)g.FILTERED);
     SVB_LAUNCH_CHECK(); h->launches++;
@@ -535,6 +592,10 @@ extern "C" int svb_bm_compute_dev(svb_bm_t* h, const uint8_t* left, const uint8_
         }
         k_validate_check<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(
             copy, disp, H, W, minX1, maxX1, g.FILTERED, h->prm.disp12MaxDiff * 16, g.lofs + g.r, W - g.r, keys);
+        SVB_LAUNCH_CHECK(); h->launches++;
+    }
+    if (g.minD > 0 && g.lofs + g.width1 > W) {
+        k_bm_spill<<<dim3(g.lofs + g.width1 - W, B), 32, 0, st>>>(lp, rdesc, g, disp);
         SVB_LAUNCH_CHECK(); h->launches++;
     }
     if (h->prm.speckleWindowSize > 0) {

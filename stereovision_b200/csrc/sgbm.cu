@@ -906,6 +906,38 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                         kmin = min(kmin, min(klo, khi));
                     }
                     kmin = __reduce_min_sync(FULLMASK, kmin);
+                    if constexpr (MASK == 1) {
+                        // cv2's 3WAY argmin runs 8 int16 lanes over d (lane = d mod 8): within a lane a later d with an
+                        // EQUAL cost replaces the earlier one, across lanes the lowest recorded d wins (oracle/sgbm_oracle.c).
+                        // Only visible without a uniqueness test (any tie further than 1 apart is rejected otherwise).
+                        if (g.mode == SVB_MODE_SGBM_3WAY && g.uniq == 0) {
+                            const uint32_t m2 = pk_dup(kmin >> 16);
+                            uint32_t ties = 0;
+#pragma unroll
+                            for (int k = 0; k < NP; ++k) {
+                                const uint32_t x = S[k] ^ m2;
+                                ties += ((x & 0xffffu) == 0u) + ((x >> 16) == 0u);
+                            }
+                            if (__reduce_add_sync(FULLMASK, ties) > 1u) {
+                                int bestd = 0x7fff;
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) {
+                                    int v = -1;
+#pragma unroll
+                                    for (int k = 0; k < NP; ++k) {
+                                        const int dlo = NP * lane + k;
+                                        if ((dlo & 7) != j) continue;
+                                        const uint32_t x = S[k] ^ m2;
+                                        if ((x >> 16) == 0u) v = max(v, dlo + g.HALF);
+                                        else if ((x & 0xffffu) == 0u) v = max(v, dlo);
+                                    }
+                                    v = __reduce_max_sync(FULLMASK, v);
+                                    if (v >= 0) bestd = min(bestd, v);
+                                }
+                                kmin = (kmin & 0xffff0000u) | (uint32_t)bestd;
+                            }
+                        }
+                    }
                     const int th = wta_threshold(g, (int)(kmin >> 16));
                     // uniqueness: count disparities with S < th; the ones at best-1..best+1 are taken out later
                     const uint32_t th2 = pk_dup((uint32_t)th);
@@ -1034,8 +1066,17 @@ struct svb_sgbm {
     std::vector<Ev> evs;
     // last compute (for debug_stages)
     SgbmGeo last_geo{};
-    size_t off_C = 0, off_S = 0, off_raw = 0, off_err = 0;
+    size_t off_C = 0, off_S = 0, off_raw = 0;
     bool have_last = false;
+    // The wavefront's error flag (a wait that ran into its spin limit) lives in its own small allocation and is
+    // STICKY: kernels only ever set it.  Every compute copies it to a pinned host word behind its kernels and
+    // records ev_last there; the next compute on the handle (or svb_sgbm_check) reports a tripped flag.
+    // ev_last also orders successive computes of the handle that arrive on DIFFERENT streams: they share one
+    // workspace (ticket counter, progress flags, carry, C and S volumes) and must not overlap on the device.
+    int* d_err = nullptr;
+    int* h_err = nullptr;           // pinned
+    cudaEvent_t ev_last = nullptr;
+    bool pending = false;           // a compute has been enqueued whose flag has not been looked at yet
 };
 
 static int make_geo(const svb_sgbm_params& p, int H, int W, int cn, SgbmGeo& g)
@@ -1152,6 +1193,9 @@ extern "C" void svb_sgbm_destroy(svb_sgbm_t* h)
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_run) cudaStreamDestroy(h->s_run);
     if (h->s_out) cudaStreamDestroy(h->s_out);
+    if (h->ev_last) cudaEventDestroy(h->ev_last);
+    if (h->d_err) cudaFree(h->d_err);
+    if (h->h_err) cudaFreeHost(h->h_err);
     h->ws.release(); h->stage_in.release(); h->stage_out.release();
     delete h;
 }
@@ -1325,7 +1369,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     SweepArgs a;
     a.C = Cv; a.S = Sv;
     a.carry = (uint32_t*)(ws + L.carry); a.cmin = (uint32_t*)(ws + L.cmin);
-    a.ticket = sync; a.err = sync + 1; a.prog = sync + 16;
+    a.ticket = sync; a.err = h->d_err; a.prog = sync + 16;
     a.raw = raw; a.key = key;
     // Rows per band: sw_rows(NP).  A sweep WITHOUT inter-row paths (the last sweep of MODE_SGBM / 3WAY: <- only) has
     // independent rows, so a small batch (a single live frame) gets shorter bands there and spreads over all SMs
@@ -1405,6 +1449,18 @@ extern "C" int svb_sgbm_compute_dev(svb_sgbm_t* h, const uint8_t* left, const ui
 static int sgbm_compute_impl(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
                              int B, int H, int W, int cn, int16_t* disp, void* stream, const HostPipe* hp);
 
+// the last compute has finished: look at the flag it copied out, clear a tripped one on both sides
+static int take_sweep_err(svb_sgbm* h)
+{
+    h->pending = false;
+    if (!*h->h_err) return SVB_OK;
+    *h->h_err = 0;
+    SVB_CUDA(cudaMemset(h->d_err, 0, sizeof(int)));
+    svb_set_error("k_sweep: an inter-band wait exceeded its spin limit; the disparities of the computes on this "
+                  "handle since the last check are invalid");
+    return SVB_ERR_CUDA;
+}
+
 extern "C" int svb_sgbm_compute_cn_dev(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
                                        int B, int H, int W, int cn, int16_t* disp, void* stream)
 {
@@ -1427,6 +1483,22 @@ static int sgbm_compute_impl(svb_sgbm_t* h, const uint8_t* left, const uint8_t* 
     const int nb = pick_chunk(h, g, B);
     const SgbmLayout L = make_layout(g, nb);
     cudaStream_t st = (cudaStream_t)stream;
+    if (!h->ev_last) {
+        SVB_CUDA(cudaEventCreateWithFlags(&h->ev_last, cudaEventDisableTiming));
+        SVB_CUDA(cudaMalloc((void**)&h->d_err, 256));
+        SVB_CUDA(cudaMemset(h->d_err, 0, 256));
+        SVB_CUDA(cudaHostAlloc((void**)&h->h_err, sizeof(int), cudaHostAllocDefault));
+        *h->h_err = 0;
+    } else {
+        // the previous compute of this handle: report its flag if it has finished (no synchronisation here) ...
+        if (h->pending && cudaEventQuery(h->ev_last) == cudaSuccess) {
+            rc = take_sweep_err(h);
+            if (rc != SVB_OK) return rc;
+        }
+        (void)cudaGetLastError();                            // cudaErrorNotReady is not an error
+        // ... and keep this one behind it, whatever stream it arrives on (one workspace per handle)
+        SVB_CUDA(cudaStreamWaitEvent(st, h->ev_last, 0));
+    }
     if (L.total > h->ws.cap) {
         rc = h->ws.reserve(L.total);
         if (rc != SVB_OK) return rc;
@@ -1447,17 +1519,31 @@ static int sgbm_compute_impl(svb_sgbm_t* h, const uint8_t* left, const uint8_t* 
         }
         if (rc != SVB_OK) return rc;
     }
-    h->last_geo = g; h->off_C = L.C; h->off_S = L.S; h->off_raw = L.raw; h->off_err = L.sync + 4; h->have_last = true;
+    h->last_geo = g; h->off_C = L.C; h->off_S = L.S; h->off_raw = L.raw; h->have_last = true;
+    SVB_CUDA(cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
+    SVB_CUDA(cudaEventRecord(h->ev_last, st));
+    h->pending = true;
     return SVB_OK;
 }
 
-// Synchronise and report a wavefront wait that hit its spin limit (cannot happen unless the
-// device was reset underneath us; results of that call are invalid).
-static int check_sweep_err(svb_sgbm* h)
+// Wait for the handle's last compute and report a wavefront wait that hit its spin limit (cannot happen
+// unless the device was reset underneath us or two processes share the workspace; the results of the
+// computes since the last check are invalid).  This is what a *_dev caller polls at its own sync points;
+// the *_host entry points call it before they return.
+extern "C" int svb_sgbm_check(svb_sgbm_t* h)
 {
-    int e = 0;
-    SVB_CUDA(cudaMemcpy(&e, (const char*)h->ws.p + h->off_err, 4, cudaMemcpyDeviceToHost));
-    if (e) { svb_set_error("k_sweep: inter-band wait exceeded its spin limit"); return SVB_ERR_CUDA; }
+    if (!h) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
+    if (!h->ev_last || !h->pending) return SVB_OK;
+    SVB_CUDA(cudaEventSynchronize(h->ev_last));
+    return take_sweep_err(h);
+}
+static int check_sweep_err(svb_sgbm* h) { return svb_sgbm_check(h); }
+// Test hook: raise the flag as a timed-out wait would, so that the reporting path can be exercised.
+extern "C" int svb_sgbm_debug_trip_error(svb_sgbm_t* h)
+{
+    if (!h || !h->d_err) { svb_set_error("no previous compute"); return SVB_ERR_PARAM; }
+    const int one = 1;
+    SVB_CUDA(cudaMemcpy(h->d_err, &one, sizeof(int), cudaMemcpyHostToDevice));
     return SVB_OK;
 }
 

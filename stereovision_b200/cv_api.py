@@ -43,15 +43,45 @@ def _is_tensor(x):
 
 
 def _ensure_device(device=None):
-    """cudaSetDevice for the calling thread (the reference calls from a pool thread,
-    fused_depth_map.py:2591)."""
+    """Make `device` (default: torch's current device) the CUDA device of the calling thread for the rest of the
+    public call -- libsvb launches on the runtime's current device, and the reference calls from a pool thread
+    (fused_depth_map.py:2591).  Compared against torch's live current device on every call, never a cached
+    value; `_restores_device` puts the caller's device back when the public function returns."""
     torch = _torch()
+    if not torch.cuda.is_available():
+        raise _lib.SvbError("no CUDA device available; stereovision_b200 has no CPU fallback")
+    cur = torch.cuda.current_device()
     if device is None:
-        device = torch.cuda.current_device() if torch.cuda.is_available() else 0
-    if getattr(_tls, "device", None) != device:
-        _lib.check(_lib.lib().svb_init(int(device)))
-        _tls.device = device
+        device = cur
+    device = int(device)
+    if device != cur:
+        torch.cuda.set_device(device)
+    seen = getattr(_tls, "inited", None)
+    if seen is None:
+        seen = _tls.inited = set()
+    if device not in seen:                    # once per (thread, device): context + sm_100 check
+        _lib.check(_lib.lib().svb_init(device))
+        seen.add(device)
     return device
+
+
+def _restores_device(fn):
+    """Decorator of every public entry point: whatever device the call had to select (inputs living on another
+    GPU than the thread's current one), the caller's current device is restored on the way out."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        torch = _torch()
+        if not torch.cuda.is_available():
+            return fn(*args, **kwargs)
+        prev = torch.cuda.current_device()
+        try:
+            return fn(*args, **kwargs)
+        finally:
+            if torch.cuda.current_device() != prev:
+                torch.cuda.set_device(prev)
+    return wrapper
 
 
 def _stream_ptr():
@@ -59,32 +89,62 @@ def _stream_ptr():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+_POOL_PER_THREAD = 4          # matcher handles (device workspaces) a thread keeps alive; least recently used goes first
+
+
+def _destroy(kind, h):
+    L = _lib.lib()
+    (L.svb_sgbm_destroy if kind == "sgbm" else L.svb_bm_destroy)(h)
+
+
 def _handle(kind, params, device):
-    key = (threading.get_ident(), device, kind, params)
+    """The calling thread's handle for (device, kind, params).  The reference builds a new matcher object per frame
+    (depth_map.py:894) and changes parameters live (fused_depth_map.py:3241-3289), so handles are pooled per thread
+    (a handle is never shared between threads) and the pool is an LRU: a thread keeps at most _POOL_PER_THREAD
+    handles, evicted ones -- and everything a finished thread left behind -- are destroyed (svb_*_destroy frees the
+    device workspace)."""
+    me = threading.get_ident()
+    key = (me, device, kind, params)
     with _pool_lock:
-        h = _pool.get(key)
-    if h is None:
-        L = _lib.lib()
-        out = ctypes.c_void_p()
-        if kind == "sgbm":
-            prm = _lib.SgbmParams(*params)
-            _lib.check(L.svb_sgbm_create(ctypes.byref(prm), ctypes.byref(out)))
-        else:
-            prm = _lib.BmParams(*params)
-            _lib.check(L.svb_bm_create(ctypes.byref(prm), ctypes.byref(out)))
-        h = out
-        with _pool_lock:
-            _pool[key] = h
-    return h
+        h = _pool.pop(key, None)
+        if h is not None:
+            _pool[key] = h                    # most recently used last (dicts keep insertion order)
+            return h
+    L = _lib.lib()
+    out = ctypes.c_void_p()
+    if kind == "sgbm":
+        prm = _lib.SgbmParams(*params)
+        _lib.check(L.svb_sgbm_create(ctypes.byref(prm), ctypes.byref(out)))
+    else:
+        prm = _lib.BmParams(*params)
+        _lib.check(L.svb_bm_create(ctypes.byref(prm), ctypes.byref(out)))
+    alive = {t.ident for t in threading.enumerate()}
+    doomed = []
+    with _pool_lock:
+        _pool[key] = out
+        mine = [k for k in _pool if k[0] == me]
+        for k in mine[:max(0, len(mine) - _POOL_PER_THREAD)]:
+            doomed.append((k[2], _pool.pop(k)))
+        for k in [k for k in _pool if k[0] not in alive]:
+            doomed.append((k[2], _pool.pop(k)))
+    for kd, hd in doomed:                      # svb_*_destroy waits for the handle's own work (cudaFree)
+        _destroy(kd, hd)
+    return out
 
 
 def release_workspaces():
-    """Free every cached matcher handle (device workspaces)."""
-    L = _lib.lib()
+    """Free every cached matcher handle (device workspaces).  Call it when no other thread is inside compute()."""
     with _pool_lock:
-        for (_, _, kind, _), h in _pool.items():
-            (L.svb_sgbm_destroy if kind == "sgbm" else L.svb_bm_destroy)(h)
+        items = list(_pool.items())
         _pool.clear()
+    for (_, _, kind, _), h in items:
+        _destroy(kind, h)
+
+
+def pool_size():
+    """Number of live matcher handles (all threads)."""
+    with _pool_lock:
+        return len(_pool)
 
 
 def _check_pair(left, right):
@@ -111,6 +171,7 @@ class _Matcher:
     def _params(self):
         raise NotImplementedError
 
+    @_restores_device
     def compute(self, left, right):
         """disparity = matcher.compute(left, right) -> int16 (x16 fixed point), same shape."""
         _check_pair(left, right)
@@ -149,6 +210,14 @@ class _Matcher:
 
     def _pre_compute(self, h):
         pass
+
+    def check(self):
+        """Wait for this thread's last compute() with these parameters and raise if the aggregation kernels flagged
+        a timed-out inter-CTA wait (svb_sgbm_check).  NumPy calls check before they return; for torch-tensor
+        calls (asynchronous, no hidden sync) this is the caller's hook at its own synchronisation point."""
+        h = getattr(self, "_last", None)
+        if h is not None and self._kind == "sgbm":
+            _lib.check(_lib.lib().svb_sgbm_check(h))
 
     def last_launches(self):
         L = _lib.lib()
@@ -272,10 +341,29 @@ _map_cache = {}
 _map_cache_lock = threading.Lock()
 
 
+_MAP_FULL_CHECK_BYTES = 4 << 20
+
+
 def _map_sample(a):
+    """Fingerprint of a map's contents: the whole array for maps up to 4 MB (a 640x480 CV_16SC2 map is 1.2 MB,
+    about 0.1 ms), XOR-folded as 64-bit words; 4096 strided elements plus the tail beyond that (hashing 12 MB of
+    1080p maps on every frame would cost more than the remap).  In-place recalibration of a large map should go
+    through invalidate_map_cache() -- or keep the maps on the device (initUndistortRectifyMap(as_tensor=True),
+    load_stereo_calibration(device_maps=True)), which bypasses the cache."""
     flat = a.reshape(-1)
-    step = max(1, flat.size // 257)
+    if flat.nbytes <= _MAP_FULL_CHECK_BYTES:
+        raw = flat.view(np.uint8)
+        n8 = raw.size // 8 * 8
+        fold = int(np.bitwise_xor.reduce(raw[:n8].view(np.uint64))) if n8 else 0
+        return (fold, int(raw[:n8].view(np.uint64)[::7].sum(dtype=np.uint64)) if n8 else 0, raw[n8:].tobytes())
+    step = max(1, flat.size // 4096)
     return flat[::step].tobytes() + flat[-64:].tobytes()
+
+
+def invalidate_map_cache():
+    """Drop every cached device copy of a rectification map."""
+    with _map_cache_lock:
+        _map_cache.clear()
 
 
 def _cached_map(a):
@@ -303,6 +391,7 @@ def _cached_map(a):
     return t
 
 
+@_restores_device
 def remap(src, map1, map2, interpolation=INTER_LINEAR, to_gray=False):
     """cv2.remap(src, map1, map2, cv2.INTER_LINEAR) for the fixed-point maps the reference
     builds with initUndistortRectifyMap(..., CV_16SC2) (depth_map.py:633-638, 815-826).
@@ -339,6 +428,7 @@ def remap(src, map1, map2, interpolation=INTER_LINEAR, to_gray=False):
     return _ret(out, was)
 
 
+@_restores_device
 def cvtColor(src, code=COLOR_BGR2GRAY):
     """cv2.cvtColor(img, cv2.COLOR_BGR2GRAY) (depth_map.py:871-879)."""
     if code != COLOR_BGR2GRAY:
@@ -353,6 +443,7 @@ def cvtColor(src, code=COLOR_BGR2GRAY):
     return _ret(out, was)
 
 
+@_restores_device
 def medianBlur(src, ksize):
     """cv2.medianBlur: ksize 3 on int16 (as inside StereoSGBM) or 5 on float32 (depth_map.py:912)."""
     torch = _torch()
@@ -373,6 +464,7 @@ def medianBlur(src, ksize):
     return _ret(out, was)
 
 
+@_restores_device
 def filterSpeckles(img, newVal, maxSpeckleSize, maxDiff):
     """cv2.filterSpeckles(img, newVal, maxSpeckleSize, maxDiff) on int16; returns the filtered
     image (tensors are modified in place like cv2 does, NumPy inputs get a filtered copy back
@@ -394,6 +486,7 @@ def filterSpeckles(img, newVal, maxSpeckleSize, maxDiff):
     return img
 
 
+@_restores_device
 def validateDisparity(disparity, cost, minDisparity, numberOfDisparities, disp12MaxDiff=1):
     """cv2.validateDisparity(disparity, cost, minDisparity, numberOfDisparities[, disp12MaxDiff]): the
     left-right check StereoBM runs when disp12MaxDiff >= 0.  disparity int16 (x16), cost int16 or int32,
@@ -418,6 +511,7 @@ def validateDisparity(disparity, cost, minDisparity, numberOfDisparities, disp12
     return disparity
 
 
+@_restores_device
 def reprojectImageTo3D(disparity, Q, handleMissingValues=False):
     """cv2.reprojectImageTo3D(disparity, Q): int16 input is NOT divided by 16."""
     torch = _torch()
@@ -438,6 +532,7 @@ def reprojectImageTo3D(disparity, Q, handleMissingValues=False):
     return _ret(out, was)
 
 
+@_restores_device
 def disparity_to_depth(disp16, fx=700.0, baseline=0.08, min_disp=0.0, min_depth=0.3, max_depth=2.0):
     """The tail of depth_map.create_depth_map (depth_map.py:909-933) in one kernel:
     disparity = disp16/16 -> medianBlur 5 -> depth = fx*B/(d+1e-6), clip, validity mask.
@@ -462,6 +557,7 @@ def disparity_to_depth(disp16, fx=700.0, baseline=0.08, min_disp=0.0, min_depth=
 CV_16SC2 = 11
 
 
+@_restores_device
 def initUndistortRectifyMap(cameraMatrix, distCoeffs, R, newCameraMatrix, size, m1type=CV_16SC2, device=None,
                             as_tensor=False):
     """cv2.initUndistortRectifyMap(K, dist, R, P, (W, H), cv2.CV_16SC2) -> (map1 s16 [H,W,2], map2 u16 [H,W])

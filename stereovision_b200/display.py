@@ -15,7 +15,7 @@ import ctypes
 import numpy as np
 
 from . import _lib
-from .cv_api import _ensure_device, _ret, _stream_ptr, _to_dev, _torch
+from .cv_api import _ensure_device, _restores_device, _ret, _stream_ptr, _to_dev, _torch
 from .fusion import _scratch
 
 COLORMAP_JET, COLORMAP_TURBO = 2, 20
@@ -27,6 +27,7 @@ def _is_f64_scalar(x):
     return isinstance(x, np.floating) and not isinstance(x, (np.float32, np.float16))
 
 
+@_restores_device
 def _run(src, kind, colormap, params=None, want_index=False, batched=None):
     torch = _torch()
     s, was = _to_dev(src)
@@ -81,6 +82,7 @@ def disparity_colormap(disparity, colormap=COLORMAP_JET, alpha=0, beta=255, retu
     return _run(disparity, _MINMAX_F32, colormap, (0, 0, 0, alpha, beta), return_index)
 
 
+@_restores_device
 def legend_range(fused_u8):
     """(min, max) over the non-zero pixels of a u8 map, (0, 0) if there are none -- int32 [2] or [B,2]."""
     torch = _torch()

@@ -13,7 +13,7 @@ import ctypes
 import numpy as np
 
 from . import _lib
-from .cv_api import _ensure_device, _is_tensor, _ret, _stream_ptr, _to_dev, _torch, cvtColor
+from .cv_api import _ensure_device, _restores_device, _is_tensor, _ret, _stream_ptr, _to_dev, _torch, cvtColor
 
 # fused_depth_map.py:80-116
 FUSION_WEIGHTS = {"stereo_base": 0.8, "midas_max_fill": 0.9, "flow_max_fill": 0.5}
@@ -60,6 +60,7 @@ def _scratch(nbytes, device):
     return _torch().empty(int(nbytes), dtype=_torch().uint8, device=device)
 
 
+@_restores_device
 def normalize_disparity(disparity, min_disp, num_disp):
     """(disparity_normalized f32 in 0..254, confidence f32 0/1) -- fused_depth_map.py:1010-1029."""
     torch = _torch()
@@ -71,6 +72,7 @@ def normalize_disparity(disparity, min_disp, num_disp):
     return _ret(norm, was), _ret(conf, was)
 
 
+@_restores_device
 def calibrate_midas_to_stereo(midas_depth, stereo_disparity, stereo_confidence):
     """fused_depth_map.py:1169-1257.  Maps must already share a shape (the reference's cv2.resize
     branch belongs to its MiDaS wrapper, out of scope)."""
@@ -88,6 +90,7 @@ def calibrate_midas_to_stereo(midas_depth, stereo_disparity, stereo_confidence):
     return _ret(out, was)
 
 
+@_restores_device
 def normalize_to_stereo_range(depth_map, stereo_disparity):
     """fused_depth_map.py:1503-1554."""
     if depth_map is None or stereo_disparity is None:
@@ -104,6 +107,7 @@ def normalize_to_stereo_range(depth_map, stereo_disparity):
     return _ret(out, was)
 
 
+@_restores_device
 def percentiles(values, mask=None, mask_thr=0.0, mask_mode=0):
     """np.percentile(values[mask], 5 / 95) per image (mask_mode as in include/svb.h).
     Returns (float64 [B,2], counts uint32 [B])."""
@@ -120,6 +124,7 @@ def percentiles(values, mask=None, mask_thr=0.0, mask_mode=0):
     return _ret(out, was), _ret(cnt, was)
 
 
+@_restores_device
 def fuse_depth_maps(stereo_depth, stereo_conf, midas_depth_calibrated, midas_conf, flow_depth_normalized,
                     camera_moving, use_stereo=True, use_midas=True, use_flow=True, fusion_params=None,
                     return_float=False):
@@ -162,6 +167,7 @@ def fuse_depth_maps(stereo_depth, stereo_conf, midas_depth_calibrated, midas_con
     return _ret(out8, was)
 
 
+@_restores_device
 def occlusion_stats(gray, block_size=48):
     """Per image: (mean block std, low-variance block ratio, global std, entropy, mean) --
     fused_depth_map.py:170-240.  gray: u8 [H,W] or [B,H,W]; returns float64 [5] or [B,5]."""

@@ -13,10 +13,11 @@ import ctypes
 import numpy as np
 
 from . import _lib
-from .cv_api import _ensure_device, _is_tensor, _ret, _stream_ptr, _to_dev, _torch, cvtColor
+from .cv_api import _ensure_device, _restores_device, _is_tensor, _ret, _stream_ptr, _to_dev, _torch, cvtColor
 from .fusion import _f32_maps, _scratch
 
 
+@_restores_device
 def bilateralFilter(src, d, sigmaColor, sigmaSpace):
     """cv2.bilateralFilter(src, d, sigmaColor, sigmaSpace) for float32 [H,W] / [B,H,W]; d odd, <= 15
     (the reference only uses 9, 75, 75)."""
@@ -35,6 +36,7 @@ def bilateralFilter(src, d, sigmaColor, sigmaSpace):
     return _ret(out, was)
 
 
+@_restores_device
 def upsample_normalize(prediction, size):
     """F.interpolate(prediction[:, None], size=size, mode="bicubic", align_corners=False) followed by the
     per-image 0..255 min-max normalisation of fused_depth_map.py:1134-1145.  -> float32 [B,]H,W."""
@@ -53,6 +55,7 @@ def upsample_normalize(prediction, size):
     return _ret(out, was)
 
 
+@_restores_device
 def contrast_confidence(frame):
     """cv2.normalize(cv2.absdiff(gray, cv2.GaussianBlur(gray, (5, 5), 0)), None, 0, 1, cv2.NORM_MINMAX)
     (fused_depth_map.py:1150-1156).  frame: u8 gray [H,W] / [B,H,W] or BGR [H,W,3] / [B,H,W,3]; -> u8."""
@@ -86,6 +89,7 @@ def midas_postprocess(prediction, frame):
     return _ret(depth, was), _ret(conf, _is_tensor(frame))
 
 
+@_restores_device
 def flow_residual_depth(flow, homography, stable_depth=None, camera_moving=True):
     """OpticalFlowDepthEstimator.estimate_depth after calcOpticalFlowFarneback / findHomography
     (fused_depth_map.py:1386-1403): residual of the dense flow against the ego-motion homography ->

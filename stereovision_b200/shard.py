@@ -58,4 +58,9 @@ def compute_sharded(matcher, left, right, gather=True):
         out = torch.zeros((0,) + tuple(left.shape[1:]), dtype=torch.int16, device=ref.device)
     elif not hasattr(out, "new_zeros"):
         out = torch.from_numpy(out)
+    if gather:
+        import torch.distributed as dist
+        # NCCL moves device memory only: a NumPy-path result goes to this rank's GPU for the collective
+        if dist.is_available() and dist.is_initialized() and dist.get_backend() == "nccl" and not out.is_cuda:
+            out = out.cuda()
     return gather_outputs(out, B) if gather else out

@@ -27,6 +27,11 @@ SGBM_CASES = [
     dict(H=64, W=141, seed=21, prm=_p(0, 64, 5, MODE_HH4)),
     dict(H=70, W=120, seed=22, prm=_p(-8, 32, 9, MODE_HH4, uniq=5, d12=2, cap=31, spw=0)),
     dict(H=33, W=230, seed=23, prm=_p(4, 144, 3, MODE_HH4, uniq=15)),
+    # 3WAY without a uniqueness test: cv2's 8-lane argmin breaks cost ties its own way (later d within a lane, then
+    # the lowest lane result); both pairs contain such ties (d = 28 / 60 and d = 5 / 21).  Also minDisparity > 0.
+    dict(H=43, W=151, seed=519, prm=_p(7, 64, 7, MODE_3WAY, uniq=0, spw=0)),
+    dict(H=41, W=159, seed=520, prm=_p(16, 48, 5, MODE_3WAY, uniq=0, spw=0)),
+    dict(H=67, W=140, seed=91, prm=_p(4, 32, 5, MODE_3WAY)),
 ]
 
 # 3-channel input (cv2 sums the BT cost over the colour channels); P1/P2 as the reference's
@@ -70,6 +75,14 @@ BM_CASES = [
          set={"PreFilterType": 0, "PreFilterSize": 5, "PreFilterCap": 63, "MinDisparity": -4}),
     dict(H=66, W=120, seed=41, numDisparities=16, blockSize=7, noise=20,
          set={"PreFilterType": 0, "PreFilterSize": 31, "PreFilterCap": 10, "Disp12MaxDiff": 1}),
+    # minDisparity > 0: cv2 evaluates minDisparity positions past the row end; the spill of the last ROI row lands
+    # in the first columns of row H - blockSize/2 and survives (oracle/bm_oracle.c)
+    dict(H=75, W=149, seed=42, numDisparities=16, blockSize=5,
+         set={"MinDisparity": 14, "UniquenessRatio": 0, "TextureThreshold": 0}),
+    dict(H=60, W=196, seed=43, numDisparities=48, blockSize=9, noise=12,
+         set={"MinDisparity": 11, "UniquenessRatio": 0, "SpeckleWindowSize": 6, "SpeckleRange": 8}),
+    dict(H=64, W=150, seed=44, numDisparities=32, blockSize=7, noise=20,
+         set={"MinDisparity": 5, "Disp12MaxDiff": 1, "SpeckleWindowSize": 20, "SpeckleRange": 2}),
 ]
 
 

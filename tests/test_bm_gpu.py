@@ -30,10 +30,10 @@ def test_bm_matches_golden(golden, i):
 
 def test_bm_random_params_vs_oracle():
     rng = np.random.default_rng(77)
-    for it in range(32):
+    for it in range(48):
         D = int(rng.choice([16, 32, 64, 96, 128]))
         bs = int(rng.choice([5, 7, 9, 15, 21]))
-        minD = int(rng.choice([0, 0, -4, -20]))
+        minD = int(rng.choice([0, 0, -4, -20, 1, 5, 13]))     # > 0: cv2's row-end spill (oracle/bm_oracle.c)
         H = int(rng.integers(bs + 6, 80))
         W = int(rng.integers(D + abs(minD) + bs + 8, D + abs(minD) + 140))
         kw = dict(numDisparities=D, blockSize=bs, minDisparity=minD, preFilterCap=int(rng.choice([5, 31, 63])),

@@ -77,11 +77,11 @@ def test_sgbm_stages_match_oracle(mode):
 def test_sgbm_random_params_vs_oracle():
     _torch()
     rng = np.random.default_rng(123)
-    for it in range(32):
+    for it in range(48):
         D = int(rng.choice([16, 32, 48, 64, 96, 128, 192]))
         bs = int(rng.choice([1, 3, 5, 7, 9, 11]))
         mode = int(rng.choice([0, 1, 2, 3]))
-        minD = 0 if mode == 2 else int(rng.choice([0, 0, -8, 4, 16]))
+        minD = int(rng.choice([0, 0, -8, 4, 16]))
         if mode == 2 and bs == 1:
             bs = 3
         H = int(rng.integers(20, 70))
@@ -229,6 +229,29 @@ def test_sgbm_color_random_params_vs_oracle():
         l = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
         r = np.roll(l, -int(rng.integers(1, 9)), axis=1)
         r = np.clip(r.astype(np.int16) + rng.integers(-10, 11, r.shape), 0, 255).astype(np.uint8)
+        got = svb.StereoSGBM_create(**prm).compute(l, r)
+        ref = oracle.sgbm_compute(l, r, **prm)
+        assert np.array_equal(got, ref), (H, W, prm, int((got != ref).sum()))
+
+
+def test_sgbm_3way_ties_and_min_disparity_vs_oracle():
+    """SGBM_3WAY where cv2 has its own rules (pinned in the oracle by live cv2, 270/270 random cases): cost ties
+    without a uniqueness test (8-lane argmin), minDisparity on both sides of zero.  Coarse grey levels make ties
+    frequent."""
+    _torch()
+    rng = np.random.default_rng(2024)
+    for it in range(40):
+        D = int(rng.choice([16, 32, 48, 64, 96, 160]))
+        bs = int(rng.choice([3, 5, 7]))
+        minD = int(rng.integers(-16, 17))
+        H = int(rng.integers(30, 80))
+        W = int(rng.integers(D + abs(minD) + bs + 8, D + abs(minD) + 100))
+        prm = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=8 * bs * bs, P2=32 * bs * bs, disp12MaxDiff=1,
+                   preFilterCap=63, uniquenessRatio=int(rng.choice([0, 0, 10])), speckleWindowSize=int(rng.choice([0, 30])),
+                   speckleRange=2, mode=2)
+        l, r, _ = make_pair(H, W, max(D, 16), seed=3000 + it, noise=int(rng.choice([0, 6])))
+        if rng.random() < 0.5:
+            l, r = (l // 32 * 32).astype(np.uint8), (r // 32 * 32).astype(np.uint8)
         got = svb.StereoSGBM_create(**prm).compute(l, r)
         ref = oracle.sgbm_compute(l, r, **prm)
         assert np.array_equal(got, ref), (H, W, prm, int((got != ref).sum()))

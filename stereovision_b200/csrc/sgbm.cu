@@ -58,6 +58,9 @@ __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 2 ? 24 : (NP ==
 #ifndef SW_FMA_ADDS
 #define SW_FMA_ADDS 1          // P1 and sum additions of the recurrence as IMADs (FMA pipe) instead of ALU-pipe adds
 #endif
+#ifndef SW_SEAM_FMA
+#define SW_SEAM_FMA 0          // 1: seam fix-ups of the disparity neighbours as IMAD / IMAD.HI instead of PRMTs (measured: 14.1 -> 15.8 ms, the multiply sits on the recurrence's critical path)
+#endif
 #ifndef SW_SLEEP_NS
 #define SW_SLEEP_NS 40         // back-off while a row waits for its neighbour's progress counter
 #endif
@@ -498,8 +501,18 @@ __device__ __forceinline__ uint32_t sgm_step(uint32_t (&Lq)[NP], const uint32_t 
     // two seams: word 0's high half continues word HALF-1's low half, and the ends see the wall
     uint32_t prev = __shfl_sync(FULLMASK, Lq[NP - 1], (lane + 31) & 31);
     uint32_t next = __shfl_sync(FULLMASK, Lq[0], (lane + 1) & 31);
+#if SW_SEAM_FMA
+    // the two seam fix-ups as integer multiply-adds (FMA pipe; the ALU pipe is the busy one and PRMT is half rate
+    // there): x * 2^16 + wall = (lo = wall, hi = x.lo);  hi32(x * 2^16) + (wall << 16) = (lo = x.hi, hi = wall)
+    {
+        const uint32_t sh = one << 16;                       // 65536, opaque: the compiler would turn it back into a shift
+        if (lane == 0) asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(prev) : "r"(prev), "r"(sh), "r"(WALL));
+        if (lane == 31) asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(next) : "r"(next), "r"(sh), "r"(WALL << 16));
+    }
+#else
     if (lane == 0) prev = __byte_perm(prev, WALL2, 0x1054);     // (lo = wall, hi = lane31.lo)
     if (lane == 31) next = __byte_perm(next, WALL2, 0x5432);    // (lo = lane0.hi, hi = wall)
+#endif
     const uint32_t mqP2 = mq2 + P2P2;                        // halves < 65536: no carry
     uint32_t up = prev;
     uint32_t mloc = 0xffffffffu;
@@ -566,18 +579,70 @@ __device__ __forceinline__ void cp_async_vec_s(uint32_t sdst, const uint32_t* gs
     }
 }
 
+// Shared-memory vector accesses by 32-bit shared-space address (no generic-address arithmetic in the rows' loop).
+// volatile: kept in order with the progress-flag accesses (also volatile asm); the immediate offset is folded.
+template <int NP, int OFS, int I = 0>
+__device__ __forceinline__ void lds_vec(uint32_t sa, uint32_t (&v)[NP])
+{
+    if constexpr (NP % 4 == 0) {
+        if constexpr (I < NP / 4) {
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4 + %5];"
+                         : "=r"(v[4 * I]), "=r"(v[4 * I + 1]), "=r"(v[4 * I + 2]), "=r"(v[4 * I + 3]) : "r"(sa), "n"(OFS + 16 * I));
+            lds_vec<NP, OFS, I + 1>(sa, v);
+        }
+    } else if constexpr (NP % 2 == 0) {
+        if constexpr (I < NP / 2) {
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2 + %3];" : "=r"(v[2 * I]), "=r"(v[2 * I + 1]) : "r"(sa), "n"(OFS + 8 * I));
+            lds_vec<NP, OFS, I + 1>(sa, v);
+        }
+    } else if constexpr (I < NP) {
+        asm volatile("ld.shared.u32 %0, [%1 + %2];" : "=r"(v[I]) : "r"(sa), "n"(OFS + 4 * I));
+        lds_vec<NP, OFS, I + 1>(sa, v);
+    }
+}
+template <int NP, int OFS, int I = 0>
+__device__ __forceinline__ void sts_vec(uint32_t sa, const uint32_t (&v)[NP])
+{
+    if constexpr (NP % 4 == 0) {
+        if constexpr (I < NP / 4) {
+            asm volatile("st.shared.v4.u32 [%0 + %1], {%2, %3, %4, %5};" ::"r"(sa), "n"(OFS + 16 * I), "r"(v[4 * I]),
+                         "r"(v[4 * I + 1]), "r"(v[4 * I + 2]), "r"(v[4 * I + 3]));
+            sts_vec<NP, OFS, I + 1>(sa, v);
+        }
+    } else if constexpr (NP % 2 == 0) {
+        if constexpr (I < NP / 2) {
+            asm volatile("st.shared.v2.u32 [%0 + %1], {%2, %3};" ::"r"(sa), "n"(OFS + 8 * I), "r"(v[2 * I]), "r"(v[2 * I + 1]));
+            sts_vec<NP, OFS, I + 1>(sa, v);
+        }
+    } else if constexpr (I < NP) {
+        asm volatile("st.shared.u32 [%0 + %1], %2;" ::"r"(sa), "n"(OFS + 4 * I), "r"(v[I]));
+        sts_vec<NP, OFS, I + 1>(sa, v);
+    }
+}
+template <int OFS>
+__device__ __forceinline__ uint32_t lds_u32(uint32_t sa)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1 + %2];" : "=r"(v) : "r"(sa), "n"(OFS));
+    return v;
+}
+template <int OFS>
+__device__ __forceinline__ void sts_u32(uint32_t sa, uint32_t v)
+{
+    asm volatile("st.shared.u32 [%0 + %1], %2;" ::"r"(sa), "n"(OFS), "r"(v));
+}
+
 // Uniqueness threshold of A.4: a disparity d counts against the winner iff S[d] < th.
+template <bool MAY3WAY>
 __device__ __forceinline__ int wta_threshold(const SgbmGeo& g, int minS)
 {
-    const int f = 100 - g.uniq;
+    const int f = 100 - g.uniq;                              // >= 1 (make_geo rejects uniquenessRatio >= 100)
     int th;
-    if (g.mode == SVB_MODE_SGBM_3WAY) {
+    if (MAY3WAY && g.mode == SVB_MODE_SGBM_3WAY) {
         // cv2's 3WAY vector loop: Sp[d] < (short)(100*minS/(100-u) + 1) (oracle/sgbm_oracle.c)
         const unsigned x = 100u * (unsigned)minS;
         th = g.uniq > 0 ? (int)(int16_t)((g.thMul ? __umulhi(x, g.thMul) : x) + 1u) : 0;
         th = max(th, 0);
-    } else if (f <= 0) {
-        th = minS > 0 ? 0x8000 : 0;                          // S*0 < minS*100
     } else {
         const unsigned x = (unsigned)minS * 100u + (unsigned)f - 1u;   // S*f < minS*100  <=>  S < ceil(minS*100/f)
         th = (int)(g.thMul ? __umulhi(x, g.thMul) : x);
@@ -625,7 +690,7 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
     constexpr int VW = NP * 32, ROWW = sw_roww(NP);
     constexpr int SW_R = sw_rows(NP), RING = sw_ring(NP, LAST), NS = sw_stage(NP, LAST), PFD = NS - 1;
     constexpr int PATHW = RING * ROWW, RINGW = 3 * PATHW;
-    extern __shared__ __align__(16) uint32_t smem[];
+    extern __shared__ __align__(128) uint32_t smem[];
     uint32_t* ring = smem;                                   // [SW_R + 1][3][RING][ROWW] (+1: what the last row writes)
     uint32_t* cstage = ring + (SW_R + 1) * RINGW;            // [SW_R][NS][VW] cp.async ring of C columns
     uint32_t* sstage = cstage + SW_R * NS * VW;              // [SW_R][NS][VW] (last sweep) ... and of S1 columns
@@ -653,8 +718,6 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
     uint32_t* mysc = wsc + rw * VW;
     const uint32_t cst_s = smem_u32(cstage + (size_t)rw * NS * VW + NP * lane);   // this lane's slice, slot 0
     const uint32_t sst_s = smem_u32(sstage + (size_t)rw * NS * VW + NP * lane);
-    const uint32_t* cst = cstage + (size_t)rw * NS * VW;
-    const uint32_t* sst = sstage + (size_t)rw * NS * VW;
 
     auto zero_col = [&](uint32_t* rbase, int p, uint32_t slotoff) {   // one column of one path: vector + its minimum
         const uint32_t z[NP] = {};
@@ -821,8 +884,14 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
             }
         }
         int seenP = 0, seenS = 0;
-        uint32_t o_m1 = (RING - 1) * ROWW, o_0 = 0, o_p1 = ROWW;   // ring offsets (words) of columns i-1, i, i+1
-        uint32_t cs_cur = 0, cs_prev = (NS - 1) * VW;              // stage offsets (words) of columns i, i-1
+        // Shared-space byte addresses of this lane's slice in the input ring slots of columns i-1, i, i+1 (path 0;
+        // path p is PATHW words further, the output ring RINGW words further) -- rotated, never recomputed
+        const uint32_t rin_s = smem_u32(ring_in + NP * lane), rin_end = rin_s + PATHW * 4;
+        uint32_t a_m1 = rin_s + (RING - 1) * ROWW * 4, a_0 = rin_s, a_p1 = rin_s + ROWW * 4;
+        const uint32_t tail = (uint32_t)(VW - NP * lane) * 4;      // from a lane's slice to the slot's minima
+        uint32_t cs_cur = 0, cs_prev = (NS - 1) * VW * 4;          // stage offsets (bytes) of columns i, i-1
+        // columns <= lim may run without looking at the neighbours' counters again
+        int lim = VERT && SW_EXPERIMENT != 6 ? -1 : 0x7fffffff;
         const uint32_t* gC = pC0 + (ptrdiff_t)PFD * cstep;         // this lane's slice of column i + PFD
         const uint32_t* gS = pS0 + (ptrdiff_t)PFD * cstep;
         uint32_t* pS = a.S + rowbase + (size_t)x0 * VW + NP * lane;
@@ -834,22 +903,21 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
             // column i + 1 of the row above is only needed by the diagonal-from-ahead path: without it (3WAY, HH4) a row
             // follows the row above one column behind instead of two (a single frame's dependent chain gets shorter)
             constexpr int NEED = (MASK & 8) ? 2 : 1;
-            if (SW_EXPERIMENT != 6 && VERT && seenP < i + NEED) {
+            if (i > lim) {                                   // one compare on the common path
                 while ((seenP = lds_acquire_cta(done_pred)) < i + NEED) __nanosleep(SW_SLEEP_NS);
-            }
-            if (SW_EXPERIMENT != 6 && VERT && seenS < i - RING + 2) {
                 while ((seenS = lds_acquire_cta(done_succ)) < i - RING + 2) __nanosleep(SW_SLEEP_NS);
+                lim = min(seenP - NEED, seenS + RING - 2);
             }
             // column i + PFD -> the stage slot column i - 1 has just left
             if (SW_EXPERIMENT != 3 && SW_EXPERIMENT != 5) {
-                cp_async_vec_s<NP>(cst_s + cs_prev * 4, gC);
-                if (LAST) cp_async_vec_s<NP>(sst_s + cs_prev * 4, gS);
+                cp_async_vec_s<NP>(cst_s + cs_prev, gC);
+                if (LAST) cp_async_vec_s<NP>(sst_s + cs_prev, gS);
             }
             asm volatile("cp.async.commit_group;");
             asm volatile("cp.async.wait_group %0;" ::"n"(PFD) : "memory");
             uint32_t C[NP], S[NP];
-            vec_ld<NP>(cst + cs_cur, lane, C, LdPlain());
-            if (LAST) vec_ld<NP>(sst + cs_cur, lane, S, LdPlain());
+            lds_vec<NP, 0>(cst_s + cs_cur, C);
+            if (LAST) lds_vec<NP, 0>(sst_s + cs_cur, S);
             else {
 #pragma unroll
                 for (int k = 0; k < NP; ++k) S[k] = 0u;
@@ -858,12 +926,9 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
             uint32_t Lt[3][NP], mq2[3];
             if (VERT) {
 #pragma unroll
-                for (int p = 0; p < 3; ++p) {
-                    if (!(MASK & (2 << p))) continue;
-                    const uint32_t so = p == 0 ? o_m1 : (p == 1 ? o_0 : o_p1);
-                    vec_ld<NP>(ring_in + p * PATHW + so, lane, Lt[p], LdPlain());
-                    mq2[p] = ring_in[so + VW + p];
-                }
+                if (MASK & 2) { lds_vec<NP, 0>(a_m1, Lt[0]); mq2[0] = lds_u32<0>(a_m1 + tail); }
+                if (MASK & 4) { lds_vec<NP, PATHW * 4>(a_0, Lt[1]); mq2[1] = lds_u32<4>(a_0 + tail); }
+                if (MASK & 8) { lds_vec<NP, 2 * PATHW * 4>(a_p1, Lt[2]); mq2[2] = lds_u32<8>(a_p1 + tail); }
             }
             uint32_t sum[NP];                                // FAST: plain sum of this sweep's L_r
 #pragma unroll
@@ -886,8 +951,10 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                         if (FAST) sum[k] = SW_FMA_ADDS ? add_fma(Lt[p][k], one, sum[k]) : sum[k] + Lt[p][k];
                         else S[k] = pk_addmin(S[k], Lt[p][k], WALL2);
                     }
-                    vec_st<NP>(ring_out + p * PATHW + o_0, lane, Lt[p]);
-                    if (lane == 0) ring_out[o_0 + VW + p] = m2;
+                    // the output ring is the next row's input ring: RINGW words further; lane 0's slice starts the slot
+                    if (p == 0) { sts_vec<NP, RINGW * 4>(a_0, Lt[0]); if (lane == 0) sts_u32<(RINGW + VW) * 4>(a_0, m2); }
+                    if (p == 1) { sts_vec<NP, (RINGW + PATHW) * 4>(a_0, Lt[1]); if (lane == 0) sts_u32<(RINGW + VW + 1) * 4>(a_0, m2); }
+                    if (p == 2) { sts_vec<NP, (RINGW + 2 * PATHW) * 4>(a_0, Lt[2]); if (lane == 0) sts_u32<(RINGW + VW + 2) * 4>(a_0, m2); }
                 }
             }
             if (FAST) {
@@ -938,7 +1005,7 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                             }
                         }
                     }
-                    const int th = wta_threshold(g, (int)(kmin >> 16));
+                    const int th = wta_threshold<MASK == 1>(g, (int)(kmin >> 16));
                     // uniqueness: count disparities with S < th; the ones at best-1..best+1 are taken out later
                     const uint32_t th2 = pk_dup((uint32_t)th);
                     uint32_t bits = 0;
@@ -965,7 +1032,7 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                             const int x = xc + g.minX1;
                             const size_t rowpix = ((size_t)b * g.H + y) * g.W;
                             const int minS = (int)(rkey >> 16), bst = (int)(rkey & 0xffffu);
-                            const int thr = wta_threshold(g, minS);
+                            const int thr = wta_threshold<MASK == 1>(g, minS);
                             const int s1 = (int)(rtap & 0xffffu), s2 = (int)(rtap >> 16);
                             int out = g.INV;
                             if (minS < (int)WALL) {
@@ -996,8 +1063,8 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
             // (after the publication: its fence then has no global store of this column to wait for)
             if (!LAST && SW_EXPERIMENT != 4 && SW_EXPERIMENT != 5) vec_st<NP>(pS - NP * lane, lane, S);
             gC += cstep; gS += cstep; pS += cstep;
-            o_m1 = o_0; o_0 = o_p1; o_p1 = o_p1 + ROWW == PATHW ? 0u : o_p1 + ROWW;
-            cs_prev = cs_cur; cs_cur = cs_cur + VW == NS * VW ? 0u : cs_cur + VW;
+            a_m1 = a_0; a_0 = a_p1; a_p1 = a_p1 + ROWW * 4 == rin_end ? rin_s : a_p1 + ROWW * 4;
+            cs_prev = cs_cur; cs_cur = cs_cur + VW * 4 == NS * VW * 4 ? 0u : cs_cur + VW * 4;
         }
         if (VERT && nloop) {
             // virtual column w1 for the row below (its diagonal-from-ahead predecessor at the last column),
@@ -1006,7 +1073,7 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                 seenS = lds_acquire_cta(done_succ);
                 if (seenS < w1 - RING + 2) __nanosleep(SW_SLEEP_NS);
             }
-            zero_col(ring_out, 2, o_0);
+            zero_col(ring_out, 2, (uint32_t)(w1 % RING) * ROWW);
             __syncwarp();
             if (lane == 0) sts_release_cta(&s_done[warp], w1 + 8);
         }

@@ -137,6 +137,17 @@ int svb_median5_f32_dev(const float* src_dev, int B, int H, int W, float* dst_de
  *      labels_dev: caller scratch of B*H*W int32 (2 arrays: 2*B*H*W*4 bytes). */
 int svb_filter_speckles_s16_dev(int16_t* img_dev, int B, int H, int W, int newVal,
                                 int maxSpeckleSize, int maxDiff, int32_t* scratch_dev, void* stream);
+/* The same filter for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments minus the scratch: labels and counts live in a static device array inside libsvb.so
+ * sized for B*H*W <= SVB_SPECKLE_STATIC_MAX_PIXELS (16 MiB, held by every GPU that loads the library until the
+ * process exits); larger inputs are rejected with SVB_ERR_UNSUPPORTED.  The call performs no cudaMalloc / cudaFree
+ * and calls no allocating routine; the first call on each device looks the array's device address up once
+ * (cudaGetSymbolAddress; make that first call outside a graph capture).  Every call shares the one array:
+ * calls that overlap on the GPU (different streams or threads) race -- serialise them. */
+#define SVB_SPECKLE_STATIC_MAX_PIXELS 2097152   /* 2 Mi pixels: one 1920x1080 frame, or e.g. six 640x480 frames */
+int svb_filter_speckles_s16_static(int16_t* img_dev, int B, int H, int W, int newVal,
+                                   int maxSpeckleSize, int maxDiff, void* stream);
 
 /* ---- depth_map.py:909-933 fused: disparity = s16/16 -> medianBlur 5 -> depth = fx*B/(d+1e-6),
  *      clip [min_depth,max_depth], zero where invalid.  disp16 s16 [B,H,W] -> disparity f32, depth f32. */

@@ -68,6 +68,7 @@ SIGNATURES = {
     "svb_median3_s16_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "svb_median5_f32_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "svb_filter_speckles_s16_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "svb_filter_speckles_s16_static": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "svb_disp_to_depth_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_double, c_double, c_double, c_double,
                                       c_double, c_void_p, c_void_p, c_void_p]),
     "svb_reproject3d_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, ctypes.POINTER(c_double), c_int,

@@ -6,6 +6,7 @@
 //   disparity -> depth                      depth_map.py:909-933
 //   reprojectImageTo3D                      BASELINE.json (Q from depth_map.py:625)
 #include "svb_common.cuh"
+#include <mutex>
 #include <float.h>
 #include <algorithm>
 
@@ -283,6 +284,50 @@ extern "C" int svb_filter_speckles_s16_dev(int16_t* img, int B, int H, int W, in
     k_ccl_apply<<<svb_ceil_div(n, 256), 256, 0, st>>>(img, n, newVal, maxSpeckleSize, label, count);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// svb_filter_speckles_s16_static: the same filter for callers that cannot allocate (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The labels + counts live in a file-scope device array of SVB_SPECKLE_STATIC_MAX_PIXELS pixels
+// (2 x int32 each = 16 MiB, held by every GPU that loads the library until the process exits).  In host code the
+// array's NAME is only a host-side stand-in: its device address is fetched once per device, with that device
+// current, through cudaGetSymbolAddress and handed to the kernels.  Nothing here calls cudaMalloc / cudaFree or
+// an allocating library routine.  The array keeps the previous call's contents; nothing has to be cleared by
+// the host because k_ccl_runs writes every label and zeroes every count of the n pixels before they are read.
+// Every call (any stream, any thread) shares the array: calls that overlap on the GPU race.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) int32_t g_speckle_scratch[2 * (size_t)SVB_SPECKLE_STATIC_MAX_PIXELS];
+#define SVB_STATIC_MAX_DEVICES 64
+static int32_t* g_speckle_scratch_dev[SVB_STATIC_MAX_DEVICES] = {};    // device address per device ordinal
+static std::mutex g_speckle_scratch_mu;
+
+extern "C" int svb_filter_speckles_s16_static(int16_t* img, int B, int H, int W, int newVal, int maxSpeckleSize,
+                                              int maxDiff, void* stream)
+{
+    if (!img || B <= 0 || H <= 0 || W <= 0) { svb_set_error("filterSpeckles (static): bad argument"); return SVB_ERR_PARAM; }
+    const size_t n = (size_t)B * H * W;
+    if (n > (size_t)SVB_SPECKLE_STATIC_MAX_PIXELS) {
+        svb_set_error("filterSpeckles (static): B*H*W = %zu pixels exceeds the built-in scratch of %d pixels "
+                      "(SVB_SPECKLE_STATIC_MAX_PIXELS); use svb_filter_speckles_s16_dev with caller scratch",
+                      n, SVB_SPECKLE_STATIC_MAX_PIXELS);
+        return SVB_ERR_UNSUPPORTED;
+    }
+    int dev = -1;
+    SVB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= SVB_STATIC_MAX_DEVICES) { svb_set_error("filterSpeckles (static): device ordinal %d unsupported", dev); return SVB_ERR_UNSUPPORTED; }
+    int32_t* scratch;
+    {
+        std::lock_guard<std::mutex> lk(g_speckle_scratch_mu);
+        if (!g_speckle_scratch_dev[dev]) {                   // set-up, once per device, this device current
+            void* ptr = nullptr;
+            SVB_CUDA(cudaGetSymbolAddress(&ptr, g_speckle_scratch));
+            if (!ptr) { svb_set_error("filterSpeckles (static): cudaGetSymbolAddress returned a null address"); return SVB_ERR_CUDA; }
+            g_speckle_scratch_dev[dev] = (int32_t*)ptr;
+        }
+        scratch = g_speckle_scratch_dev[dev];
+    }
+    return svb_filter_speckles_s16_dev(img, B, H, W, newVal, maxSpeckleSize, maxDiff, scratch, stream);
 }
 
 // ---------------------------------------------------------------------------------------

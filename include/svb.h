@@ -126,6 +126,13 @@ int svb_validate_disparity_dev(int16_t* disp_dev, const void* cost_dev, int cost
 int svb_remap_u8_dev(const uint8_t* src_dev, int B, int Hs, int Ws, int C,
                      const int16_t* map1_dev, const uint16_t* map2_dev, int Ho, int Wo,
                      uint8_t* dst_dev, int to_gray, void* stream);
+/* ---- cv2.resize(src, (Wd, Hd), interpolation=cv2.INTER_LINEAR) (fused_depth_map.py:473-476: both camera frames on
+ *      every processed frame, PROCESSING_SCALE 0.33; depth_map.py:776, 809-811; fused_depth_map.py:1214-1217: a
+ *      float32 mono map to the stereo shape).  u8: C = 1 or 3 interleaved channels, src [B,Hs,Ws,C] -> dst
+ *      [B,Hd,Wd,C], bit-exact with cv2 4.13 (11-bit fixed-point weights).  f32: one channel, 1e-6 relative. */
+int svb_resize_u8_dev(const uint8_t* src_dev, int B, int Hs, int Ws, int C, uint8_t* dst_dev, int Hd, int Wd,
+                      void* stream);
+int svb_resize_f32_dev(const float* src_dev, int B, int Hs, int Ws, float* dst_dev, int Hd, int Wd, void* stream);
 /* cv2.cvtColor(img, COLOR_BGR2GRAY): u8 [n,3] -> u8 [n] */
 int svb_bgr2gray_dev(const uint8_t* bgr_dev, size_t npix, uint8_t* gray_dev, void* stream);
 

@@ -100,6 +100,23 @@ def remap(src, map1, map2):
     return dst
 
 
+def resize(src, dsize):
+    """cv2.resize(src, dsize=(W, H), interpolation=cv2.INTER_LINEAR): u8 with 1 or 3 channels (bit-exact,
+    fused_depth_map.py:473-476, depth_map.py:809-811) or float32 single channel (fused_depth_map.py:1214-1217)."""
+    Wd, Hd = int(dsize[0]), int(dsize[1])
+    if src.dtype == np.float32:
+        src = np.ascontiguousarray(src)
+        assert src.ndim == 2
+        dst = np.empty((Hd, Wd), np.float32)
+        lib().orc_resize_f32(_p(src, ctypes.c_float), src.shape[0], src.shape[1], _p(dst, ctypes.c_float), Hd, Wd)
+        return dst
+    src = np.ascontiguousarray(src, np.uint8)
+    C = 1 if src.ndim == 2 else src.shape[2]
+    dst = np.empty((Hd, Wd) if src.ndim == 2 else (Hd, Wd, C), np.uint8)
+    lib().orc_resize_u8(_p(src, ctypes.c_uint8), src.shape[0], src.shape[1], C, _p(dst, ctypes.c_uint8), Hd, Wd)
+    return dst
+
+
 def bgr2gray(bgr):
     """cv2.cvtColor(img, COLOR_BGR2GRAY) (depth_map.py:871-879)."""
     bgr = np.ascontiguousarray(bgr, np.uint8)

@@ -50,9 +50,13 @@ def percentile(values, q, scalar_q=True):
 
 
 def calibrate_midas_to_stereo(midas, stereo_disparity, stereo_conf):
-    """fused_depth_map.py:1169-1257 (shapes equal: the resize branch is display glue)."""
+    """fused_depth_map.py:1169-1257, including the cv2.resize(INTER_LINEAR) of a mono map of another shape
+    (:1214-1217; oracle.resize restates it)."""
     m = np.asarray(midas, f32)
     s = np.asarray(stereo_disparity, f32)
+    if m.shape != s.shape:
+        from . import resize
+        m = resize(np.ascontiguousarray(m), (s.shape[1], s.shape[0]))
     rel = np.asarray(stereo_conf) > 0.7
     if int(rel.sum()) < 100:
         mmin, mmax = percentile(m, 5), percentile(m, 95)

@@ -141,3 +141,84 @@ void orc_reproject3d(const float* disp, int H, int W, const double* Q /* 4x4 row
             if (handleMissing && d <= minv) o[2] = 10000.f;
         }
 }
+
+/* ---------------------------------------------------------------------------------------
+ * cv2.resize(src, dsize, interpolation=INTER_LINEAR) -- the reference resizes both camera frames on every
+ * processed frame (fused_depth_map.py:473-476, PROCESSING_SCALE = 0.33; depth_map.py:776, 809-811) and a mono
+ * map to the stereo shape (fused_depth_map.py:1214-1217, float32).  OpenCV 4.13 imgproc/src/resize.cpp restated;
+ * pinned against live cv2 (300/300 random u8 cases bit-exact, up- and down-scale, 1 and 3 channels).
+ *
+ * Coordinates: f = (float)((d + 0.5) * scale - 0.5), scale = 1.0 / ((double)dsize / ssize); s = floor(f); f -= s.
+ * Horizontally s is clamped to the image with the fraction reset to 0 (s < 0 -> s = 0, f = 0; s >= ssize-1 ->
+ * s = ssize-1, f = 0).  VERTICALLY the fraction is NOT reset: the two tap rows are clipped into the image and keep
+ * their split weights (that changes the rounding in the first / last output rows when upscaling -- probed).
+ * u8: weights are round-half-even(w * 2048) as int16, the horizontal pass keeps 32-bit sums, the vertical pass is
+ * (((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2.
+ * ------------------------------------------------------------------------------------- */
+#include <math.h>
+static void resize_axis(int ssize, int dsize, int clamp_fraction, int* ofs, float* w /* 2 per entry */)
+{
+    const double scale = 1.0 / ((double)dsize / ssize);
+    for (int d = 0; d < dsize; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)floorf(f);
+        f -= (float)s;
+        if (clamp_fraction) {
+            if (s < 0) { f = 0.f; s = 0; }
+            if (s >= ssize - 1) { f = 0.f; s = ssize - 1; }
+        }
+        ofs[d] = s; w[2 * d] = 1.f - f; w[2 * d + 1] = f;
+    }
+}
+static inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+void orc_resize_u8(const uint8_t* src, int Hs, int Ws, int C, uint8_t* dst, int Hd, int Wd)
+{
+    int* xo = (int*)malloc(sizeof(int) * (size_t)(Wd + Hd));
+    int* yo = xo + Wd;
+    float* xw = (float*)malloc(sizeof(float) * 2 * (size_t)(Wd + Hd));
+    float* yw = xw + 2 * Wd;
+    resize_axis(Ws, Wd, 1, xo, xw);
+    resize_axis(Hs, Hd, 0, yo, yw);
+    for (int y = 0; y < Hd; ++y) {
+        const int y0 = clampi(yo[y], 0, Hs - 1), y1 = clampi(yo[y] + 1, 0, Hs - 1);
+        const int b0 = (int)lrintf(yw[2 * y] * 2048.f), b1 = (int)lrintf(yw[2 * y + 1] * 2048.f);
+        for (int x = 0; x < Wd; ++x) {
+            const int x0 = xo[x], x1 = x0 + 1 < Ws ? x0 + 1 : Ws - 1;
+            const int a0 = (int)lrintf(xw[2 * x] * 2048.f), a1 = (int)lrintf(xw[2 * x + 1] * 2048.f);
+            for (int c = 0; c < C; ++c) {
+                const int S0 = src[((size_t)y0 * Ws + x0) * C + c] * a0 + src[((size_t)y0 * Ws + x1) * C + c] * a1;
+                const int S1 = src[((size_t)y1 * Ws + x0) * C + c] * a0 + src[((size_t)y1 * Ws + x1) * C + c] * a1;
+                dst[((size_t)y * Wd + x) * C + c] =
+                    (uint8_t)((((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2);
+            }
+        }
+    }
+    free(xo); free(xw);
+}
+
+/* float32, one channel (fused_depth_map.py:1214-1217).  This build of cv2 (IPP) computes the source coordinate
+ * and its fraction in double and rounds the weight to float once (probed: 1.2e-7 relative, i.e. summation order,
+ * against 1e-5 for the float coordinates of the u8 path); same border rules.  Tolerance 1e-6 relative. */
+void orc_resize_f32(const float* src, int Hs, int Ws, float* dst, int Hd, int Wd)
+{
+    const double sx = 1.0 / ((double)Wd / Ws), sy = 1.0 / ((double)Hd / Hs);
+    for (int y = 0; y < Hd; ++y) {
+        const double fy = (y + 0.5) * sy - 0.5;
+        const int ys = (int)floor(fy);
+        const float wy1 = (float)(fy - ys), wy0 = 1.f - wy1;
+        const int y0 = clampi(ys, 0, Hs - 1), y1 = clampi(ys + 1, 0, Hs - 1);
+        for (int x = 0; x < Wd; ++x) {
+            double fx = (x + 0.5) * sx - 0.5;
+            int xs = (int)floor(fx);
+            double fr = fx - xs;
+            if (xs < 0) { fr = 0; xs = 0; }
+            if (xs >= Ws - 1) { fr = 0; xs = Ws - 1; }
+            const int x1 = xs + 1 < Ws ? xs + 1 : Ws - 1;
+            const float wx1 = (float)fr, wx0 = 1.f - wx1;
+            const float r0 = src[(size_t)y0 * Ws + xs] * wx0 + src[(size_t)y0 * Ws + x1] * wx1;
+            const float r1 = src[(size_t)y1 * Ws + xs] * wx0 + src[(size_t)y1 * Ws + x1] * wx1;
+            dst[(size_t)y * Wd + x] = r0 * wy0 + r1 * wy1;
+        }
+    }
+}

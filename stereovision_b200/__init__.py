@@ -10,14 +10,14 @@ from .cv_api import (  # noqa: F401
     STEREO_BM_PREFILTER_NORMALIZED_RESPONSE, STEREO_BM_PREFILTER_XSOBEL,
     INTER_LINEAR, COLOR_BGR2GRAY,
     StereoSGBM, StereoBM, StereoSGBM_create, StereoBM_create,
-    remap, cvtColor, medianBlur, filterSpeckles, validateDisparity, reprojectImageTo3D, disparity_to_depth,
+    remap, resize, cvtColor, medianBlur, filterSpeckles, validateDisparity, reprojectImageTo3D, disparity_to_depth,
     initUndistortRectifyMap, CV_16SC2,
     release_workspaces, pool_size, invalidate_map_cache,
 )
 
 from .fusion import (  # noqa: F401
     normalize_disparity, calibrate_midas_to_stereo, normalize_to_stereo_range, fuse_depth_maps,
-    detect_camera_occlusion, occlusion_stats, percentiles,
+    detect_camera_occlusion, occlusion_stats, percentiles, OcclusionMonitor,
 )
 
 from .mono import (  # noqa: F401
@@ -27,6 +27,9 @@ from .mono import (  # noqa: F401
 from .display import (  # noqa: F401
     COLORMAP_JET, COLORMAP_TURBO, applyColorMap, clip_colormap, depth_colormap, depth_display_colormap,
     disparity_colormap, legend_range, legend_depth_range,
+)
+from .calib import (  # noqa: F401
+    stereoRectify, Rodrigues, load_stereo_calibration, load_stereo_calibration_with_scaling, CALIB_ZERO_DISPARITY,
 )
 from ._lib import SvbError  # noqa: F401
 

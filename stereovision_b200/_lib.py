@@ -65,6 +65,8 @@ SIGNATURES = {
     "svb_remap_u8_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
                                  c_void_p, c_int, c_void_p]),
     "svb_bgr2gray_dev": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p]),
+    "svb_resize_u8_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
+    "svb_resize_f32_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
     "svb_median3_s16_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "svb_median5_f32_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "svb_filter_speckles_s16_dev": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),

@@ -623,3 +623,106 @@ extern "C" int svb_init_undistort_rectify_map_dev(const double* K9, const double
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// cv2.resize(src, dsize, interpolation=INTER_LINEAR): u8 (1 or 3 interleaved channels, bit-exact) and f32.
+// Reference call sites: fused_depth_map.py:473-476 (both camera frames, EVERY processed frame, PROCESSING_SCALE
+// 0.33), depth_map.py:776, 809-811 (capture size != calibration size), fused_depth_map.py:1214-1217 (mono map to
+// the stereo shape, float32).  Arithmetic as restated and pinned in oracle/imgproc_oracle.c (orc_resize_*):
+// source coordinate in double without FMA contraction, cast to float, horizontal fraction reset where the tap
+// clamps, vertical taps clipped WITHOUT resetting the fraction, 11-bit weights (round half even), 32-bit
+// horizontal sums, (((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2.
+// One thread per destination pixel; the four source taps of neighbouring threads share sectors (downscaling
+// reads at most scale^2 source bytes per output byte, once: the kernel is a streaming read).
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void resize_coord_u8(int d, double scale, int ssize, bool clamp, int& s, int& w0, int& w1)
+{
+    float f = (float)__dadd_rn(__dmul_rn((double)d + 0.5, scale), -0.5);
+    s = (int)floorf(f);
+    f = __fsub_rn(f, (float)s);
+    if (clamp) {
+        if (s < 0) { f = 0.f; s = 0; }
+        if (s >= ssize - 1) { f = 0.f; s = ssize - 1; }
+    }
+    w0 = __float2int_rn(__fmul_rn(__fsub_rn(1.f, f), 2048.f));
+    w1 = __float2int_rn(__fmul_rn(f, 2048.f));
+}
+
+template <int C>
+__global__ void __launch_bounds__(256) k_resize_u8(const uint8_t* __restrict__ src, int Hs, int Ws,
+                                                   uint8_t* __restrict__ dst, int Hd, int Wd, double sx, double sy)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= Wd) return;
+    int xs, a0, a1, ys, b0, b1;
+    resize_coord_u8(x, sx, Ws, true, xs, a0, a1);
+    resize_coord_u8(y, sy, Hs, false, ys, b0, b1);
+    const int x1 = min(xs + 1, Ws - 1);
+    const int y0 = min(max(ys, 0), Hs - 1), y1 = min(max(ys + 1, 0), Hs - 1);
+    const uint8_t* img = src + (size_t)blockIdx.z * Hs * Ws * C;
+    const uint8_t *r0 = img + (size_t)y0 * Ws * C, *r1 = img + (size_t)y1 * Ws * C;
+    uint8_t* o = dst + (((size_t)blockIdx.z * Hd + y) * Wd + x) * C;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        const int S0 = r0[xs * C + c] * a0 + r0[x1 * C + c] * a1;
+        const int S1 = r1[xs * C + c] * a0 + r1[x1 * C + c] * a1;
+        o[c] = (uint8_t)((((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2);
+    }
+}
+
+// float32, one channel: coordinate and fraction in double, weight rounded to float once (what this cv2 build does,
+// oracle/imgproc_oracle.c); products and sums as separate float operations.
+__global__ void __launch_bounds__(256) k_resize_f32(const float* __restrict__ src, int Hs, int Ws,
+                                                    float* __restrict__ dst, int Hd, int Wd, double sx, double sy)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= Wd) return;
+    const double fy = __dadd_rn(__dmul_rn((double)y + 0.5, sy), -0.5);
+    const int ys = (int)floor(fy);
+    const float wy1 = (float)(fy - (double)ys), wy0 = __fsub_rn(1.f, wy1);
+    const int y0 = min(max(ys, 0), Hs - 1), y1 = min(max(ys + 1, 0), Hs - 1);
+    double fx = __dadd_rn(__dmul_rn((double)x + 0.5, sx), -0.5);
+    int xs = (int)floor(fx);
+    double fr = fx - (double)xs;
+    if (xs < 0) { fr = 0; xs = 0; }
+    if (xs >= Ws - 1) { fr = 0; xs = Ws - 1; }
+    const int x1 = min(xs + 1, Ws - 1);
+    const float wx1 = (float)fr, wx0 = __fsub_rn(1.f, wx1);
+    const float* img = src + (size_t)blockIdx.z * Hs * Ws;
+    const float *p0 = img + (size_t)y0 * Ws, *p1 = img + (size_t)y1 * Ws;
+    const float r0 = __fadd_rn(__fmul_rn(p0[xs], wx0), __fmul_rn(p0[x1], wx1));
+    const float r1 = __fadd_rn(__fmul_rn(p1[xs], wx0), __fmul_rn(p1[x1], wx1));
+    dst[((size_t)blockIdx.z * Hd + y) * Wd + x] = __fadd_rn(__fmul_rn(r0, wy0), __fmul_rn(r1, wy1));
+}
+
+static int resize_check(const void* src, const void* dst, int B, int Hs, int Ws, int Hd, int Wd)
+{
+    if (!src || !dst) { svb_set_error("resize: null argument"); return SVB_ERR_PARAM; }
+    if (B <= 0 || Hs <= 0 || Ws <= 0) { svb_set_error("resize: empty source (cv2: !ssize.empty())"); return SVB_ERR_PARAM; }
+    if (Hd <= 0 || Wd <= 0) { svb_set_error("resize: empty destination size (cv2: !dsize.empty())"); return SVB_ERR_PARAM; }
+    if (Hd > 65535 || B > 65535) { svb_set_error("resize: more than 65535 rows or images unsupported"); return SVB_ERR_UNSUPPORTED; }
+    return SVB_OK;
+}
+
+extern "C" int svb_resize_u8_dev(const uint8_t* src, int B, int Hs, int Ws, int C, uint8_t* dst, int Hd, int Wd, void* stream)
+{
+    int rc = resize_check(src, dst, B, Hs, Ws, Hd, Wd);
+    if (rc != SVB_OK) return rc;
+    if (C != 1 && C != 3) { svb_set_error("resize: 1 or 3 channels (got %d)", C); return SVB_ERR_UNSUPPORTED; }
+    const double sx = 1.0 / ((double)Wd / Ws), sy = 1.0 / ((double)Hd / Hs);      // cv2: scale = 1 / inv_scale
+    const dim3 grid(svb_ceil_div(Wd, 256), Hd, B);
+    if (C == 1) k_resize_u8<1><<<grid, 256, 0, (cudaStream_t)stream>>>(src, Hs, Ws, dst, Hd, Wd, sx, sy);
+    else k_resize_u8<3><<<grid, 256, 0, (cudaStream_t)stream>>>(src, Hs, Ws, dst, Hd, Wd, sx, sy);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+extern "C" int svb_resize_f32_dev(const float* src, int B, int Hs, int Ws, float* dst, int Hd, int Wd, void* stream)
+{
+    int rc = resize_check(src, dst, B, Hs, Ws, Hd, Wd);
+    if (rc != SVB_OK) return rc;
+    const double sx = 1.0 / ((double)Wd / Ws), sy = 1.0 / ((double)Hd / Hs);
+    k_resize_f32<<<dim3(svb_ceil_div(Wd, 256), Hd, B), 256, 0, (cudaStream_t)stream>>>(src, Hs, Ws, dst, Hd, Wd, sx, sy);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}

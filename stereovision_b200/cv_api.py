@@ -429,6 +429,49 @@ def remap(src, map1, map2, interpolation=INTER_LINEAR, to_gray=False):
 
 
 @_restores_device
+def resize(src, dsize, dst=None, fx=0, fy=0, interpolation=INTER_LINEAR):
+    """cv2.resize(src, dsize, interpolation=cv2.INTER_LINEAR) -- cv2's positional order; INTER_LINEAR is also
+    cv2's default (depth_map.py:776).  dsize = (width, height); dsize None/(0, 0) takes round(fx * W), round(fy * H)
+    like cv2.  u8 [H,W] / [H,W,3] / [B,H,W] / [B,H,W,3] (bit-exact; fused_depth_map.py:473-476, depth_map.py:809-811)
+    or float32 [H,W] / [B,H,W] (fused_depth_map.py:1214-1217).  A source that already has the size comes back as a
+    copy, as from cv2."""
+    if interpolation != INTER_LINEAR:
+        raise NotImplementedError("only INTER_LINEAR is on the reference's path")
+    if dst is not None:
+        raise NotImplementedError("resize: pass no dst (the result is returned)")
+    torch = _torch()
+    s, was = _to_dev(src)
+    if s.dtype not in (torch.uint8, torch.float32):
+        raise ValueError("resize: src must be 8-bit or float32")
+    if s.ndim == 2:
+        B, C, batched = 1, 1, False
+    elif s.ndim == 3 and s.shape[-1] == 3 and s.dtype == torch.uint8:
+        B, C, batched = 1, 3, False
+    elif s.ndim == 3:
+        B, C, batched = int(s.shape[0]), 1, True
+    elif s.ndim == 4 and s.shape[-1] == 3 and s.dtype == torch.uint8:
+        B, C, batched = int(s.shape[0]), 3, True
+    else:
+        raise ValueError(f"unsupported src shape {tuple(s.shape)}")
+    Hs, Ws = (int(s.shape[1]), int(s.shape[2])) if batched else (int(s.shape[0]), int(s.shape[1]))
+    if dsize is None or tuple(dsize) == (0, 0):
+        if not (fx > 0 and fy > 0):
+            raise ValueError("resize: either dsize or both fx and fy must be non-zero (cv2: inv_scale_x > 0)")
+        Wd, Hd = int(round(Ws * fx)), int(round(Hs * fy))     # cv2: saturate_cast<int>(ssize * inv_scale)
+    else:
+        Wd, Hd = int(dsize[0]), int(dsize[1])
+    _ensure_device(s.device.index)
+    oshape = ([B] if batched else []) + [Hd, Wd] + ([3] if C == 3 else [])
+    out = torch.empty(oshape, dtype=s.dtype, device=s.device)
+    L = _lib.lib()
+    if s.dtype == torch.uint8:
+        _lib.check(L.svb_resize_u8_dev(s.data_ptr(), B, Hs, Ws, C, out.data_ptr(), Hd, Wd, _stream_ptr()))
+    else:
+        _lib.check(L.svb_resize_f32_dev(s.data_ptr(), B, Hs, Ws, out.data_ptr(), Hd, Wd, _stream_ptr()))
+    return _ret(out, was)
+
+
+@_restores_device
 def cvtColor(src, code=COLOR_BGR2GRAY):
     """cv2.cvtColor(img, cv2.COLOR_BGR2GRAY) (depth_map.py:871-879)."""
     if code != COLOR_BGR2GRAY:

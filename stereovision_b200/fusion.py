@@ -13,7 +13,7 @@ import ctypes
 import numpy as np
 
 from . import _lib
-from .cv_api import _ensure_device, _restores_device, _is_tensor, _ret, _stream_ptr, _to_dev, _torch, cvtColor
+from .cv_api import _ensure_device, _restores_device, _is_tensor, _ret, _stream_ptr, _to_dev, _torch, cvtColor, resize
 
 # fused_depth_map.py:80-116
 FUSION_WEIGHTS = {"stereo_base": 0.8, "midas_max_fill": 0.9, "flow_max_fill": 0.5}
@@ -74,11 +74,19 @@ def normalize_disparity(disparity, min_disp, num_disp):
 
 @_restores_device
 def calibrate_midas_to_stereo(midas_depth, stereo_disparity, stereo_confidence):
-    """fused_depth_map.py:1169-1257.  Maps must already share a shape (the reference's cv2.resize
-    branch belongs to its MiDaS wrapper, out of scope)."""
+    """fused_depth_map.py:1169-1257, including its first step: a mono map of another shape is resized to the
+    stereo shape with cv2.resize(INTER_LINEAR) (:1214-1217) -- on the device (svb.resize, float32)."""
     if midas_depth is None or stereo_disparity is None:
         return None
     torch = _torch()
+    if tuple(midas_depth.shape) != tuple(stereo_disparity.shape):
+        if len(midas_depth.shape) != len(stereo_disparity.shape):
+            raise ValueError(f"shape mismatch: {tuple(midas_depth.shape)} vs {tuple(stereo_disparity.shape)}")
+        if not _is_tensor(midas_depth):
+            midas_depth = np.asarray(midas_depth, np.float32)
+        elif midas_depth.dtype != torch.float32:
+            midas_depth = midas_depth.float()
+        midas_depth = resize(midas_depth, (int(stereo_disparity.shape[-1]), int(stereo_disparity.shape[-2])))
     (m, s, c), was, B, H, W = _f32_maps(midas_depth, stereo_disparity, stereo_confidence)
     _ensure_device(m.device.index)
     L = _lib.lib()
@@ -230,3 +238,52 @@ def detect_camera_occlusion(left_img, right_img, occlusion_threshold=0.45):
     else:
         result = "none"
     return result, ls, rs
+
+
+class OcclusionMonitor:
+    """The occlusion hysteresis of the reference's main loop (fused_depth_map.py:2325-2337 state, :2515-2571 update):
+    every `check_interval`-th frame the detector runs; a detected state that differs from the accepted one must
+    be seen on `hysteresis_frames` consecutive checks before it is accepted (a check that agrees with the accepted
+    state resets the count); accepting 'left' / 'right' switches stereo off, accepting 'none' / 'both' switches
+    it back on (with both cameras covered the reference keeps stereo running).  Host logic on three scalars per
+    check; the image statistics behind `detect` run on the device.
+
+        mon = OcclusionMonitor()
+        for frame_counter, (left, right) in enumerate(frames):
+            use_stereo = mon.update(frame_counter, left, right)
+    """
+
+    def __init__(self, hysteresis_frames=5, check_interval=2, occlusion_threshold=0.45, use_stereo=True, detect=None):
+        self.hysteresis_frames = int(hysteresis_frames)          # OCCLUSION_HYSTERESIS_FRAMES
+        self.check_interval = int(check_interval)                # OCCLUSION_CHECK_INTERVAL
+        self.occlusion_threshold = occlusion_threshold
+        self.state = "none"                                      # occlusion_state
+        self.counter = 0                                         # occlusion_hysteresis_counter
+        self.use_stereo = bool(use_stereo)                       # USE_STEREO
+        self.left_score = self.right_score = 0.0
+        self.last_detected = "none"
+        self._detect = detect or detect_camera_occlusion
+
+    def update(self, frame_counter, left_img, right_img):
+        """One iteration of the reference's loop body; returns whether stereo is enabled for this frame."""
+        if frame_counter % self.check_interval != 0:
+            return self.use_stereo
+        new_state, self.left_score, self.right_score = self._detect(left_img, right_img,
+                                                                    occlusion_threshold=self.occlusion_threshold)
+        self.last_detected = new_state
+        return self.observe(new_state)
+
+    def observe(self, new_state):
+        """The state machine alone, fed with a detector result."""
+        if new_state == self.state:
+            self.counter = 0
+            return self.use_stereo
+        self.counter += 1
+        if self.counter >= self.hysteresis_frames:
+            self.state = new_state
+            self.counter = 0
+            if self.state in ("left", "right"):
+                self.use_stereo = False
+            elif self.state in ("none", "both"):
+                self.use_stereo = True
+        return self.use_stereo

@@ -80,3 +80,27 @@ def make_aux_depths(disp_true, seed=0):
         y0, x0 = int(rng.integers(0, H - H // 6)), int(rng.integers(0, W - W // 6))
         flow[y0:y0 + H // 6, x0:x0 + W // 6] = 0.0
     return midas.astype(np.float32), np.clip(flow, 0, 255).astype(np.float32)
+
+
+def synthetic_calibration(W, H):
+    """The synthetic stereo calibration of SURVEY 8(d) as the 7 keys the reference's loaders read
+    (depth_map.py:613-619): fx = fy = 0.78 W, slightly off-centre principal point, mild radial / tangential
+    distortion, a small relative rotation, T = 6 cm along -x (the reference's unit is centimetres)."""
+    from .calib import Rodrigues
+    fx = 0.78 * W
+    K = np.array([[fx, 0, W / 2 + 3], [0, fx, H / 2 - 2], [0, 0, 1]], np.float64)
+    return dict(mtx_left=K.copy(), dist_left=np.array([[-0.10, 0.02, 1e-3, -1e-3, 0]], np.float64),
+                mtx_right=K.copy(), dist_right=np.array([[-0.09, 0.015, -1e-3, 1e-3, 0]], np.float64),
+                R=Rodrigues(np.array([0.01, -0.02, 0.005])), T=np.array([[-6.0], [0.05], [0.02]]), img_size=(W, H))
+
+
+def write_calibration_pkl(path, W, H):
+    """Write the synthetic calibration where the reference looks for it (output/stereo_calibration_data.pkl,
+    depth_map.py:22) -- BASELINE.json configs[0] 'synthetic calib .pkl'.  Returns the dict written."""
+    import os
+    import pickle
+    d = synthetic_calibration(W, H)
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    with open(path, "wb") as f:
+        pickle.dump(d, f)
+    return d

@@ -12,7 +12,8 @@ import numpy as np
 
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", ".."))
 from stereovision_b200.synth import make_pair, to_bgr  # noqa: E402
-from tests.golden_cases import SGBM_CASES, SGBM_COLOR_CASES, BM_CASES, color_pair, synth_calibration  # noqa: E402
+from tests.golden_cases import (SGBM_CASES, SGBM_COLOR_CASES, BM_CASES, RESIZE_CASES, color_pair, synth_calibration,  # noqa: E402
+                                resize_case_input)
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -86,6 +87,9 @@ def main():
         m1, m2 = cv2.initUndistortRectifyMap(K, D, R, P, (Wm, Hm), cv2.CV_16SC2)
         out[f"maps_{tag}_m1"], out[f"maps_{tag}_m2"] = m1, m2
         out[f"maps_{tag}_dist"] = np.zeros(0) if D is None else np.asarray(D, np.float64)
+    # cv2.resize(INTER_LINEAR): the reference's per-frame downscale and its float32 mono-map resize
+    for i, c in enumerate(RESIZE_CASES):
+        out[f"resize_{i}"] = cv2.resize(resize_case_input(c), c["dsize"], interpolation=cv2.INTER_LINEAR)
     np.savez_compressed(os.path.join(HERE, "golden.npz"), **out)
     print("wrote", os.path.join(HERE, "golden.npz"), os.path.getsize(os.path.join(HERE, "golden.npz")), "bytes")
 

@@ -32,6 +32,8 @@ def main():
             norm, disp, _, conf = ref.create_depth_map_stereo_scaled(lb, rb, c["min_disp"], c["num_disp"], c["window"])
             cal = ref.calibrate_midas_to_stereo(midas, disp, conf)
             cal_few = ref.calibrate_midas_to_stereo(midas, disp, np.zeros_like(conf))
+            # a mono map of another shape: the reference resizes it first (fused_depth_map.py:1214-1217)
+            cal_rs = ref.calibrate_midas_to_stereo(np.ascontiguousarray(midas[::2, ::3]), disp, conf)
             flow_n = ref.normalize_to_stereo_range(flow, disp)
             ref.fusion_params.update(defaults)
             ref.fusion_params.update(c["params"])
@@ -44,6 +46,7 @@ def main():
         out[f"conf_{i}"] = conf.astype(np.uint8)
         out[f"cal_{i}"] = cal
         out[f"calfew_{i}"] = cal_few
+        out[f"calrs_{i}"] = cal_rs
         out[f"flown_{i}"] = flow_n
         out[f"fused_{i}"] = fused
         out[f"fusedm_{i}"] = fused_m

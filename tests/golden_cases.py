@@ -189,3 +189,31 @@ def dense_disparity(c=None):
     d = rng.integers(-16, 320 * 16, (c["H"], c["W"])).astype(np.float32) / np.float32(16.0)
     d[:, :40] = rng.integers(1, 16 * 16, (c["H"], 40)).astype(np.float32) / np.float32(16.0)     # plenty of near range
     return d
+
+
+# cv2.resize(INTER_LINEAR) (fused_depth_map.py:473-476, depth_map.py:809-811, fused_depth_map.py:1214-1217):
+# (source H, W, channels or "f32", destination (W, H)).  The first is the reference's own case: a 640x480 BGR frame
+# to int(640 * 0.33) x int(480 * 0.33) (fused_depth_map.py:385-386).
+RESIZE_CASES = [
+    dict(H=480, W=640, ch=3, dsize=(211, 158), seed=81),
+    dict(H=97, W=131, ch=1, dsize=(200, 150), seed=82),       # upscale, odd sizes: the first / last rows split weights
+    dict(H=120, W=160, ch=3, dsize=(80, 60), seed=83),        # exact 2x down
+    dict(H=77, W=101, ch=3, dsize=(33, 41), seed=84),
+    dict(H=64, W=48, ch=1, dsize=(48, 64), seed=85),          # same size: a copy
+    dict(H=96, W=128, ch="f32", dsize=(211, 158), seed=86),   # mono map (384-ish network output) to the stereo shape
+    dict(H=150, W=200, ch="f32", dsize=(131, 97), seed=87),
+]
+
+
+def resize_case_input(c):
+    rng = np.random.default_rng(c["seed"])
+    if c["ch"] == "f32":
+        yy, xx = np.mgrid[0:c["H"], 0:c["W"]]
+        return (400.0 + 300.0 * np.sin(xx / 9.0) * np.cos(yy / 7.0) + rng.normal(0, 25.0, (c["H"], c["W"]))).astype(np.float32)
+    shape = (c["H"], c["W"]) if c["ch"] == 1 else (c["H"], c["W"], 3)
+    return rng.integers(0, 256, shape, dtype=np.uint8)
+
+
+# Calibration-file path (depth_map.py:591-668, fused_depth_map.py:307-442): synthetic .pkl at this size, the
+# scaled loader at the reference's default PROCESSING_SCALE = 0.33 and two more.
+CALIB_CASE = dict(W=320, H=240, scales=(1.0, 0.5, 0.33))

@@ -47,6 +47,12 @@ def test_calibration_and_range_match_reference(gf, i):
     disp, conf = gf[f"disp_{i}"], gf[f"conf_{i}"].astype(np.float32)
     assert _close(svb.calibrate_midas_to_stereo(midas, disp, conf), gf[f"cal_{i}"])
     assert _close(svb.calibrate_midas_to_stereo(midas, disp, np.zeros_like(conf)), gf[f"calfew_{i}"])
+    # a mono map of another shape is resized to the stereo shape on the device first (fused_depth_map.py:1214-1217)
+    small = np.ascontiguousarray(midas[::2, ::3])
+    assert _close(svb.calibrate_midas_to_stereo(small, disp, conf), gf[f"calrs_{i}"])
+    import torch
+    dev = svb.calibrate_midas_to_stereo(torch.from_numpy(small).cuda(), torch.from_numpy(disp).cuda(), torch.from_numpy(conf).cuda())
+    assert _close(dev.cpu().numpy(), gf[f"calrs_{i}"])
     assert _close(svb.normalize_to_stereo_range(flow, disp), gf[f"flown_{i}"])
 
 
@@ -154,3 +160,19 @@ def test_occlusion_stats_shapes():
         st = svb.occlusion_stats(g)
         for b in range(2):
             np.testing.assert_allclose(st[b], np.array(F.occlusion_stats(g[b])), rtol=RTOL, atol=1e-9)
+
+
+def test_occlusion_monitor_replays_a_left_occluded_sequence():
+    """fused_depth_map.py:2515-2571 with the real detector: the left camera is covered from frame 4 on -> five
+    differing checks (every 2nd frame) later stereo is switched off; uncovered again -> switched back on."""
+    from stereovision_b200.synth import make_pair, to_bgr
+    l, r, _ = make_pair(240, 320, 32, seed=5)
+    lb, rb = to_bgr(l), to_bgr(r)
+    covered = np.full_like(lb, 22) + (lb // 64)
+    mon = svb.OcclusionMonitor()
+    hist = []
+    for k in range(40):
+        left = covered if 4 <= k < 24 else lb
+        hist.append(mon.update(k, left, rb))
+    assert mon.last_detected == "none"
+    assert hist[:12] == [True] * 12 and hist[12:32] == [False] * 20 and hist[32:] == [True] * 8

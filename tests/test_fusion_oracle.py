@@ -40,6 +40,7 @@ def test_fusion_oracle_matches_reference(gf, i):
     cal = F.calibrate_midas_to_stereo(midas, disp, conf)
     assert _close(cal, gf[f"cal_{i}"])
     assert _close(F.calibrate_midas_to_stereo(midas, disp, np.zeros_like(conf)), gf[f"calfew_{i}"])
+    assert _close(F.calibrate_midas_to_stereo(np.ascontiguousarray(midas[::2, ::3]), disp, conf), gf[f"calrs_{i}"])
     fn = F.normalize_to_stereo_range(flow, disp)
     assert _close(fn, gf[f"flown_{i}"])
     fu, _ = F.fuse_depth_maps(norm, conf, gf[f"cal_{i}"], None, gf[f"flown_{i}"], c["moving"], fusion_params=c["params"])

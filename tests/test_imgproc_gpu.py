@@ -143,3 +143,54 @@ def test_init_undistort_rectify_map_full_size_and_errors(golden):
         svb.initUndistortRectifyMap(K, np.zeros(6), R, P, (64, 48))          # cv2 rejects 6 coefficients too
     with pytest.raises(NotImplementedError):
         svb.initUndistortRectifyMap(K, np.r_[np.zeros(12), 0.01, 0.0], R, P, (64, 48))
+
+
+def test_resize_matches_golden_and_oracle(golden):
+    """cv2.resize(INTER_LINEAR) on the device (fused_depth_map.py:473-476: both frames every processed frame;
+    :1214-1217: float32 mono map): u8 bit-exact against cv2's goldens and the oracle, float32 within 1e-6 relative;
+    NumPy and tensor inputs, batched."""
+    import torch
+    from tests.golden_cases import RESIZE_CASES, resize_case_input
+    for i, c in enumerate(RESIZE_CASES):
+        src = resize_case_input(c)
+        ref = golden[f"resize_{i}"]
+        got = svb.resize(src, c["dsize"], interpolation=svb.INTER_LINEAR)
+        assert got.shape == ref.shape and got.dtype == ref.dtype, i
+        if c["ch"] == "f32":
+            assert float(np.abs(got - ref).max()) <= 1e-6 * float(np.abs(ref).max()), i
+            assert float(np.abs(got - oracle.resize(src, c["dsize"])).max()) <= 1e-6 * float(np.abs(ref).max()), i
+        else:
+            assert np.array_equal(got, ref), (i, int((got != ref).sum()))
+            assert np.array_equal(got, oracle.resize(src, c["dsize"])), i
+        batch = torch.from_numpy(np.stack([src, src[::-1].copy()])).cuda()
+        out = svb.resize(batch, c["dsize"]).cpu().numpy()
+        assert out.shape[0] == 2
+        if c["ch"] == "f32":
+            assert float(np.abs(out[0] - ref).max()) <= 1e-6 * float(np.abs(ref).max())
+        else:
+            assert np.array_equal(out[0], ref) and np.array_equal(out[1], oracle.resize(src[::-1].copy(), c["dsize"]))
+    # fx / fy form and cv2's argument checks
+    src = resize_case_input(RESIZE_CASES[0])
+    assert svb.resize(src, None, fx=0.33, fy=0.33).shape == (round(480 * 0.33), round(640 * 0.33), 3)
+    with pytest.raises(ValueError):
+        svb.resize(src, (0, 0))
+    with pytest.raises(NotImplementedError):
+        svb.resize(src, (10, 10), interpolation=3)
+
+
+def test_resize_random_sizes_vs_oracle():
+    rng = np.random.default_rng(11)
+    for it in range(60):
+        sh, sw = int(rng.integers(1, 200)), int(rng.integers(1, 260))
+        if it % 4 == 0:
+            dsize = (max(1, int(sw * 0.33)), max(1, int(sh * 0.33)))
+        else:
+            dsize = (int(rng.integers(1, 300)), int(rng.integers(1, 300)))
+        ch = int(rng.choice([1, 3]))
+        src = rng.integers(0, 256, (sh, sw) if ch == 1 else (sh, sw, 3), dtype=np.uint8)
+        got = svb.resize(src, dsize)
+        assert np.array_equal(got, oracle.resize(src, dsize)), (sh, sw, dsize, ch)
+    # 1080p frame at the reference's scale
+    src = rng.integers(0, 256, (1080, 1920, 3), dtype=np.uint8)
+    dsize = (int(1920 * 0.33), int(1080 * 0.33))
+    assert np.array_equal(svb.resize(src, dsize), oracle.resize(src, dsize))

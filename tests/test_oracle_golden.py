@@ -115,3 +115,16 @@ def test_undistort_rectify_map_oracle_matches_golden(golden, tag):
     m1, m2 = init_undistort_rectify_map(*map_case(golden, tag))
     assert m1.dtype == np.int16 and m2.dtype == np.uint16
     assert np.array_equal(m1, golden[f"maps_{tag}_m1"]) and np.array_equal(m2, golden[f"maps_{tag}_m2"])
+
+
+def test_resize_oracle_matches_golden(golden):
+    """cv2.resize(INTER_LINEAR): u8 bit-exact, float32 within 1e-6 relative (fused_depth_map.py:473-476, 1214-1217)."""
+    from tests.golden_cases import RESIZE_CASES, resize_case_input
+    for i, c in enumerate(RESIZE_CASES):
+        got = oracle.resize(resize_case_input(c), c["dsize"])
+        ref = golden[f"resize_{i}"]
+        assert got.shape == ref.shape and got.dtype == ref.dtype, i
+        if c["ch"] == "f32":
+            assert float(np.abs(got - ref).max()) <= 1e-6 * float(np.abs(ref).max()), i
+        else:
+            assert np.array_equal(got, ref), i

@@ -65,9 +65,15 @@ __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 2 ? 24 : (NP ==
 #define SW_SLEEP_NS 40         // back-off while a row waits for its neighbour's progress counter
 #endif
 // ring slots per path between two rows (>= 4; every extra slot is a column of slack between rows)
+// Measured at 1080p / D256 / HH, 32 pairs (ms per launch): the last sweep with (ring, staging slots) = (4,4) 23.7,
+// (4,3) 22.6, (5,3) 22.2, (6,2) 21.7: with 4 slots a row has 2 columns of slack to its neighbours and polls on every
+// column (ncu: 4 polls per column on either side); the staging ring of C and S1 gives its shared memory to the
+// inter-row rings.  The first sweep (it also writes S1) wants the deeper staging: (6,4) 14.2, (6,3) 14.6, (6,2) 14.9.
 #ifndef SW_RING_FIRST
 #define SW_RING_FIRST 6
-#define SW_RING_LAST 4
+#endif
+#ifndef SW_RING_LAST
+#define SW_RING_LAST 6
 #endif
 // NP <= 2 (numDisparities <= 128) leaves most of the shared memory unused: deeper rings and staging there
 #ifndef SW_RING_SMALL
@@ -80,7 +86,13 @@ __host__ __device__ constexpr int sw_ring(int NP, bool last)
     return NP <= 2 ? (last ? SW_RING_SMALL_LAST : SW_RING_SMALL) : (NP <= 4 ? (last ? SW_RING_LAST : SW_RING_FIRST) : 4);
 }
 // slots of the per-row cp.async staging ring for C (and S1 in the last sweep); prefetch distance = slots - 1
-__host__ __device__ constexpr int sw_stage(int NP, bool last) { return NP <= 2 ? SW_STAGE_SMALL : (NP <= 4 ? 4 : (last ? 3 : 4)); }
+#ifndef SW_STAGE_LAST
+#define SW_STAGE_LAST 2
+#endif
+#ifndef SW_STAGE_FIRST
+#define SW_STAGE_FIRST 4
+#endif
+__host__ __device__ constexpr int sw_stage(int NP, bool last) { return NP <= 2 ? SW_STAGE_SMALL : (NP <= 4 ? (last ? SW_STAGE_LAST : SW_STAGE_FIRST) : (last ? 3 : 4)); }
 __host__ __device__ constexpr int sw_roww(int NP) { return NP * 32 + 4; }     // ring row: the vector, its minimum, pad to 16 B
 __host__ __device__ constexpr size_t sw_smem_words(int NP, bool last)
 {

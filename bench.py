@@ -46,13 +46,18 @@ def b_alg_bytes(wl):
     return 4 * wl["W"] * wl["H"] + 4 * wl["W"] * wl["H"] * wl["D"]
 
 
-# DRAM bytes per pair and launch (dram__bytes_read.sum + dram__bytes_write.sum) from the committed
-# ncu --set full capture profiles/r01_v6_ncu_top3_summary_b8.txt (8 pairs per launch).
-NCU_TRAFFIC_PER_PAIR = {
-    "sgbm_1080p_d256_hh": {"k_cost": (0.873369 + 7.302557) / 8 * 1e9,
-                           "k_sweep<first>": (7.441713 + 8.516373) / 8 * 1e9,
-                           "k_sweep<last+wta>": (14.898929 + 1.292766) / 8 * 1e9},
-}
+def ncu_traffic_per_pair(workload):
+    """DRAM bytes per pair and launch of each big kernel (dram__bytes_read.sum + dram__bytes_write.sum) from the
+    committed summary of the latest `ncu --set full` capture (profiles/r02_ncu_traffic.json, written by
+    tools/ncu_traffic.py from the .ncu-rep).  Returns ({kernel: bytes per pair}, source) or ({}, None)."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")))
+        if d.get("workload") != workload:
+            return {}, None
+        return ({k: v["dram_bytes_per_pair"] for k, v in d["kernels"].items()},
+                f"profiles/r02_ncu_traffic.json ({d['source']}, {d['pairs_per_launch']} pairs per launch, scaled to this batch)")
+    except Exception:
+        return {}, None
 
 
 def kernel_alg_bytes(wl, name):
@@ -220,6 +225,87 @@ def run_reference_arm(args, wl, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def pageable_leg(wl, prm, Lh, Rh, steps):
+    """What the reference's call site sees (depth_map.py:909): svb.StereoSGBM_create(...).compute(left, right) with
+    ordinary (pageable) NumPy arrays in and a NumPy array out, a new matcher object per call like the reference's."""
+    import stereovision_b200 as svb
+    out = svb.StereoSGBM_create(**prm).compute(Lh, Rh)        # warm-up: workspace, staging buffers
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        out = svb.StereoSGBM_create(**prm).compute(Lh, Rh)
+    return time.perf_counter() - t0, out
+
+
+def fullpath_leg(wl, prm, npairs, steps, with_cpu):
+    """north_star's full frame path on identical inputs: cv2.remap x 2 (BGR, CV_16SC2 maps from the synthetic
+    calibration) -> cvtColor x 2 -> StereoSGBM.compute -> reprojectImageTo3D.  GPU: NumPy in / NumPy out through the
+    cv2-shaped API (pageable copies inside), and tensors in / tensors out; CPU: the same calls on cv2, one pair
+    per host thread."""
+    import torch
+    import stereovision_b200 as svb
+    from stereovision_b200 import calib
+    from stereovision_b200.synth import synthetic_calibration, to_bgr
+    H, W = wl["H"], wl["W"]
+    c = synthetic_calibration(W, H)
+    R1, R2, P1, P2, Q, _, _ = calib.stereoRectify(c["mtx_left"], c["dist_left"], c["mtx_right"], c["dist_right"], (W, H),
+                                                  c["R"], c["T"], alpha=0)
+    ml = svb.initUndistortRectifyMap(c["mtx_left"], c["dist_left"], R1, P1, (W, H))
+    mr = svb.initUndistortRectifyMap(c["mtx_right"], c["dist_right"], R2, P2, (W, H))
+    Lg, Rg = make_inputs(wl, npairs, seed0=200)
+    Lb, Rb = np.stack([to_bgr(x) for x in Lg]), np.stack([to_bgr(x) for x in Rg])
+
+    def gpu(lb, rb, m_l, m_r):
+        lr, rr = svb.remap(lb, m_l[0], m_l[1], svb.INTER_LINEAR), svb.remap(rb, m_r[0], m_r[1], svb.INTER_LINEAR)
+        gl, gr = svb.cvtColor(lr, svb.COLOR_BGR2GRAY), svb.cvtColor(rr, svb.COLOR_BGR2GRAY)
+        d = svb.StereoSGBM_create(**prm).compute(gl, gr)
+        return svb.reprojectImageTo3D(d, Q)
+    res = {"pairs_per_step": npairs, "stages": "remap x2 (BGR) + cvtColor x2 + StereoSGBM.compute + reprojectImageTo3D"}
+    gpu(Lb, Rb, ml, mr)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        pts = gpu(Lb, Rb, ml, mr)
+    res["gpu_numpy_io_pairs_per_s"] = npairs * steps / (time.perf_counter() - t0)
+    res["h2d_bytes_per_step"], res["d2h_bytes_per_step"] = int(Lb.nbytes + Rb.nbytes), int(pts.nbytes)
+    dl, dr = torch.from_numpy(Lb).cuda(), torch.from_numpy(Rb).cuda()
+    tml = [torch.from_numpy(m).cuda() for m in ml]
+    tmr = [torch.from_numpy(m).cuda() for m in mr]
+    gpu(dl, dr, tml, tmr)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        gpu(dl, dr, tml, tmr)
+    torch.cuda.synchronize()
+    res["gpu_device_resident_pairs_per_s"] = npairs * steps / (time.perf_counter() - t0)
+    if with_cpu:
+        try:
+            import cv2
+            from concurrent.futures import ThreadPoolExecutor
+            cv2.setNumThreads(1)
+            cores = len(os.sched_getaffinity(0))
+            avail = [int(l.split()[1]) * 1024 for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0]
+            threads = max(1, min(cores, int(0.6 * avail / (6 * H * W * wl["D"] + (64 << 20)))))
+
+            def one(i):
+                k = i % npairs
+                lr = cv2.remap(Lb[k], ml[0], ml[1], cv2.INTER_LINEAR)
+                rr = cv2.remap(Rb[k], mr[0], mr[1], cv2.INTER_LINEAR)
+                d = cv2.StereoSGBM_create(**prm).compute(cv2.cvtColor(lr, cv2.COLOR_BGR2GRAY), cv2.cvtColor(rr, cv2.COLOR_BGR2GRAY))
+                return cv2.reprojectImageTo3D(d, Q)
+            t0 = time.perf_counter()
+            with ThreadPoolExecutor(threads) as ex:
+                ref = list(ex.map(one, range(threads)))
+            res["cpu_pairs_per_s"] = threads / (time.perf_counter() - t0)
+            res["cpu_cores"], res["cpu_kind"] = threads, "reference (cv2, one pair per thread)"
+            # same inputs, same calls: the 3-D points must agree (disparity bit-exact -> points within 1e-4 relative)
+            a, b = pts[0], ref[0]
+            fin = np.isfinite(a) & np.isfinite(b)
+            res["points_match_cv2"] = bool(np.array_equal(np.isfinite(a), np.isfinite(b)) and
+                                           np.allclose(a[fin], b[fin], rtol=1e-4, atol=1e-4))
+        except ImportError:
+            res["cpu_pairs_per_s"] = None
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -230,6 +316,11 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="pairs per GPU per step (0 = workload default)")
     ap.add_argument("--ref-pairs", type=int, default=0, help="pairs per step of the CPU arm (0 = #cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --batch pairs per GPU (default); strong: --total-pairs split over the GPUs (SURVEY 8(d))")
+    ap.add_argument("--total-pairs", type=int, default=64, help="pairs of the whole job under --scaling strong")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the legs beside the contract's numbers (pageable NumPy e2e, full frame path, NCCL gather)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))
@@ -260,6 +351,10 @@ def main():
     _lib.check(L.svb_init(local))
 
     B = args.batch or wl["batch"]
+    if args.scaling == "strong":                              # fixed total work: contiguous shards, first ranks take the rest
+        from stereovision_b200.shard import shard_range
+        a0, a1 = shard_range(args.total_pairs, rank, world)
+        B = max(a1 - a0, 1)
     H, W, D = wl["H"], wl["W"], wl["D"]
     prm = sgbm_params(wl)
     Lh, Rh = make_inputs(wl, B, seed0=1000 * rank)
@@ -324,14 +419,52 @@ def main():
     _lib.check(L.svb_sgbm_check(h))
     parity = parity_check(args.workload, {"value(dev)": Od.cpu().numpy(), "e2e(host)": Op.numpy()},
                           seed0=1000 * rank, nuniq=min(B, 4))
-    tmax = torch.tensor([ms, e2e_s * 1e3, 0.0 if parity["sha256_match"] else 1.0], dtype=torch.float64, device=dev)
+    # ---- legs beside the contract's numbers (all outside the timed regions above)
+    extras = {}
+    if world > 1 and not args.no_extras:
+        # the one collective this path has: gather every rank's disparities (NCCL), check what arrived
+        from stereovision_b200.shard import gather_outputs, shard_sizes
+        import hashlib
+        sizes = [B] * world if args.scaling == "weak" else shard_sizes(args.total_pairs, world)
+        total = sum(sizes)
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        gather_outputs(Od, total)                               # warm-up (communicator set-up)
+        barrier()
+        g0.record(stream)
+        allout = gather_outputs(Od, total)
+        g1.record(stream)
+        barrier()
+        extras["gather_gbs"] = allout.numel() * 2 * (world - 1) / world / (g0.elapsed_time(g1) / 1e3) / 1e9
+        pinned = load_pinned_hashes()
+        ok, off = True, 0
+        for r, n in enumerate(sizes):                           # pair 0 of every rank's shard, as it arrived HERE
+            want = pinned.get(f"{args.workload}/seed{1000 * r}", {}).get("sha256")
+            got = hashlib.sha256(allout[off].cpu().numpy().tobytes()).hexdigest()
+            ok = ok and want is not None and got == want
+            off += n
+        extras["gathered_match"] = ok
+        del allout
+    L.svb_sgbm_destroy(h)
+    h = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        dt, outp = pageable_leg(wl, prm, Lh, Rh, min(args.steps, 3))
+        extras["e2e_pageable"] = {"value": B * min(args.steps, 3) / dt, "unit": "pairs/s",
+                                  "call": "svb.StereoSGBM_create(**prm).compute(np_left, np_right), pageable NumPy in / NumPy out",
+                                  "h2d_bytes_per_step": 2 * B * H * W, "d2h_bytes_per_step": 2 * B * H * W,
+                                  "equals_pinned_path": bool(np.array_equal(outp, Op.numpy()))}
+        import stereovision_b200 as svb_pkg
+        svb_pkg.release_workspaces()
+        extras["fullpath"] = fullpath_leg(wl, prm, 8, 2, not args.no_cpu_baseline)
+        svb_pkg.release_workspaces()
+    tmax = torch.tensor([ms, e2e_s * 1e3, 0.0 if parity["sha256_match"] and extras.get("gathered_match", True) else 1.0],
+                        dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     ms, e2e_ms = float(tmax[0]), float(tmax[1])
     parity["all_ranks_match"] = float(tmax[2]) == 0.0
 
     if rank == 0:
-        pairs = B * world * args.steps
+        pairs = (B * world if args.scaling == "weak" else args.total_pairs) * args.steps
         value = pairs / (ms / 1e3)
         e2e = pairs / (e2e_ms / 1e3)
         balg = b_alg_bytes(wl)
@@ -349,11 +482,12 @@ def main():
             dms, dl = stages[dom]
             # the hot path as one unit: B_alg x pairs over the summed device time of its kernels
             ach = balg * B * args.steps / (sgbm_ms / 1e3) / 1e9
-            tr = NCU_TRAFFIC_PER_PAIR.get(args.workload, {}).get(dom)
+            traffic, traffic_src = ncu_traffic_per_pair(args.workload)
+            tr = traffic.get(dom)
             kalg = kernel_alg_bytes(wl, dom)
             roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                     "traffic": tr * B if tr else None,
-                    "traffic_source": "ncu dram bytes of the dominant kernel per launch (profiles/r01_v6_ncu_top3_summary_b8.txt, scaled to this batch)" if tr else None,
+                    "traffic_source": ("ncu dram bytes of the dominant kernel per launch: " + traffic_src) if tr else None,
                     "dominant_kernel_alg_bytes_per_launch": kalg * B if kalg else None,
                     "dominant_kernel_achieved": (kalg * B / (dms / max(dl, 1) / 1e3) / 1e9) if kalg else None,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
@@ -365,18 +499,24 @@ def main():
         line = {
             "metric": "stereo_pairs_per_sec", "value": value, "unit": "pairs/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16",
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "u16",
             "data": "synthetic",
             "config": {"workload": args.workload, "H": H, "W": W, "numDisparities": D, "mode": wl["mode"],
                        "blockSize": 5, "pairs_per_gpu_per_step": B, "l2_policy": "inputs+volumes >> L2 (126 MB)", "host_numa_cpus": numa,
                        "gdisp_evals_per_s": value * H * W * D / 1e9},
-            "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": 2 * B * H * W * world,
-                    "d2h_bytes_per_step": 2 * B * H * W * world},
+            "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": 2 * H * W * (pairs // args.steps),
+                    "d2h_bytes_per_step": 2 * H * W * (pairs // args.steps)},
             "gpu_launches": launches * world,
             "parity": parity,
+            "multi_gpu_identical": (parity["all_ranks_match"] if world > 1 else None),
             "clocks": sampler.summary(),
             "roofline": roof,
         }
+        line.update(extras)
+        if args.scaling == "strong":
+            line["config"]["total_pairs"] = args.total_pairs
+            line["config"]["strong_scaling_note"] = ("fixed total work: fewer pairs per launch leave the wavefront's ramp-up and "
+                                                     "ramp-down (one band per SM at a time) a larger share of each sweep")
         if world == 1 and not args.no_cpu_baseline:
             cores = len(os.sched_getaffinity(0))
             dt, kind, used = cpu_reference_run(wl, cores, cores)
@@ -385,7 +525,8 @@ def main():
         sys.stdout.flush()
         os.dup2(real_stdout, 1)
         print(json.dumps(line), flush=True)
-    L.svb_sgbm_destroy(h)
+    if h is not None:
+        L.svb_sgbm_destroy(h)
     if world > 1:
         dist.destroy_process_group()
 

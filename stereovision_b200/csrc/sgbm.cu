@@ -717,17 +717,16 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
     const uint32_t P1P1 = pk_dup(g.P1), P2P2 = pk_dup(g.P2);
     const int dir = a.dir;
     const uint32_t one = a.njobs > 0;                        // 1, opaque to the compiler (add_fma)
-    uint32_t padm[NP], dpk[NP];
+    uint32_t padm[NP];
 #pragma unroll
     for (int k = 0; k < NP; ++k) {
         const int w = NP * lane + k;
         padm[k] = (w >= g.D ? 0xffffu : 0u) | (w + g.HALF >= g.D ? 0xffff0000u : 0u);
-        dpk[k] = ((uint32_t)(w + g.HALF) << 16) | (uint32_t)w;    // the two disparities of word k
     }
     const int rw = helper ? 0 : warp;
     uint32_t* ring_in = ring + (size_t)rw * RINGW;
     uint32_t* ring_out = ring_in + RINGW;                    // input ring of warp + 1
-    uint32_t* mysc = wsc + rw * VW;
+    const uint32_t mysc_s = smem_u32(wsc + rw * VW);         // (last sweep) this row's S vector of the current column
     const uint32_t cst_s = smem_u32(cstage + (size_t)rw * NS * VW + NP * lane);   // this lane's slice, slot 0
     const uint32_t sst_s = smem_u32(sstage + (size_t)rw * NS * VW + NP * lane);
 
@@ -977,14 +976,16 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                 if (a.storeS) vec_st<NP>(pS - NP * lane, lane, S);
                 if (y >= keep) {
                     // ---- WTA (A.4): argmin with lowest-d tie break via keys (S << 16 | d)
+                    // (the lane's own 2 NP keys carry compile-time local indices k / HALF + k; the lane's first
+                    //  disparity NP * lane is added once, before the warp-wide minimum)
                     uint32_t kmin = 0xffffffffu;
 #pragma unroll
                     for (int k = 0; k < NP; ++k) {
-                        const uint32_t klo = __byte_perm(S[k], dpk[k], 0x1054);
-                        const uint32_t khi = __byte_perm(S[k], dpk[k], 0x3276);
+                        const uint32_t klo = __byte_perm(S[k], (uint32_t)k, 0x1054);
+                        const uint32_t khi = __byte_perm(S[k], (uint32_t)(32 * NP + k), 0x3254);
                         kmin = min(kmin, min(klo, khi));
                     }
-                    kmin = __reduce_min_sync(FULLMASK, kmin);
+                    kmin = __reduce_min_sync(FULLMASK, kmin + (uint32_t)(NP * lane));
                     if constexpr (MASK == 1) {
                         // cv2's 3WAY argmin runs 8 int16 lanes over d (lane = d mod 8): within a lane a later d with an
                         // EQUAL cost replaces the earlier one, across lanes the lowest recorded d wins (oracle/sgbm_oracle.c).
@@ -1020,21 +1021,37 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                     const int th = wta_threshold<MASK == 1>(g, (int)(kmin >> 16));
                     // uniqueness: count disparities with S < th; the ones at best-1..best+1 are taken out later
                     const uint32_t th2 = pk_dup((uint32_t)th);
-                    uint32_t bits = 0;
+                    uint32_t lt[NP];
 #pragma unroll
                     for (int k = 0; k < NP; ++k) {
-                        uint32_t lt = __vsub2(S[k], th2);                 // S, th in [0, 0x8000]: bit 15 = (S < th)
-                        if (!FULL) lt &= ~padm[k];
-                        bits |= (lt >> k) & (0x80008000u >> k);
+                        lt[k] = __vsub2(S[k], th2);                        // S, th in [0, 0x8000]: bit 15 = (S < th)
+                        if (!FULL) lt[k] &= ~padm[k];
+                    }
+                    uint32_t bits = 0;
+                    if constexpr (NP == 4) {                               // the sign bytes of four words in two permutes
+                        bits = (__byte_perm(lt[0], lt[1], 0x7351) & 0x80808080u) |
+                               ((__byte_perm(lt[2], lt[3], 0x7351) & 0x80808080u) >> 1);
+                    } else if constexpr (NP == 2) {
+                        bits = __byte_perm(lt[0], lt[1], 0x7351) & 0x80808080u;
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < NP; ++k) bits |= (lt[k] >> k) & (0x80008000u >> k);
                     }
                     const uint32_t cnt = __reduce_add_sync(FULLMASK, (uint32_t)__popc(bits));
-                    vec_st<NP>(mysc, lane, S);
+                    // subpixel taps S[best - 1], S[best + 1] through the row's scratch vector (shared-space addresses;
+                    // disparity d sits in half d / HALF of word d % HALF)
+                    sts_vec<NP, 0>(mysc_s + NP * 4 * lane, S);
                     __syncwarp();
-                    const uint16_t* sv = reinterpret_cast<const uint16_t*>(mysc);
                     const int best = (int)(kmin & 0xffffu);
-                    auto tap = [&](int d) { return (uint32_t)sv[d < g.HALF ? 2 * d : 2 * (d - g.HALF) + 1]; };
-                    const uint32_t sm1v = best > 0 ? tap(best - 1) : 0u;
-                    const uint32_t sp1v = best < g.D - 1 ? tap(best + 1) : 0u;
+                    auto tap = [&](int d) {
+                        uint32_t v;
+                        const uint32_t ad = mysc_s + 4u * (uint32_t)d - (d >= 32 * NP ? (uint32_t)(4 * 32 * NP - 2) : 0u);
+                        asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(ad));
+                        return v;
+                    };
+                    const uint32_t tm1 = tap(max(best - 1, 0)), tp1 = tap(min(best + 1, g.D - 1));
+                    const uint32_t sm1v = best > 0 ? tm1 : 0u;
+                    const uint32_t sp1v = best < g.D - 1 ? tp1 : 0u;
                     if (lane == (i & 31)) { rkey = kmin; rcnt = cnt; rtap = sm1v | (sp1v << 16); }
                     if ((i & 31) == 31 || i == w1 - 1) {
                         // 32 columns decided at once: lane j finishes column (i & ~31) + j

@@ -717,6 +717,7 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
     const uint32_t P1P1 = pk_dup(g.P1), P2P2 = pk_dup(g.P2);
     const int dir = a.dir;
     const uint32_t one = a.njobs > 0;                        // 1, opaque to the compiler (add_fma)
+    const uint32_t himask = 0u - (one << 16);                // 0xffff0000 in a register (keeps the WTA keys' LOP3 a single op)
     uint32_t padm[NP];
 #pragma unroll
     for (int k = 0; k < NP; ++k) {
@@ -981,8 +982,8 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                     uint32_t kmin = 0xffffffffu;
 #pragma unroll
                     for (int k = 0; k < NP; ++k) {
-                        const uint32_t klo = __byte_perm(S[k], (uint32_t)k, 0x1054);
-                        const uint32_t khi = __byte_perm(S[k], (uint32_t)(32 * NP + k), 0x3254);
+                        const uint32_t klo = S[k] * 65536u + (uint32_t)k;                  // one IMAD (FMA pipe)
+                        const uint32_t khi = (S[k] & himask) | (uint32_t)(32 * NP + k);     // one LOP3
                         kmin = min(kmin, min(klo, khi));
                     }
                     kmin = __reduce_min_sync(FULLMASK, kmin + (uint32_t)(NP * lane));

@@ -63,56 +63,74 @@ __global__ void __launch_bounds__(256) k_median3_s16(const int16_t* __restrict__
 // on load (exact), fusing depth_map.py:909 with :912.  DEPTH: also emit
 // depth_map.py:926-933 (depth = fxB / (d + 1e-6), clip, validity mask) in the epilogue.
 // DEPTH 2: the same in float64, which is what NumPy computes when fx comes from a float64 camera matrix (:917).
+// Two vertically adjacent outputs per thread (rows 2t, 2t + 1): their windows share four rows = 20 samples.  A
+// shared sample with 13 larger shared samples cannot be the median of either window (rank 13 of 25), nor one with 13
+// smaller: the 7 smallest and 7 largest of the 20 are dropped ONCE (forgetful selection, 7 rounds), and each output
+// is the 6th of the 6 survivors + its own 5 samples (5 rounds): ~96 compare-exchanges per output instead of ~150,
+// 15 loads instead of 25.  (The kernel is bound by the selection network, not by memory.)  Exact: order statistics.
 template <bool FROM_S16, int DEPTH>
 __global__ void __launch_bounds__(256) k_median5_f32(const void* __restrict__ src_, int H, int W,
                                                      float* __restrict__ dst, void* __restrict__ depth_,
                                                      double fxB64, float min_disp, double min_depth64, double max_depth64)
 {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y0 = 2 * blockIdx.y;
     if (x >= W) return;
     const size_t img = (size_t)blockIdx.z * H * W;
-    float s[25];
+    int xx[5];
 #pragma unroll
-    for (int j = 0; j < 5; ++j) {
-        const size_t ro = img + (size_t)min(max(y + j - 2, 0), H - 1) * W;
-#pragma unroll
-        for (int i = 0; i < 5; ++i) {
-            const int xx = min(max(x + i - 2, 0), W - 1);
-            if (FROM_S16) s[j * 5 + i] = (float)((const int16_t*)src_)[ro + xx] * 0.0625f;
-            else s[j * 5 + i] = ((const float*)src_)[ro + xx];
-        }
-    }
+    for (int i = 0; i < 5; ++i) xx[i] = min(max(x + i - 2, 0), W - 1);
+    auto ld = [&](int row, int i) -> float {
+        const size_t o = img + (size_t)min(max(row, 0), H - 1) * W + xx[i];
+        return FROM_S16 ? (float)((const int16_t*)src_)[o] * 0.0625f : ((const float*)src_)[o];
+    };
     float v[14];
+    {
+        float c[20];                                         // rows y0 - 1 .. y0 + 2 (clamped): in both windows
 #pragma unroll
-    for (int i = 0; i < 14; ++i) v[i] = s[i];
-    minmax<14>(v); v[0] = s[14];
-    minmax<13>(v); v[0] = s[15];
-    minmax<12>(v); v[0] = s[16];
-    minmax<11>(v); v[0] = s[17];
-    minmax<10>(v); v[0] = s[18];
-    minmax<9>(v); v[0] = s[19];
-    minmax<8>(v); v[0] = s[20];
-    minmax<7>(v); v[0] = s[21];
-    minmax<6>(v); v[0] = s[22];
-    minmax<5>(v); v[0] = s[23];
-    minmax<4>(v); v[0] = s[24];
-    minmax<3>(v);
-    const float d = v[1];
-    const size_t o = img + (size_t)y * W + x;
-    dst[o] = d;
-    if (DEPTH == 1) {
-        // NumPy float32 semantics of depth_map.py:926-933
-        float* depth = (float*)depth_;
-        const float fxB = (float)fxB64, min_depth = (float)min_depth64, max_depth = (float)max_depth64;
-        const float z = __fdiv_rn(fxB, __fadd_rn(d, 1e-6f));
-        const float zc = fminf(fmaxf(z, min_depth), max_depth);
-        const bool valid = (d > min_disp) && (zc >= min_depth) && (zc <= max_depth);
-        depth[o] = valid ? zc : 0.f;
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int i = 0; i < 5; ++i) c[j * 5 + i] = ld(y0 - 1 + j, i);
+#pragma unroll
+        for (int i = 0; i < 14; ++i) v[i] = c[i];
+        minmax<14>(v); v[0] = c[14];
+        minmax<13>(v); v[0] = c[15];
+        minmax<12>(v); v[0] = c[16];
+        minmax<11>(v); v[0] = c[17];
+        minmax<10>(v); v[0] = c[18];
+        minmax<9>(v); v[0] = c[19];
+        minmax<8>(v);                                        // survivors: v[1..6]
     }
-    if (DEPTH == 2) {
-        const double z = __ddiv_rn(fxB64, (double)__fadd_rn(d, 1e-6f));
-        const double zc = fmin(fmax(z, min_depth64), max_depth64);
-        ((double*)depth_)[o] = (d > min_disp) ? zc : 0.0;
+    const float fxB = (float)fxB64, min_depth = (float)min_depth64, max_depth = (float)max_depth64;
+#pragma unroll
+    for (int o2 = 0; o2 < 2; ++o2) {
+        const int y = y0 + o2;
+        if (y >= H) break;
+        float e[5], w[14];
+#pragma unroll
+        for (int i = 0; i < 5; ++i) e[i] = ld(o2 ? y0 + 3 : y0 - 2, i);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) w[i] = v[1 + i];
+        w[6] = e[0];
+        minmax<7>(w); w[0] = e[1];
+        minmax<6>(w); w[0] = e[2];
+        minmax<5>(w); w[0] = e[3];
+        minmax<4>(w); w[0] = e[4];
+        minmax<3>(w);
+        const float d = w[1];
+        const size_t o = img + (size_t)y * W + x;
+        dst[o] = d;
+        if (DEPTH == 1) {
+            // NumPy float32 semantics of depth_map.py:926-933
+            const float z = __fdiv_rn(fxB, __fadd_rn(d, 1e-6f));
+            const float zc = fminf(fmaxf(z, min_depth), max_depth);
+            const bool valid = (d > min_disp) && (zc >= min_depth) && (zc <= max_depth);
+            ((float*)depth_)[o] = valid ? zc : 0.f;
+        }
+        if (DEPTH == 2) {
+            const double z = __ddiv_rn(fxB64, (double)__fadd_rn(d, 1e-6f));
+            const double zc = fmin(fmax(z, min_depth64), max_depth64);
+            ((double*)depth_)[o] = (d > min_disp) ? zc : 0.0;
+        }
     }
 }
 
@@ -127,7 +145,7 @@ extern "C" int svb_median3_s16_dev(const int16_t* src, int B, int H, int W, int1
 extern "C" int svb_median5_f32_dev(const float* src, int B, int H, int W, float* dst, void* stream)
 {
     if (!src || !dst || B <= 0 || H <= 0 || W <= 0) { svb_set_error("median5: bad argument"); return SVB_ERR_PARAM; }
-    k_median5_f32<false, 0><<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(
+    k_median5_f32<false, 0><<<dim3(svb_ceil_div(W, 256), (H + 1) / 2, B), 256, 0, (cudaStream_t)stream>>>(
         src, H, W, dst, nullptr, 0.0, 0.f, 0.0, 0.0);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
@@ -141,7 +159,7 @@ extern "C" int svb_disp_to_depth_dev(const int16_t* disp16, int B, int H, int W,
         svb_set_error("disp_to_depth: bad argument"); return SVB_ERR_PARAM;
     }
     // Python computes fx*BASELINE in double, NumPy then casts the scalar to float32
-    k_median5_f32<true, 1><<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(
+    k_median5_f32<true, 1><<<dim3(svb_ceil_div(W, 256), (H + 1) / 2, B), 256, 0, (cudaStream_t)stream>>>(
         disp16, H, W, disparity, depth, fx * baseline, (float)min_disp, min_depth, max_depth);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
@@ -154,7 +172,7 @@ extern "C" int svb_disp_to_depth_f64_dev(const int16_t* disp16, int B, int H, in
     if (!disp16 || !disparity || !depth || B <= 0 || H <= 0 || W <= 0) {
         svb_set_error("disp_to_depth_f64: bad argument"); return SVB_ERR_PARAM;
     }
-    k_median5_f32<true, 2><<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(
+    k_median5_f32<true, 2><<<dim3(svb_ceil_div(W, 256), (H + 1) / 2, B), 256, 0, (cudaStream_t)stream>>>(
         disp16, H, W, disparity, depth, fx * baseline, (float)min_disp, min_depth, max_depth);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
@@ -338,14 +356,42 @@ extern "C" int svb_filter_speckles_s16_static(int16_t* img, int B, int H, int W,
 // ---------------------------------------------------------------------------------------
 // one destination pixel of cv2.remap (A.7): fixed-point bilinear tap of the 2x2 source block, BORDER_CONSTANT 0
 template <int C>
-__device__ __forceinline__ void remap_pixel(const uint8_t* __restrict__ img, int Hs, int Ws, int sx, int sy, int f,
-                                            int (&out)[C])
+__device__ __forceinline__ void remap_pixel(const uint8_t* __restrict__ img, const uint8_t* lim, int Hs, int Ws, int sx,
+                                            int sy, int f, int (&out)[C])
 {
     const int fx = f & 31, fy = f >> 5;
     const int w00 = (32 - fy) * (32 - fx) * 32, w01 = (32 - fy) * fx * 32;
     const int w10 = fy * (32 - fx) * 32, w11 = fy * fx * 32;
     const bool x0 = sx >= 0 && sx < Ws, x1 = sx + 1 >= 0 && sx + 1 < Ws;
     const bool y0 = sy >= 0 && sy < Hs, y1 = sy + 1 >= 0 && sy + 1 < Hs;
+    if constexpr (C == 3) {
+        // Interior pixel: the two taps of a source row are 6 contiguous bytes; fetch them as aligned 32-bit words
+        // (three loads and two funnel shifts per row instead of six byte loads -- the kernel is bound by the number
+        // of load instructions, not by bytes).  `lim` = last address from which a 12-byte read stays inside src.
+        const uint8_t* p0 = img + ((size_t)sy * Ws + sx) * 3;
+        const uint8_t* p1 = p0 + (size_t)Ws * 3;
+        if (x0 && x1 && y0 && y1 && p1 <= lim) {
+            uint32_t lo[2], hi[2];
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                const uintptr_t pa = (uintptr_t)(r ? p1 : p0);
+                const uint32_t* w = reinterpret_cast<const uint32_t*>(pa & ~(uintptr_t)3);
+                const uint32_t sh = (uint32_t)(pa & 3) * 8;
+                const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+                lo[r] = __funnelshift_r(w0, w1, sh);
+                hi[r] = __funnelshift_r(w1, w2, sh);
+            }
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                // tap x0 = bytes 0..2, tap x1 = bytes 3..5 of (lo, hi)
+                const int a00 = (lo[0] >> (8 * c)) & 0xff, a10 = (lo[1] >> (8 * c)) & 0xff;
+                const int a01 = c == 0 ? (lo[0] >> 24) : ((hi[0] >> (8 * (c - 1))) & 0xff);
+                const int a11 = c == 0 ? (lo[1] >> 24) : ((hi[1] >> (8 * (c - 1))) & 0xff);
+                out[c] = min(max((16384 + w00 * a00 + w01 * a01 + w10 * a10 + w11 * a11) >> 15, 0), 255);
+            }
+            return;
+        }
+    }
 #pragma unroll
     for (int c = 0; c < C; ++c) {
         int acc = 16384;
@@ -374,7 +420,8 @@ __global__ void __launch_bounds__(256) k_remap_u8(const uint8_t* __restrict__ sr
     const size_t mo = (size_t)y * Wo + x;
     const short2 m1 = reinterpret_cast<const short2*>(map1)[mo];
     int out[C];
-    remap_pixel<C>(src + (size_t)blockIdx.z * Hs * Ws * C, Hs, Ws, m1.x, m1.y, map2[mo] & 1023, out);
+    remap_pixel<C>(src + (size_t)blockIdx.z * Hs * Ws * C, src + (size_t)gridDim.z * Hs * Ws * C - 16, Hs, Ws, m1.x, m1.y,
+                   map2[mo] & 1023, out);
     const size_t o = ((size_t)blockIdx.z * Ho + y) * Wo + x;
     if (GRAY) {
         dst[o] = (uint8_t)gray_of(out[0], out[1], out[C - 1]);
@@ -398,6 +445,7 @@ __global__ void __launch_bounds__(256) k_remap_u8x4(const uint8_t* __restrict__ 
     const int4 m1 = *reinterpret_cast<const int4*>(map1 + 2 * mo);          // 4 x (sx | sy << 16)
     const uint2 m2 = *reinterpret_cast<const uint2*>(map2 + mo);            // 4 x u16
     const uint8_t* img = src + (size_t)blockIdx.z * Hs * Ws * C;
+    const uint8_t* lim = src + (size_t)gridDim.z * Hs * Ws * C - 16;       // word loads stay inside the batch
     const int mm[4] = {m1.x, m1.y, m1.z, m1.w};
     const unsigned ff[4] = {m2.x & 0xffffu, m2.x >> 16, m2.y & 0xffffu, m2.y >> 16};
     constexpr int CO = GRAY ? 1 : C;
@@ -405,7 +453,7 @@ __global__ void __launch_bounds__(256) k_remap_u8x4(const uint8_t* __restrict__ 
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         int out[C];
-        remap_pixel<C>(img, Hs, Ws, (int)(short)(mm[q] & 0xffff), mm[q] >> 16, (int)(ff[q] & 1023u), out);
+        remap_pixel<C>(img, lim, Hs, Ws, (int)(short)(mm[q] & 0xffff), mm[q] >> 16, (int)(ff[q] & 1023u), out);
         if (GRAY) px[q] = (uint8_t)gray_of(out[0], out[1], out[C - 1]);
         else {
 #pragma unroll
@@ -441,7 +489,7 @@ extern "C" int svb_remap_u8_dev(const uint8_t* src, int B, int Hs, int Ws, int C
     return SVB_OK;
 }
 
-// BGR -> gray (A.8), 4 pixels per thread where possible
+// BGR -> gray (A.8): four pixels per thread -- three 32-bit loads, one 32-bit store -- when both pointers allow it
 __global__ void __launch_bounds__(256) k_bgr2gray(const uint8_t* __restrict__ bgr, size_t n, uint8_t* __restrict__ gray)
 {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -449,10 +497,25 @@ __global__ void __launch_bounds__(256) k_bgr2gray(const uint8_t* __restrict__ bg
     const uint8_t* p = bgr + 3 * i;
     gray[i] = (uint8_t)((3735 * p[0] + 19235 * p[1] + 9798 * p[2] + 16384) >> 15);
 }
+__global__ void __launch_bounds__(256) k_bgr2gray_x4(const uint32_t* __restrict__ bgr, size_t n4, uint32_t* __restrict__ gray)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    const uint32_t a = __ldg(bgr + 3 * i), b = __ldg(bgr + 3 * i + 1), c = __ldg(bgr + 3 * i + 2);   // B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3
+    auto gr = [](uint32_t B, uint32_t G, uint32_t R) { return (3735u * B + 19235u * G + 9798u * R + 16384u) >> 15; };
+    const uint32_t g0 = gr(a & 0xff, (a >> 8) & 0xff, (a >> 16) & 0xff);
+    const uint32_t g1 = gr(a >> 24, b & 0xff, (b >> 8) & 0xff);
+    const uint32_t g2 = gr((b >> 16) & 0xff, b >> 24, c & 0xff);
+    const uint32_t g3 = gr((c >> 8) & 0xff, (c >> 16) & 0xff, c >> 24);
+    gray[i] = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+}
 extern "C" int svb_bgr2gray_dev(const uint8_t* bgr, size_t npix, uint8_t* gray, void* stream)
 {
     if (!bgr || !gray || npix == 0) { svb_set_error("bgr2gray: bad argument"); return SVB_ERR_PARAM; }
-    k_bgr2gray<<<svb_ceil_div(npix, 256), 256, 0, (cudaStream_t)stream>>>(bgr, npix, gray);
+    const size_t n4 = (((uintptr_t)bgr | (uintptr_t)gray) & 3) == 0 ? npix / 4 : 0;
+    if (n4) k_bgr2gray_x4<<<svb_ceil_div(n4, 256), 256, 0, (cudaStream_t)stream>>>((const uint32_t*)bgr, n4, (uint32_t*)gray);
+    if (npix > 4 * n4)
+        k_bgr2gray<<<svb_ceil_div(npix - 4 * n4, 256), 256, 0, (cudaStream_t)stream>>>(bgr + 12 * n4, npix - 4 * n4, gray + 4 * n4);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

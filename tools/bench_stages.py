@@ -24,7 +24,6 @@ def main():
     import torch
     import stereovision_b200 as svb
     from stereovision_b200.synth import make_pair, make_aux_depths, to_bgr
-    from tests.golden_cases import synth_calibration
     H, W, B = a.H, a.W, a.batch
     peak = 6551.0
     try:
@@ -37,15 +36,13 @@ def main():
     rep = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(dev).unsqueeze(0).repeat(B, *([1] * x.ndim)).contiguous()
     bgr = rep(to_bgr(l))
     gray_l, gray_r = rep(l), rep(r)
-    try:
-        cal = synth_calibration(W, H)
-        m1, m2 = torch.from_numpy(cal["left_map1"]).to(dev), torch.from_numpy(cal["left_map2"]).to(dev)
-        Q = cal["Q"]
-    except Exception:                                   # cv2 missing: identity maps
-        xs, ys = np.meshgrid(np.arange(W), np.arange(H))
-        m1 = torch.from_numpy(np.stack([xs, ys], -1).astype(np.int16)).to(dev)
-        m2 = torch.zeros((H, W), dtype=torch.uint16, device=dev)
-        Q = np.array([[1, 0, 0, -W / 2], [0, 1, 0, -H / 2], [0, 0, 0, 0.78 * W], [0, 0, 1 / 6.0, 0]], np.float64)
+    # rectification maps from the synthetic calibration through the package's own path (host stereoRectify + device maps)
+    from stereovision_b200 import calib
+    from stereovision_b200.synth import synthetic_calibration
+    sc = synthetic_calibration(W, H)
+    R1, _, P1, _, Q, _, _ = calib.stereoRectify(sc["mtx_left"], sc["dist_left"], sc["mtx_right"], sc["dist_right"], (W, H),
+                                                sc["R"], sc["T"], alpha=0)
+    m1, m2 = svb.initUndistortRectifyMap(sc["mtx_left"], sc["dist_left"], R1, P1, (W, H), as_tensor=True)
     disp16 = rep((gt * 16).astype(np.int16))
     dispf = disp16.float() / 16.0
     midas_d, flow_d = rep(midas), rep(flow)
@@ -70,6 +67,8 @@ def main():
     Hm = np.array([[1.01, 0.002, 1.5], [-0.003, 0.99, -2.0], [1e-6, -2e-6, 1.0]])
     rows = [
         ("initUndistortRectifyMap (N1, per map pair)", lambda: svb.initUndistortRectifyMap(Kc, dc, None, Kc, (W, H), as_tensor=True), 6 * px / B),
+        ("resize BGR x0.33 (a1, fused_depth_map.py:473-476)", lambda: svb.resize(bgr, (int(W * 0.33), int(H * 0.33))), 3 * px + 3 * int(W * 0.33) * int(H * 0.33)),
+        ("cvtColor BGR2GRAY (a2)", lambda: svb.cvtColor(bgr), 4 * px),
         ("remap BGR + gray (a1,a2)", lambda: svb.remap(bgr, m1, m2, svb.INTER_LINEAR, to_gray=True), (3 + 1) * px),
         ("remap BGR (a1)", lambda: svb.remap(bgr, m1, m2, svb.INTER_LINEAR), 6 * px),
         ("s16->f32 + median5 + depth (a10,a11)", lambda: svb.disparity_to_depth(disp16), 10 * px),

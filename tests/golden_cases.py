@@ -217,3 +217,8 @@ def resize_case_input(c):
 # Calibration-file path (depth_map.py:591-668, fused_depth_map.py:307-442): synthetic .pkl at this size, the
 # scaled loader at the reference's default PROCESSING_SCALE = 0.33 and two more.
 CALIB_CASE = dict(W=320, H=240, scales=(1.0, 0.5, 0.33))
+
+
+# BASELINE.json config 5 at its own size: 1080p stereo depth (D = 256) + two synthetic mono maps, normal and with
+# the right camera covered (tests/golden/make_golden_fusion_1080p.py).
+FUSION_1080P = dict(H=1080, W=1920, seed=45, min_disp=0, num_disp=256, window=5, moving=True, params={})

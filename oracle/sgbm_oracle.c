@@ -7,9 +7,11 @@
  * The arithmetic itself lives in the un-vendored third-party dependency
  * OpenCV (opencv-python-headless 4.13.0.92, modules/calib3d/src/stereosgbm.cpp);
  * this file restates its published algorithm as distilled in SURVEY.md
- * Appendix A.1-A.5.  Parity is pinned by tests/test_oracle_vs_cv2.py (live cv2
- * where importable) and by the golden vectors under tests/golden/ that were
- * produced by cv2 4.13.0 with tests/golden/make_golden.py.
+ * Appendix A.1-A.5.  Parity is pinned by the golden vectors under tests/golden/
+ * that cv2 4.13.0 produced (tests/golden/make_golden.py -> tests/test_oracle_golden.py),
+ * by the SHA-256 of cv2's output at the BASELINE sizes (make_golden_fullsize.py ->
+ * tests/test_fullsize_oracle.py: 1080p / D256 / HH, 720p / D128, 480p / D320 / 3WAY), and
+ * by live-cv2 fuzz runs in the authoring container (counts in DESIGN.md section 2).
  *
  * Written for clarity, not speed: the whole cost volume C and the aggregated
  * volume S are materialised so that the stages can be handed to the tests.

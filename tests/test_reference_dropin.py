@@ -1,6 +1,9 @@
-"""GPU: the per-frame functions of depth_map.py re-typed with `cv2.` -> `svb.` exactly as
-INTEGRATION.md section 2 prescribes, against outputs of the UNMODIFIED reference functions
-(tests/golden/golden_dropin.npz, made by tests/golden/make_golden_dropin.py from /root/reference).
+"""GPU: the per-frame functions of depth_map.py re-typed with `cv2.` -> `hot.` exactly as INTEGRATION.md section 2
+prescribes -- `hot` being the `_HotPath` alias of that section (svb where svb has the name, cv2 for everything else)
+-- against outputs of the UNMODIFIED reference functions (tests/golden/golden_dropin.npz, made by
+tests/golden/make_golden_dropin.py from /root/reference).  /root/reference does not exist on the GPU box and the
+build container has no GPU, so the functions are re-typed here; the last test monkey-patches the imported reference
+module itself and runs wherever both a GPU and /root/reference exist (skipped otherwise).
 """
 import os
 
@@ -14,6 +17,19 @@ from tests.golden_cases import DROPIN_CASE
 
 pytestmark = pytest.mark.gpu
 
+try:
+    import cv2
+except Exception:                                     # the alias then only ever resolves svb names
+    cv2 = None
+
+
+class _HotPath:                       # INTEGRATION.md section 2, verbatim: cv2 for capture/GUI, svb for the per-frame path
+    def __getattr__(self, name):
+        return getattr(svb, name) if hasattr(svb, name) else getattr(cv2, name)
+
+
+hot = _HotPath()
+
 
 @pytest.fixture(scope="module")
 def gd():
@@ -22,21 +38,21 @@ def gd():
 
 def apply_stereo_rectification(left_img, right_img, stereo_calib):
     """depth_map.py:779-834 with the binding of INTEGRATION.md."""
-    left_rectified = svb.remap(left_img, stereo_calib["left_map1"], stereo_calib["left_map2"], svb.INTER_LINEAR)
-    right_rectified = svb.remap(right_img, stereo_calib["right_map1"], stereo_calib["right_map2"], svb.INTER_LINEAR)
+    left_rectified = hot.remap(left_img, stereo_calib["left_map1"], stereo_calib["left_map2"], hot.INTER_LINEAR)
+    right_rectified = hot.remap(right_img, stereo_calib["right_map1"], stereo_calib["right_map2"], hot.INTER_LINEAR)
     return left_rectified, right_rectified
 
 
 def create_depth_map(left_img, right_img, MIN_DISP, NUM_DISP, WINDOW_SIZE, min_depth=0.3, max_depth=2.0):
     """depth_map.py:837-939 (without the colormap) with the binding of INTEGRATION.md."""
-    gray_left = svb.cvtColor(left_img, svb.COLOR_BGR2GRAY) if left_img.ndim == 3 else left_img
-    gray_right = svb.cvtColor(right_img, svb.COLOR_BGR2GRAY) if right_img.ndim == 3 else right_img
-    stereo = svb.StereoSGBM_create(
+    gray_left = hot.cvtColor(left_img, hot.COLOR_BGR2GRAY) if left_img.ndim == 3 else left_img
+    gray_right = hot.cvtColor(right_img, hot.COLOR_BGR2GRAY) if right_img.ndim == 3 else right_img
+    stereo = hot.StereoSGBM_create(
         minDisparity=MIN_DISP, numDisparities=NUM_DISP, blockSize=WINDOW_SIZE,
         P1=8 * 3 * WINDOW_SIZE ** 2, P2=32 * 3 * WINDOW_SIZE ** 2, disp12MaxDiff=1, uniquenessRatio=10,
-        speckleWindowSize=100, speckleRange=32, preFilterCap=63, mode=svb.STEREO_SGBM_MODE_SGBM_3WAY)
+        speckleWindowSize=100, speckleRange=32, preFilterCap=63, mode=hot.STEREO_SGBM_MODE_SGBM_3WAY)
     disparity = stereo.compute(gray_left, gray_right).astype(np.float32) / 16.0
-    disparity = svb.medianBlur(disparity, 5)
+    disparity = hot.medianBlur(disparity, 5)
     fx = 700
     BASELINE = 0.08
     depth = (fx * BASELINE) / (disparity + 1e-6)
@@ -79,5 +95,34 @@ def test_fused_depth_kernel_matches_reference(gd):
                                 P2=32 * 3 * ws ** 2, disp12MaxDiff=1, uniquenessRatio=10, speckleWindowSize=100,
                                 speckleRange=32, preFilterCap=63, mode=svb.STEREO_SGBM_MODE_SGBM_3WAY).compute(gl, gr)
     depth, disp = svb.disparity_to_depth(d16, fx=700.0, baseline=0.08, min_disp=minD, min_depth=0.3, max_depth=2.0)
+    assert np.array_equal(disp, gd["disparity"])
+    np.testing.assert_allclose(depth, gd["depth"], rtol=1e-4, atol=0)
+
+
+def test_hotpath_alias_resolves_svb_first_and_cv2_for_the_rest():
+    assert hot.remap is svb.remap and hot.StereoSGBM_create is svb.StereoSGBM_create and hot.resize is svb.resize
+    assert hot.STEREO_SGBM_MODE_SGBM_3WAY == 2 and hot.INTER_LINEAR == 1 and hot.COLOR_BGR2GRAY == 6
+    if cv2 is not None:                               # GUI / capture names fall through to cv2
+        assert hot.putText is cv2.putText and hot.FONT_HERSHEY_SIMPLEX == cv2.FONT_HERSHEY_SIMPLEX
+        assert hot.INTER_LINEAR == cv2.INTER_LINEAR and hot.COLOR_BGR2GRAY == cv2.COLOR_BGR2GRAY
+
+
+def test_monkeypatched_reference_module(gd, monkeypatch):
+    """The reference's own depth_map.py with its module-level `cv2` replaced by the alias."""
+    import contextlib
+    import io
+    import sys
+    if not os.path.isdir("/root/reference") or cv2 is None:
+        pytest.skip("needs /root/reference and cv2 next to the GPU")
+    monkeypatch.syspath_prepend("/root/reference")
+    with contextlib.redirect_stdout(io.StringIO()):
+        import depth_map as ref
+    monkeypatch.setattr(ref, "cv2", hot)
+    lb, rb = _pair()
+    calib = {k: gd[k] for k in ("left_map1", "left_map2", "right_map1", "right_map2")}
+    with contextlib.redirect_stdout(io.StringIO()):
+        lr, rr = ref.apply_stereo_rectification(lb, rb, calib)
+        depth, disp, _ = ref.create_depth_map(lr, rr, None)
+    assert np.array_equal(lr, gd["left_rect"]) and np.array_equal(rr, gd["right_rect"])
     assert np.array_equal(disp, gd["disparity"])
     np.testing.assert_allclose(depth, gd["depth"], rtol=1e-4, atol=0)

@@ -510,8 +510,11 @@ __global__ void k_blend(BlendArgs a, int H, int W, GaussTaps g, float* __restric
     kmin = __reduce_min_sync(0xffffffffu, kmin);
     kmax = __reduce_max_sync(0xffffffffu, kmax);
     if ((threadIdx.x & 31) == 0) {
-        if (kmin != 0xffffffffu) atomicMin(&fs[b].kmin, kmin);
-        if (kmax) atomicMax(&fs[b].kmax, kmax);
+        // min / max only ever move one way: a warp whose value cannot improve the current one (a plain L2 read, possibly
+        // stale, which is safe for a monotone target) skips the atomic -- half a million same-address atomics per call
+        // had made this kernel latency-bound (ncu: 8.7 % issue-active at 410 GB/s)
+        if (kmin != 0xffffffffu && kmin < __ldcg(&fs[b].kmin)) atomicMin(&fs[b].kmin, kmin);
+        if (kmax && kmax > __ldcg(&fs[b].kmax)) atomicMax(&fs[b].kmax, kmax);
     }
 }
 
@@ -828,8 +831,8 @@ __global__ void k_minmax_f32(const float* __restrict__ src, size_t n, FuseState*
     kmin = __reduce_min_sync(0xffffffffu, kmin);
     kmax = __reduce_max_sync(0xffffffffu, kmax);
     if ((threadIdx.x & 31) == 0) {
-        if (kmin != 0xffffffffu) atomicMin(&fs[b].kmin, kmin);
-        if (kmax) atomicMax(&fs[b].kmax, kmax);
+        if (kmin != 0xffffffffu && kmin < __ldcg(&fs[b].kmin)) atomicMin(&fs[b].kmin, kmin);
+        if (kmax && kmax > __ldcg(&fs[b].kmax)) atomicMax(&fs[b].kmax, kmax);
     }
 }
 
@@ -907,8 +910,8 @@ __global__ void __launch_bounds__(256) k_resize_bicubic(const float* __restrict_
         kmin = __reduce_min_sync(0xffffffffu, kmin);
         kmax = __reduce_max_sync(0xffffffffu, kmax);
         if ((threadIdx.x & 31) == 0) {
-            if (kmin != 0xffffffffu) atomicMin(&fs[b].kmin, kmin);
-            if (kmax) atomicMax(&fs[b].kmax, kmax);
+            if (kmin != 0xffffffffu && kmin < __ldcg(&fs[b].kmin)) atomicMin(&fs[b].kmin, kmin);
+            if (kmax && kmax > __ldcg(&fs[b].kmax)) atomicMax(&fs[b].kmax, kmax);
         }
     }
 }
@@ -981,8 +984,8 @@ __global__ void __launch_bounds__(CC_X* CC_Y) k_contrast_u8(const unsigned char*
     cmin = __reduce_min_sync(0xffffffffu, cmin);
     cmax = __reduce_max_sync(0xffffffffu, cmax);
     if ((tid & 31) == 0) {
-        atomicMin(&fs[b].kmin, cmin);
-        atomicMax(&fs[b].kmax, cmax);
+        if (cmin < __ldcg(&fs[b].kmin)) atomicMin(&fs[b].kmin, cmin);
+        if (cmax > __ldcg(&fs[b].kmax)) atomicMax(&fs[b].kmax, cmax);
     }
 }
 

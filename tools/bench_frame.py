@@ -1,5 +1,6 @@
 #!/usr/bin/env python
 """BASELINE.json configs[0]: one live frame through the depth_map.py path (640x480 BGR pair, synthetic calibration):
+calibration .pkl on disk -> load_stereo_calibration (host stereoRectify + device maps), then per frame
 remap x2 -> BGR2GRAY x2 -> StereoSGBM -> /16 -> medianBlur 5 -> depth, and reprojectImageTo3D.
 Host arrays in, host arrays out, one frame at a time: the latency the reference's camera loop sees.  Times the
 engine (cv2-shaped Python surface, the INTEGRATION.md binding) and cv2 itself on the same frame; checks the
@@ -8,8 +9,7 @@ import json, os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import stereovision_b200 as svb
-from stereovision_b200.synth import make_pair, to_bgr
-from tests.golden_cases import synth_calibration
+from stereovision_b200.synth import make_pair, to_bgr, write_calibration_pkl
 
 H, W = 480, 640
 CASES = {"script": dict(D=320, bs=7, mode=2), "c1": dict(D=64, bs=5, mode=2), "c1_sgbm": dict(D=64, bs=5, mode=0)}
@@ -39,7 +39,14 @@ def timeit(fn, n):
 
 def main():
     import cv2
-    cal = synth_calibration(W, H)
+    import tempfile
+    with tempfile.TemporaryDirectory() as tmp:               # the reference's file: output/stereo_calibration_data.pkl
+        path = os.path.join(tmp, "output", "stereo_calibration_data.pkl")
+        write_calibration_pkl(path, W, H)
+        svb.load_stereo_calibration(path)                    # warm-up (context, kernels)
+        t0 = time.perf_counter()
+        cal = svb.load_stereo_calibration(path)
+        load_ms = (time.perf_counter() - t0) * 1e3
     out = {}
     for name, c in CASES.items():
         l, r, _ = make_pair(H, W, min(c["D"], 128), seed=9)
@@ -51,7 +58,8 @@ def main():
         assert np.allclose(a[2][fin], b[2][fin], rtol=1e-4, atol=1e-5)
         out[name] = {"svb_ms_per_frame": timeit(lambda: frame(svb, lb, rb, cal, **c), 20),
                      "cv2_ms_per_frame": timeit(lambda: frame(cv2, lb, rb, cal, **c), 3), **c}
-    print(json.dumps({"workload": "depth_map.py frame path 640x480 (BASELINE configs[0])", "cv2_threads": cv2.getNumThreads(),
+    print(json.dumps({"workload": "depth_map.py frame path 640x480 (BASELINE configs[0]), calibration from a .pkl",
+                      "load_stereo_calibration_ms": load_ms, "cv2_threads": cv2.getNumThreads(),
                       "frames": out}))
 
 

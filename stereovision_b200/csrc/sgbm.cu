@@ -799,12 +799,16 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                         for (int p = 0; p < 3; ++p) {
                             if (!(MASK & (2 << p))) continue;
                             const uint32_t* src = carry_in + ((size_t)cl * 3 + p) * VW;
-                            if constexpr (NP % 4 == 0) {
-                                cp_async_vec_s<NP>(ring0_s + (p * PATHW + so + NP * lane) * 4, src + NP * lane);
-                            } else {                         // 4-byte cp.async would go through L1: copy through registers
-                                uint32_t v[NP];
-                                vec_ld<NP>(src, lane, v, LdCg());
-                                vec_st<NP>(ring0 + p * PATHW + so, lane, v);
+                            // 16-byte cp.async.cg whatever the vector width (L2 only: the carry was written by another
+                            // CTA of this launch; the 4- and 8-byte forms would cache it in L1).  A vector is VW / 4
+                            // 16-byte pieces: fewer than 32 for numDisparities <= 192, where a synchronous copy through
+                            // registers (one dependent L2 round trip per column) used to pace the whole wavefront.
+#pragma unroll
+                            for (int q = 0; q < (VW / 4 + 31) / 32; ++q) {
+                                const int piece = lane + 32 * q;
+                                if (VW / 4 % 32 == 0 || piece < VW / 4)
+                                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring0_s + (p * PATHW + so + 4 * piece) * 4),
+                                                 "l"(src + 4 * piece));
                             }
                         }
                         if (lane == 0)

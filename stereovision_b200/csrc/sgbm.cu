@@ -148,16 +148,15 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
                                                    int nimg, int ch, SgbmGeo g, uint32_t* __restrict__ ldesc,
                                                    uint32_t* __restrict__ rdesc)
 {
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
-    int y = blockIdx.y, b = blockIdx.z;
-    if (x >= g.W) return;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;     // left pixel x, and right ENTRY x (grid covers max(W, Wp))
+    const int y = blockIdx.y, b = blockIdx.z;
     const int H = g.H, W = g.W;
-    {
+    if (x < W) {
         const uint8_t* img = left + (size_t)b * H * W * g.cn + ch;
         int c0[3], c1[3];
 #pragma unroll
         for (int k = 0; k < 3; ++k) bt_channels(img, H, W, g.cn, y, min(max(x + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
-        uint32_t* rec = ldesc + ((size_t)(b * H + y) * W + x) * 8;
+        uint32_t rec[8];
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
             const int* p = c ? c1 : c0;
@@ -170,28 +169,38 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
             rec[c * 4 + 2] = pk_dup((uint32_t)u0);
             rec[c * 4 + 3] = pk_dup((uint32_t)(1 - u1));     // v - u1 = ~(-v) + (1 - u1)
         }
+        uint4* dst = reinterpret_cast<uint4*>(ldesc + ((size_t)(b * H + y) * W + x) * 8);   // 32-byte records: two 128-bit stores
+        dst[0] = make_uint4(rec[0], rec[1], rec[2], rec[3]);
+        dst[1] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
     }
-    {
+    if (x < g.Wp) {
+        // entry x of the six planes = a[x] | a[x - HALF] << 16: both halves are computed here (the second pixel's
+        // prefilter is recomputed from L1) so that every plane gets ONE coalesced 32-bit store per entry instead of two
+        // 16-bit stores at a 4-byte stride; halves whose pixel lies outside the image are 0.
         const uint8_t* img = right + (size_t)b * H * W * g.cn + ch;
-        int c0[3], c1[3];
+        uint32_t ent[6] = {0, 0, 0, 0, 0, 0};
 #pragma unroll
-        for (int k = 0; k < 3; ++k) bt_channels(img, H, W, g.cn, y, min(max(x + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
-        uint16_t* base = reinterpret_cast<uint16_t*>(rdesc + (size_t)(b * H + y) * 6 * g.Wp);
+        for (int half = 0; half < 2; ++half) {
+            const int xr = half ? x - g.HALF : x;
+            if (xr < 0 || xr >= W) continue;
+            int c0[3], c1[3];
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-            const int* p = c ? c1 : c0;
-            int v = p[1];
-            int va = x < W - 1 ? (v + p[2]) / 2 : v;
-            int vb = x > 0 ? (v + p[0]) / 2 : v;
-            int v0 = min(min(va, vb), v), v1 = max(max(va, vb), v);
-            const uint16_t ops[3] = {(uint16_t)(-v1), (uint16_t)v0, (uint16_t)(-v)};
+            for (int k = 0; k < 3; ++k) bt_channels(img, H, W, g.cn, y, min(max(xr + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
 #pragma unroll
-            for (int o = 0; o < 3; ++o) {
-                uint16_t* plane = base + (size_t)(c * 3 + o) * 2 * g.Wp;
-                plane[2 * x] = ops[o];                                   // low half of entry x
-                if (x + g.HALF < g.Wp) plane[2 * (x + g.HALF) + 1] = ops[o];   // high half of entry x + HALF
+            for (int c = 0; c < 2; ++c) {
+                const int* p = c ? c1 : c0;
+                int v = p[1];
+                int va = xr < W - 1 ? (v + p[2]) / 2 : v;
+                int vb = xr > 0 ? (v + p[0]) / 2 : v;
+                int v0 = min(min(va, vb), v), v1 = max(max(va, vb), v);
+                const uint32_t ops[3] = {(uint32_t)(-v1) & 0xffffu, (uint32_t)v0 & 0xffffu, (uint32_t)(-v) & 0xffffu};
+#pragma unroll
+                for (int o = 0; o < 3; ++o) ent[c * 3 + o] |= ops[o] << (16 * half);
             }
         }
+        uint32_t* base = rdesc + (size_t)(b * H + y) * 6 * g.Wp + x;
+#pragma unroll
+        for (int q = 0; q < 6; ++q) base[(size_t)q * g.Wp] = ent[q];
     }
 }
 
@@ -1410,7 +1419,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     for (int ch = 0; ch < g.cn; ++ch) {
     {
         ProfScope ps(h, CAT_PREFILTER, st);
-        k_prefilter<<<dim3(svb_ceil_div(g.W, 256), g.H, ns), 256, 0, st>>>(
+        k_prefilter<<<dim3(svb_ceil_div(std::max(g.W, g.Wp), 256), g.H, ns), 256, 0, st>>>(
             left + s0 * hw * g.cn, right + s0 * hw * g.cn, ns, ch, g, ldesc + s0 * hw * 8,
             rdesc + (size_t)s0 * g.H * 6 * g.Wp);
     }

@@ -53,8 +53,8 @@ def test_static_scratch_speckle_filter_matches_the_allocating_entry_point():
             free_before = torch.cuda.mem_get_info()[0]
         _lib.check(lib.svb_filter_speckles_s16_static(got.data_ptr(), B, H, W, inv, max_size, max_diff, st))
         torch.cuda.synchronize()
-        if k > 0:                                             # the call itself took no device memory
-            assert torch.cuda.mem_get_info()[0] >= free_before
+        if k > 0:                                             # the call itself took no device memory (1 MiB of slack for
+            assert torch.cuda.mem_get_info()[0] >= free_before - (1 << 20)   # whatever else shares the GPU)
         g, w = got.cpu().numpy(), want.cpu().numpy()
         assert int((w != src).sum()) > 0, "the filter removed nothing: the case does not test anything"
         assert np.array_equal(g, w), f"call {k}: {int((g != w).sum())} pixels differ from svb_filter_speckles_s16_dev"
@@ -78,3 +78,34 @@ def test_static_scratch_rejects_sizes_beyond_its_maximum():
     with pytest.raises(NotImplementedError):
         _lib.check(rc)
     assert lib.svb_filter_speckles_s16_static(None, 1, 8, 8, -16, 10, 16, st) == -1
+
+
+def test_static_scratch_call_can_be_captured_in_a_cuda_graph():
+    """The use case in one test: a cudaMalloc / cudaFree / synchronising call inside a stream capture invalidates the
+    capture, so an entry point that captures cleanly and replays correctly allocates nothing.  (The first call per
+    device, which looks the scratch address up, is made before the capture, as include/svb.h says.)"""
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    lib = _lib.lib()
+    rng = np.random.default_rng(99)
+    B, H, W, inv = 2, 120, 200, -16
+    src = _disparity_like(rng, B, H, W, inv)
+    want = torch.from_numpy(src).cuda()
+    scratch = torch.empty(2 * want.numel(), dtype=torch.int32, device="cuda")
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.check(lib.svb_filter_speckles_s16_dev(want.data_ptr(), B, H, W, inv, 60, 32, scratch.data_ptr(), st))
+    warm = torch.from_numpy(src).cuda()
+    _lib.check(lib.svb_filter_speckles_s16_static(warm.data_ptr(), B, H, W, inv, 60, 32, st))   # set-up outside the capture
+    torch.cuda.synchronize()
+    buf = torch.from_numpy(src).cuda()
+    pristine = buf.clone()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        cs = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        rc = lib.svb_filter_speckles_s16_static(buf.data_ptr(), B, H, W, inv, 60, 32, cs)
+    assert rc == 0, lib.svb_last_error()
+    for _ in range(2):                                        # two replays on fresh input
+        buf.copy_(pristine)
+        graph.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(buf, want)

@@ -72,6 +72,11 @@ int svb_sgbm_compute_cn_dev(svb_sgbm_t* h, const uint8_t* left_dev, const uint8_
                             int B, int H, int W, int cn, int16_t* disp_dev, void* stream);
 int svb_sgbm_compute_cn_host(svb_sgbm_t* h, const uint8_t* left_host, const uint8_t* right_host,
                              int B, int H, int W, int cn, int16_t* disp_host);
+/* The device call on a PITCHED input batch: row_pitch / img_pitch are the bytes between consecutive rows / images of
+ * both inputs (a crop of a larger frame, a padded capture buffer; img_pitch 0 = H * row_pitch, both 0 = dense).
+ * What cv2 does with a non-contiguous Mat view; the output stays dense. */
+int svb_sgbm_compute_pitched_dev(svb_sgbm_t* h, const uint8_t* left_dev, const uint8_t* right_dev, int B, int H, int W,
+                                 int cn, ptrdiff_t row_pitch, ptrdiff_t img_pitch, int16_t* disp_dev, void* stream);
 /* Test hook: copy internal stages of the LAST compute (chunk 0, image 0) to host buffers
  * (any may be NULL).  C,S: u16 [rows,width1,D] (3WAY: kept rows only are meaningful),
  * raw: s16 [H,W] disparity before median/speckle.  The aggregated volume S only exists in

@@ -48,6 +48,8 @@ SIGNATURES = {
     "svb_sgbm_compute_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "svb_sgbm_compute_cn_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "svb_sgbm_compute_cn_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "svb_sgbm_compute_pitched_dev": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, ctypes.c_ssize_t,
+                                             ctypes.c_ssize_t, c_void_p, c_void_p]),
     "svb_sgbm_set_debug": (c_int, [c_void_p, c_int]),
     "svb_sgbm_debug_stages": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "svb_sgbm_last_launches": (c_int, [c_void_p]),

@@ -109,6 +109,7 @@ struct SgbmGeo {
     int cn;                    // image channels (1, or 3: interleaved colour -- cv2 sums the BT cost of every channel)
     int Wp;                    // words per plane row of the right descriptors
     unsigned thMul;            // floor(2^32 / (100 - uniq)) + 1: exact division of the uniqueness threshold (0: divisor <= 1)
+    long long rowPitch, imgPitch;   // bytes between image rows / between images of the INPUT batch (dense: W*cn, H*W*cn)
 };
 
 __host__ __device__ inline void job_rows(const SgbmGeo& g, int n, int& ys, int& ye, int& keep)
@@ -132,12 +133,12 @@ __host__ __device__ inline void job_rows(const SgbmGeo& g, int n, int& ys, int& 
 // i.e. the operands of disparity index w (low) and w + HALF (high) for left pixel x = xr + w.
 // ------------------------------------------------------------------------------------------
 // img points at channel ch of pixel (0,0); cn = pixel stride in bytes
-__device__ __forceinline__ void bt_channels(const uint8_t* img, int H, int W, int cn, int y, int x, int ftzero,
-                                            int& p0, int& p1)
+__device__ __forceinline__ void bt_channels(const uint8_t* img, long long pitch, int H, int W, int cn, int y, int x,
+                                            int ftzero, int& p0, int& p1)
 {
     if (x <= 0 || x >= W - 1) { p0 = p1 = ftzero; return; }
     int yn = y > 0 ? y - 1 : y, ys = y < H - 1 ? y + 1 : y;
-    const uint8_t *r = img + (size_t)y * W * cn, *rn = img + (size_t)yn * W * cn, *rs = img + (size_t)ys * W * cn;
+    const uint8_t *r = img + y * pitch, *rn = img + yn * pitch, *rs = img + ys * pitch;
     const int e = (x + 1) * cn, w = (x - 1) * cn;
     int g = 2 * ((int)r[e] - r[w]) + ((int)rn[e] - rn[w]) + ((int)rs[e] - rs[w]);
     g = max(-ftzero, min(ftzero, g));
@@ -152,10 +153,10 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
     const int y = blockIdx.y, b = blockIdx.z;
     const int H = g.H, W = g.W;
     if (x < W) {
-        const uint8_t* img = left + (size_t)b * H * W * g.cn + ch;
+        const uint8_t* img = left + b * g.imgPitch + ch;
         int c0[3], c1[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) bt_channels(img, H, W, g.cn, y, min(max(x + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
+        for (int k = 0; k < 3; ++k) bt_channels(img, g.rowPitch, H, W, g.cn, y, min(max(x + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
         uint32_t rec[8];
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
@@ -177,7 +178,7 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
         // entry x of the six planes = a[x] | a[x - HALF] << 16: both halves are computed here (the second pixel's
         // prefilter is recomputed from L1) so that every plane gets ONE coalesced 32-bit store per entry instead of two
         // 16-bit stores at a 4-byte stride; halves whose pixel lies outside the image are 0.
-        const uint8_t* img = right + (size_t)b * H * W * g.cn + ch;
+        const uint8_t* img = right + b * g.imgPitch + ch;
         uint32_t ent[6] = {0, 0, 0, 0, 0, 0};
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
@@ -185,7 +186,7 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
             if (xr < 0 || xr >= W) continue;
             int c0[3], c1[3];
 #pragma unroll
-            for (int k = 0; k < 3; ++k) bt_channels(img, H, W, g.cn, y, min(max(xr + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
+            for (int k = 0; k < 3; ++k) bt_channels(img, g.rowPitch, H, W, g.cn, y, min(max(xr + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 const int* p = c ? c1 : c0;
@@ -1238,6 +1239,7 @@ static int make_geo(const svb_sgbm_params& p, int H, int W, int cn, SgbmGeo& g)
         g.rowsMax = std::max(g.rowsMax, ye - ys);
     }
     g.Wp = ((W + g.HALF + 3) & ~3) + 4;
+    g.rowPitch = (long long)W * cn; g.imgPitch = (long long)H * W * cn;
     return SVB_OK;
 }
 
@@ -1420,7 +1422,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     {
         ProfScope ps(h, CAT_PREFILTER, st);
         k_prefilter<<<dim3(svb_ceil_div(std::max(g.W, g.Wp), 256), g.H, ns), 256, 0, st>>>(
-            left + s0 * hw * g.cn, right + s0 * hw * g.cn, ns, ch, g, ldesc + s0 * hw * 8,
+            left + s0 * g.imgPitch, right + s0 * g.imgPitch, ns, ch, g, ldesc + s0 * hw * 8,
             rdesc + (size_t)s0 * g.H * 6 * g.Wp);
     }
     SVB_LAUNCH_CHECK(); h->launches++;
@@ -1557,7 +1559,8 @@ extern "C" int svb_sgbm_compute_dev(svb_sgbm_t* h, const uint8_t* left, const ui
 }
 
 static int sgbm_compute_impl(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
-                             int B, int H, int W, int cn, int16_t* disp, void* stream, const HostPipe* hp);
+                             int B, int H, int W, int cn, int16_t* disp, void* stream, const HostPipe* hp,
+                             long long row_pitch = 0, long long img_pitch = 0);
 
 // the last compute has finished: look at the flag it copied out, clear a tripped one on both sides
 static int take_sweep_err(svb_sgbm* h)
@@ -1576,15 +1579,33 @@ extern "C" int svb_sgbm_compute_cn_dev(svb_sgbm_t* h, const uint8_t* left, const
 {
     return sgbm_compute_impl(h, left, right, B, H, W, cn, disp, stream, nullptr);
 }
+// The same on a pitched input batch: row_pitch / img_pitch in BYTES between rows / images of both
+// inputs (a crop of a larger frame, a padded capture buffer); 0 = dense.  The output stays dense.
+extern "C" int svb_sgbm_compute_pitched_dev(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right, int B, int H, int W,
+                                            int cn, ptrdiff_t row_pitch, ptrdiff_t img_pitch, int16_t* disp, void* stream)
+{
+    if (row_pitch < 0 || img_pitch < 0) { svb_set_error("negative pitch"); return SVB_ERR_PARAM; }
+    return sgbm_compute_impl(h, left, right, B, H, W, cn, disp, stream, nullptr, (long long)row_pitch, (long long)img_pitch);
+}
 
 static int sgbm_compute_impl(svb_sgbm_t* h, const uint8_t* left, const uint8_t* right,
-                             int B, int H, int W, int cn, int16_t* disp, void* stream, const HostPipe* hp)
+                             int B, int H, int W, int cn, int16_t* disp, void* stream, const HostPipe* hp,
+                             long long row_pitch, long long img_pitch)
 {
     if (!h || !left || !right || !disp) { svb_set_error("null argument"); return SVB_ERR_PARAM; }
     if (B <= 0) { svb_set_error("batch must be >= 1"); return SVB_ERR_PARAM; }
     SgbmGeo g;
     int rc = make_geo(h->prm, H, W, cn, g);
     if (rc != SVB_OK) return rc;
+    if (row_pitch || img_pitch) {                            // pitched input batch (bytes); 0 = dense
+        const long long rp = row_pitch ? row_pitch : (long long)W * cn, ip = img_pitch ? img_pitch : rp * H;
+        if (rp < (long long)W * cn || (B > 1 && ip < rp * (H - 1) + (long long)W * cn)) {
+            svb_set_error("pitches too small: row_pitch %lld < W*cn or images overlap (img_pitch %lld)", rp, ip);
+            return SVB_ERR_PARAM;
+        }
+        g.rowPitch = rp;
+        g.imgPitch = ip;
+    }
     if (!h->num_sms) {
         int dev = 0;
         SVB_CUDA(cudaGetDevice(&dev));
@@ -1622,7 +1643,7 @@ static int sgbm_compute_impl(svb_sgbm_t* h, const uint8_t* left, const uint8_t* 
         const int n = std::min(nb, B - b0);
         const size_t off = (size_t)b0 * H * W;
         switch (g.NP) {
-#define CASE(N) case N: rc = run_chunk<N>(h, g, L, left + off * cn, right + off * cn, n, disp + off, st, hp, b0); break;
+#define CASE(N) case N: rc = run_chunk<N>(h, g, L, left + b0 * g.imgPitch, right + b0 * g.imgPitch, n, disp + off, st, hp, b0); break;
             CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
 #undef CASE
             default: svb_set_error("bad NP"); rc = SVB_ERR_UNSUPPORTED;

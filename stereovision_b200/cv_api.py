@@ -165,6 +165,29 @@ def _check_pair(left, right):
             raise ValueError("images must be 8-bit (CV_8U)")
 
 
+def _row_pitches(left, right, cn):
+    """(row_pitch, img_pitch) in bytes when both tensors are non-contiguous views whose pixels are contiguous within a
+    row and whose strides agree (a crop of a larger frame, a padded buffer) -- what svb_sgbm_compute_pitched_dev
+    takes without a copy; None for dense tensors or anything else (those go through .contiguous())."""
+    if left.is_contiguous() and right.is_contiguous():
+        return None
+    if tuple(left.stride()) != tuple(right.stride()):
+        return None
+    st = list(left.stride())
+    if cn == 3:
+        if st[-1] != 1 or st[-2] != 3:
+            return None
+        st = st[:-1]
+        st[-1] = 1
+    if st[-1] != 1 or st[-2] < left.shape[-1 if cn == 1 else -2] * cn:
+        return None
+    row = int(st[-2])
+    img = int(st[0]) if len(st) == 3 else 0
+    if len(st) == 3 and left.shape[0] > 1 and img < row * (int(left.shape[1]) - 1) + int(left.shape[2]) * cn:
+        return None
+    return row, img
+
+
 class _Matcher:
     _kind = None
 
@@ -193,9 +216,14 @@ class _Matcher:
             dev = _ensure_device(left.device.index)
             h = _handle(self._kind, self._params(), dev)
             self._pre_compute(h)
-            l, r = left.contiguous(), right.contiguous()
             out = torch.empty(oshape, dtype=torch.int16, device=left.device)
-            _lib.check(dev_fn(h, l.data_ptr(), r.data_ptr(), B, H, W, out.data_ptr(), _stream_ptr()))
+            pitches = _row_pitches(left, right, cn) if self._kind == "sgbm" else None
+            if pitches is not None:                           # a crop / padded view: no copy, pitched C-ABI call
+                _lib.check(L.svb_sgbm_compute_pitched_dev(h, left.data_ptr(), right.data_ptr(), B, H, W, cn, pitches[0],
+                                                          pitches[1], out.data_ptr(), _stream_ptr()))
+            else:
+                l, r = left.contiguous(), right.contiguous()
+                _lib.check(dev_fn(h, l.data_ptr(), r.data_ptr(), B, H, W, out.data_ptr(), _stream_ptr()))
             self._last = h
             return out
         dev = _ensure_device()

@@ -170,3 +170,43 @@ def test_callers_current_device_is_restored():
     assert torch.cuda.current_device() == 0
     for o in (out, out1, out0, out1b):
         assert np.array_equal(o.cpu().numpy(), ref)
+
+
+def test_pitched_inputs_without_a_copy():
+    """SURVEY 8(b) row_pitch / img_pitch: a crop of a larger frame (rows not adjacent in memory, images not adjacent in
+    the batch) goes through svb_sgbm_compute_pitched_dev as it is and gives the bytes of the dense copy; gray and BGR,
+    the raw C ABI and the cv2-shaped surface (which used to .contiguous() every view)."""
+    torch = _torch()
+    lib = _lib.lib()
+    H, W, B = 60, 200, 3
+    big_l = torch.randint(0, 256, (B, H + 13, W + 24), dtype=torch.uint8, device="cuda")
+    big_r = torch.randint(0, 256, (B, H + 13, W + 24), dtype=torch.uint8, device="cuda")
+    for b in range(B):
+        l, r, _ = make_pair(H, W, 64, seed=400 + b)
+        big_l[b, 5:5 + H, 8:8 + W] = torch.from_numpy(l).cuda()
+        big_r[b, 5:5 + H, 8:8 + W] = torch.from_numpy(r).cuda()
+    vl, vr = big_l[:, 5:5 + H, 8:8 + W], big_r[:, 5:5 + H, 8:8 + W]
+    assert not vl.is_contiguous()
+    m = svb.StereoSGBM_create(**PRM)
+    want = m.compute(vl.contiguous(), vr.contiguous())
+    got = m.compute(vl, vr)                                    # the pitched path
+    assert torch.equal(got, want)
+    assert np.array_equal(got[1].cpu().numpy(), oracle.sgbm_compute(vl[1].cpu().numpy(), vr[1].cpu().numpy(), **PRM))
+    # one image of the batch, every second image (img_pitch = 2 frames)
+    assert torch.equal(m.compute(vl[2], vr[2]), want[2])
+    assert torch.equal(m.compute(vl[::2], vr[::2]), want[::2])
+    # raw C ABI, pitches in bytes; too small a pitch is rejected
+    h = ctypes.c_void_p()
+    _lib.check(lib.svb_sgbm_create(ctypes.byref(_lib.SgbmParams(*[PRM[k] for k in ORDER])), ctypes.byref(h)))
+    out = torch.empty((B, H, W), dtype=torch.int16, device="cuda")
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    rc = lib.svb_sgbm_compute_pitched_dev(h, vl.data_ptr(), vr.data_ptr(), B, H, W, 1, vl.stride(1), vl.stride(0), out.data_ptr(), st)
+    assert rc == 0 and lib.svb_sgbm_check(h) == 0 and torch.equal(out, want)
+    assert lib.svb_sgbm_compute_pitched_dev(h, vl.data_ptr(), vr.data_ptr(), B, H, W, 1, W - 1, 0, out.data_ptr(), st) == -1
+    lib.svb_sgbm_destroy(h)
+    # BGR crop
+    cl = torch.randint(0, 256, (H + 4, W + 6, 3), dtype=torch.uint8, device="cuda")
+    cr = torch.roll(cl, -5, dims=1)
+    wl, wr = cl[2:2 + H, 3:3 + W], cr[2:2 + H, 3:3 + W]
+    prm3 = dict(PRM, P1=600, P2=2400)
+    assert torch.equal(svb.StereoSGBM_create(**prm3).compute(wl, wr), svb.StereoSGBM_create(**prm3).compute(wl.contiguous(), wr.contiguous()))

@@ -31,6 +31,7 @@ from .display import (  # noqa: F401
 from .calib import (  # noqa: F401
     stereoRectify, Rodrigues, load_stereo_calibration, load_stereo_calibration_with_scaling, CALIB_ZERO_DISPARITY,
 )
+from . import frame  # noqa: F401  (frame.apply_stereo_rectification / frame.create_depth_map: one upload, one download)
 from ._lib import SvbError  # noqa: F401
 
 __version__ = "0.1.0"

@@ -126,3 +126,40 @@ def test_monkeypatched_reference_module(gd, monkeypatch):
     assert np.array_equal(lr, gd["left_rect"]) and np.array_equal(rr, gd["right_rect"])
     assert np.array_equal(disp, gd["disparity"])
     np.testing.assert_allclose(depth, gd["depth"], rtol=1e-4, atol=0)
+
+
+def test_frame_level_functions_match_the_reference(gd):
+    """svb.frame.apply_stereo_rectification / create_depth_map: the reference's two per-frame functions with one upload
+    and one download per frame (NumPy in / NumPy out, and tensors in / tensors out with device-resident maps)."""
+    import torch
+    minD, D, ws = (int(v) for v in gd["params"])
+    lb, rb = _pair()
+    H, W = lb.shape[:2]
+    calib = {k: gd[k] for k in ("left_map1", "left_map2", "right_map1", "right_map2")}
+    calib["img_size"] = (W, H)
+    lr, rr = svb.frame.apply_stereo_rectification(lb, rb, calib)
+    assert np.array_equal(lr, gd["left_rect"]) and np.array_equal(rr, gd["right_rect"])
+    depth, disp, cmap = svb.frame.create_depth_map(lr, rr, None, min_disp=minD, num_disp=D, window_size=ws)
+    assert depth.dtype == np.float32 and np.array_equal(disp, gd["disparity"])
+    np.testing.assert_allclose(depth, gd["depth"], rtol=1e-4, atol=0)
+    assert cmap.shape == (H, W, 3) and np.array_equal(cmap, svb.depth_colormap(disp, 700, 0.08, 0.3, 2.0))
+    # a float64 fx from the calibration dict -> float64 depth like the reference (depth_map.py:917)
+    c64 = {"calibration_data": {"camera_matrix": np.array([[700.0, 0, 0], [0, 700.0, 0], [0, 0, 1.0]])}}
+    depth64, _, _ = svb.frame.create_depth_map(lr, rr, c64, min_disp=minD, num_disp=D, window_size=ws)
+    assert depth64.dtype == np.float64 and np.allclose(depth64, gd["depth"], rtol=1e-4)
+    # device-resident maps and frames: nothing touches the host
+    dcal = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in calib.items() if k != "img_size"}
+    dcal["img_size"] = (W, H)
+    tl, tr = svb.frame.apply_stereo_rectification(torch.from_numpy(lb).cuda(), torch.from_numpy(rb).cuda(), dcal, as_tensor=True)
+    td, tdisp, tc = svb.frame.create_depth_map(tl, tr, None, min_disp=minD, num_disp=D, window_size=ws, as_tensor=True)
+    assert tdisp.is_cuda and np.array_equal(tdisp.cpu().numpy(), gd["disparity"]) and np.array_equal(tc.cpu().numpy(), cmap)
+    # a frame of another size is resized to the calibration size first (depth_map.py:805-811)
+    big = svb.resize(lb, (W + 40, H + 30))
+    l2, _ = svb.frame.apply_stereo_rectification(big, big, calib)
+    assert l2.shape == lr.shape
+    # the reference's error behaviour: zeros, never an exception (depth_map.py:941-946)
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        z, zd, zc = svb.frame.create_depth_map(lr[:, :100], rr[:, :100], None, min_disp=minD, num_disp=D, window_size=ws)
+    assert z.shape == (H, 100) and not z.any() and not zd.any() and zc.shape == (H, 100, 3)

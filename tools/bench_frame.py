@@ -47,6 +47,8 @@ def main():
         t0 = time.perf_counter()
         cal = svb.load_stereo_calibration(path)
         load_ms = (time.perf_counter() - t0) * 1e3
+    import torch
+    dcal = {k: (torch.from_numpy(v).cuda() if isinstance(v, np.ndarray) and k.endswith(("map1", "map2")) else v) for k, v in cal.items()}
     out = {}
     for name, c in CASES.items():
         l, r, _ = make_pair(H, W, min(c["D"], 128), seed=9)
@@ -56,7 +58,11 @@ def main():
         assert np.array_equal(a[0], b[0]), name
         fin = np.isfinite(b[2])
         assert np.allclose(a[2][fin], b[2][fin], rtol=1e-4, atol=1e-5)
+        def frame_api():                                     # svb.frame: one upload, one download (device-resident maps)
+            lr, rr = svb.frame.apply_stereo_rectification(lb, rb, dcal, as_tensor=True)
+            return svb.frame.create_depth_map(lr, rr, None, min_disp=0, num_disp=c["D"], window_size=c["bs"])
         out[name] = {"svb_ms_per_frame": timeit(lambda: frame(svb, lb, rb, cal, **c), 20),
+                     "svb_frame_api_ms_per_frame": timeit(frame_api, 20) if c["mode"] == 2 else None,
                      "cv2_ms_per_frame": timeit(lambda: frame(cv2, lb, rb, cal, **c), 3), **c}
     print(json.dumps({"workload": "depth_map.py frame path 640x480 (BASELINE configs[0]), calibration from a .pkl",
                       "load_stereo_calibration_ms": load_ms, "cv2_threads": cv2.getNumThreads(),

@@ -159,6 +159,16 @@ def bind_to_gpu_numa_node(torch, local):
     return None
 
 
+def config_of(args, wl, B):
+    """The `config` object of BOTH arms (the reference arm runs on this arm's configuration; what differs -- the CPU
+    sample -- is described in its cpu_baseline.sample)."""
+    cfg = {"workload": args.workload, "H": wl["H"], "W": wl["W"], "numDisparities": wl["D"], "mode": wl["mode"],
+           "blockSize": 5, "pairs_per_gpu_per_step": B, "l2_policy": "inputs+volumes >> L2 (126 MB)"}
+    if args.scaling == "strong":
+        cfg["total_pairs"] = args.total_pairs
+    return cfg
+
+
 def cpu_reference_run(wl, npairs, threads):
     """The reference's own CPU implementation of the path: cv2.StereoSGBM.compute
     (depth_map.py:894-909) over `npairs` distinct pairs, one pair per worker thread (cv2
@@ -214,10 +224,9 @@ def run_reference_arm(args, wl, rank, world):
     line = {
         "impl": "reference", "metric": "stereo_pairs_per_sec", "value": pairs_s, "unit": unit,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16", "data": "synthetic",
-        "config": {"workload": args.workload, "H": wl["H"], "W": wl["W"], "numDisparities": wl["D"],
-                   "mode": wl["mode"], "pairs_per_step": sample,
-                   "gdisp_evals_per_s": pairs_s * wl["H"] * wl["W"] * wl["D"] / 1e9},
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "u16", "data": "synthetic",
+        "config": config_of(args, wl, args.batch or wl["batch"]),
+        "gdisp_evals_per_s": pairs_s * wl["H"] * wl["W"] * wl["D"] / 1e9,
         "cpu_baseline": {"value": pairs_s, "unit": unit, "cores": used, "kind": kind,
                          "sample": f"{sample} distinct pairs per step, one pair per thread, cv2.setNumThreads(1)"},
         "e2e": {"value": pairs_s, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -501,9 +510,8 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "u16",
             "data": "synthetic",
-            "config": {"workload": args.workload, "H": H, "W": W, "numDisparities": D, "mode": wl["mode"],
-                       "blockSize": 5, "pairs_per_gpu_per_step": B, "l2_policy": "inputs+volumes >> L2 (126 MB)", "host_numa_cpus": numa,
-                       "gdisp_evals_per_s": value * H * W * D / 1e9},
+            "config": config_of(args, wl, B), "host_numa_cpus": numa,
+            "gdisp_evals_per_s": value * H * W * D / 1e9,
             "e2e": {"value": e2e, "unit": "pairs/s", "h2d_bytes_per_step": 2 * H * W * (pairs // args.steps),
                     "d2h_bytes_per_step": 2 * H * W * (pairs // args.steps)},
             "gpu_launches": launches * world,
@@ -514,8 +522,7 @@ def main():
         }
         line.update(extras)
         if args.scaling == "strong":
-            line["config"]["total_pairs"] = args.total_pairs
-            line["config"]["strong_scaling_note"] = ("fixed total work: fewer pairs per launch leave the wavefront's ramp-up and "
+            line["strong_scaling_note"] = ("fixed total work: fewer pairs per launch leave the wavefront's ramp-up and "
                                                      "ramp-down (one band per SM at a time) a larger share of each sweep")
         if world == 1 and not args.no_cpu_baseline:
             cores = len(os.sched_getaffinity(0))

@@ -61,6 +61,9 @@ __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 2 ? 24 : (NP ==
 #ifndef SW_SEAM_FMA
 #define SW_SEAM_FMA 0          // 1: seam fix-ups of the disparity neighbours as IMAD / IMAD.HI instead of PRMTs (measured: 14.1 -> 15.8 ms, the multiply sits on the recurrence's critical path)
 #endif
+#ifndef SW_HLAST
+#define SW_HLAST 1             // 0: k_sweep for every last sweep (A/B timing of k_hlast)
+#endif
 #ifndef SW_SLEEP_NS
 #define SW_SLEEP_NS 40         // back-off while a row waits for its neighbour's progress counter
 #endif
@@ -1125,6 +1128,150 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// k_hlast<G>: the last sweep of MODE_SGBM / SGBM_3WAY (one horizontal path + S = S1 + L + WTA, rows independent of
+// each other) for numDisparities 64 and 128, where k_sweep's warp-per-pixel layout leaves three quarters / half of
+// every packed instruction's lanes' worth of work on the table: a warp carries G = 4 / 2 ROWS at once, each in a group
+// of WD = 32 / G lanes with 4 words (8 disparities) per lane -- the instruction stream of the 256-disparity case
+// serving G pixels.  No rings, no flags, no helper warps: neighbours by group-relative shuffles, reductions by xor
+// butterflies inside the group, C and S1 straight from global memory two columns ahead in registers.
+// Same arithmetic as k_sweep<NP, VAR >= 1, MASK 1, LAST> (the tests compare both against the oracle).
+// ------------------------------------------------------------------------------------------
+#define HL_WARPS 8
+template <int G>
+__global__ void __launch_bounds__(HL_WARPS * 32) k_hlast(const SweepArgs a, const SgbmGeo g)
+{
+    constexpr int NP = 4 / G, VW = 32 * NP, WD = 32 / G, HF = 32 * NP;     // HF = g.HALF
+    extern __shared__ __align__(16) uint32_t smem[];                          // [HL_WARPS][G][VW]: S of the current column
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, gl = lane & (WD - 1), grp = lane / WD;
+    const int w1 = g.width1, dir = a.dir;
+    const uint32_t P1P1 = pk_dup(g.P1), P2P2 = pk_dup(g.P2);
+    const uint32_t one = a.njobs > 0, himask = 0u - (one << 16);
+    const uint32_t sc_s = smem_u32(smem + ((size_t)warp * G + grp) * VW);    // this group's scratch vector
+    const int blocksPerJob = (g.rowsMax + G - 1) / G;
+    const long long units = (long long)a.njobs * blocksPerJob;
+    const uint32_t selPrev = gl == 0 ? 0x1054u : 0x3210u, selNext = gl == WD - 1 ? 0x5432u : 0x3210u;
+    auto bmin = [&](uint32_t v) {                                            // min over the group, in every lane of it
+#pragma unroll
+        for (int o = WD / 2; o; o >>= 1) v = min(v, __shfl_xor_sync(FULLMASK, v, o));
+        return v;
+    };
+    for (long long u = (long long)blockIdx.x * HL_WARPS + warp; u < units; u += (long long)gridDim.x * HL_WARPS) {
+        const int job = (int)(u / blocksPerJob), rb = (int)(u % blocksPerJob);
+        int ys, ye, keep;
+        job_rows(g, job % g.nstripes, ys, ye, keep);
+        const int nrows = ye - ys;
+        const int row0 = rb * G + grp;
+        const bool valid = row0 < nrows && ys + row0 >= keep;               // 3WAY overlap rows: nothing depends on them
+        if (!__any_sync(FULLMASK, valid)) continue;
+        const int row = min(row0, nrows - 1);                               // an idle group re-reads a valid row, stores nothing
+        const int y = ys + row, b = job / g.nstripes;
+        const size_t rowbase = (((size_t)job * g.rowsMax + row) * w1) * VW;
+        const int x0 = dir > 0 ? 0 : w1 - 1;
+        const ptrdiff_t cstep = (ptrdiff_t)dir * VW;
+        const uint4* pC = reinterpret_cast<const uint4*>(a.C + rowbase + (size_t)x0 * VW + 4 * gl);
+        const uint4* pS = reinterpret_cast<const uint4*>(a.S + rowbase + (size_t)x0 * VW + 4 * gl);
+        const ptrdiff_t st4 = cstep / 4;
+        // two columns ahead in registers; the loop is unrolled by two so that each buffer is refilled in place (no
+        // register rotation), pointers advance incrementally and stop at the row's last column
+        uint4 cb[2], sb[2];
+        cb[0] = __ldg(pC); sb[0] = __ldg(pS);
+        const uint4 *qC = pC + (w1 > 1 ? st4 : 0), *qS = pS + (w1 > 1 ? st4 : 0);
+        cb[1] = __ldg(qC); sb[1] = __ldg(qS);
+        int left = w1 - 2;                                   // columns beyond the two in flight
+        uint32_t Lh[4] = {0, 0, 0, 0};
+        uint32_t minh2 = 0;
+        uint32_t rkey = 0, rcnt = 0, rtap = 0;
+        const size_t rowpix = ((size_t)b * g.H + y) * g.W;
+        auto column = [&](const int i, uint4& cbuf, uint4& sbuf) {
+            const uint32_t C[4] = {cbuf.x, cbuf.y, cbuf.z, cbuf.w};
+            uint32_t S[4] = {sbuf.x, sbuf.y, sbuf.z, sbuf.w};
+            if (left > 0) { qC += st4; qS += st4; }
+            --left;
+            cbuf = __ldg(qC); sbuf = __ldg(qS);                // column i + 2 (or the last one again)
+            // ---- horizontal path (A.3), predecessor = the previous column
+            uint32_t prev = __shfl_sync(FULLMASK, Lh[3], (gl + WD - 1) & (WD - 1), WD);
+            uint32_t next = __shfl_sync(FULLMASK, Lh[0], (gl + 1) & (WD - 1), WD);
+            prev = __byte_perm(prev, WALL2, selPrev);        // group lane 0: (lo = wall, hi = last lane's lo); others: unchanged
+            next = __byte_perm(next, WALL2, selNext);        // last group lane: (lo = lane 0's hi, hi = wall)
+            const uint32_t mqP2 = minh2 + P2P2;
+            uint32_t up = prev, mloc = 0xffffffffu;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t dn = k + 1 < 4 ? Lh[k + 1] : next;
+                uint32_t t = add_fma(pk_min(up, dn), one, P1P1);
+                t = pk_min(pk_min(t, Lh[k]), mqP2);
+                const uint32_t L = C[k] + t - minh2;
+                up = Lh[k];
+                Lh[k] = L;
+                mloc = pk_min(mloc, L);
+            }
+            minh2 = bmin(pk_min(mloc, __byte_perm(mloc, 0, 0x1032)));        // equal halves: u32 min = packed min
+#pragma unroll
+            for (int k = 0; k < 4; ++k) S[k] = pk_addmin(S[k], Lh[k], WALL2);
+            // ---- WTA (A.4), as in k_sweep: keys (S << 16 | d), lowest d wins ties
+            uint32_t kmin = 0xffffffffu;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t klo = S[k] * 65536u + (uint32_t)k;
+                const uint32_t khi = (S[k] & himask) | (uint32_t)(HF + k);
+                kmin = min(kmin, min(klo, khi));
+            }
+            kmin = bmin(kmin + (uint32_t)(4 * gl));
+            const int th = wta_threshold<true>(g, (int)(kmin >> 16));
+            const uint32_t th2 = pk_dup((uint32_t)th);
+            uint32_t lt[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) lt[k] = __vsub2(S[k], th2);
+            uint32_t cnt = (uint32_t)__popc((__byte_perm(lt[0], lt[1], 0x7351) & 0x80808080u) |
+                                            ((__byte_perm(lt[2], lt[3], 0x7351) & 0x80808080u) >> 1));
+#pragma unroll
+            for (int o = WD / 2; o; o >>= 1) cnt += __shfl_xor_sync(FULLMASK, cnt, o);
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(sc_s + 16 * gl), "r"(S[0]), "r"(S[1]), "r"(S[2]), "r"(S[3]));
+            __syncwarp();
+            const int best = (int)(kmin & 0xffffu);
+            auto tap = [&](int d) {
+                uint32_t v;
+                const uint32_t ad = sc_s + 4u * (uint32_t)d - (d >= HF ? (uint32_t)(4 * HF - 2) : 0u);
+                asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(ad));
+                return v;
+            };
+            const uint32_t tm1 = tap(max(best - 1, 0)), tp1 = tap(min(best + 1, g.D - 1));
+            const uint32_t sm1v = best > 0 ? tm1 : 0u, sp1v = best < g.D - 1 ? tp1 : 0u;
+            if (gl == (i & (WD - 1))) { rkey = kmin; rcnt = cnt; rtap = sm1v | (sp1v << 16); }
+            if ((i & (WD - 1)) == WD - 1 || i == w1 - 1) {
+                // WD columns of this row decided at once: lane j of the group finishes column (i & ~(WD-1)) + j
+                const int ci = (i & ~(WD - 1)) + gl;
+                if (ci <= i && valid) {
+                    const int xc = dir > 0 ? ci : w1 - 1 - ci;
+                    const int x = xc + g.minX1;
+                    const int minS = (int)(rkey >> 16), bst = (int)(rkey & 0xffffu);
+                    const int thr = wta_threshold<true>(g, minS);
+                    const int t1 = (int)(rtap & 0xffffu), t2 = (int)(rtap >> 16);
+                    int out = g.INV;
+                    if (minS < (int)WALL) {
+                        const int excl = (minS < thr) + (bst > 0 && t1 < thr) + (bst < g.D - 1 && t2 < thr);
+                        if ((int)rcnt <= excl) {
+                            int dsub = bst * 16;
+                            if (bst > 0 && bst < g.D - 1) {
+                                const int den = max(t1 + t2 - 2 * minS, 1);
+                                dsub += ((t1 - t2) * 16 + den) / (2 * den);
+                            }
+                            out = dsub + g.minD * 16;
+                            atomicMin(a.key + rowpix + (x - bst - g.minD), ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+                        }
+                    }
+                    a.raw[rowpix + x] = (int16_t)out;
+                }
+            }
+            __syncwarp();                                    // the scratch vector is rewritten by the next column
+        };
+        int i = 0;
+        for (; i + 1 < w1; i += 2) { column(i, cb[0], sb[0]); column(i + 1, cb[1], sb[1]); }
+        if (i < w1) column(i, cb[0], sb[0]);
+    }
+}
+
 // LR consistency (A.4): invalidate iff both roundings of d disagree with the right-view map.
 __global__ void __launch_bounds__(256) k_lrcheck(int16_t* __restrict__ raw, const uint32_t* __restrict__ disp2key,
                                                  SgbmGeo g, int nimg)
@@ -1514,6 +1661,21 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         ProfScope ps(h, CAT_SWEEP2, st);
         a.dir = -1;
         if (g.mode != SVB_MODE_HH && g.mode != SVB_MODE_HH4) set_band_rows(rows_free);
+        // numDisparities 64 / 128 with a horizontal-only last sweep: several rows per warp (k_hlast); not for the debug
+        // S dump, nor for cv2's 3WAY tie rule without a uniqueness test (k_sweep has that special case)
+        const bool hlast = SW_HLAST && (NP == 1 || NP == 2) && var >= 1 && g.mode != SVB_MODE_HH && g.mode != SVB_MODE_HH4 &&
+                           !h->debug && !(g.mode == SVB_MODE_SGBM_3WAY && g.uniq == 0);
+        if (hlast) {
+            constexpr int G = NP == 1 ? 4 : 2;               // (only instantiated meaningfully for NP <= 2)
+            const long long units = (long long)njobs * ((g.rowsMax + G - 1) / G);
+            const size_t smem = (size_t)HL_WARPS * 128 * 4;
+            int per_sm = 0;
+            SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_hlast<G>, HL_WARPS * 32, smem));
+            const int grid = (int)std::min<long long>((units + HL_WARPS - 1) / HL_WARPS, (long long)h->num_sms * std::max(per_sm, 1));
+            k_hlast<G><<<grid, HL_WARPS * 32, smem, st>>>(a, g);
+            SVB_LAUNCH_CHECK();
+            rc = SVB_OK;
+        } else
         rc = g.mode == SVB_MODE_HH    ? launch_sweep_var<NP, 15, true>(h, a, g, var, st)
              : g.mode == SVB_MODE_HH4 ? launch_sweep_var<NP, 5, true>(h, a, g, var, st)
                                       : launch_sweep_var<NP, 1, true>(h, a, g, var, st);

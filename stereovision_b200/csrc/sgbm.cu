@@ -1138,10 +1138,13 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
 // Same arithmetic as k_sweep<NP, VAR >= 1, MASK 1, LAST> (the tests compare both against the oracle).
 // ------------------------------------------------------------------------------------------
 #define HL_WARPS 8
-template <int G>
+// G rows per warp in groups of WD = 32 / G lanes, WPL = NP * G words per lane.  <1,4> and <2,2> are the multi-row forms
+// (4 words per lane); <NP,1> is one row per warp for any width (what k_sweep<NP, ., 1, true> computes, without its
+// ring / ticket / staging bookkeeping and with several CTAs per SM).
+template <int NP, int G>
 __global__ void __launch_bounds__(HL_WARPS * 32) k_hlast(const SweepArgs a, const SgbmGeo g)
 {
-    constexpr int NP = 4 / G, VW = 32 * NP, WD = 32 / G, HF = 32 * NP;     // HF = g.HALF
+    constexpr int VW = 32 * NP, WD = 32 / G, HF = 32 * NP, WPL = NP * G;     // HF = g.HALF
     extern __shared__ __align__(16) uint32_t smem[];                          // [HL_WARPS][G][VW]: S of the current column
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, gl = lane & (WD - 1), grp = lane / WD;
     const int w1 = g.width1, dir = a.dir;
@@ -1151,10 +1154,21 @@ __global__ void __launch_bounds__(HL_WARPS * 32) k_hlast(const SweepArgs a, cons
     const int blocksPerJob = (g.rowsMax + G - 1) / G;
     const long long units = (long long)a.njobs * blocksPerJob;
     const uint32_t selPrev = gl == 0 ? 0x1054u : 0x3210u, selNext = gl == WD - 1 ? 0x5432u : 0x3210u;
-    auto bmin = [&](uint32_t v) {                                            // min over the group, in every lane of it
+    auto gmin = [&](uint32_t v) {                                            // min over the group, in every lane of it
+        if constexpr (G == 1) return __reduce_min_sync(FULLMASK, v);
+        else {
 #pragma unroll
-        for (int o = WD / 2; o; o >>= 1) v = min(v, __shfl_xor_sync(FULLMASK, v, o));
-        return v;
+            for (int o = WD / 2; o; o >>= 1) v = min(v, __shfl_xor_sync(FULLMASK, v, o));
+            return v;
+        }
+    };
+    auto gsum = [&](uint32_t v) {
+        if constexpr (G == 1) return __reduce_add_sync(FULLMASK, v);
+        else {
+#pragma unroll
+            for (int o = WD / 2; o; o >>= 1) v += __shfl_xor_sync(FULLMASK, v, o);
+            return v;
+        }
     };
     for (long long u = (long long)blockIdx.x * HL_WARPS + warp; u < units; u += (long long)gridDim.x * HL_WARPS) {
         const int job = (int)(u / blocksPerJob), rb = (int)(u % blocksPerJob);
@@ -1169,36 +1183,38 @@ __global__ void __launch_bounds__(HL_WARPS * 32) k_hlast(const SweepArgs a, cons
         const size_t rowbase = (((size_t)job * g.rowsMax + row) * w1) * VW;
         const int x0 = dir > 0 ? 0 : w1 - 1;
         const ptrdiff_t cstep = (ptrdiff_t)dir * VW;
-        const uint4* pC = reinterpret_cast<const uint4*>(a.C + rowbase + (size_t)x0 * VW + 4 * gl);
-        const uint4* pS = reinterpret_cast<const uint4*>(a.S + rowbase + (size_t)x0 * VW + 4 * gl);
-        const ptrdiff_t st4 = cstep / 4;
+        const uint32_t* pC = a.C + rowbase + (size_t)x0 * VW;
+        const uint32_t* pS = a.S + rowbase + (size_t)x0 * VW;
         // two columns ahead in registers; the loop is unrolled by two so that each buffer is refilled in place (no
         // register rotation), pointers advance incrementally and stop at the row's last column
-        uint4 cb[2], sb[2];
-        cb[0] = __ldg(pC); sb[0] = __ldg(pS);
-        const uint4 *qC = pC + (w1 > 1 ? st4 : 0), *qS = pS + (w1 > 1 ? st4 : 0);
-        cb[1] = __ldg(qC); sb[1] = __ldg(qS);
+        uint32_t cb[2][WPL], sb[2][WPL];
+        vec_ld<WPL>(pC, gl, cb[0], LdNc()); vec_ld<WPL>(pS, gl, sb[0], LdNc());
+        const uint32_t *qC = pC + (w1 > 1 ? cstep : 0), *qS = pS + (w1 > 1 ? cstep : 0);
+        vec_ld<WPL>(qC, gl, cb[1], LdNc()); vec_ld<WPL>(qS, gl, sb[1], LdNc());
         int left = w1 - 2;                                   // columns beyond the two in flight
-        uint32_t Lh[4] = {0, 0, 0, 0};
+        uint32_t Lh[WPL];
+#pragma unroll
+        for (int k = 0; k < WPL; ++k) Lh[k] = 0;
         uint32_t minh2 = 0;
         uint32_t rkey = 0, rcnt = 0, rtap = 0;
         const size_t rowpix = ((size_t)b * g.H + y) * g.W;
-        auto column = [&](const int i, uint4& cbuf, uint4& sbuf) {
-            const uint32_t C[4] = {cbuf.x, cbuf.y, cbuf.z, cbuf.w};
-            uint32_t S[4] = {sbuf.x, sbuf.y, sbuf.z, sbuf.w};
-            if (left > 0) { qC += st4; qS += st4; }
+        auto column = [&](const int i, uint32_t (&cbuf)[WPL], uint32_t (&sbuf)[WPL]) {
+            uint32_t C[WPL], S[WPL];
+#pragma unroll
+            for (int k = 0; k < WPL; ++k) { C[k] = cbuf[k]; S[k] = sbuf[k]; }
+            if (left > 0) { qC += cstep; qS += cstep; }
             --left;
-            cbuf = __ldg(qC); sbuf = __ldg(qS);                // column i + 2 (or the last one again)
+            vec_ld<WPL>(qC, gl, cbuf, LdNc()); vec_ld<WPL>(qS, gl, sbuf, LdNc());     // column i + 2 (or the last one again)
             // ---- horizontal path (A.3), predecessor = the previous column
-            uint32_t prev = __shfl_sync(FULLMASK, Lh[3], (gl + WD - 1) & (WD - 1), WD);
+            uint32_t prev = __shfl_sync(FULLMASK, Lh[WPL - 1], (gl + WD - 1) & (WD - 1), WD);
             uint32_t next = __shfl_sync(FULLMASK, Lh[0], (gl + 1) & (WD - 1), WD);
             prev = __byte_perm(prev, WALL2, selPrev);        // group lane 0: (lo = wall, hi = last lane's lo); others: unchanged
             next = __byte_perm(next, WALL2, selNext);        // last group lane: (lo = lane 0's hi, hi = wall)
             const uint32_t mqP2 = minh2 + P2P2;
             uint32_t up = prev, mloc = 0xffffffffu;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint32_t dn = k + 1 < 4 ? Lh[k + 1] : next;
+            for (int k = 0; k < WPL; ++k) {
+                const uint32_t dn = k + 1 < WPL ? Lh[k + 1] : next;
                 uint32_t t = add_fma(pk_min(up, dn), one, P1P1);
                 t = pk_min(pk_min(t, Lh[k]), mqP2);
                 const uint32_t L = C[k] + t - minh2;
@@ -1206,28 +1222,34 @@ __global__ void __launch_bounds__(HL_WARPS * 32) k_hlast(const SweepArgs a, cons
                 Lh[k] = L;
                 mloc = pk_min(mloc, L);
             }
-            minh2 = bmin(pk_min(mloc, __byte_perm(mloc, 0, 0x1032)));        // equal halves: u32 min = packed min
+            minh2 = gmin(pk_min(mloc, __byte_perm(mloc, 0, 0x1032)));        // equal halves: u32 min = packed min
 #pragma unroll
-            for (int k = 0; k < 4; ++k) S[k] = pk_addmin(S[k], Lh[k], WALL2);
+            for (int k = 0; k < WPL; ++k) S[k] = pk_addmin(S[k], Lh[k], WALL2);
             // ---- WTA (A.4), as in k_sweep: keys (S << 16 | d), lowest d wins ties
             uint32_t kmin = 0xffffffffu;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
+            for (int k = 0; k < WPL; ++k) {
                 const uint32_t klo = S[k] * 65536u + (uint32_t)k;
                 const uint32_t khi = (S[k] & himask) | (uint32_t)(HF + k);
                 kmin = min(kmin, min(klo, khi));
             }
-            kmin = bmin(kmin + (uint32_t)(4 * gl));
+            kmin = gmin(kmin + (uint32_t)(WPL * gl));
             const int th = wta_threshold<true>(g, (int)(kmin >> 16));
             const uint32_t th2 = pk_dup((uint32_t)th);
-            uint32_t lt[4];
+            uint32_t lt[WPL];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) lt[k] = __vsub2(S[k], th2);
-            uint32_t cnt = (uint32_t)__popc((__byte_perm(lt[0], lt[1], 0x7351) & 0x80808080u) |
-                                            ((__byte_perm(lt[2], lt[3], 0x7351) & 0x80808080u) >> 1));
+            for (int k = 0; k < WPL; ++k) lt[k] = __vsub2(S[k], th2);
+            uint32_t bits = 0;
+            if constexpr (WPL == 4) {
+                bits = (__byte_perm(lt[0], lt[1], 0x7351) & 0x80808080u) | ((__byte_perm(lt[2], lt[3], 0x7351) & 0x80808080u) >> 1);
+            } else if constexpr (WPL == 2) {
+                bits = __byte_perm(lt[0], lt[1], 0x7351) & 0x80808080u;
+            } else {
 #pragma unroll
-            for (int o = WD / 2; o; o >>= 1) cnt += __shfl_xor_sync(FULLMASK, cnt, o);
-            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(sc_s + 16 * gl), "r"(S[0]), "r"(S[1]), "r"(S[2]), "r"(S[3]));
+                for (int k = 0; k < WPL; ++k) bits |= (lt[k] >> k) & (0x80008000u >> k);
+            }
+            const uint32_t cnt = gsum((uint32_t)__popc(bits));
+            sts_vec<WPL, 0>(sc_s + 4 * WPL * gl, S);
             __syncwarp();
             const int best = (int)(kmin & 0xffffu);
             auto tap = [&](int d) {
@@ -1663,16 +1685,16 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         if (g.mode != SVB_MODE_HH && g.mode != SVB_MODE_HH4) set_band_rows(rows_free);
         // numDisparities 64 / 128 with a horizontal-only last sweep: several rows per warp (k_hlast); not for the debug
         // S dump, nor for cv2's 3WAY tie rule without a uniqueness test (k_sweep has that special case)
-        const bool hlast = SW_HLAST && (NP == 1 || NP == 2) && var >= 1 && g.mode != SVB_MODE_HH && g.mode != SVB_MODE_HH4 &&
-                           !h->debug && !(g.mode == SVB_MODE_SGBM_3WAY && g.uniq == 0);
+        const bool hlast = SW_HLAST && var >= 1 && g.mode != SVB_MODE_HH && g.mode != SVB_MODE_HH4 && !h->debug &&
+                           !(g.mode == SVB_MODE_SGBM_3WAY && g.uniq == 0);
         if (hlast) {
-            constexpr int G = NP == 1 ? 4 : 2;               // (only instantiated meaningfully for NP <= 2)
+            constexpr int G = NP == 1 ? 4 : (NP == 2 ? 2 : 1);
             const long long units = (long long)njobs * ((g.rowsMax + G - 1) / G);
-            const size_t smem = (size_t)HL_WARPS * 128 * 4;
+            const size_t smem = (size_t)HL_WARPS * G * 32 * NP * 4;
             int per_sm = 0;
-            SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_hlast<G>, HL_WARPS * 32, smem));
+            SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_hlast<NP, G>, HL_WARPS * 32, smem));
             const int grid = (int)std::min<long long>((units + HL_WARPS - 1) / HL_WARPS, (long long)h->num_sms * std::max(per_sm, 1));
-            k_hlast<G><<<grid, HL_WARPS * 32, smem, st>>>(a, g);
+            k_hlast<NP, G><<<grid, HL_WARPS * 32, smem, st>>>(a, g);
             SVB_LAUNCH_CHECK();
             rc = SVB_OK;
         } else

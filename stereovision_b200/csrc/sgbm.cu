@@ -61,6 +61,9 @@ __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 2 ? 24 : (NP ==
 #ifndef SW_SEAM_FMA
 #define SW_SEAM_FMA 0          // 1: seam fix-ups of the disparity neighbours as IMAD / IMAD.HI instead of PRMTs (measured: 14.1 -> 15.8 ms, the multiply sits on the recurrence's critical path)
 #endif
+#ifndef SW_UNROLL2
+#define SW_UNROLL2 0           // 1: the rows' column loop unrolled by two (experiment)
+#endif
 #ifndef SW_HLAST
 #define SW_HLAST 1             // 0: k_sweep for every last sweep (A/B timing of k_hlast)
 #endif
@@ -304,6 +307,9 @@ __device__ __forceinline__ void vec_st(uint32_t* p, int lane, const uint32_t (&v
 // mapping (lane l <-> words NP*l..) so that shared and global accesses are 128-bit.
 // ------------------------------------------------------------------------------------------
 #define CK_WARPS 16
+#ifndef CK_BUDGET_KB
+#define CK_BUDGET_KB 200       // shared memory per CTA (experiment knob: 109 = two CTAs per SM at numDisparities 256 / blockSize 5)
+#endif
 #define CK_PC 32               // pixel-cost columns per strip (2 per warp)
 // staged entries per plane: the disparity window of the strip + 8 so that the window can start on a
 // 16-byte boundary (TMA needs the inner coordinate's byte offset 16-byte aligned -- measured, tools/tma_test.cu)
@@ -928,6 +934,9 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
         const int* done_pred = warp > 0 ? &s_done[warp - 1] : s_load;
         const int* done_succ = &s_done[warp + 1];
 
+#if SW_UNROLL2
+#pragma unroll 2
+#endif
         for (int i = 0; i < nloop; ++i) {
             // column i + 1 of the row above is only needed by the diagonal-from-ahead path: without it (3WAY, HH4) a row
             // follows the row above one column behind instead of two (a single frame's dependent chain gets shorter)
@@ -966,7 +975,7 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
                 minh2 = sgm_step<NP, FULL>(Lh, C, minh2, P1P1, P2P2, lane, padm, one);
 #pragma unroll
                 for (int k = 0; k < NP; ++k) {
-                    if (FAST) sum[k] = SW_FMA_ADDS ? add_fma(Lh[k], one, sum[k]) : sum[k] + Lh[k];
+                    if (FAST) sum[k] = Lh[k];                 // the first term of the sum
                     else S[k] = pk_addmin(S[k], Lh[k], WALL2);
                 }
             }
@@ -1604,7 +1613,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         ca.job0 = s0 * g.nstripes;
         const int njobs = ns * g.nstripes;                   // jobs of this launch
         const size_t fixed = ((size_t)2 * ck_nblk(NP) * ck_blkw(NP) + 2 * CK_PC * 8 + (size_t)2 * CK_PC * VW) * 4;
-        const size_t budget = 200 * 1024;
+        const size_t budget = (size_t)CK_BUDGET_KB * 1024;
         int OC = CK_PC - 2 * g.r;
         while (OC > 1 && fixed + (size_t)OC * bs * VW * 4 > budget) --OC;
         if (OC < 1 || fixed + (size_t)OC * bs * VW * 4 > budget) {

@@ -45,6 +45,15 @@ int svb_version(void);
 /* Select + initialise the CUDA device for the calling thread (cudaSetDevice). */
 int svb_init(int device);
 int svb_device_count(void);
+/* Copies between PAGEABLE host arrays and device memory for the cv2-shaped calls that take NumPy arrays the way the
+ * reference's call sites pass them (depth_map.py:815-826, 909; fused_depth_map.py:480-491).  Replaces the implicit
+ * host<->device traffic of handing such an array to a device library: a few host threads move the data through two
+ * pinned staging chunks while the DMA engine moves the previous chunk (a plain cudaMemcpy from pageable memory is a
+ * single-threaded staged copy in the driver).  h2d returns once the host array has been read (the DMA of the last
+ * chunk may still be in flight on `stream`); d2h returns when dst_host is complete.  Pinned or registered host
+ * memory is copied with one cudaMemcpyAsync.  One staging area per process: calls serialise. */
+int svb_copy_h2d(void* dst_dev, const void* src_host, size_t bytes, void* stream);
+int svb_copy_d2h(void* dst_host, const void* src_dev, size_t bytes, void* stream);
 
 /* ---- cv2.StereoSGBM_create(...)  (depth_map.py:894-906, fused_depth_map.py:988-1000) */
 typedef struct {

@@ -40,6 +40,8 @@ SIGNATURES = {
     "svb_version": (c_int, []),
     "svb_init": (c_int, [c_int]),
     "svb_device_count": (c_int, []),
+    "svb_copy_h2d": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
+    "svb_copy_d2h": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "svb_sgbm_create": (c_int, [ctypes.POINTER(SgbmParams), ctypes.POINTER(c_void_p)]),
     "svb_sgbm_destroy": (None, [c_void_p]),
     "svb_sgbm_workspace_bytes": (c_size_t, [c_void_p, c_int, c_int, c_int]),

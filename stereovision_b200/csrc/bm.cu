@@ -13,6 +13,9 @@
 #include "svb_common.cuh"
 #include <algorithm>
 #include <new>
+#include <thread>
+#include <vector>
+#include <string.h>
 
 struct BmGeo {
     int H, W, D, NP, minD, bs, r, cap, tex, uniq, FILTERED;
@@ -420,7 +423,8 @@ struct svb_bm {
     // *_host pipeline: upload of sub-batch i+1 and download of sub-batch i-1 overlap the kernels of sub-batch i
     // (every BM kernel is per image, so sub-batches cost nothing on the device)
     cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
-    cudaEvent_t ev_in[4] = {}, ev_done[4] = {};
+    cudaEvent_t ev_in[4] = {}, ev_done[4] = {}, ev_mark[4] = {};
+    SvbPinBuf pin_in, pin_out;      // pinned staging when the caller's host buffers are pageable (NumPy arrays)
     // successive computes of one handle share its workspace: a compute that arrives on another stream waits here
     cudaEvent_t ev_last = nullptr;
 };
@@ -485,12 +489,14 @@ extern "C" void svb_bm_destroy(svb_bm_t* h)
     for (int i = 0; i < 4; ++i) {
         if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]);
         if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
+        if (h->ev_mark[i]) cudaEventDestroy(h->ev_mark[i]);
     }
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_run) cudaStreamDestroy(h->s_run);
     if (h->s_out) cudaStreamDestroy(h->s_out);
     if (h->ev_last) cudaEventDestroy(h->ev_last);
     h->ws.release(); h->stage_in.release(); h->stage_out.release();
+    h->pin_in.release(); h->pin_out.release();
     delete h;
 }
 extern "C" int svb_bm_last_launches(const svb_bm_t* h) { return h ? h->launches : 0; }
@@ -628,13 +634,42 @@ extern "C" int svb_bm_compute_host(svb_bm_t* h, const uint8_t* left, const uint8
         for (int i = 0; i < 4; ++i) {
             SVB_CUDA(cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming));
             SVB_CUDA(cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+            SVB_CUDA(cudaEventCreateWithFlags(&h->ev_mark[i], cudaEventDisableTiming));
         }
     }
     const int nsub = std::min(B, 4), per = (B + nsub - 1) / nsub;
     const size_t hw = (size_t)H * W;
+    // Pageable caller buffers (NumPy arrays) of a batch: staged through pinned memory by the host pool, image by image
+    // on the way in and per downloaded sub-range on the way out (see svb_sgbm_compute_cn_host)
+    const bool staged = B > 1 && 4 * n >= ((size_t)8 << 20) && svb_host_pageable(left) && svb_host_pageable(right) &&
+                        svb_host_pageable(disp);
+    std::vector<std::atomic<int>> flags(staged ? B : 0);
+    SvbTaskGroup gin, gout;
+    int16_t* user_out = disp;
+    if (staged) {
+        rc = h->pin_in.reserve(2 * n);
+        if (rc != SVB_OK) return rc;
+        rc = h->pin_out.reserve(2 * n);
+        if (rc != SVB_OK) return rc;
+        uint8_t* pl = (uint8_t*)h->pin_in.p;
+        uint8_t* pr = pl + n;
+        for (auto& f : flags) f.store(0, std::memory_order_relaxed);
+        const uint8_t *ul = left, *ur = right;
+        for (int b = 0; b < B; ++b)
+            svb_pool_submit(&gin, [=, &flags] {
+                memcpy(pl + b * hw, ul + b * hw, hw);
+                memcpy(pr + b * hw, ur + b * hw, hw);
+                flags[b].store(1, std::memory_order_release);
+            });
+        left = pl; right = pr; disp = (int16_t*)h->pin_out.p;
+    }
+    struct Waiter { SvbTaskGroup *a, *b; ~Waiter() { svb_pool_wait(a); svb_pool_wait(b); } } waiter{&gin, &gout};   // on every return path
     int launches = 0, i = 0;
     for (int b0 = 0; b0 < B; b0 += per, ++i) {
         const int nb = std::min(per, B - b0);
+        if (staged)
+            for (int b = b0; b < b0 + nb; ++b)
+                while (!flags[b].load(std::memory_order_acquire)) std::this_thread::yield();
         SVB_CUDA(cudaMemcpyAsync(dl + b0 * hw, left + b0 * hw, nb * hw, cudaMemcpyHostToDevice, h->s_in));
         SVB_CUDA(cudaMemcpyAsync(dr + b0 * hw, right + b0 * hw, nb * hw, cudaMemcpyHostToDevice, h->s_in));
         SVB_CUDA(cudaEventRecord(h->ev_in[i], h->s_in));
@@ -645,6 +680,21 @@ extern "C" int svb_bm_compute_host(svb_bm_t* h, const uint8_t* left, const uint8
         SVB_CUDA(cudaEventRecord(h->ev_done[i], h->s_run));
         SVB_CUDA(cudaStreamWaitEvent(h->s_out, h->ev_done[i], 0));
         SVB_CUDA(cudaMemcpyAsync(disp + b0 * hw, dout + b0 * hw, nb * hw * 2, cudaMemcpyDeviceToHost, h->s_out));
+        if (staged) SVB_CUDA(cudaEventRecord(h->ev_mark[i], h->s_out));
+    }
+    if (staged) {
+        const int parts = svb_pool_threads();
+        i = 0;
+        for (int b0 = 0; b0 < B; b0 += per, ++i) {
+            const int nb = std::min(per, B - b0);
+            SVB_CUDA(cudaEventSynchronize(h->ev_mark[i]));
+            const size_t bytes = (size_t)nb * hw * 2, chunk = (bytes / parts + 4095) & ~(size_t)4095;
+            const char* src = (const char*)(disp + b0 * hw);
+            char* dst = (char*)(user_out + b0 * hw);
+            for (size_t o = 0; o < bytes; o += chunk)
+                svb_pool_submit(&gout, [=] { memcpy(dst + o, src + o, std::min(chunk, bytes - o)); });
+        }
+        svb_pool_wait(&gout);
     }
     h->launches = launches;
     SVB_CUDA(cudaStreamSynchronize(h->s_out));

@@ -134,6 +134,114 @@ __global__ void __launch_bounds__(256) k_median5_f32(const void* __restrict__ sr
     }
 }
 
+// The same selection for the s16 disparity, TWO horizontally adjacent pixels per compare-exchange: the median commutes
+// with the monotone map s16 -> float(s16) / 16 (depth_map.py:909-912 convert first, the result is the same float), so
+// the order statistics are taken on packed s16x2 words (one VIMNMX.S16x2 per min / max of two pixels) and only the
+// four medians of a thread's 2 x 2 output block are converted.  Halves the selection network's instructions per pixel.
+struct s16x2 { uint32_t v; };
+template <> __device__ __forceinline__ void cex<s16x2>(s16x2& a, s16x2& b)
+{
+    const uint32_t lo = __vmins2(a.v, b.v), hi = __vmaxs2(a.v, b.v);
+    a.v = lo; b.v = hi;
+}
+template <int DEPTH>
+__global__ void __launch_bounds__(256) k_median5_s16x2(const int16_t* __restrict__ src, int H, int W,
+                                                       float* __restrict__ dst, void* __restrict__ depth_,
+                                                       double fxB64, float min_disp, double min_depth64, double max_depth64)
+{
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x), y0 = 2 * blockIdx.y;
+    if (x >= W) return;
+    const size_t img = (size_t)blockIdx.z * H * W;
+    int xx[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) xx[i] = min(max(x + i - 2, 0), W - 1);
+    // window row `row` of the pixel pair (x, x + 1): word i = (column x + i - 2, column x + i - 1), replicate border
+    // (interior pairs of a 4-byte aligned row: three 32-bit loads and two permutes instead of six 16-bit loads)
+    const bool interior = x >= 2 && x + 3 < W;
+    auto ldrow = [&](int row, s16x2* o) {
+        const size_t ro = img + (size_t)min(max(row, 0), H - 1) * W;
+        const unsigned short* r = reinterpret_cast<const unsigned short*>(src) + ro;
+        if (interior && !(reinterpret_cast<uintptr_t>(r + x) & 3)) {
+            const uint32_t* q = reinterpret_cast<const uint32_t*>(r + x - 2);
+            const uint32_t a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+            o[0].v = a; o[1].v = __byte_perm(a, b, 0x5432); o[2].v = b; o[3].v = __byte_perm(b, c, 0x5432); o[4].v = c;
+        } else {
+            uint32_t p[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) p[i] = __ldg(r + xx[i]);
+#pragma unroll
+            for (int i = 0; i < 5; ++i) o[i].v = p[i] | (p[i + 1] << 16);
+        }
+    };
+    s16x2 v[14];
+    {
+        s16x2 c[20];                                         // rows y0 - 1 .. y0 + 2: in both windows
+#pragma unroll
+        for (int j = 0; j < 4; ++j) ldrow(y0 - 1 + j, c + 5 * j);
+#pragma unroll
+        for (int i = 0; i < 14; ++i) v[i] = c[i];
+        minmax<14>(v); v[0] = c[14];
+        minmax<13>(v); v[0] = c[15];
+        minmax<12>(v); v[0] = c[16];
+        minmax<11>(v); v[0] = c[17];
+        minmax<10>(v); v[0] = c[18];
+        minmax<9>(v); v[0] = c[19];
+        minmax<8>(v);                                        // survivors: v[1..6]
+    }
+    const float fxB = (float)fxB64, min_depth = (float)min_depth64, max_depth = (float)max_depth64;
+#pragma unroll
+    for (int o2 = 0; o2 < 2; ++o2) {
+        const int y = y0 + o2;
+        if (y >= H) break;
+        s16x2 e[5], w[14];
+        ldrow(o2 ? y0 + 3 : y0 - 2, e);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) w[i] = v[1 + i];
+        w[6] = e[0];
+        minmax<7>(w); w[0] = e[1];
+        minmax<6>(w); w[0] = e[2];
+        minmax<5>(w); w[0] = e[3];
+        minmax<4>(w); w[0] = e[4];
+        minmax<3>(w);
+        float dd[2], zf[2];
+        double zd[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int d16 = h ? (int)w[1].v >> 16 : (int)(int16_t)(w[1].v & 0xffffu);
+            const float d = (float)d16 * 0.0625f;            // exact
+            dd[h] = d;
+            if (DEPTH == 1) {
+                // NumPy float32 semantics of depth_map.py:926-933
+                const float z = __fdiv_rn(fxB, __fadd_rn(d, 1e-6f));
+                const float zc = fminf(fmaxf(z, min_depth), max_depth);
+                const bool valid = (d > min_disp) && (zc >= min_depth) && (zc <= max_depth);
+                zf[h] = valid ? zc : 0.f;
+            }
+            if (DEPTH == 2) {
+                const double z = __ddiv_rn(fxB64, (double)__fadd_rn(d, 1e-6f));
+                const double zc = fmin(fmax(z, min_depth64), max_depth64);
+                zd[h] = (d > min_disp) ? zc : 0.0;
+            }
+        }
+        const size_t o = img + (size_t)y * W + x;
+        const bool al = !(reinterpret_cast<uintptr_t>(dst + o) & 7) &&
+                        (DEPTH == 0 || !(reinterpret_cast<uintptr_t>(depth_) + o * (DEPTH == 2 ? 8 : 4) & (DEPTH == 2 ? 15 : 7)));
+        if (x + 1 < W && al) {                               // both pixels, 8- / 16-byte aligned: one store each
+            *reinterpret_cast<float2*>(dst + o) = make_float2(dd[0], dd[1]);
+            if (DEPTH == 1) *reinterpret_cast<float2*>((float*)depth_ + o) = make_float2(zf[0], zf[1]);
+            if (DEPTH == 2) *reinterpret_cast<double2*>((double*)depth_ + o) = make_double2(zd[0], zd[1]);
+        } else {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (x + h >= W) break;
+                dst[o + h] = dd[h];
+                if (DEPTH == 1) ((float*)depth_)[o + h] = zf[h];
+                if (DEPTH == 2) ((double*)depth_)[o + h] = zd[h];
+            }
+        }
+    }
+}
+
 extern "C" int svb_median3_s16_dev(const int16_t* src, int B, int H, int W, int16_t* dst, void* stream)
 {
     if (!src || !dst || B <= 0 || H <= 0 || W <= 0) { svb_set_error("median3: bad argument"); return SVB_ERR_PARAM; }
@@ -159,8 +267,8 @@ extern "C" int svb_disp_to_depth_dev(const int16_t* disp16, int B, int H, int W,
         svb_set_error("disp_to_depth: bad argument"); return SVB_ERR_PARAM;
     }
     // Python computes fx*BASELINE in double, NumPy then casts the scalar to float32
-    k_median5_f32<true, 1><<<dim3(svb_ceil_div(W, 256), (H + 1) / 2, B), 256, 0, (cudaStream_t)stream>>>(
-        disp16, H, W, disparity, depth, fx * baseline, (float)min_disp, min_depth, max_depth);
+    k_median5_s16x2<1><<<dim3(svb_ceil_div(W, 512), (H + 1) / 2, B), 256, 0, (cudaStream_t)stream>>>(
+        disp16, H, W, disparity, (void*)depth, fx * baseline, (float)min_disp, min_depth, max_depth);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
@@ -172,8 +280,8 @@ extern "C" int svb_disp_to_depth_f64_dev(const int16_t* disp16, int B, int H, in
     if (!disp16 || !disparity || !depth || B <= 0 || H <= 0 || W <= 0) {
         svb_set_error("disp_to_depth_f64: bad argument"); return SVB_ERR_PARAM;
     }
-    k_median5_f32<true, 2><<<dim3(svb_ceil_div(W, 256), (H + 1) / 2, B), 256, 0, (cudaStream_t)stream>>>(
-        disp16, H, W, disparity, depth, fx * baseline, (float)min_disp, min_depth, max_depth);
+    k_median5_s16x2<2><<<dim3(svb_ceil_div(W, 512), (H + 1) / 2, B), 256, 0, (cudaStream_t)stream>>>(
+        disp16, H, W, disparity, (void*)depth, fx * baseline, (float)min_disp, min_depth, max_depth);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

@@ -29,6 +29,8 @@
 // per-band progress counters (release/acquire).  Bands are handed out by an atomic ticket in
 // dependency order, so a waiting CTA only ever waits on a CTA that is already running.
 #include "svb_common.cuh"
+#include <thread>
+#include <string.h>
 #include <algorithm>
 #include <type_traits>
 #include <new>
@@ -1343,6 +1345,8 @@ struct svb_sgbm {
     size_t ws_limit = 0;            // 0: 60 % of the free device memory at first use
     SvbBuf ws;
     SvbBuf stage_in, stage_out;     // device staging for the *_host entry point
+    SvbPinBuf pin_in, pin_out;      // pinned staging when the caller's host buffers are pageable (NumPy arrays)
+    std::vector<cudaEvent_t> ev_mark;   // one per downloaded sub-range of such a call
     // *_host pipeline: H2D of sub-batch i+1 and D2H of sub-batch i-1 overlap the kernels of sub-batch i
     cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
     std::vector<cudaEvent_t> ev_in, ev_done;
@@ -1486,7 +1490,9 @@ extern "C" void svb_sgbm_destroy(svb_sgbm_t* h)
     if (h->ev_last) cudaEventDestroy(h->ev_last);
     if (h->d_err) cudaFree(h->d_err);
     if (h->h_err) cudaFreeHost(h->h_err);
+    for (auto& e : h->ev_mark) cudaEventDestroy(e);
     h->ws.release(); h->stage_in.release(); h->stage_out.release();
+    h->pin_in.release(); h->pin_out.release();
     delete h;
 }
 extern "C" size_t svb_sgbm_workspace_bytes(const svb_sgbm_t* h, int B, int H, int W)
@@ -1563,6 +1569,11 @@ struct HostPipe {
     int16_t* hout;                     // host disparities of the whole batch
     size_t pin, pout;                  // bytes per image in, elements per image out
     int nsub;                          // sub-ranges per chunk
+    // pageable caller buffers: hl / hr / hout are pinned staging; staged[i] turns 1 once image i of both inputs has
+    // been copied there by the host pool, marks collects (event after the download, first image, count)
+    std::atomic<int>* staged = nullptr;
+    struct Mark { cudaEvent_t ev; int first, count; };
+    std::vector<Mark>* marks = nullptr;
 };
 
 template <int NP>
@@ -1586,6 +1597,9 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     for (int s0 = 0; s0 < nb; s0 += per) {
     const int ns = std::min(per, nb - s0);
     if (hp) {                                               // upload this sub-range while the previous one computes
+        if (hp->staged)
+            for (int i = base + s0; i < base + s0 + ns; ++i)
+                while (!hp->staged[i].load(std::memory_order_acquire)) std::this_thread::yield();
         uint8_t* dl = const_cast<uint8_t*>(left) + s0 * hp->pin;
         uint8_t* dr = const_cast<uint8_t*>(right) + s0 * hp->pin;
         SVB_CUDA(cudaMemcpyAsync(dl, hp->hl + (base + s0) * hp->pin, ns * hp->pin, cudaMemcpyHostToDevice, h->s_in));
@@ -1739,6 +1753,16 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
             SVB_CUDA(cudaStreamWaitEvent(h->s_out, h->ev_done[evi], 0));
             SVB_CUDA(cudaMemcpyAsync(hp->hout + (base + s0) * hp->pout, disp + s0 * hw, ns * hw * 2,
                                      cudaMemcpyDeviceToHost, h->s_out));
+            if (hp->marks) {
+                const size_t k = hp->marks->size();
+                while (h->ev_mark.size() <= k) {
+                    cudaEvent_t e;
+                    SVB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                    h->ev_mark.push_back(e);
+                }
+                SVB_CUDA(cudaEventRecord(h->ev_mark[k], h->s_out));
+                hp->marks->push_back({h->ev_mark[k], base + s0, ns});
+            }
             ++evi;
         }
     }
@@ -1907,8 +1931,58 @@ extern "C" int svb_sgbm_compute_cn_host(svb_sgbm_t* h, const uint8_t* left, cons
     hp.hl = left; hp.hr = right; hp.hout = disp;
     hp.pin = (size_t)H * W * cn; hp.pout = (size_t)H * W;
     hp.nsub = SVB_HOST_PIPE;
+    // Pageable caller buffers (the reference's call site: NumPy arrays, depth_map.py:909) of a batch: the host pool
+    // copies them image by image into pinned staging while the first sub-ranges already upload and compute, and copies
+    // each downloaded sub-range out while the later ones are still on the device.
+    const bool staged = B > 1 && 2 * nin + 2 * n >= ((size_t)8 << 20) && svb_host_pageable(left) && svb_host_pageable(right) &&
+                        svb_host_pageable(disp);
+    if (!staged) {
+        rc = sgbm_compute_impl(h, dl, dr, B, H, W, cn, dout, h->s_run, &hp);
+        if (rc != SVB_OK) { cudaDeviceSynchronize(); return rc; }
+        SVB_CUDA(cudaStreamSynchronize(h->s_out));
+        SVB_CUDA(cudaStreamSynchronize(h->s_run));
+        return check_sweep_err(h);
+    }
+    rc = h->pin_in.reserve(2 * nin);
+    if (rc != SVB_OK) return rc;
+    rc = h->pin_out.reserve(2 * n);
+    if (rc != SVB_OK) return rc;
+    uint8_t* pl = (uint8_t*)h->pin_in.p;
+    uint8_t* pr = pl + nin;
+    int16_t* po = (int16_t*)h->pin_out.p;
+    std::vector<std::atomic<int>> flags(B);
+    for (auto& f : flags) f.store(0, std::memory_order_relaxed);
+    std::vector<HostPipe::Mark> marks;
+    SvbTaskGroup gin, gout;
+    struct Waiter { SvbTaskGroup *a, *b; ~Waiter() { svb_pool_wait(a); svb_pool_wait(b); } } waiter{&gin, &gout};   // on every return path
+    const size_t pin = hp.pin, pout = hp.pout;
+    for (int i = 0; i < B; ++i)
+        svb_pool_submit(&gin, [=, &flags] {
+            memcpy(pl + i * pin, left + i * pin, pin);
+            memcpy(pr + i * pin, right + i * pin, pin);
+            flags[i].store(1, std::memory_order_release);
+        });
+    hp.hl = pl; hp.hr = pr; hp.hout = po;
+    hp.staged = flags.data();
+    hp.marks = &marks;
     rc = sgbm_compute_impl(h, dl, dr, B, H, W, cn, dout, h->s_run, &hp);
+    svb_pool_wait(&gin);                                     // (the tasks read the caller's arrays and `flags`)
     if (rc != SVB_OK) { cudaDeviceSynchronize(); return rc; }
+    const int parts = svb_pool_threads();
+    for (const auto& m : marks) {
+        if (cudaEventSynchronize(m.ev) != cudaSuccess) {     // (tasks in flight write the caller's array: wait first)
+            svb_pool_wait(&gout);
+            SVB_CUDA(cudaGetLastError());
+            svb_set_error("download of a disparity sub-range failed");
+            return SVB_ERR_CUDA;
+        }
+        const size_t bytes = (size_t)m.count * pout * 2, per = (bytes / parts + 4095) & ~(size_t)4095;
+        const char* src = (const char*)(po + (size_t)m.first * pout);
+        char* dst = (char*)(disp + (size_t)m.first * pout);
+        for (size_t o = 0; o < bytes; o += per)
+            svb_pool_submit(&gout, [=] { memcpy(dst + o, src + o, std::min(per, bytes - o)); });
+    }
+    svb_pool_wait(&gout);
     SVB_CUDA(cudaStreamSynchronize(h->s_out));
     SVB_CUDA(cudaStreamSynchronize(h->s_run));
     return check_sweep_err(h);

@@ -49,6 +49,38 @@ struct SvbBuf {
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
+// Grow-only pinned host buffer owned by a handle (staging for pageable caller buffers).
+struct SvbPinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes)
+    {
+        if (bytes <= cap) return SVB_OK;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocDefault);
+        if (e != cudaSuccess) {
+            svb_set_error("cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+            cudaGetLastError();
+            return SVB_ERR_NOMEM;
+        }
+        cap = bytes;
+        return SVB_OK;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+// A few host threads that move data between the caller's PAGEABLE arrays and pinned staging (core.cu).  The reference's
+// call site hands NumPy arrays to compute(); a cudaMemcpy from pageable memory is a single-threaded staged copy inside
+// the driver (~9 GB/s here) that blocks the calling thread, which is what `e2e_pageable` used to pay.
+#include <atomic>
+#include <functional>
+struct SvbTaskGroup { std::atomic<int> pending{0}; };
+void svb_pool_submit(SvbTaskGroup* g, std::function<void()> fn);
+void svb_pool_wait(SvbTaskGroup* g);                     // returns when every task submitted to g has run
+int svb_pool_threads();
+bool svb_host_pageable(const void* p);                   // not pinned / registered / device memory
+
 #ifdef __CUDACC__
 // ---- packed u16x2 helpers (map 1:1 to VIADD.16x2 / VIMNMX.U16x2 / VIADDMNMX.U16x2 on sm_100a)
 __device__ __forceinline__ uint32_t pk_min(uint32_t a, uint32_t b) { return __vminu2(a, b); }

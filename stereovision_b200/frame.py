@@ -22,11 +22,11 @@ def _up(img):
     """NumPy -> CUDA tensor (one copy); tensors pass through."""
     if _is_tensor(img):
         return img
-    return _torch().from_numpy(np.ascontiguousarray(img)).cuda()
+    return _cv._upload(np.ascontiguousarray(img))
 
 
 def _down(t, as_tensor):
-    return t if as_tensor else t.cpu().numpy()
+    return t if as_tensor else _cv._download(t)
 
 
 def apply_stereo_rectification(left_img, right_img, stereo_calib, as_tensor=False):

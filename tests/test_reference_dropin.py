@@ -155,8 +155,15 @@ def test_frame_level_functions_match_the_reference(gd):
     assert tdisp.is_cuda and np.array_equal(tdisp.cpu().numpy(), gd["disparity"]) and np.array_equal(tc.cpu().numpy(), cmap)
     # a frame of another size is resized to the calibration size first (depth_map.py:805-811)
     big = svb.resize(lb, (W + 40, H + 30))
-    l2, _ = svb.frame.apply_stereo_rectification(big, big, calib)
+    l2, r2 = svb.frame.apply_stereo_rectification(big, big, calib)
     assert l2.shape == lr.shape
+    try:                                                      # ... bit for bit what the reference's two cv2 calls give
+        import cv2
+        small = cv2.resize(big, (W, H), interpolation=cv2.INTER_LINEAR)
+        assert np.array_equal(l2, cv2.remap(small, gd["left_map1"], gd["left_map2"], cv2.INTER_LINEAR))
+        assert np.array_equal(r2, cv2.remap(small, gd["right_map1"], gd["right_map2"], cv2.INTER_LINEAR))
+    except ImportError:
+        pass
     # the reference's error behaviour: zeros, never an exception (depth_map.py:941-946)
     import warnings
     with warnings.catch_warnings():

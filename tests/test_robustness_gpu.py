@@ -210,3 +210,81 @@ def test_pitched_inputs_without_a_copy():
     wl, wr = cl[2:2 + H, 3:3 + W], cr[2:2 + H, 3:3 + W]
     prm3 = dict(PRM, P1=600, P2=2400)
     assert torch.equal(svb.StereoSGBM_create(**prm3).compute(wl, wr), svb.StereoSGBM_create(**prm3).compute(wl.contiguous(), wr.contiguous()))
+
+
+def test_pageable_numpy_batches_go_through_pinned_staging():
+    """The reference's call site hands NumPy (pageable) arrays to compute() (depth_map.py:909).  Batches of them are
+    copied to pinned staging by the library's host threads while the first sub-ranges already run, and copied out per
+    downloaded sub-range (svb_sgbm_compute_cn_host); the bytes must be those of the device path -- also when the
+    workspace limit forces several chunks, for colour input, and for arrays that were pinned by the caller."""
+    torch = _torch()
+    H, W, B = 480, 640, 9                                     # 9 x (2 x 0.3 + 0.6) MB > the 8 MB threshold; odd batch
+    L = np.stack([make_pair(H, W, 64, seed=700 + b)[0] for b in range(B)])
+    R = np.stack([make_pair(H, W, 64, seed=700 + b)[1] for b in range(B)])
+    m = svb.StereoSGBM_create(**PRM)
+    want = m.compute(torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()).cpu().numpy()
+    got = m.compute(L, R)
+    assert got.dtype == np.int16 and np.array_equal(got, want)
+    assert np.array_equal(got[4], oracle.sgbm_compute(L[4], R[4], **PRM))
+    # several chunks: a workspace limit of ~3 pairs
+    lib = _lib.lib()
+    h = ctypes.c_void_p()
+    _lib.check(lib.svb_sgbm_create(ctypes.byref(_lib.SgbmParams(*[PRM[k] for k in ORDER])), ctypes.byref(h)))
+    per = lib.svb_sgbm_workspace_bytes(h, 1, H, W)
+    _lib.check(lib.svb_sgbm_set_workspace_limit(h, int(3.5 * per)))
+    out = np.empty((B, H, W), np.int16)
+    _lib.check(lib.svb_sgbm_compute_cn_host(h, L.ctypes.data, R.ctypes.data, B, H, W, 1, out.ctypes.data))
+    assert np.array_equal(out, want)
+    # pinned caller buffers take the direct path; same bytes
+    pl, pr = torch.from_numpy(L).pin_memory(), torch.from_numpy(R).pin_memory()
+    po = torch.empty((B, H, W), dtype=torch.int16).pin_memory()
+    _lib.check(lib.svb_sgbm_compute_cn_host(h, pl.data_ptr(), pr.data_ptr(), B, H, W, 1, po.data_ptr()))
+    assert np.array_equal(po.numpy(), want)
+    lib.svb_sgbm_destroy(h)
+    # colour (BGR) batch
+    Lc, Rc = np.repeat(L[:5, :, :, None], 3, axis=3), np.repeat(R[:5, :, :, None], 3, axis=3)
+    prm3 = dict(PRM, P1=600, P2=2400)
+    m3 = svb.StereoSGBM_create(**prm3)
+    assert np.array_equal(m3.compute(Lc, Rc), m3.compute(torch.from_numpy(Lc).cuda(), torch.from_numpy(Rc).cuda()).cpu().numpy())
+
+
+def test_pageable_numpy_batches_stereobm():
+    """The same staging for svb_bm_compute_host: a NumPy batch above the threshold gives the bytes of the device path."""
+    torch = _torch()
+    H, W, B = 480, 640, 11
+    L = np.stack([make_pair(H, W, 64, seed=800 + b)[0] for b in range(B)])
+    R = np.stack([make_pair(H, W, 64, seed=800 + b)[1] for b in range(B)])
+    bm = svb.StereoBM_create(numDisparities=64, blockSize=15)
+    want = bm.compute(torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()).cpu().numpy()
+    assert np.array_equal(bm.compute(L, R), want)
+    assert np.array_equal(want[3], oracle.bm_compute(L[3], R[3], numDisparities=64, blockSize=15))
+
+
+def test_staged_copies_round_trip_numpy_arrays():
+    """svb_copy_h2d / svb_copy_d2h (pinned staging + host threads for pageable NumPy arrays): sizes around the chunk
+    size, several dtypes, a pinned source, and the public calls that use them (a 1080p BGR cvtColor)."""
+    torch = _torch()
+    from stereovision_b200 import cv_api
+    rng = np.random.default_rng(5)
+    for n in ((4 << 20) + 1, (8 << 20) - 3, (8 << 20), (8 << 20) + 4099, (33 << 20) + 7):
+        a = rng.integers(0, 256, n, dtype=np.uint8)
+        t = cv_api._upload(a)
+        assert t.is_cuda and t.dtype == torch.uint8 and np.array_equal(t.cpu().numpy(), a)
+        assert np.array_equal(cv_api._download(t), a)
+    for dt in (np.int16, np.float32, np.float64):
+        a = rng.standard_normal((3, 700, 1100)).astype(dt) if dt != np.int16 else rng.integers(-3000, 3000, (3, 700, 1100)).astype(dt)
+        b = cv_api._download(cv_api._upload(a))
+        assert b.dtype == a.dtype and b.shape == a.shape and np.array_equal(b, a)
+    # raw C ABI with a pinned source and destination: the direct path
+    lib = _lib.lib()
+    src = torch.arange(6 << 20, dtype=torch.int32).pin_memory()
+    dev = torch.empty_like(src, device="cuda")
+    dst = torch.empty_like(src).pin_memory()
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.check(lib.svb_copy_h2d(dev.data_ptr(), src.data_ptr(), src.numel() * 4, st))
+    _lib.check(lib.svb_copy_d2h(dst.data_ptr(), dev.data_ptr(), src.numel() * 4, st))
+    assert torch.equal(dst, src)
+    # through a public call: NumPy in, NumPy out
+    img = rng.integers(0, 256, (1080, 1920, 3), dtype=np.uint8)
+    g = svb.cvtColor(img, svb.COLOR_BGR2GRAY)
+    assert isinstance(g, np.ndarray) and np.array_equal(g, oracle.bgr2gray(img))

@@ -468,38 +468,50 @@ __device__ __forceinline__ void remap_pixel(const uint8_t* __restrict__ img, con
                                             int sy, int f, int (&out)[C])
 {
     const int fx = f & 31, fy = f >> 5;
-    const int w00 = (32 - fy) * (32 - fx) * 32, w01 = (32 - fy) * fx * 32;
-    const int w10 = fy * (32 - fx) * 32, w11 = fy * fx * 32;
-    const bool x0 = sx >= 0 && sx < Ws, x1 = sx + 1 >= 0 && sx + 1 < Ws;
-    const bool y0 = sy >= 0 && sy < Hs, y1 = sy + 1 >= 0 && sy + 1 < Hs;
     if constexpr (C == 3) {
         // Interior pixel: the two taps of a source row are 6 contiguous bytes; fetch them as aligned 32-bit words
         // (three loads and two funnel shifts per row instead of six byte loads -- the kernel is bound by the number
         // of load instructions, not by bytes).  `lim` = last address from which a 12-byte read stays inside src.
-        const uint8_t* p0 = img + ((size_t)sy * Ws + sx) * 3;
-        const uint8_t* p1 = p0 + (size_t)Ws * 3;
-        if (x0 && x1 && y0 && y1 && p1 <= lim) {
+        // (32-bit byte offsets from the image's 4-byte aligned base: one 64-bit address per source row)
+        const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(img) & 3);
+        const uint32_t* base = reinterpret_cast<const uint32_t*>(img - mis);
+        const uint32_t o0 = ((uint32_t)sy * (uint32_t)Ws + (uint32_t)sx) * 3u + mis, o1 = o0 + (uint32_t)Ws * 3u;
+        const size_t room = (size_t)(lim - reinterpret_cast<const uint8_t*>(base));   // (the rest of the batch: may exceed 32 bits)
+        const uint32_t limoff = room > 0xffffffffull ? 0xffffffffu : (uint32_t)room;
+        if ((unsigned)sx < (unsigned)(Ws - 1) && (unsigned)sy < (unsigned)(Hs - 1) && o1 <= limoff) {   // all four taps inside
             uint32_t lo[2], hi[2];
 #pragma unroll
             for (int r = 0; r < 2; ++r) {
-                const uintptr_t pa = (uintptr_t)(r ? p1 : p0);
-                const uint32_t* w = reinterpret_cast<const uint32_t*>(pa & ~(uintptr_t)3);
-                const uint32_t sh = (uint32_t)(pa & 3) * 8;
+                const uint32_t o = r ? o1 : o0;
+                const uint32_t* w = base + (o >> 2);
+                const uint32_t sh = (o & 3u) * 8u;
                 const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
                 lo[r] = __funnelshift_r(w0, w1, sh);
                 hi[r] = __funnelshift_r(w1, w2, sh);
             }
+            // tap x0 = bytes 0..2, tap x1 = bytes 3..5 of (lo, hi).  Two exact stages instead of four products per
+            // channel: h_r = (32 - fx) a_r0 + fx a_r1 as byte dot products (the weight words select the channel's two
+            // bytes, so no byte is extracted), v = (32 - fy) h_0 + fy h_1, and (32 v + 16384) >> 15 = (v + 512) >> 10.
+            // Non-negative weights that sum to 32768 keep the result in [0, 255]: no clamp.
+            const uint32_t gx = 32u - (uint32_t)fx, ux = (uint32_t)fx;
+            const uint32_t wB = gx | (ux << 24), wGl = gx << 8, wRl = gx << 16, wRh = ux << 8;
+            const int gy = 32 - fy;
+            int h[2][3];
 #pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                // tap x0 = bytes 0..2, tap x1 = bytes 3..5 of (lo, hi)
-                const int a00 = (lo[0] >> (8 * c)) & 0xff, a10 = (lo[1] >> (8 * c)) & 0xff;
-                const int a01 = c == 0 ? (lo[0] >> 24) : ((hi[0] >> (8 * (c - 1))) & 0xff);
-                const int a11 = c == 0 ? (lo[1] >> 24) : ((hi[1] >> (8 * (c - 1))) & 0xff);
-                out[c] = min(max((16384 + w00 * a00 + w01 * a01 + w10 * a10 + w11 * a11) >> 15, 0), 255);
+            for (int r = 0; r < 2; ++r) {
+                h[r][0] = __dp4a(lo[r], wB, 0u);
+                h[r][1] = __dp4a(hi[r], ux, __dp4a(lo[r], wGl, 0u));
+                h[r][2] = __dp4a(hi[r], wRh, __dp4a(lo[r], wRl, 0u));
             }
+#pragma unroll
+            for (int c = 0; c < 3; ++c) out[c] = (gy * h[0][c] + fy * h[1][c] + 512) >> 10;
             return;
         }
     }
+    const int w00 = (32 - fy) * (32 - fx) * 32, w01 = (32 - fy) * fx * 32;
+    const int w10 = fy * (32 - fx) * 32, w11 = fy * fx * 32;
+    const bool x0 = sx >= 0 && sx < Ws, x1 = sx + 1 >= 0 && sx + 1 < Ws;
+    const bool y0 = sy >= 0 && sy < Hs, y1 = sy + 1 >= 0 && sy + 1 < Hs;
 #pragma unroll
     for (int c = 0; c < C; ++c) {
         int acc = 16384;

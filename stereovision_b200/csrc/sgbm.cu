@@ -109,7 +109,9 @@ __host__ __device__ constexpr size_t sw_smem_words(int NP, bool last)
 }
 #define SW_FLAG_EVERY 8        // carry progress is published every this many columns
 #define SW_SPIN_LIMIT (1 << 24)
+#ifndef SVB_HOST_PIPE
 #define SVB_HOST_PIPE 4        // sub-ranges per chunk in the *_host entry points (upload / per-image kernels / download overlap)
+#endif
 
 struct SgbmGeo {
     int H, W, D, Dp, NP, HALF, minD, minX1, width1, bs, r, ftzero;

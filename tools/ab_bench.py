@@ -22,6 +22,8 @@ for tag in args:
     try:
         d = json.loads(p.stdout.strip().splitlines()[-1])
         st = {k: round(v, 2) for k, v in d["roofline"]["stages_ms_per_step"].items()}
-        print(f"{tag:10s} {d['value']:8.1f} pairs/s  e2e {d['e2e']['value']:8.1f}  parity {d['parity']['sha256_match']}  {st}", flush=True)
+        pg = (d.get("e2e_pageable") or {}).get("value")
+        print(f"{tag:10s} {d['value']:8.1f} pairs/s  e2e {d['e2e']['value']:8.1f}  pageable {pg if pg is None else round(pg, 1)}  "
+              f"parity {d['parity']['sha256_match']}  {st}", flush=True)
     except Exception as e:
         print(tag, "FAILED", e, p.stderr[-1500:], flush=True)

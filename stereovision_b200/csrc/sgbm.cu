@@ -45,7 +45,10 @@
 #define SW_ROWS4 18
 #endif
 // rows (= warps) per band
-__host__ __device__ constexpr int sw_rows(int NP) { return NP <= 2 ? 24 : (NP == 3 ? 22 : (NP == 4 ? SW_ROWS4 : (NP == 5 ? 16 : 8))); }
+#ifndef SW_ROWS_SMALL
+#define SW_ROWS_SMALL 30           // rows per band for numDisparities <= 128 (32 warps of <= 64 registers; 24 -> 30: 480p / D64 first sweep 6.3 -> 5.4 ms)
+#endif
+__host__ __device__ constexpr int sw_rows(int NP) { return NP <= 2 ? SW_ROWS_SMALL : (NP == 3 ? 22 : (NP == 4 ? SW_ROWS4 : (NP == 5 ? 16 : 8))); }
 #ifndef SW_EXPERIMENT
 #define SW_EXPERIMENT 0        // timing experiments only (results are wrong): 3 = no C/S1 loads, 4 = no S1 stores, 5 = both, 6 = no row hand-off waits
 #endif

@@ -51,6 +51,7 @@ extern "C" int svb_init(int device)
 #include <thread>
 #include <vector>
 #include <sched.h>
+#include <unistd.h>
 namespace {
 struct SvbPool {
     std::mutex m;
@@ -79,7 +80,16 @@ struct SvbPool {
 };
 // created at the first pageable call and never destroyed: its threads sleep on the condition variable until the
 // process ends (joining them from a static destructor would race with interpreter shutdown)
-SvbPool& svb_pool() { static SvbPool* p = new SvbPool(); return *p; }
+// (a forked child inherits the object but not its threads: it gets a pool of its own)
+SvbPool& svb_pool()
+{
+    static std::mutex mk;
+    static SvbPool* p = nullptr;
+    static pid_t owner = 0;
+    std::lock_guard<std::mutex> l(mk);
+    if (!p || owner != getpid()) { p = new SvbPool(); owner = getpid(); }
+    return *p;
+}
 }  // namespace
 
 void svb_pool_submit(SvbTaskGroup* g, std::function<void()> fn)

@@ -66,6 +66,9 @@ __host__ __device__ constexpr int sw_rows(int NP) { return NP <= 2 ? SW_ROWS_SMA
 #ifndef SW_SEAM_FMA
 #define SW_SEAM_FMA 0          // 1: seam fix-ups of the disparity neighbours as IMAD / IMAD.HI instead of PRMTs (measured: 14.1 -> 15.8 ms, the multiply sits on the recurrence's critical path)
 #endif
+#ifndef SW_WAVE
+#define SW_WAVE 1              // 0: k_sweep for every first sweep (A/B timing of k_wave)
+#endif
 #ifndef SW_UNROLL2
 #define SW_UNROLL2 0           // 1: the rows' column loop unrolled by two (experiment)
 #endif
@@ -1145,6 +1148,306 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
 }
 
 // ------------------------------------------------------------------------------------------
+// k_wave<NP, MASK>: the FIRST sweep (paths -> and the ones from the previous row, S1 out) for numDisparities <= 128,
+// where k_sweep's warp-per-pixel loop spends ~100 of its ~140 instructions per column on per-vector overhead (shuffles,
+// seams, reductions, ring and flag bookkeeping, polling) whatever the vector holds.  Here a warp carries G = 4 / NP
+// CONSECUTIVE ROWS in lockstep, each in a group of WD = 32 / G lanes with 4 words (8 disparities) per lane -- the
+// instruction stream of the 256-disparity case serving G pixels.  Group g runs SKEW columns behind group g - 1 (the
+// predecessors (y-1, x-1..x+1) are then complete), so inside a warp the rows hand their L_r over through the same
+// shared-memory rings as in k_sweep but need no flags: program order and __syncwarp do it.  Between warps (last group
+// of warp w -> first group of warp w + 1), towards the previous / next band (loader / drain helper warps, L2 carry) and
+// for the band dispenser everything is k_sweep's protocol.  Predecessors outside the image (column -1, column w1) are
+// zeroed by the READER, so the rings hold real columns only.  FULL vectors (D == Dp) with plain sums (VAR 2) only.
+// ------------------------------------------------------------------------------------------
+#ifndef WV_WARPS1
+#define WV_WARPS1 15           // row warps per CTA at numDisparities <= 64 (4 rows each)
+#endif
+#ifndef WV_WARPS2
+#define WV_WARPS2 18           // ... at numDisparities <= 128 (2 rows each; 15 / 18 warps: first sweep 720p / D128 9.41 / 9.13 ms)
+#endif
+__host__ __device__ constexpr int wv_warps(int NP) { return NP == 1 ? WV_WARPS1 : WV_WARPS2; }
+__host__ __device__ constexpr int wv_rows(int NP) { return wv_warps(NP) * (4 / NP); }
+__host__ __device__ constexpr size_t wv_smem_words(int NP)
+{
+    return (size_t)(wv_rows(NP) + 1) * 3 * 6 * (NP * 32 + 4) + (size_t)wv_rows(NP) * 4 * NP * 32;
+}
+template <int NP, int MASK>
+__global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const SweepArgs a, const SgbmGeo g)
+{
+    static_assert(NP == 1 || NP == 2, "k_wave: numDisparities <= 128");
+    constexpr int G = 4 / NP, WD = 32 / G;                   // rows per warp, lanes per row (4 words per lane)
+    constexpr int WV_WARPS = wv_warps(NP);
+    constexpr int VW = NP * 32, ROWW = VW + 4, ROWS = WV_WARPS * G;
+    constexpr int RING = 6, NS = 4, PFD = NS - 1;
+    constexpr int PATHW = RING * ROWW, RINGW = 3 * PATHW;
+    constexpr int SKEW = (MASK & 8) ? 2 : 1;                 // columns a row runs behind the row above
+    extern __shared__ __align__(128) uint32_t smem[];
+    uint32_t* ring = smem;                                   // [ROWS + 1][3][RING][ROWW] (+1: what the last row writes)
+    uint32_t* cstage = ring + (ROWS + 1) * RINGW;            // [ROWS][NS][VW] cp.async ring of C columns
+    __shared__ int s_ticket;
+    __shared__ int s_done[ROWS + 2];                         // [k]: columns published by row k (or the drain for k = nact); [ROWS + 1]: by the loader
+    int* const s_load = &s_done[ROWS + 1];
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool helper = warp >= WV_WARPS;                    // WV_WARPS: carry loader, WV_WARPS + 1: carry drain
+    const int grp = lane / WD, l = lane % WD;
+    const int w1 = g.width1, dir = a.dir;
+    const uint32_t P1P1 = pk_dup(g.P1), P2P2 = pk_dup(g.P2);
+    const uint32_t one = a.njobs > 0;                        // 1, opaque to the compiler (add_fma)
+    const int rw = helper ? 0 : warp * G + grp;              // this lane's row within the band
+    uint32_t* ring_in = ring + (size_t)rw * RINGW;
+    const int srcPrev = (lane & ~(WD - 1)) | ((l + WD - 1) & (WD - 1)), srcNext = (lane & ~(WD - 1)) | ((l + 1) & (WD - 1));
+    const uint32_t selPrev = l == 0 ? 0x1054u : 0x3210u, selNext = l == WD - 1 ? 0x5432u : 0x3210u;
+    const uint32_t cst_s = smem_u32(cstage + (size_t)rw * NS * VW + 4 * l);    // this lane's slice, stage slot 0
+    // minimum over a row's group of lanes for TWO paths at once: (a, a) and (b, b) travel as (a, b)
+    auto gmin2 = [&](uint32_t ma, uint32_t mb, uint32_t& ra, uint32_t& rb) {
+        uint32_t v = __byte_perm(ma, mb, 0x7610);
+#pragma unroll
+        for (int o = WD / 2; o; o >>= 1) v = pk_min(v, __shfl_xor_sync(FULLMASK, v, o));
+        ra = __byte_perm(v, v, 0x1010);
+        rb = __byte_perm(v, v, 0x3232);
+    };
+    // one path's recurrence step for this lane's 4 words; returns the lane's minimum of the new L in both halves
+    auto step = [&](uint32_t (&Lq)[4], const uint32_t (&C)[4], uint32_t mq2) {
+        uint32_t prev = __shfl_sync(FULLMASK, Lq[3], srcPrev);
+        uint32_t next = __shfl_sync(FULLMASK, Lq[0], srcNext);
+        prev = __byte_perm(prev, WALL2, selPrev);            // group lane 0: (lo = wall, hi = last lane's lo)
+        next = __byte_perm(next, WALL2, selNext);            // last group lane: (lo = lane 0's hi, hi = wall)
+        const uint32_t mqP2 = mq2 + P2P2;
+        uint32_t up = prev, mloc = 0xffffffffu;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t dn = k < 3 ? Lq[k + 1] : next;
+            uint32_t t = add_fma(pk_min(up, dn), one, P1P1);
+            t = pk_min(pk_min(t, Lq[k]), mqP2);
+            const uint32_t L = C[k] + t - mq2;
+            up = Lq[k];
+            Lq[k] = L;
+            mloc = pk_min(mloc, L);
+        }
+        return pk_min(mloc, __byte_perm(mloc, 0, 0x1032));
+    };
+
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_ticket = atomicAdd(a.ticket, 1);
+        __syncthreads();
+        const int t = s_ticket;
+        if (t >= a.njobs * a.bandsPerJob) break;
+        const int job = t % a.njobs, band = t / a.njobs;
+        int ys, ye, keep;
+        job_rows(g, job % g.nstripes, ys, ye, keep);
+        const int nrows = ye - ys, r0 = band * ROWS;
+        const int nact = min(ROWS, nrows - r0);
+        if (nact <= 0) continue;
+        const bool rowAct = !helper && rw < nact;
+        const int gLast = min(G - 1, nact - 1 - warp * G);   // last active group of this warp (< 0: none)
+        const int nL = band > 0 ? w1 : 0;                    // carry columns the loader brings in
+        const int nD = (r0 + nact < nrows) ? w1 : 0;         // carry columns the drain takes out
+
+        if (rowAct) {
+            if (l == 0) s_done[rw] = 0;
+            if (rw == 0 && band == 0)                        // first row of the job: no previous row at all
+                for (int q = l; q < RINGW; q += WD) ring_in[q] = 0;
+        } else if (warp == WV_WARPS && lane == 0) {
+            *s_load = nL ? 0 : w1 + 64;                      // no carry to wait for: row 0 runs free
+            s_done[nact] = nD ? 0 : w1 + 64;                 // nobody below the last row: it never waits
+        }
+        __syncthreads();
+
+        if (helper) {
+            const int* prog_pred = a.prog + (size_t)job * a.bandsPerJob + band - 1;
+            int* prog_mine = a.prog + (size_t)job * a.bandsPerJob + band;
+            if (warp == WV_WARPS && nL) {
+                // ---- loader: the previous band's carry -> row 0's ring (as in k_sweep)
+                const uint32_t* carry_in = a.carry + (((size_t)job * 2 + ((band + 1) & 1)) * w1) * 3 * VW;
+                const uint32_t* cmin_in = a.cmin + (((size_t)job * 2 + ((band + 1) & 1)) * w1) * 4;
+                const uint32_t ring0_s = smem_u32(ring);
+                constexpr int DEPTH = RING - 2;
+                int seen0 = 0, seenG = 0, cl = 0, cp = 0;    // next column to request / to publish
+                bool dead = false;
+                long long spins = 0;
+                while (cp < nL) {
+                    bool can = cl < nL && cl - cp < DEPTH;
+                    if (can && seen0 < cl - RING + 2) { seen0 = lds_acquire_cta(&s_done[0]); can = seen0 >= cl - RING + 2; }
+                    if (can && seenG < cl + 1) { seenG = ld_acquire_gpu(prog_pred); can = seenG >= cl + 1; }
+                    if (can) {
+                        const uint32_t so = (uint32_t)(cl % RING) * ROWW;
+#pragma unroll
+                        for (int p = 0; p < 3; ++p) {
+                            if (!(MASK & (2 << p))) continue;
+                            const uint32_t* src = carry_in + ((size_t)cl * 3 + p) * VW;
+                            if (lane < VW / 4)
+                                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring0_s + (p * PATHW + so + 4 * lane) * 4),
+                                             "l"(src + 4 * lane));
+                        }
+                        if (lane == 0)
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring0_s + (so + VW) * 4),
+                                         "l"(cmin_in + (size_t)cl * 4));
+                        asm volatile("cp.async.commit_group;");
+                        ++cl;
+                        spins = 0;
+                    } else if (cp < cl) {
+                        switch (cl - cp - 1) {
+                            case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
+                            case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
+                            case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
+                            default: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
+                        }
+                        __syncwarp();
+                        ++cp;
+                        if (lane == 0) sts_release_cta(s_load, cp);
+                        spins = 0;
+                    } else {
+                        if (++spins > SW_SPIN_LIMIT) { dead = true; break; }
+                        __nanosleep(SW_SLEEP_NS);
+                    }
+                }
+                if (lane == 0) {
+                    if (dead) atomicExch(a.err, 1);
+                    sts_release_cta(s_load, w1 + 64);        // final count (or: let the rows run out)
+                }
+                asm volatile("cp.async.wait_all;" ::: "memory");
+            }
+            if (warp == WV_WARPS + 1 && nD) {
+                // ---- drain: the last row's output ring -> the carry for the next band
+                uint32_t* carry_out = a.carry + (((size_t)job * 2 + (band & 1)) * w1) * 3 * VW;
+                uint32_t* cmin_out = a.cmin + (((size_t)job * 2 + (band & 1)) * w1) * 4;
+                const uint32_t* ringD = ring + (size_t)nact * RINGW;
+                int seenL = 0;
+                long long spins = 0;
+                for (int cd = 0; cd < nD; ++cd) {
+                    while (seenL < cd + 1) {
+                        seenL = lds_acquire_cta(&s_done[nact - 1]);
+                        if (seenL < cd + 1) {
+                            if (++spins > SW_SPIN_LIMIT) { if (lane == 0) atomicExch(a.err, 1); seenL = w1 + 64; }
+                            __nanosleep(SW_SLEEP_NS);
+                        }
+                    }
+                    const uint32_t so = (uint32_t)(cd % RING) * ROWW;
+#pragma unroll
+                    for (int p = 0; p < 3; ++p) {
+                        if (!(MASK & (2 << p))) continue;
+                        if (lane < VW / 4)
+                            *reinterpret_cast<uint4*>(carry_out + ((size_t)cd * 3 + p) * VW + 4 * lane) =
+                                *reinterpret_cast<const uint4*>(ringD + p * PATHW + so + 4 * lane);
+                    }
+                    if (lane < 4) cmin_out[(size_t)cd * 4 + lane] = ringD[so + VW + lane];
+                    __syncwarp();
+                    if (lane == 0) {
+                        sts_release_cta(&s_done[nact], cd + 2);          // the slot of column cd is free again
+                        if ((cd & (SW_FLAG_EVERY - 1)) == SW_FLAG_EVERY - 1 || cd == w1 - 1) st_release_gpu(prog_mine, cd + 1);
+                    }
+                }
+            }
+            continue;
+        }
+
+        if (gLast < 0) continue;                             // no active row in this warp
+        // ---- the rows: group grp handles row r0 + rw, column c = step - SKEW * grp
+        const int sr = min(r0 + rw, nrows - 1);              // (an idle group re-reads a valid row, stores nothing)
+        const int row = dir > 0 ? sr : nrows - 1 - sr;       // storage row within the job
+        const size_t rowbase = (((size_t)job * g.rowsMax + row) * w1) * VW;
+        const int x0 = dir > 0 ? 0 : w1 - 1;
+        const ptrdiff_t cstep = (ptrdiff_t)dir * VW;
+        const uint32_t* pC0 = a.C + rowbase + (size_t)x0 * VW + 4 * l;
+        uint32_t* pS0 = a.S + rowbase + (size_t)x0 * VW + 4 * l;
+        auto ccol = [&](int c) { return pC0 + (ptrdiff_t)min(max(c, 0), w1 - 1) * cstep; };   // this lane's slice of column c (clamped)
+        const int nsteps = w1 + SKEW * gLast;
+#pragma unroll
+        for (int s = 0; s < PFD; ++s) {
+            cp_async_vec_s<4>(cst_s + s * VW * 4, ccol(s - SKEW * grp));
+            asm volatile("cp.async.commit_group;");
+        }
+        uint32_t Lh[4] = {0u, 0u, 0u, 0u};
+        uint32_t minh2 = 0;
+        int seenP = 0, seenS = 0;
+        // shared-space byte addresses of this lane's slice in the input ring slots of columns c-1, c, c+1 (path 0)
+        const uint32_t rin_s = smem_u32(ring_in + 4 * l), rin_end = rin_s + PATHW * 4;
+        auto slot_of = [&](int c) { return rin_s + (uint32_t)(((c % RING) + RING) % RING) * (ROWW * 4); };
+        uint32_t a_m1 = slot_of(-SKEW * grp - 1), a_0 = slot_of(-SKEW * grp), a_p1 = slot_of(-SKEW * grp + 1);
+        const uint32_t tail = (uint32_t)(VW - 4 * l) * 4;   // from a lane's slice to the slot's minima
+        uint32_t cs_cur = 0, cs_prev = (NS - 1) * VW * 4;
+        const int* done_pred = warp > 0 ? &s_done[warp * G - 1] : s_load;
+        const int* done_succ = &s_done[warp * G + gLast + 1];
+        const uint32_t done_mine = smem_u32(&s_done[rw]);
+        long long spins = 0;
+
+        for (int st = 0; st < nsteps; ++st) {
+            const int c = st - SKEW * grp;                   // this group's column
+            const bool valid = rowAct && (unsigned)c < (unsigned)w1;
+            // group 0 needs the row above (previous warp / loader) SKEW columns ahead; the last active group needs its
+            // ring slot back from the row below (next warp / drain)
+            {
+                const int needP = min(st + SKEW, w1), needS = st - SKEW * gLast - RING + 2;
+                while (seenP < needP || seenS < needS) {
+                    seenP = lds_acquire_cta(done_pred);
+                    seenS = lds_acquire_cta(done_succ);
+                    if (seenP < needP || seenS < needS) {
+                        if (++spins > SW_SPIN_LIMIT) { if (lane == 0) atomicExch(a.err, 1); seenP = seenS = w1 + 64; }
+                        __nanosleep(SW_SLEEP_NS);
+                    }
+                }
+            }
+            cp_async_vec_s<4>(cst_s + cs_prev, ccol(c + PFD));
+            asm volatile("cp.async.commit_group;");
+            asm volatile("cp.async.wait_group %0;" ::"n"(PFD) : "memory");
+            uint32_t C[4];
+            lds_vec<4, 0>(cst_s + cs_cur, C);
+            uint32_t Lt[3][4], mq2[3];
+            if (MASK & 2) { lds_vec<4, 0>(a_m1, Lt[0]); mq2[0] = lds_u32<0>(a_m1 + tail); }
+            if (MASK & 4) { lds_vec<4, PATHW * 4>(a_0, Lt[1]); mq2[1] = lds_u32<4>(a_0 + tail); }
+            if (MASK & 8) { lds_vec<4, 2 * PATHW * 4>(a_p1, Lt[2]); mq2[2] = lds_u32<8>(a_p1 + tail); }
+            if (c <= 0) {                                    // column 0: nothing to the left (and nothing at column -1 above)
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { Lh[k] = 0u; if (MASK & 2) Lt[0][k] = 0u; }
+                minh2 = 0u;
+                if (MASK & 2) mq2[0] = 0u;
+            }
+            if ((MASK & 8) && c == w1 - 1) {                 // last column: nothing at column w1 above
+#pragma unroll
+                for (int k = 0; k < 4; ++k) Lt[2][k] = 0u;
+                mq2[2] = 0u;
+            }
+            uint32_t sum[4], mh, mv[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu};
+            mh = step(Lh, C, minh2);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) sum[k] = Lh[k];
+#pragma unroll
+            for (int p = 0; p < 3; ++p) {
+                if (!(MASK & (2 << p))) continue;
+                mv[p] = step(Lt[p], C, mq2[p]);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) sum[k] = add_fma(Lt[p][k], one, sum[k]);
+            }
+            // minima over the row: two paths per butterfly
+            uint32_t m0, m1, m2;
+            if constexpr (MASK == 15) {
+                gmin2(mh, mv[0], minh2, m0);
+                gmin2(mv[1], mv[2], m1, m2);
+            } else {                                         // MASK 5: -> and the vertical path
+                gmin2(mh, mv[1], minh2, m1);
+                m0 = m2 = 0u;
+            }
+            if (valid) {
+                // the output ring is the next row's input ring: RINGW words further; group lane 0's slice starts the slot
+                if (MASK & 2) { sts_vec<4, RINGW * 4>(a_0, Lt[0]); if (l == 0) sts_u32<(RINGW + VW) * 4>(a_0, m0); }
+                if (MASK & 4) { sts_vec<4, (RINGW + PATHW) * 4>(a_0, Lt[1]); if (l == 0) sts_u32<(RINGW + VW + 1) * 4>(a_0, m1); }
+                if (MASK & 8) { sts_vec<4, (RINGW + 2 * PATHW) * 4>(a_0, Lt[2]); if (l == 0) sts_u32<(RINGW + VW + 2) * 4>(a_0, m2); }
+            }
+            __syncwarp();
+            if (valid && l == 0) asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(done_mine), "r"(c + 1) : "memory");
+            if (valid) *reinterpret_cast<uint4*>(pS0 + (ptrdiff_t)c * cstep) = make_uint4(sum[0], sum[1], sum[2], sum[3]);
+            a_m1 = a_0; a_0 = a_p1; a_p1 = a_p1 + ROWW * 4 == rin_end ? rin_s : a_p1 + ROWW * 4;
+            cs_prev = cs_cur; cs_cur = cs_cur + VW * 4 == NS * VW * 4 ? 0u : cs_cur + VW * 4;
+        }
+        __syncwarp();
+        if (rowAct && l == 0) sts_release_cta(&s_done[rw], w1 + 64);   // a final count no column index reaches
+        asm volatile("cp.async.wait_all;" ::: "memory");
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // k_hlast<G>: the last sweep of MODE_SGBM / SGBM_3WAY (one horizontal path + S = S1 + L + WTA, rows independent of
 // each other) for numDisparities 64 and 128, where k_sweep's warp-per-pixel layout leaves three quarters / half of
 // every packed instruction's lanes' worth of work on the table: a warp carries G = 4 / 2 ROWS at once, each in a group
@@ -1436,7 +1739,9 @@ static SgbmLayout make_layout(const SgbmGeo& g, int nb)
 {
     SgbmLayout L; size_t o = 0;
     const size_t njobs = (size_t)nb * g.nstripes;
-    L.bands = (g.rowsMax + sw_rows(g.NP) - 1) / sw_rows(g.NP);
+    // progress flags: one per band of the SHORTEST bands a sweep kernel of this width uses
+    const int brmin = g.NP <= 2 ? std::min(sw_rows(g.NP), wv_rows(g.NP)) : sw_rows(g.NP);
+    L.bands = (g.rowsMax + brmin - 1) / brmin;
     L.ldesc = o; o += al256((size_t)nb * g.H * g.W * 32);
     L.rdesc = o; o += al256((size_t)nb * g.H * 6 * g.Wp * 4);
     const size_t vol = njobs * g.rowsMax * g.width1 * g.Dp * 2;
@@ -1552,6 +1857,23 @@ static int launch_sweep(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, cudaS
     SVB_CUDA(cudaMemsetAsync(a.ticket, 0, 4, st));
     SVB_CUDA(cudaMemsetAsync(a.prog, 0, (size_t)tickets * 4, st));
     kfn<<<grid, (SW_R + 2) * 32, smem, st>>>(a, g);   // SW_R rows + the two carry helper warps
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+template <int NP, int MASK>
+static int launch_wave(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, cudaStream_t st)
+{
+    auto kfn = k_wave<NP, MASK>;
+    const size_t smem = wv_smem_words(NP) * 4;
+    SVB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, (wv_warps(NP) + 2) * 32, smem));
+    if (per_sm < 1) { svb_set_error("k_wave does not fit on an SM (smem %zu)", smem); return SVB_ERR_UNSUPPORTED; }
+    const long long tickets = (long long)a.njobs * a.bandsPerJob;
+    const int grid = (int)std::min<long long>(tickets, (long long)h->num_sms * per_sm);
+    SVB_CUDA(cudaMemsetAsync(a.ticket, 0, 4, st));
+    SVB_CUDA(cudaMemsetAsync(a.prog, 0, (size_t)tickets * 4, st));
+    kfn<<<grid, (wv_warps(NP) + 2) * 32, smem, st>>>(a, g);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
@@ -1702,8 +2024,18 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     {
         ProfScope ps(h, CAT_SWEEP1, st);
         a.dir = 1;
-        rc = (g.mode == SVB_MODE_SGBM_3WAY || g.mode == SVB_MODE_HH4) ? launch_sweep_var<NP, 5, false>(h, a, g, var, st)
-                                                                      : launch_sweep_var<NP, 15, false>(h, a, g, var, st);
+        const bool two = g.mode == SVB_MODE_SGBM_3WAY || g.mode == SVB_MODE_HH4;
+        bool wave = false;
+        if constexpr (NP <= 2) {
+            // numDisparities <= 128 with plain sums: several rows per warp (k_wave)
+            wave = SW_WAVE && var == 2;
+            if (wave) {
+                set_band_rows(wv_rows(NP));
+                rc = two ? launch_wave<NP, 5>(h, a, g, st) : launch_wave<NP, 15>(h, a, g, st);
+                set_band_rows(rows_full);
+            }
+        }
+        if (!wave) rc = two ? launch_sweep_var<NP, 5, false>(h, a, g, var, st) : launch_sweep_var<NP, 15, false>(h, a, g, var, st);
         if (rc != SVB_OK) return rc;
         h->launches++;
     }

@@ -1169,7 +1169,7 @@ __host__ __device__ constexpr int wv_warps(int NP) { return NP == 1 ? WV_WARPS1 
 __host__ __device__ constexpr int wv_rows(int NP) { return wv_warps(NP) * (4 / NP); }
 __host__ __device__ constexpr size_t wv_smem_words(int NP)
 {
-    return (size_t)(wv_rows(NP) + 1) * 3 * 6 * (NP * 32 + 4) + (size_t)wv_rows(NP) * 4 * NP * 32;
+    return (size_t)(wv_rows(NP) + 1) * 3 * 6 * (NP * 32 + 4) + (size_t)wv_rows(NP) * 4 * NP * 32 + (NP * 32 + 4);
 }
 template <int NP, int MASK>
 __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const SweepArgs a, const SgbmGeo g)
@@ -1184,6 +1184,7 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
     extern __shared__ __align__(128) uint32_t smem[];
     uint32_t* ring = smem;                                   // [ROWS + 1][3][RING][ROWW] (+1: what the last row writes)
     uint32_t* cstage = ring + (ROWS + 1) * RINGW;            // [ROWS][NS][VW] cp.async ring of C columns
+    uint32_t* zrow = cstage + ROWS * NS * VW;                // [ROWW] zeros: the predecessor vector (and minimum) outside the image
     __shared__ int s_ticket;
     __shared__ int s_done[ROWS + 2];                         // [k]: columns published by row k (or the drain for k = nact); [ROWS + 1]: by the loader
     int* const s_load = &s_done[ROWS + 1];
@@ -1191,6 +1192,7 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool helper = warp >= WV_WARPS;                    // WV_WARPS: carry loader, WV_WARPS + 1: carry drain
     const int grp = lane / WD, l = lane % WD;
+    if (threadIdx.x < ROWW) zrow[threadIdx.x] = 0;           // (the band loop starts with a block barrier)
     const int w1 = g.width1, dir = a.dir;
     const uint32_t P1P1 = pk_dup(g.P1), P2P2 = pk_dup(g.P2);
     const uint32_t one = a.njobs > 0;                        // 1, opaque to the compiler (add_fma)
@@ -1372,13 +1374,17 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
         const int* done_succ = &s_done[warp * G + gLast + 1];
         const uint32_t done_mine = smem_u32(&s_done[rw]);
         long long spins = 0;
+        const uint32_t z_vec = smem_u32(zrow + 4 * l), z_min = smem_u32(zrow + VW);
+        const uint32_t* gC = ccol(PFD - SKEW * grp);          // this lane's slice of the column requested at this step
+        uint32_t* pS = pS0;                                   // ... of S1 at this group's column (from column 0 on)
+        int lim = -1;                                         // steps <= lim may run without looking at the neighbours' counters
 
         for (int st = 0; st < nsteps; ++st) {
             const int c = st - SKEW * grp;                   // this group's column
-            const bool valid = rowAct && (unsigned)c < (unsigned)w1;
+            const bool incol = (unsigned)c < (unsigned)w1, valid = rowAct && incol;
             // group 0 needs the row above (previous warp / loader) SKEW columns ahead; the last active group needs its
             // ring slot back from the row below (next warp / drain)
-            {
+            if (st > lim) {
                 const int needP = min(st + SKEW, w1), needS = st - SKEW * gLast - RING + 2;
                 while (seenP < needP || seenS < needS) {
                     seenP = lds_acquire_cta(done_pred);
@@ -1388,26 +1394,32 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
                         __nanosleep(SW_SLEEP_NS);
                     }
                 }
+                lim = min(seenP >= w1 ? 0x3fffffff : seenP - SKEW, seenS + RING - 2 + SKEW * gLast);
             }
-            cp_async_vec_s<4>(cst_s + cs_prev, ccol(c + PFD));
+            cp_async_vec_s<4>(cst_s + cs_prev, gC);
+            if ((unsigned)(c + PFD) < (unsigned)(w1 - 1)) gC += cstep;      // next request: column clamp(c + 1 + PFD)
             asm volatile("cp.async.commit_group;");
             asm volatile("cp.async.wait_group %0;" ::"n"(PFD) : "memory");
             uint32_t C[4];
             lds_vec<4, 0>(cst_s + cs_cur, C);
             uint32_t Lt[3][4], mq2[3];
-            if (MASK & 2) { lds_vec<4, 0>(a_m1, Lt[0]); mq2[0] = lds_u32<0>(a_m1 + tail); }
-            if (MASK & 4) { lds_vec<4, PATHW * 4>(a_0, Lt[1]); mq2[1] = lds_u32<4>(a_0 + tail); }
-            if (MASK & 8) { lds_vec<4, 2 * PATHW * 4>(a_p1, Lt[2]); mq2[2] = lds_u32<8>(a_p1 + tail); }
-            if (c <= 0) {                                    // column 0: nothing to the left (and nothing at column -1 above)
-#pragma unroll
-                for (int k = 0; k < 4; ++k) { Lh[k] = 0u; if (MASK & 2) Lt[0][k] = 0u; }
-                minh2 = 0u;
-                if (MASK & 2) mq2[0] = 0u;
+            // (predecessors outside the image -- column -1 for the diagonal from behind, column w1 for the one from
+            //  ahead -- are read from the row of zeros)
+            if (MASK & 2) {
+                const bool out = c <= 0;
+                lds_vec<4, 0>(out ? z_vec : a_m1, Lt[0]);
+                mq2[0] = lds_u32<0>(out ? z_min : a_m1 + tail);
             }
-            if ((MASK & 8) && c == w1 - 1) {                 // last column: nothing at column w1 above
+            if (MASK & 4) { lds_vec<4, PATHW * 4>(a_0, Lt[1]); mq2[1] = lds_u32<4>(a_0 + tail); }
+            if (MASK & 8) {
+                const bool out = c == w1 - 1;
+                lds_vec<4, 2 * PATHW * 4>(out ? z_vec - 2 * PATHW * 4 : a_p1, Lt[2]);
+                mq2[2] = lds_u32<8>(out ? z_min - 8 : a_p1 + tail);
+            }
+            if (c <= 0) {                                    // column 0: nothing to the left
 #pragma unroll
-                for (int k = 0; k < 4; ++k) Lt[2][k] = 0u;
-                mq2[2] = 0u;
+                for (int k = 0; k < 4; ++k) Lh[k] = 0u;
+                minh2 = 0u;
             }
             uint32_t sum[4], mh, mv[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu};
             mh = step(Lh, C, minh2);
@@ -1437,7 +1449,8 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
             }
             __syncwarp();
             if (valid && l == 0) asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(done_mine), "r"(c + 1) : "memory");
-            if (valid) *reinterpret_cast<uint4*>(pS0 + (ptrdiff_t)c * cstep) = make_uint4(sum[0], sum[1], sum[2], sum[3]);
+            if (valid) *reinterpret_cast<uint4*>(pS) = make_uint4(sum[0], sum[1], sum[2], sum[3]);
+            if (incol) pS += cstep;
             a_m1 = a_0; a_0 = a_p1; a_p1 = a_p1 + ROWW * 4 == rin_end ? rin_s : a_p1 + ROWW * 4;
             cs_prev = cs_cur; cs_cur = cs_cur + VW * 4 == NS * VW * 4 ? 0u : cs_cur + VW * 4;
         }

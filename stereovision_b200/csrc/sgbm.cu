@@ -1163,22 +1163,30 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
 #define WV_WARPS1 15           // row warps per CTA at numDisparities <= 64 (4 rows each)
 #endif
 #ifndef WV_WARPS2
-#define WV_WARPS2 18           // ... at numDisparities <= 128 (2 rows each; 15 / 18 warps: first sweep 720p / D128 9.41 / 9.13 ms)
+#define WV_WARPS2 18           // ... at numDisparities <= 128 with 2 rows each (15 / 18 warps: first sweep 720p / D128 9.41 / 9.13 ms)
 #endif
-__host__ __device__ constexpr int wv_warps(int NP) { return NP == 1 ? WV_WARPS1 : WV_WARPS2; }
-__host__ __device__ constexpr int wv_rows(int NP) { return wv_warps(NP) * (4 / NP); }
+#ifndef WV_WARPS2X
+#define WV_WARPS2X 12          // ... at numDisparities <= 128 with 4 rows each (8 words per lane)
+#endif
+#ifndef WV_G2
+#define WV_G2 2                // rows per warp at numDisparities <= 128: 2, or 4 (8 words per lane, 4-slot rings, 12 warps: 720p / D128 9.1 -> 11.1 ms)
+#endif
+__host__ __device__ constexpr int wv_g(int NP) { return NP == 1 ? 4 : WV_G2; }
+__host__ __device__ constexpr int wv_warps(int NP) { return NP == 1 ? WV_WARPS1 : (WV_G2 == 4 ? WV_WARPS2X : WV_WARPS2); }
+__host__ __device__ constexpr int wv_rows(int NP) { return wv_warps(NP) * wv_g(NP); }
+__host__ __device__ constexpr int wv_ring(int NP) { return NP * wv_g(NP) == 8 ? 4 : 6; }   // 8 words per lane: shallower rings so that enough rows fit
 __host__ __device__ constexpr size_t wv_smem_words(int NP)
 {
-    return (size_t)(wv_rows(NP) + 1) * 3 * 6 * (NP * 32 + 4) + (size_t)wv_rows(NP) * 4 * NP * 32 + (NP * 32 + 4);
+    return (size_t)(wv_rows(NP) + 1) * 3 * wv_ring(NP) * (NP * 32 + 4) + (size_t)wv_rows(NP) * 4 * NP * 32 + (NP * 32 + 4);
 }
 template <int NP, int MASK>
 __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const SweepArgs a, const SgbmGeo g)
 {
     static_assert(NP == 1 || NP == 2, "k_wave: numDisparities <= 128");
-    constexpr int G = 4 / NP, WD = 32 / G;                   // rows per warp, lanes per row (4 words per lane)
+    constexpr int G = wv_g(NP), WD = 32 / G, WPL = NP * G;   // rows per warp, lanes per row, words per lane (4 or 8)
     constexpr int WV_WARPS = wv_warps(NP);
     constexpr int VW = NP * 32, ROWW = VW + 4, ROWS = WV_WARPS * G;
-    constexpr int RING = 6, NS = 4, PFD = NS - 1;
+    constexpr int RING = wv_ring(NP), NS = 4, PFD = NS - 1;
     constexpr int PATHW = RING * ROWW, RINGW = 3 * PATHW;
     constexpr int SKEW = (MASK & 8) ? 2 : 1;                 // columns a row runs behind the row above
     extern __shared__ __align__(128) uint32_t smem[];
@@ -1200,7 +1208,7 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
     uint32_t* ring_in = ring + (size_t)rw * RINGW;
     const int srcPrev = (lane & ~(WD - 1)) | ((l + WD - 1) & (WD - 1)), srcNext = (lane & ~(WD - 1)) | ((l + 1) & (WD - 1));
     const uint32_t selPrev = l == 0 ? 0x1054u : 0x3210u, selNext = l == WD - 1 ? 0x5432u : 0x3210u;
-    const uint32_t cst_s = smem_u32(cstage + (size_t)rw * NS * VW + 4 * l);    // this lane's slice, stage slot 0
+    const uint32_t cst_s = smem_u32(cstage + (size_t)rw * NS * VW + WPL * l);    // this lane's slice, stage slot 0
     // minimum over a row's group of lanes for TWO paths at once: (a, a) and (b, b) travel as (a, b)
     auto gmin2 = [&](uint32_t ma, uint32_t mb, uint32_t& ra, uint32_t& rb) {
         uint32_t v = __byte_perm(ma, mb, 0x7610);
@@ -1210,16 +1218,16 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
         rb = __byte_perm(v, v, 0x3232);
     };
     // one path's recurrence step for this lane's 4 words; returns the lane's minimum of the new L in both halves
-    auto step = [&](uint32_t (&Lq)[4], const uint32_t (&C)[4], uint32_t mq2) {
-        uint32_t prev = __shfl_sync(FULLMASK, Lq[3], srcPrev);
+    auto step = [&](uint32_t (&Lq)[WPL], const uint32_t (&C)[WPL], uint32_t mq2) {
+        uint32_t prev = __shfl_sync(FULLMASK, Lq[WPL - 1], srcPrev);
         uint32_t next = __shfl_sync(FULLMASK, Lq[0], srcNext);
         prev = __byte_perm(prev, WALL2, selPrev);            // group lane 0: (lo = wall, hi = last lane's lo)
         next = __byte_perm(next, WALL2, selNext);            // last group lane: (lo = lane 0's hi, hi = wall)
         const uint32_t mqP2 = mq2 + P2P2;
         uint32_t up = prev, mloc = 0xffffffffu;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t dn = k < 3 ? Lq[k + 1] : next;
+        for (int k = 0; k < WPL; ++k) {
+            const uint32_t dn = k < WPL - 1 ? Lq[k + 1] : next;
             uint32_t t = add_fma(pk_min(up, dn), one, P1P1);
             t = pk_min(pk_min(t, Lq[k]), mqP2);
             const uint32_t L = C[k] + t - mq2;
@@ -1352,29 +1360,31 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
         const size_t rowbase = (((size_t)job * g.rowsMax + row) * w1) * VW;
         const int x0 = dir > 0 ? 0 : w1 - 1;
         const ptrdiff_t cstep = (ptrdiff_t)dir * VW;
-        const uint32_t* pC0 = a.C + rowbase + (size_t)x0 * VW + 4 * l;
-        uint32_t* pS0 = a.S + rowbase + (size_t)x0 * VW + 4 * l;
+        const uint32_t* pC0 = a.C + rowbase + (size_t)x0 * VW + WPL * l;
+        uint32_t* pS0 = a.S + rowbase + (size_t)x0 * VW + WPL * l;
         auto ccol = [&](int c) { return pC0 + (ptrdiff_t)min(max(c, 0), w1 - 1) * cstep; };   // this lane's slice of column c (clamped)
         const int nsteps = w1 + SKEW * gLast;
 #pragma unroll
         for (int s = 0; s < PFD; ++s) {
-            cp_async_vec_s<4>(cst_s + s * VW * 4, ccol(s - SKEW * grp));
+            cp_async_vec_s<WPL>(cst_s + s * VW * 4, ccol(s - SKEW * grp));
             asm volatile("cp.async.commit_group;");
         }
-        uint32_t Lh[4] = {0u, 0u, 0u, 0u};
+        uint32_t Lh[WPL];
+#pragma unroll
+        for (int k = 0; k < WPL; ++k) Lh[k] = 0u;
         uint32_t minh2 = 0;
         int seenP = 0, seenS = 0;
         // shared-space byte addresses of this lane's slice in the input ring slots of columns c-1, c, c+1 (path 0)
-        const uint32_t rin_s = smem_u32(ring_in + 4 * l), rin_end = rin_s + PATHW * 4;
+        const uint32_t rin_s = smem_u32(ring_in + WPL * l), rin_end = rin_s + PATHW * 4;
         auto slot_of = [&](int c) { return rin_s + (uint32_t)(((c % RING) + RING) % RING) * (ROWW * 4); };
         uint32_t a_m1 = slot_of(-SKEW * grp - 1), a_0 = slot_of(-SKEW * grp), a_p1 = slot_of(-SKEW * grp + 1);
-        const uint32_t tail = (uint32_t)(VW - 4 * l) * 4;   // from a lane's slice to the slot's minima
+        const uint32_t tail = (uint32_t)(VW - WPL * l) * 4;   // from a lane's slice to the slot's minima
         uint32_t cs_cur = 0, cs_prev = (NS - 1) * VW * 4;
         const int* done_pred = warp > 0 ? &s_done[warp * G - 1] : s_load;
         const int* done_succ = &s_done[warp * G + gLast + 1];
         const uint32_t done_mine = smem_u32(&s_done[rw]);
         long long spins = 0;
-        const uint32_t z_vec = smem_u32(zrow + 4 * l), z_min = smem_u32(zrow + VW);
+        const uint32_t z_vec = smem_u32(zrow + WPL * l), z_min = smem_u32(zrow + VW);
         const uint32_t* gC = ccol(PFD - SKEW * grp);          // this lane's slice of the column requested at this step
         uint32_t* pS = pS0;                                   // ... of S1 at this group's column (from column 0 on)
         int lim = -1;                                         // steps <= lim may run without looking at the neighbours' counters
@@ -1396,41 +1406,41 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
                 }
                 lim = min(seenP >= w1 ? 0x3fffffff : seenP - SKEW, seenS + RING - 2 + SKEW * gLast);
             }
-            cp_async_vec_s<4>(cst_s + cs_prev, gC);
+            cp_async_vec_s<WPL>(cst_s + cs_prev, gC);
             if ((unsigned)(c + PFD) < (unsigned)(w1 - 1)) gC += cstep;      // next request: column clamp(c + 1 + PFD)
             asm volatile("cp.async.commit_group;");
             asm volatile("cp.async.wait_group %0;" ::"n"(PFD) : "memory");
-            uint32_t C[4];
-            lds_vec<4, 0>(cst_s + cs_cur, C);
-            uint32_t Lt[3][4], mq2[3];
+            uint32_t C[WPL];
+            lds_vec<WPL, 0>(cst_s + cs_cur, C);
+            uint32_t Lt[3][WPL], mq2[3];
             // (predecessors outside the image -- column -1 for the diagonal from behind, column w1 for the one from
             //  ahead -- are read from the row of zeros)
             if (MASK & 2) {
                 const bool out = c <= 0;
-                lds_vec<4, 0>(out ? z_vec : a_m1, Lt[0]);
+                lds_vec<WPL, 0>(out ? z_vec : a_m1, Lt[0]);
                 mq2[0] = lds_u32<0>(out ? z_min : a_m1 + tail);
             }
-            if (MASK & 4) { lds_vec<4, PATHW * 4>(a_0, Lt[1]); mq2[1] = lds_u32<4>(a_0 + tail); }
+            if (MASK & 4) { lds_vec<WPL, PATHW * 4>(a_0, Lt[1]); mq2[1] = lds_u32<4>(a_0 + tail); }
             if (MASK & 8) {
                 const bool out = c == w1 - 1;
-                lds_vec<4, 2 * PATHW * 4>(out ? z_vec - 2 * PATHW * 4 : a_p1, Lt[2]);
+                lds_vec<WPL, 2 * PATHW * 4>(out ? z_vec - 2 * PATHW * 4 : a_p1, Lt[2]);
                 mq2[2] = lds_u32<8>(out ? z_min - 8 : a_p1 + tail);
             }
             if (c <= 0) {                                    // column 0: nothing to the left
 #pragma unroll
-                for (int k = 0; k < 4; ++k) Lh[k] = 0u;
+                for (int k = 0; k < WPL; ++k) Lh[k] = 0u;
                 minh2 = 0u;
             }
-            uint32_t sum[4], mh, mv[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu};
+            uint32_t sum[WPL], mh, mv[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu};
             mh = step(Lh, C, minh2);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) sum[k] = Lh[k];
+            for (int k = 0; k < WPL; ++k) sum[k] = Lh[k];
 #pragma unroll
             for (int p = 0; p < 3; ++p) {
                 if (!(MASK & (2 << p))) continue;
                 mv[p] = step(Lt[p], C, mq2[p]);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) sum[k] = add_fma(Lt[p][k], one, sum[k]);
+                for (int k = 0; k < WPL; ++k) sum[k] = add_fma(Lt[p][k], one, sum[k]);
             }
             // minima over the row: two paths per butterfly
             uint32_t m0, m1, m2;
@@ -1443,13 +1453,17 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
             }
             if (valid) {
                 // the output ring is the next row's input ring: RINGW words further; group lane 0's slice starts the slot
-                if (MASK & 2) { sts_vec<4, RINGW * 4>(a_0, Lt[0]); if (l == 0) sts_u32<(RINGW + VW) * 4>(a_0, m0); }
-                if (MASK & 4) { sts_vec<4, (RINGW + PATHW) * 4>(a_0, Lt[1]); if (l == 0) sts_u32<(RINGW + VW + 1) * 4>(a_0, m1); }
-                if (MASK & 8) { sts_vec<4, (RINGW + 2 * PATHW) * 4>(a_0, Lt[2]); if (l == 0) sts_u32<(RINGW + VW + 2) * 4>(a_0, m2); }
+                if (MASK & 2) { sts_vec<WPL, RINGW * 4>(a_0, Lt[0]); if (l == 0) sts_u32<(RINGW + VW) * 4>(a_0, m0); }
+                if (MASK & 4) { sts_vec<WPL, (RINGW + PATHW) * 4>(a_0, Lt[1]); if (l == 0) sts_u32<(RINGW + VW + 1) * 4>(a_0, m1); }
+                if (MASK & 8) { sts_vec<WPL, (RINGW + 2 * PATHW) * 4>(a_0, Lt[2]); if (l == 0) sts_u32<(RINGW + VW + 2) * 4>(a_0, m2); }
             }
             __syncwarp();
             if (valid && l == 0) asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(done_mine), "r"(c + 1) : "memory");
-            if (valid) *reinterpret_cast<uint4*>(pS) = make_uint4(sum[0], sum[1], sum[2], sum[3]);
+            if (valid) {
+#pragma unroll
+                for (int q = 0; q < WPL / 4; ++q)
+                    reinterpret_cast<uint4*>(pS)[q] = make_uint4(sum[4 * q], sum[4 * q + 1], sum[4 * q + 2], sum[4 * q + 3]);
+            }
             if (incol) pS += cstep;
             a_m1 = a_0; a_0 = a_p1; a_p1 = a_p1 + ROWW * 4 == rin_end ? rin_s : a_p1 + ROWW * 4;
             cs_prev = cs_cur; cs_cur = cs_cur + VW * 4 == NS * VW * 4 ? 0u : cs_cur + VW * 4;

@@ -208,6 +208,24 @@ def cpu_reference_run(wl, npairs, threads):
     return time.perf_counter() - t0, kind, threads
 
 
+def cpu_single_core_ms(wl, runs=3):
+    """latency of ONE pair on one host core (cv2.setNumThreads(1)), median of `runs` after the
+    all-core run has warmed everything up.  None when cv2 is not importable."""
+    try:
+        import cv2
+    except Exception:
+        return None
+    cv2.setNumThreads(1)
+    L, R = make_inputs(wl, 1, seed0=100)
+    prm = sgbm_params(wl)
+    ts = []
+    for _ in range(runs):
+        t0 = time.perf_counter()
+        cv2.StereoSGBM_create(**prm).compute(L[0], R[0])
+        ts.append(1e3 * (time.perf_counter() - t0))
+    return sorted(ts)[len(ts) // 2]
+
+
 def run_reference_arm(args, wl, rank, world):
     if rank != 0:
         return
@@ -528,7 +546,8 @@ def main():
             cores = len(os.sched_getaffinity(0))
             dt, kind, used = cpu_reference_run(wl, cores, cores)
             line["cpu_baseline"] = {"value": cores / dt, "unit": "pairs/s", "cores": used, "kind": kind,
-                                    "sample": f"{cores} distinct pairs once, one pair per thread (cv2.setNumThreads(1))"}
+                                    "sample": f"{cores} distinct pairs once, one pair per thread (cv2.setNumThreads(1))",
+                                    "single_core_ms_per_pair": cpu_single_core_ms(wl)}
         sys.stdout.flush()
         os.dup2(real_stdout, 1)
         print(json.dumps(line), flush=True)

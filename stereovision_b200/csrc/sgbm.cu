@@ -317,6 +317,9 @@ __device__ __forceinline__ void vec_st(uint32_t* p, int lane, const uint32_t (&v
 // mapping (lane l <-> words NP*l..) so that shared and global accesses are 128-bit.
 // ------------------------------------------------------------------------------------------
 #define CK_WARPS 16
+#ifndef CK_GROUPED
+#define CK_GROUPED 1           // numDisparities <= 64: k_costg (four columns per warp pass) instead of k_cost
+#endif
 #ifndef CK_BUDGET_KB
 #define CK_BUDGET_KB 200       // shared memory per CTA (experiment knob: 109 = two CTAs per SM at numDisparities 256 / blockSize 5)
 #endif
@@ -515,6 +518,160 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
                     }
                     vec_st<NP>(dst, lane, o);
                 }
+            }
+        }
+        slot = slot + 1 == bs ? 0 : slot + 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_costg<NP>: k_cost for numDisparities <= 64 (NP 1; the NP 2 form works but is not faster, see run_chunk).  There a vector
+// is 32 words, and k_cost's warp-per-vector passes run every packed instruction and every 32-bit shared-memory access for a
+// quarter of the data a 256-disparity vector gives them.  Here a warp pass covers G = 4 / NP ADJACENT COLUMNS: a group of WD = 32 / G lanes per column, 4
+// words (8 disparities) per lane, so that pixel costs, box sums, ring and volume accesses are all 128-bit per lane and
+// one STG.128 of the warp writes G whole vectors (512 contiguous bytes).  Same strip walk, TMA staging, ring and
+// arithmetic as k_cost (the tests compare the C volume of both with the oracle's); a strip is CK_WARPS * G columns wide.
+// ------------------------------------------------------------------------------------------
+__host__ __device__ constexpr int ckg_pc(int NP) { return CK_WARPS * (4 / NP); }             // pixel-cost columns per strip
+__host__ __device__ constexpr int ckg_se(int NP) { return 32 * NP + ckg_pc(NP) + 8; }        // staged entries per plane (<= 256)
+__host__ __device__ constexpr int ckg_blkw(int NP) { return (6 * ckg_se(NP) + 31) & ~31; }   // words per staged box, 128-byte padded
+template <int NP, bool FULL, bool XTRA>
+__global__ void __launch_bounds__(CK_WARPS * 32) k_costg(const __grid_constant__ CUtensorMap tmR,
+                                                         const __grid_constant__ CUtensorMap tmL,
+                                                         SgbmGeo g, CostArgs ca, uint32_t* __restrict__ vol)
+{
+    static_assert(NP == 1 || NP == 2, "k_costg: numDisparities <= 128");
+    constexpr int G = 4 / NP, WD = 32 / G, VW = NP * 32, PCG = ckg_pc(NP), SE = ckg_se(NP), BLKW = ckg_blkw(NP);
+    extern __shared__ __align__(128) uint32_t smem[];
+    __shared__ __align__(8) uint64_t mbar[2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, grp = lane / WD, l = lane % WD;
+    const int r = g.r, bs = 2 * r + 1, OC = ca.OC, PC = OC + 2 * r;
+    uint32_t* stage = smem;                                  // [2][6][SE] (each box padded to BLKW words)
+    uint32_t* lstage = stage + 2 * BLKW;                     // [2][PCG][8]
+    uint32_t* pixbuf = lstage + 2 * PCG * 8;                 // [2][PCG][VW]
+    uint32_t* ring = pixbuf + 2 * PCG * VW;                  // [OC][bs][VW]
+
+    const int strip = blockIdx.x % ca.nstrips, seg = blockIdx.x / ca.nstrips;
+    const int job = blockIdx.y + ca.job0, b = job / g.nstripes, n = job % g.nstripes;
+    int ys, ye, keep;
+    job_rows(g, n, ys, ye, keep);
+    const int ya = ys + seg * ca.rseg, yb = min(ya + ca.rseg, ye);   // output rows of this CTA
+    if (ya >= yb) return;
+    const int xs = strip * OC;                               // first output column (cost domain)
+    const int w1 = g.width1;
+    const int xbase0 = xs - r + g.minX1 - g.minD - (g.HALF - 1);
+    const int xbase = xbase0 & ~3;                           // floor to a multiple of 4 entries (16 bytes)
+    const int xl0 = xs - r + g.minX1;                        // image column of left record 0
+
+    auto issue_row = [&](int v, int buf) {                   // one thread
+        const int yy = min(max(v, ys), g.H - 1);
+        mbar_expect_tx(&mbar[buf], (6 * SE + PCG * 8) * 4);
+        tma_load_2d(stage + buf * BLKW, &tmR, xbase, (b * g.H + yy) * 6, &mbar[buf]);
+#pragma unroll
+        for (int q = 0; q < PCG / 32; ++q)                   // left records: boxes of 32 pixels (256 words)
+            tma_load_2d(lstage + (buf * PCG + 32 * q) * 8, &tmL, (xl0 + 32 * q) * 8, b * g.H + yy, &mbar[buf]);
+    };
+    if (threadIdx.x == 0) {
+        mbar_init(&mbar[0], 1);
+        mbar_init(&mbar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const int v0 = ya - r, v1 = yb - 1 + r;                  // virtual input rows (clamped on use)
+    if (threadIdx.x == 0) {
+        issue_row(v0, 0);
+        if (v0 + 1 <= v1) issue_row(v0 + 1, 1);
+    }
+    uint32_t padm[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int w = 4 * l + k;
+        padm[k] = (w >= g.D ? 0xffffu : 0u) | (w + g.HALF >= g.D ? 0xffff0000u : 0u);
+    }
+    uint32_t acc[4] = {0u, 0u, 0u, 0u};
+    // this group's strip column (pixel costs) / output column (box sums): the same index
+    const int c = G * warp + grp;
+    const int xq = min(max(xs - r + c, 0), w1 - 1);          // clamped cost column
+    const int cq = xq - (xs - r);                            // ... inside the staged window
+    // pixel-cost phase: register k of lane l <-> word 4l + k (NP 1: the four columns' entries are 32 consecutive words, and
+    // the result leaves as one 128-bit store) or word 16k + l (NP 2: 4l + k would put lanes l and l + 8 on one bank)
+    const int ebase = cq + g.HALF - 1 + (xbase0 - xbase);    // staged entry of word 0 (word w: ebase - w)
+    const int loff = cq * 8;
+    const bool has_pix = c < PC, has_out = c < OC;
+    const int xc = xs + c;                                   // output column in the cost domain
+    int slot = 0;
+
+    for (int v = v0; v <= v1; ++v) {
+        const int it = v - v0, buf = it & 1;
+        const uint32_t* st = stage + buf * BLKW;
+        const uint32_t* ls = lstage + buf * PCG * 8;
+        uint32_t* pb = pixbuf + buf * PCG * VW;
+        mbar_wait(&mbar[buf], (it >> 1) & 1);
+        // ---- pixel costs of this group's strip column, 4 words per lane
+        if (has_pix) {
+            const uint4 l0 = *reinterpret_cast<const uint4*>(ls + loff);
+            const uint4 l1 = *reinterpret_cast<const uint4*>(ls + loff + 4);
+            uint32_t pix[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int e = ebase - (NP == 1 ? 4 * l + k : WD * k + l);
+                const uint32_t v1a = st[0 * SE + e], v0a = st[1 * SE + e], nva = st[2 * SE + e];
+                const uint32_t v1b = st[3 * SE + e], v0b = st[4 * SE + e], nvb = st[5 * SE + e];
+                // as in k_cost: c0 = max(0, u - v1, v0 - u); c1 = max(0, v - u1, u0 - v); planes {-v1, v0, -v}
+                uint32_t a = __vadd2(l0.x, v1a);
+                uint32_t c0 = __viaddmax_s16x2_relu(v0a, l0.y, a);
+                uint32_t bb = __vadd2(~nva, l0.w);
+                uint32_t c1 = __viaddmax_s16x2_relu(l0.z, nva, bb);
+                uint32_t px = __vminu2(c0, c1);
+                a = __vadd2(l1.x, v1b);
+                c0 = __viaddmax_s16x2_relu(v0b, l1.y, a);
+                bb = __vadd2(~nvb, l1.w);
+                c1 = __viaddmax_s16x2_relu(l1.z, nvb, bb);
+                pix[k] = px + ((__vminu2(c0, c1) >> 2) & 0x3fff3fffu);
+            }
+            if constexpr (NP == 1) *reinterpret_cast<uint4*>(pb + c * VW + 4 * l) = make_uint4(pix[0], pix[1], pix[2], pix[3]);
+            else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) pb[c * VW + WD * k + l] = pix[k];
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0 && v + 2 <= v1) issue_row(v + 2, buf);
+        // ---- horizontal box over 2r+1 columns, vertical running sum, store
+        if (has_out) {
+            const uint32_t* pcol = pb + c * VW + 4 * l;
+            uint4 hs = *reinterpret_cast<const uint4*>(pcol);
+            for (int j = 1; j < bs; ++j) {
+                const uint4 t = *reinterpret_cast<const uint4*>(pcol + j * VW);
+                hs.x += t.x; hs.y += t.y; hs.z += t.z; hs.w += t.w;
+            }
+            uint32_t* rg = ring + ((size_t)c * bs + slot) * VW + 4 * l;
+            if (it >= bs) {                                  // ring holds hs(v - bs) in `slot`
+                const uint4 t = *reinterpret_cast<const uint4*>(rg);
+                acc[0] -= t.x; acc[1] -= t.y; acc[2] -= t.z; acc[3] -= t.w;
+            }
+            *reinterpret_cast<uint4*>(rg) = hs;
+            acc[0] += hs.x; acc[1] += hs.y; acc[2] += hs.z; acc[3] += hs.w;
+            const int y = v - r;                             // output row once the window is complete
+            if (it >= bs - 1 && xc < w1) {
+                uint32_t* dst = vol + (((size_t)job * g.rowsMax + (y - ys)) * w1 + xc) * VW + 4 * l;
+                uint32_t o[4];
+                if constexpr (XTRA) {
+                    // MODE_HH4: cv2 leaves the rows whose window reaches below the image at cost 0 (oracle/sgbm_oracle.c)
+                    const bool zrow = g.mode == SVB_MODE_HH4 && y + r > g.H - 1 && y > 0;
+                    uint4 t = make_uint4(0u, 0u, 0u, 0u);
+                    if (ca.accum) t = *reinterpret_cast<const uint4*>(dst);
+                    const uint32_t tt[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t cv = zrow ? 0u : acc[k] + tt[k];
+                        o[k] = FULL ? cv : ((cv & ~padm[k]) | (WALL2 & padm[k]));
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) o[k] = FULL ? acc[k] : ((acc[k] & ~padm[k]) | (WALL2 & padm[k]));
+                }
+                *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
             }
         }
         slot = slot + 1 == bs ? 0 : slot + 1;
@@ -1980,9 +2137,17 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         ca.accum = ch > 0;
         ca.job0 = s0 * g.nstripes;
         const int njobs = ns * g.nstripes;                   // jobs of this launch
-        const size_t fixed = ((size_t)2 * ck_nblk(NP) * ck_blkw(NP) + 2 * CK_PC * 8 + (size_t)2 * CK_PC * VW) * 4;
+        // numDisparities <= 64: k_costg (4 adjacent columns per warp pass, strips of 64 columns).  At numDisparities 128 (2
+        // columns per pass) it was measured slower than k_cost: 8.06 -> 8.44 ms at 720p -- the pixel phase executes the same
+        // number of loads there, only the box phase gets shorter.
+        constexpr bool GROUPED = CK_GROUPED && NP == 1;
+        constexpr int PCW = GROUPED ? CK_WARPS * (4 / (NP <= 2 ? NP : 1)) : CK_PC;   // pixel-cost columns per strip
+        constexpr int SEW = GROUPED ? 32 * NP + PCW + 8 : ck_se(NP);
+        constexpr int NBW = GROUPED ? 1 : ck_nblk(NP);
+        constexpr int BLW = GROUPED ? ((6 * SEW + 31) & ~31) : ck_blkw(NP);
+        const size_t fixed = ((size_t)2 * NBW * BLW + 2 * PCW * 8 + (size_t)2 * PCW * VW) * 4;
         const size_t budget = (size_t)CK_BUDGET_KB * 1024;
-        int OC = CK_PC - 2 * g.r;
+        int OC = PCW - 2 * g.r;
         while (OC > 1 && fixed + (size_t)OC * bs * VW * 4 > budget) --OC;
         if (OC < 1 || fixed + (size_t)OC * bs * VW * 4 > budget) {
             svb_set_error("blockSize %d too large for the cost kernel at numDisparities %d", g.bs, g.D);
@@ -1999,7 +2164,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         // TMA views: right planes [nb*H*6][Wp] u32 (box 6 x BW), left records [nb*H][W*8] u32 (box 1 x 256)
         CUtensorMap tmR, tmL;
         int rc = svb_make_tmap_2d_u32(&tmR, rdesc, (uint64_t)g.Wp, (uint64_t)nb * g.H * 6, (uint64_t)g.Wp * 4,
-                                      ck_se(NP) / ck_nblk(NP), 6);
+                                      SEW / NBW, 6);
         if (rc != SVB_OK) return rc;
         rc = svb_make_tmap_2d_u32(&tmL, ldesc, (uint64_t)g.W * 8, (uint64_t)nb * g.H, (uint64_t)g.W * 32, CK_PC * 8, 1);
         if (rc != SVB_OK) return rc;
@@ -2009,8 +2174,17 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
 #define LAUNCH_COST(F, X) do { \
             SVB_CUDA(cudaFuncSetAttribute(k_cost<NP, F, X>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
             k_cost<NP, F, X><<<grid, CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv); } while (0)
-        if (g.D == g.Dp) { if (xtra) LAUNCH_COST(true, true); else LAUNCH_COST(true, false); }
-        else             { if (xtra) LAUNCH_COST(false, true); else LAUNCH_COST(false, false); }
+#define LAUNCH_COSTG(F, X) do { \
+            SVB_CUDA(cudaFuncSetAttribute(k_costg<NP, F, X>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            k_costg<NP, F, X><<<grid, CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv); } while (0)
+        if constexpr (GROUPED) {
+            if (g.D == g.Dp) { if (xtra) LAUNCH_COSTG(true, true); else LAUNCH_COSTG(true, false); }
+            else             { if (xtra) LAUNCH_COSTG(false, true); else LAUNCH_COSTG(false, false); }
+        } else {
+            if (g.D == g.Dp) { if (xtra) LAUNCH_COST(true, true); else LAUNCH_COST(true, false); }
+            else             { if (xtra) LAUNCH_COST(false, true); else LAUNCH_COST(false, false); }
+        }
+#undef LAUNCH_COSTG
 #undef LAUNCH_COST
         SVB_LAUNCH_CHECK(); h->launches++;
     }

@@ -104,6 +104,9 @@ int svb_sgbm_last_launches(const svb_sgbm_t* h);
 int svb_sgbm_check(svb_sgbm_t* h);
 /* Test hook: raise that flag by hand. */
 int svb_sgbm_debug_trip_error(svb_sgbm_t* h);
+/* Test hook: the first sweep at numDisparities <= 128 has two kernels (rows-per-warp k_wave for launches that fill
+ * the GPU, warp-per-row k_sweep for a live frame); 1 / 0 forces one of them for every batch size, -1 = automatic. */
+int svb_sgbm_debug_force_wave(svb_sgbm_t* h, int mode);
 
 /* Per-stage device timing (CUDA events on the launching stream) for bench.py's roofline.
  * enable=1 starts/reset recording, 0 stops.  get_profile synchronises and returns the number

@@ -57,6 +57,7 @@ SIGNATURES = {
     "svb_sgbm_last_launches": (c_int, [c_void_p]),
     "svb_sgbm_check": (c_int, [c_void_p]),
     "svb_sgbm_debug_trip_error": (c_int, [c_void_p]),
+    "svb_sgbm_debug_force_wave": (c_int, [c_void_p, c_int]),
     "svb_sgbm_set_profiling": (c_int, [c_void_p, c_int]),
     "svb_sgbm_get_profile": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "svb_bm_create": (c_int, [ctypes.POINTER(BmParams), ctypes.POINTER(c_void_p)]),

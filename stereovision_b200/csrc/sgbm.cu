@@ -1845,6 +1845,7 @@ struct svb_sgbm {
     int launches = 0;
     int num_sms = 0;
     bool debug = false;             // keep the final S volume (debug_stages)
+    int force_wave = -1;            // test hook: 1 / 0 = k_wave / k_sweep for the first sweep whatever the batch size
     // optional per-stage timing with CUDA events on the launching stream (bench.py's roofline)
     bool profiling = false;
     struct Ev { int cat; cudaEvent_t a, b; };
@@ -2229,7 +2230,12 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         bool wave = false;
         if constexpr (NP <= 2) {
             // numDisparities <= 128 with plain sums: several rows per warp (k_wave)
-            wave = SW_WAVE && var == 2;
+            // ... when the launch fills the GPU, or without the diagonal paths.  One live frame in MODE_SGBM is a dependent
+            // chain of columns + 2 x rows steps, and a k_wave step (4 / 2 rows) is longer than a k_sweep step: measured
+            // 480p / D128 1.59 -> 1.82 ms, 720p / D128 2.90 -> 3.29 ms for ONE frame, while 3WAY / HH4 (one-column skew)
+            // are faster with k_wave even then (480p / D64 0.80 -> 0.77 ms)
+            const long long wtickets = (long long)njobs * ((g.rowsMax + wv_rows(NP) - 1) / wv_rows(NP));
+            wave = SW_WAVE && var == 2 && (h->force_wave < 0 ? (two || wtickets >= h->num_sms) : h->force_wave != 0);
             if (wave) {
                 set_band_rows(wv_rows(NP));
                 rc = two ? launch_wave<NP, 5>(h, a, g, st) : launch_wave<NP, 15>(h, a, g, st);
@@ -2425,6 +2431,13 @@ extern "C" int svb_sgbm_check(svb_sgbm_t* h)
 }
 static int check_sweep_err(svb_sgbm* h) { return svb_sgbm_check(h); }
 // Test hook: raise the flag as a timed-out wait would, so that the reporting path can be exercised.
+extern "C" int svb_sgbm_debug_force_wave(svb_sgbm_t* h, int mode)
+{
+    if (!h) { svb_set_error("null handle"); return SVB_ERR_PARAM; }
+    h->force_wave = mode < 0 ? -1 : (mode != 0);
+    return SVB_OK;
+}
+
 extern "C" int svb_sgbm_debug_trip_error(svb_sgbm_t* h)
 {
     if (!h || !h->d_err) { svb_set_error("no previous compute"); return SVB_ERR_PARAM; }

@@ -276,8 +276,14 @@ class StereoSGBM(_Matcher):
         (normally the last sweep consumes it in registers) so debug_stages() can return it."""
         self._debug = bool(enable)
 
+    def setDebugForceWave(self, mode):
+        """Test hook: 1 / 0 = the rows-per-warp / warp-per-row kernel for the first sweep at numDisparities <= 128
+        whatever the batch size, -1 = automatic (svb_sgbm_debug_force_wave)."""
+        self._force_wave = int(mode)
+
     def _pre_compute(self, h):
         _lib.check(_lib.lib().svb_sgbm_set_debug(h, int(getattr(self, "_debug", False))))
+        _lib.check(_lib.lib().svb_sgbm_debug_force_wave(h, int(getattr(self, "_force_wave", -1))))
 
     def debug_stages(self, H, W):
         """Test hook: (C, S, raw) of image 0 of the last compute as NumPy arrays

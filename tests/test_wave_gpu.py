@@ -34,9 +34,12 @@ def test_heights_around_the_group_and_band_sizes(D, mode):
     for k, H in enumerate(heights):
         l, r = np.ascontiguousarray(big_l[k:k + H]), np.ascontiguousarray(big_r[k:k + H])   # (crops: make_pair needs room for its scene)
         prm = _prm(D, mode)
-        got = svb.StereoSGBM_create(**prm).compute(l, r)
         want = oracle.sgbm_compute(l, r, **prm)
-        assert np.array_equal(got, want), f"D={D} mode={mode} H={H}: {int((got != want).sum())} pixels differ"
+        for force in (1, 0):                                  # both first-sweep kernels (a single image alone would pick k_sweep)
+            m = svb.StereoSGBM_create(**prm)
+            m.setDebugForceWave(force)
+            got = m.compute(l, r)
+            assert np.array_equal(got, want), f"D={D} mode={mode} H={H} wave={force}: {int((got != want).sum())} pixels differ"
 
 
 @pytest.mark.parametrize("D,minD", [(64, -8), (64, 16), (128, -24), (128, 8)])
@@ -47,7 +50,9 @@ def test_min_disparity_and_batches_with_partial_bands(D, minD):
     L, R = np.stack([p[0] for p in prs]), np.stack([p[1] for p in prs])
     for mode in (0, 2):
         prm = _prm(D, mode, minD)
-        got = svb.StereoSGBM_create(**prm).compute(torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()).cpu().numpy()
+        m = svb.StereoSGBM_create(**prm)
+        m.setDebugForceWave(1)
+        got = m.compute(torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()).cpu().numpy()
         for b in (0, B - 1):
             want = oracle.sgbm_compute(L[b], R[b], **prm)
             assert np.array_equal(got[b], want), f"D={D} minD={minD} mode={mode} image {b}: {int((got[b] != want).sum())} pixels differ"

@@ -1314,7 +1314,7 @@ __global__ void __launch_bounds__((sw_rows(NP) + 2) * 32, 1) k_sweep(const Sweep
 // shared-memory rings as in k_sweep but need no flags: program order and __syncwarp do it.  Between warps (last group
 // of warp w -> first group of warp w + 1), towards the previous / next band (loader / drain helper warps, L2 carry) and
 // for the band dispenser everything is k_sweep's protocol.  Predecessors outside the image (column -1, column w1) are
-// zeroed by the READER, so the rings hold real columns only.  FULL vectors (D == Dp) with plain sums (VAR 2) only.
+// zeroed by the READER, so the rings hold real columns only.  Plain sums (VAR 0 / 2 with sums that cannot reach 32768) only.
 // ------------------------------------------------------------------------------------------
 #ifndef WV_WARPS1
 #define WV_WARPS1 15           // row warps per CTA at numDisparities <= 64 (4 rows each)
@@ -1336,7 +1336,7 @@ __host__ __device__ constexpr size_t wv_smem_words(int NP)
 {
     return (size_t)(wv_rows(NP) + 1) * 3 * wv_ring(NP) * (NP * 32 + 4) + (size_t)wv_rows(NP) * 4 * NP * 32 + (NP * 32 + 4);
 }
-template <int NP, int MASK>
+template <int NP, int MASK, bool FULL>
 __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const SweepArgs a, const SgbmGeo g)
 {
     static_assert(NP == 1 || NP == 2, "k_wave: numDisparities <= 128");
@@ -1366,6 +1366,12 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
     const int srcPrev = (lane & ~(WD - 1)) | ((l + WD - 1) & (WD - 1)), srcNext = (lane & ~(WD - 1)) | ((l + 1) & (WD - 1));
     const uint32_t selPrev = l == 0 ? 0x1054u : 0x3210u, selNext = l == WD - 1 ? 0x5432u : 0x3210u;
     const uint32_t cst_s = smem_u32(cstage + (size_t)rw * NS * VW + WPL * l);    // this lane's slice, stage slot 0
+    uint32_t padm[WPL];                                      // !FULL (D < Dp): pad disparities keep the wall
+#pragma unroll
+    for (int k = 0; k < WPL; ++k) {
+        const int w = WPL * l + k;
+        padm[k] = (w >= g.D ? 0xffffu : 0u) | (w + g.HALF >= g.D ? 0xffff0000u : 0u);
+    }
     // minimum over a row's group of lanes for TWO paths at once: (a, a) and (b, b) travel as (a, b)
     auto gmin2 = [&](uint32_t ma, uint32_t mb, uint32_t& ra, uint32_t& rb) {
         uint32_t v = __byte_perm(ma, mb, 0x7610);
@@ -1387,7 +1393,8 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
             const uint32_t dn = k < WPL - 1 ? Lq[k + 1] : next;
             uint32_t t = add_fma(pk_min(up, dn), one, P1P1);
             t = pk_min(pk_min(t, Lq[k]), mqP2);
-            const uint32_t L = C[k] + t - mq2;
+            uint32_t L = C[k] + t - mq2;
+            if (!FULL) L = (L & ~padm[k]) | (WALL2 & padm[k]);
             up = Lq[k];
             Lq[k] = L;
             mloc = pk_min(mloc, L);
@@ -1616,6 +1623,10 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
             }
             __syncwarp();
             if (valid && l == 0) asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(done_mine), "r"(c + 1) : "memory");
+            if (!FULL) {                                     // pad disparities: the saturated sum of walls, as k_sweep<VAR 0> stores it
+#pragma unroll
+                for (int k = 0; k < WPL; ++k) sum[k] = (sum[k] & ~padm[k]) | (WALL2 & padm[k]);
+            }
             if (valid) {
 #pragma unroll
                 for (int q = 0; q < WPL / 4; ++q)
@@ -2045,10 +2056,10 @@ static int launch_sweep(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, cudaS
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
-template <int NP, int MASK>
+template <int NP, int MASK, bool FULL>
 static int launch_wave(svb_sgbm* h, const SweepArgs& a, const SgbmGeo& g, cudaStream_t st)
 {
-    auto kfn = k_wave<NP, MASK>;
+    auto kfn = k_wave<NP, MASK, FULL>;
     const size_t smem = wv_smem_words(NP) * 4;
     SVB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
@@ -2235,10 +2246,11 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
             // 480p / D128 1.59 -> 1.82 ms, 720p / D128 2.90 -> 3.29 ms for ONE frame, while 3WAY / HH4 (one-column skew)
             // are faster with k_wave even then (480p / D64 0.80 -> 0.77 ms)
             const long long wtickets = (long long)njobs * ((g.rowsMax + wv_rows(NP) - 1) / wv_rows(NP));
-            wave = SW_WAVE && var == 2 && (h->force_wave < 0 ? (two || wtickets >= h->num_sms) : h->force_wave != 0);
+            wave = SW_WAVE && (var == 2 || (var == 0 && 4 * lmax <= 32767)) && (h->force_wave < 0 ? (two || wtickets >= h->num_sms) : h->force_wave != 0);
             if (wave) {
                 set_band_rows(wv_rows(NP));
-                rc = two ? launch_wave<NP, 5>(h, a, g, st) : launch_wave<NP, 15>(h, a, g, st);
+                if (g.D == g.Dp) rc = two ? launch_wave<NP, 5, true>(h, a, g, st) : launch_wave<NP, 15, true>(h, a, g, st);
+                else rc = two ? launch_wave<NP, 5, false>(h, a, g, st) : launch_wave<NP, 15, false>(h, a, g, st);
                 set_band_rows(rows_full);
             }
         }

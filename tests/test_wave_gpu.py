@@ -57,3 +57,20 @@ def test_min_disparity_and_batches_with_partial_bands(D, minD):
             want = oracle.sgbm_compute(L[b], R[b], **prm)
             assert np.array_equal(got[b], want), f"D={D} minD={minD} mode={mode} image {b}: {int((got[b] != want).sum())} pixels differ"
         assert np.array_equal(got[2], svb.StereoSGBM_create(**prm).compute(L[2], R[2]))
+
+
+@pytest.mark.parametrize("D", [16, 48, 80, 112])
+def test_padded_disparity_vectors(D):
+    """numDisparities that do not fill the 64-wide vector blocks (D < Dp): pad disparities carry the wall through both
+    sweep kernels of the first sweep."""
+    _torch()
+    H, W = 67, D + 70
+    l, r, _ = make_pair(H, W, max(D, 32), seed=990 + D)
+    for mode in (0, 1, 2):
+        prm = _prm(D, mode)
+        want = oracle.sgbm_compute(l, r, **prm)
+        for force in (1, 0):
+            m = svb.StereoSGBM_create(**prm)
+            m.setDebugForceWave(force)
+            got = m.compute(l, r)
+            assert np.array_equal(got, want), f"D={D} mode={mode} wave={force}: {int((got != want).sum())} pixels differ"

@@ -1655,7 +1655,7 @@ __global__ void __launch_bounds__((wv_warps(NP) + 2) * 32, 1) k_wave(const Sweep
 // G rows per warp in groups of WD = 32 / G lanes, WPL = NP * G words per lane.  <1,4> and <2,2> are the multi-row forms
 // (4 words per lane); <NP,1> is one row per warp for any width (what k_sweep<NP, ., 1, true> computes, without its
 // ring / ticket / staging bookkeeping and with several CTAs per SM).
-template <int NP, int G>
+template <int NP, int G, bool FULL>
 __global__ void __launch_bounds__(HL_WARPS * 32) k_hlast(const SweepArgs a, const SgbmGeo g)
 {
     constexpr int VW = 32 * NP, WD = 32 / G, HF = 32 * NP, WPL = NP * G;     // HF = g.HALF
@@ -1668,6 +1668,12 @@ __global__ void __launch_bounds__(HL_WARPS * 32) k_hlast(const SweepArgs a, cons
     const int blocksPerJob = (g.rowsMax + G - 1) / G;
     const long long units = (long long)a.njobs * blocksPerJob;
     const uint32_t selPrev = gl == 0 ? 0x1054u : 0x3210u, selNext = gl == WD - 1 ? 0x5432u : 0x3210u;
+    uint32_t padm[WPL];                                      // !FULL (D < Dp): pad disparities keep the wall and never count
+#pragma unroll
+    for (int k = 0; k < WPL; ++k) {
+        const int w = WPL * gl + k;
+        padm[k] = (w >= g.D ? 0xffffu : 0u) | (w + g.HALF >= g.D ? 0xffff0000u : 0u);
+    }
     auto gmin = [&](uint32_t v) {                                            // min over the group, in every lane of it
         if constexpr (G == 1) return __reduce_min_sync(FULLMASK, v);
         else {
@@ -1731,7 +1737,8 @@ __global__ void __launch_bounds__(HL_WARPS * 32) k_hlast(const SweepArgs a, cons
                 const uint32_t dn = k + 1 < WPL ? Lh[k + 1] : next;
                 uint32_t t = add_fma(pk_min(up, dn), one, P1P1);
                 t = pk_min(pk_min(t, Lh[k]), mqP2);
-                const uint32_t L = C[k] + t - minh2;
+                uint32_t L = C[k] + t - minh2;
+                if (!FULL) L = (L & ~padm[k]) | (WALL2 & padm[k]);
                 up = Lh[k];
                 Lh[k] = L;
                 mloc = pk_min(mloc, L);
@@ -1752,7 +1759,7 @@ __global__ void __launch_bounds__(HL_WARPS * 32) k_hlast(const SweepArgs a, cons
             const uint32_t th2 = pk_dup((uint32_t)th);
             uint32_t lt[WPL];
 #pragma unroll
-            for (int k = 0; k < WPL; ++k) lt[k] = __vsub2(S[k], th2);
+            for (int k = 0; k < WPL; ++k) { lt[k] = __vsub2(S[k], th2); if (!FULL) lt[k] &= ~padm[k]; }
             uint32_t bits = 0;
             if constexpr (WPL == 4) {
                 bits = (__byte_perm(lt[0], lt[1], 0x7351) & 0x80808080u) | ((__byte_perm(lt[2], lt[3], 0x7351) & 0x80808080u) >> 1);
@@ -2264,16 +2271,17 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         if (g.mode != SVB_MODE_HH && g.mode != SVB_MODE_HH4) set_band_rows(rows_free);
         // numDisparities 64 / 128 with a horizontal-only last sweep: several rows per warp (k_hlast); not for the debug
         // S dump, nor for cv2's 3WAY tie rule without a uniqueness test (k_sweep has that special case)
-        const bool hlast = SW_HLAST && var >= 1 && g.mode != SVB_MODE_HH && g.mode != SVB_MODE_HH4 && !h->debug &&
+        const bool hlast = SW_HLAST && g.mode != SVB_MODE_HH && g.mode != SVB_MODE_HH4 && !h->debug &&
                            !(g.mode == SVB_MODE_SGBM_3WAY && g.uniq == 0);
         if (hlast) {
             constexpr int G = NP == 1 ? 4 : (NP == 2 ? 2 : 1);
             const long long units = (long long)njobs * ((g.rowsMax + G - 1) / G);
             const size_t smem = (size_t)HL_WARPS * G * 32 * NP * 4;
             int per_sm = 0;
-            SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_hlast<NP, G>, HL_WARPS * 32, smem));
+            auto kfn = g.D == g.Dp ? k_hlast<NP, G, true> : k_hlast<NP, G, false>;
+            SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, HL_WARPS * 32, smem));
             const int grid = (int)std::min<long long>((units + HL_WARPS - 1) / HL_WARPS, (long long)h->num_sms * std::max(per_sm, 1));
-            k_hlast<NP, G><<<grid, HL_WARPS * 32, smem, st>>>(a, g);
+            kfn<<<grid, HL_WARPS * 32, smem, st>>>(a, g);
             SVB_LAUNCH_CHECK();
             rc = SVB_OK;
         } else

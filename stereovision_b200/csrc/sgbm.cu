@@ -2172,6 +2172,15 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
             svb_set_error("blockSize %d too large for the cost kernel at numDisparities %d", g.bs, g.D);
             return SVB_ERR_UNSUPPORTED;
         }
+        // A strip whose ring leaves room for only ONE CTA per SM (numDisparities 320 and up) may do better narrower: two
+        // resident CTAs hide each other's row barrier.  Measured: 18 instead of 28 output columns at numDisparities 320 /
+        // blockSize 5 -> k_cost 4.72 -> 4.11 ms (480p, 64 pairs), 11.75 -> 10.59 ms (1080p, 16 pairs); 12 instead of 26-28
+        // columns (blockSize 7, or numDisparities 384) -> equal or slower.  Hence: only if >= 60 % of the columns remain.
+        if (CK_BUDGET_KB == 200 && fixed + (size_t)OC * bs * VW * 4 > (size_t)113 * 1024) {
+            int OC2 = OC;
+            while (OC2 > 1 && fixed + (size_t)OC2 * bs * VW * 4 > (size_t)109 * 1024) --OC2;
+            if (fixed + (size_t)OC2 * bs * VW * 4 <= (size_t)109 * 1024 && 10 * OC2 >= 6 * OC) OC = OC2;
+        }
         ca.OC = OC;
         ca.nstrips = svb_ceil_div(g.width1, OC);
         // row segments: enough CTAs to balance the SMs, few enough to keep the bs-1 warm-up rows cheap

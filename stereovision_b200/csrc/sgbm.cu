@@ -165,18 +165,33 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
                                                    int nimg, int ch, SgbmGeo g, uint32_t* __restrict__ ldesc,
                                                    uint32_t* __restrict__ rdesc)
 {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x;     // left pixel x, and right ENTRY x (grid covers max(W, Wp))
+    // A block handles 256 consecutive left pixels / right entries of one image row.  The two BT channels of every pixel
+    // the block needs -- the left window, the right window and the right window HALF pixels further left, one halo
+    // pixel on either side -- are computed ONCE into shared memory (three passes of bt_channels per thread instead of
+    // nine: the kernel was bound by its byte loads, not by its 60 bytes of output per pixel), then every thread builds
+    // its record and its entry from three neighbouring values.
+    __shared__ short sv[3][2][258];                          // [left | right | right - HALF][channel][x0 - 1 + i, clamped]
+    const int x0 = blockIdx.x * blockDim.x, t = threadIdx.x, x = x0 + t;
     const int y = blockIdx.y, b = blockIdx.z;
     const int H = g.H, W = g.W;
-    if (x < W) {
-        const uint8_t* img = left + b * g.imgPitch + ch;
-        int c0[3], c1[3];
+    const uint8_t* imgL = left + b * g.imgPitch + ch;
+    const uint8_t* imgR = right + b * g.imgPitch + ch;
+    for (int i = t; i < 258; i += 256) {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) bt_channels(img, g.rowPitch, H, W, g.cn, y, min(max(x + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
+        for (int w = 0; w < 3; ++w) {
+            const int px = x0 - 1 + i - (w == 2 ? g.HALF : 0);
+            int p0, p1;
+            bt_channels(w == 0 ? imgL : imgR, g.rowPitch, H, W, g.cn, y, min(max(px, 0), W - 1), g.ftzero, p0, p1);
+            sv[w][0][i] = (short)p0;
+            sv[w][1][i] = (short)p1;
+        }
+    }
+    __syncthreads();
+    if (x < W) {
         uint32_t rec[8];
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
-            const int* p = c ? c1 : c0;
+            const int p[3] = {sv[0][c][t], sv[0][c][t + 1], sv[0][c][t + 2]};
             int u = p[1];
             int ua = x > 0 ? (u + p[0]) / 2 : u;
             int ub = x < W - 1 ? (u + p[2]) / 2 : u;
@@ -191,21 +206,16 @@ __global__ void __launch_bounds__(256) k_prefilter(const uint8_t* __restrict__ l
         dst[1] = make_uint4(rec[4], rec[5], rec[6], rec[7]);
     }
     if (x < g.Wp) {
-        // entry x of the six planes = a[x] | a[x - HALF] << 16: both halves are computed here (the second pixel's
-        // prefilter is recomputed from L1) so that every plane gets ONE coalesced 32-bit store per entry instead of two
-        // 16-bit stores at a 4-byte stride; halves whose pixel lies outside the image are 0.
-        const uint8_t* img = right + b * g.imgPitch + ch;
+        // entry x of the six planes = a[x] | a[x - HALF] << 16 (ONE coalesced 32-bit store per plane and entry);
+        // halves whose pixel lies outside the image are 0.
         uint32_t ent[6] = {0, 0, 0, 0, 0, 0};
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
             const int xr = half ? x - g.HALF : x;
             if (xr < 0 || xr >= W) continue;
-            int c0[3], c1[3];
-#pragma unroll
-            for (int k = 0; k < 3; ++k) bt_channels(img, g.rowPitch, H, W, g.cn, y, min(max(xr + k - 1, 0), W - 1), g.ftzero, c0[k], c1[k]);
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
-                const int* p = c ? c1 : c0;
+                const int p[3] = {sv[1 + half][c][t], sv[1 + half][c][t + 1], sv[1 + half][c][t + 2]};
                 int v = p[1];
                 int va = xr < W - 1 ? (v + p[2]) / 2 : v;
                 int vb = xr > 0 ? (v + p[0]) / 2 : v;

@@ -35,30 +35,6 @@ template <int N, typename T> __device__ __forceinline__ void minmax(T (&v)[14])
 #pragma unroll
     for (int i = N / 2; i < N - 1; ++i) cex(v[i], v[N - 1]);
 }
-__global__ void __launch_bounds__(256) k_median3_s16(const int16_t* __restrict__ src, int H, int W,
-                                                     int16_t* __restrict__ dst)
-{
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
-    if (x >= W) return;
-    const size_t img = (size_t)blockIdx.z * H * W;
-    int s[9];
-#pragma unroll
-    for (int j = 0; j < 3; ++j) {
-        const int16_t* r = src + img + (size_t)min(max(y + j - 1, 0), H - 1) * W;
-#pragma unroll
-        for (int i = 0; i < 3; ++i) s[j * 3 + i] = r[min(max(x + i - 1, 0), W - 1)];
-    }
-    int v[14];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) v[i] = s[i];
-    // 9 samples: keep 6, then 5, 4, 3
-    minmax<6>(v); v[0] = s[6];
-    minmax<5>(v); v[0] = s[7];
-    minmax<4>(v); v[0] = s[8];
-    minmax<3>(v);
-    dst[img + (size_t)y * W + x] = (int16_t)v[1];
-}
-
 // 5x5 median on f32.  FROM_S16: the source is the s16 x16 disparity and is scaled by 1/16
 // on load (exact), fusing depth_map.py:909 with :912.  DEPTH: also emit
 // depth_map.py:926-933 (depth = fxB / (d + 1e-6), clip, validity mask) in the epilogue.
@@ -242,10 +218,46 @@ __global__ void __launch_bounds__(256) k_median5_s16x2(const int16_t* __restrict
     }
 }
 
+// 3x3 median of the s16 disparity (inside StereoSGBM, A.5) for TWO horizontally adjacent pixels per thread on packed
+// s16x2 words: forgetful selection (keep 6 of the 9 samples, drop min and max, take in the next) with one VIMNMX.S16x2 per
+// min / max of two pixels; replicate border by clamped loads.
+__global__ void __launch_bounds__(256) k_median3_s16x2(const int16_t* __restrict__ src, int H, int W, int16_t* __restrict__ dst)
+{
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x), y = blockIdx.y;
+    if (x >= W) return;
+    const size_t img = (size_t)blockIdx.z * H * W;
+    int xx[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) xx[i] = min(max(x + i - 1, 0), W - 1);
+    s16x2 s[9];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        const unsigned short* r = reinterpret_cast<const unsigned short*>(src) + img + (size_t)min(max(y + j - 1, 0), H - 1) * W;
+        uint32_t p[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) p[i] = __ldg(r + xx[i]);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) s[j * 3 + i].v = p[i] | (p[i + 1] << 16);   // (column x + i - 1, column x + i)
+    }
+    s16x2 v[14];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) v[i] = s[i];
+    minmax<6>(v); v[0] = s[6];
+    minmax<5>(v); v[0] = s[7];
+    minmax<4>(v); v[0] = s[8];
+    minmax<3>(v);
+    int16_t* o = dst + img + (size_t)y * W + x;
+    if (x + 1 < W && !(reinterpret_cast<uintptr_t>(o) & 3)) *reinterpret_cast<uint32_t*>(o) = v[1].v;
+    else {
+        o[0] = (int16_t)(v[1].v & 0xffffu);
+        if (x + 1 < W) o[1] = (int16_t)(v[1].v >> 16);
+    }
+}
+
 extern "C" int svb_median3_s16_dev(const int16_t* src, int B, int H, int W, int16_t* dst, void* stream)
 {
     if (!src || !dst || B <= 0 || H <= 0 || W <= 0) { svb_set_error("median3: bad argument"); return SVB_ERR_PARAM; }
-    k_median3_s16<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, (cudaStream_t)stream>>>(src, H, W, dst);
+    k_median3_s16x2<<<dim3(svb_ceil_div(W, 512), H, B), 256, 0, (cudaStream_t)stream>>>(src, H, W, dst);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

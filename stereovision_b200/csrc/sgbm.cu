@@ -1851,10 +1851,16 @@ __global__ void __launch_bounds__(256) k_lrcheck(int16_t* __restrict__ raw, cons
     if (f1 && f2) raw[rowoff + x] = (int16_t)g.INV;
 }
 
-__global__ void k_fill_s16(int16_t* p, size_t n, int16_t v)
+// raw[] = INV: eight values per thread (one 128-bit store; `p` is a 256-byte aligned workspace slice), the tail singly
+__global__ void __launch_bounds__(256) k_fill_s16(int16_t* p, size_t n, int16_t v)
 {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) p[i] = v;
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+    if (i + 8 <= n) {
+        const uint32_t w = (uint32_t)(uint16_t)v * 0x10001u;
+        *reinterpret_cast<uint4*>(p + i) = make_uint4(w, w, w, w);
+    } else {
+        for (size_t j = i; j < n; ++j) p[j] = v;
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -2230,7 +2236,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
     }
 
     const size_t npix = (size_t)nb * g.H * g.W;
-    k_fill_s16<<<svb_ceil_div(npix, 256), 256, 0, st>>>(raw, npix, (int16_t)g.INV);
+    k_fill_s16<<<svb_ceil_div(npix, 256 * 8), 256, 0, st>>>(raw, npix, (int16_t)g.INV);
     SVB_LAUNCH_CHECK(); h->launches++;
     SVB_CUDA(cudaMemsetAsync(key, 0xff, npix * 4, st));
 

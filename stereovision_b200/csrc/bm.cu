@@ -501,6 +501,191 @@ extern "C" void svb_bm_destroy(svb_bm_t* h)
 }
 extern "C" int svb_bm_last_launches(const svb_bm_t* h) { return h ? h->launches : 0; }
 
+// ------------------------------------------------------------------------------------------
+// k_bm2g: k_bm2 for numDisparities <= 64, where a vector is 32 words and k_bm2's warp-per-vector passes spend ~190 of
+// their ~200 instructions per pixel on bookkeeping around three packed SAD operations.  A warp pass covers FOUR window /
+// output columns: a group of 8 lanes per column, 4 words (8 disparities) per lane, so that the vertical sums, the row
+// buffer, the horizontal box, the argmin keys and the uniqueness count are 4 columns wide per instruction; minima and
+// counts are taken inside the groups by xor butterflies.  Strips are 128 window columns wide (k_bm2: 64): with a
+// 15-wide window 114 of them are outputs instead of 50 of 64.  Same arithmetic as k_bm2 (tests: both against the oracle).
+// ------------------------------------------------------------------------------------------
+#ifndef BM_GROUPED
+#define BM_GROUPED 1             // numDisparities <= 64: k_bm2g instead of k_bm2<1>
+#endif
+#define BMG_WARPS 16
+#ifndef BMG_PC
+#define BMG_PC 128                         // window columns per strip: BMG_NP passes of 4 per warp
+#endif
+#define BMG_NP (BMG_PC / (4 * BMG_WARPS))
+template <bool COST>
+__global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restrict__ lp, const uint32_t* __restrict__ rdesc,
+                                                         const uint8_t* __restrict__ okmap, BmGeo g, int OC, int nstrips,
+                                                         int rseg, int16_t* __restrict__ disp, int16_t* __restrict__ cost)
+{
+    constexpr int VW = 32, WD = 8;
+    extern __shared__ __align__(16) uint32_t smem[];
+    uint32_t* vbuf = smem;                                   // [2][BMG_PC][VW] vertical sums of the current row
+    uint32_t* scr = smem + 2 * BMG_PC * VW;                  // [BMG_WARPS][4][VW] per-group scratch for the subpixel taps
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, grp = lane / WD, l = lane % WD;
+    const int strip = blockIdx.x % nstrips, seg = blockIdx.x / nstrips, b = blockIdx.z;
+    const int r = g.r, bs = 2 * r + 1, D = g.D, W = g.W, H = g.H;
+    const int ya = r + seg * rseg, yb = min(ya + rseg, H - r);   // output rows of this CTA
+    if (ya >= yb) return;
+    const int xs = strip * OC;                               // first output column (width1 domain)
+
+    // row-invariant addressing of this group's two window columns (A.6: left column and right start clamp separately)
+    int lc[BMG_NP], pl[BMG_NP], m[BMG_NP][4];
+#pragma unroll
+    for (int p = 0; p < BMG_NP; ++p) {
+        const int j = xs - r + 4 * BMG_NP * warp + 4 * p + grp;
+        lc[p] = min(max(j + g.lofs, 0), W - 1);
+        const int rs = min(max(j + g.rofs, 0), W - D);
+        const int xr0 = rs + D - 1;                          // right column of disparity index d' = 0
+        pl[p] = (xr0 & 1) * g.Wh;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) m[p][k] = max((xr0 >> 1) - (4 * l + k), 0);
+    }
+    uint32_t V[BMG_NP][4];
+#pragma unroll
+    for (int p = 0; p < BMG_NP; ++p)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) V[p][k] = 0;
+    // per-lane constants of the decision: BM indices kk of this lane's eight disparities, pad flags
+    uint32_t kkpk[4], padlo[4], padhi[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int d0 = 2 * (4 * l + k);
+        kkpk[k] = (uint32_t)((D - 1 - d0) & 0xffff) | ((uint32_t)((D - 2 - d0) & 0xffff) << 16);
+        padlo[k] = d0 < D ? 0u : 0xffffffffu;
+        padhi[k] = d0 + 1 < D ? 0u : 0xffffffffu;
+    }
+    uint32_t rkey = 0, rpn = 0, roff = 0;                    // parked pixel of this lane (one of its group's up to 8)
+    int nrec = 0;                                            // pixels parked in this lane's group
+    const int R = (OC + 4 * BMG_WARPS - 1) / (4 * BMG_WARPS);    // output columns per group
+    const int oc_lo = (4 * warp + grp) * R, oc_hi = min(oc_lo + R, OC);
+    const uint8_t* limg = lp + (size_t)b * H * W;
+    const uint32_t* rimg = rdesc + (size_t)b * H * 4 * g.Wh;
+    int16_t* dimg = disp + (size_t)b * H * W;
+    int16_t* cimg = COST ? cost + (size_t)b * H * W : nullptr;
+    uint32_t* sv = scr + (size_t)(4 * warp + grp) * VW;
+
+    const int v0 = ya - r, v1 = yb - 1 + r;                  // input rows: all inside the image
+    for (int v = v0; v <= v1; ++v) {
+        const int it = v - v0, buf = it & 1;
+        // ---- vertical phase: V += |L - R|(row v) - |L - R|(row v - bs), two passes of four columns
+        {
+            const uint8_t* lrow = limg + (size_t)v * W;
+            const uint32_t* rrow = rimg + (size_t)v * 4 * g.Wh;
+            uint32_t* vb = vbuf + ((size_t)buf * BMG_PC + 4 * BMG_NP * warp + grp) * VW + 4 * l;
+#pragma unroll
+            for (int p = 0; p < BMG_NP; ++p) {
+                {
+                    const int u = lrow[lc[p]];
+                    const uint32_t U2 = pk_dup((uint32_t)u), nU2 = pk_dup((uint32_t)(-u));
+                    const uint32_t* rp = rrow + pl[p];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) V[p][k] += bm_absdiff(U2, nU2, __ldg(rp + m[p][k]), __ldg(rp + 2 * g.Wh + m[p][k]));
+                }
+                if (it >= bs) {
+                    const int u = (lrow - (size_t)bs * W)[lc[p]];
+                    const uint32_t U2 = pk_dup((uint32_t)u), nU2 = pk_dup((uint32_t)(-u));
+                    const uint32_t* rp = rrow - (size_t)bs * 4 * g.Wh + pl[p];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) V[p][k] -= bm_absdiff(U2, nU2, __ldg(rp + m[p][k]), __ldg(rp + 2 * g.Wh + m[p][k]));
+                }
+                *reinterpret_cast<uint4*>(vb + 4 * p * VW) = make_uint4(V[p][0], V[p][1], V[p][2], V[p][3]);
+            }
+        }
+        __syncthreads();
+        if (it < bs - 1) continue;                           // window not complete yet
+        // ---- horizontal phase: output row y; group (warp, grp) owns the run of output columns oc_lo .. oc_hi - 1
+        const int y = v - r;
+        const uint32_t* vb = vbuf + (size_t)buf * BMG_PC * VW + 4 * l;
+        const uint8_t* okrow = okmap + ((size_t)b * H + y) * W;
+        uint32_t s[4];
+        for (int jo = 0; jo < R; ++jo) {
+            const int oc = oc_lo + jo;
+            const int occ = min(oc, BMG_PC - bs);            // (an idle group re-reads valid columns, decides nothing)
+            if (jo == 0) {
+                uint4 t = *reinterpret_cast<const uint4*>(vb + occ * VW);
+                s[0] = t.x; s[1] = t.y; s[2] = t.z; s[3] = t.w;
+                for (int c = 1; c < bs; ++c) {
+                    t = *reinterpret_cast<const uint4*>(vb + (occ + c) * VW);
+                    s[0] += t.x; s[1] += t.y; s[2] += t.z; s[3] += t.w;
+                }
+            } else {
+                const uint4 a = *reinterpret_cast<const uint4*>(vb + (occ + bs - 1) * VW);
+                const uint4 e = *reinterpret_cast<const uint4*>(vb + (occ - 1) * VW);
+                s[0] += a.x - e.x; s[1] += a.y - e.y; s[2] += a.z - e.z; s[3] += a.w - e.w;
+            }
+            const int x = xs + oc + g.lofs;
+            bool ok = oc < oc_hi && x < W;
+            if (ok) ok = okrow[x] != 0;
+            if (!__any_sync(0xffffffffu, ok)) continue;
+            // argmin over BM index kk = D-1-d' (lowest kk = largest disparity wins ties): keys (sad << 16 | kk)
+            uint32_t key = 0xffffffffu;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t klo = __byte_perm(s[k], kkpk[k], 0x1054), khi = __byte_perm(s[k], kkpk[k], 0x3276);
+                key = min(key, min(klo | padlo[k], khi | padhi[k]));
+            }
+#pragma unroll
+            for (int o = WD / 2; o; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
+            const int minsad = (int)(key >> 16), mind = (int)(key & 0xffffu);
+            // the SADs at mind-1 / mind+1 (replicated at the ends of the range): subpixel taps, and the two entries
+            // the uniqueness test leaves out
+            *reinterpret_cast<uint4*>(sv + 4 * l) = make_uint4(s[0], s[1], s[2], s[3]);
+            __syncwarp();
+            const uint16_t* sd = reinterpret_cast<const uint16_t*>(sv);         // indexed by d' = D-1-kk
+            const bool hasp = mind + 1 < D, hasn = mind >= 1;
+            const int p = sd[hasp ? D - 2 - mind : 1], n = sd[hasn ? D - mind : D - 2];   // sad[mind+1], sad[mind-1]
+            __syncwarp();
+            if (g.uniq > 0) {
+                // cv2: reject iff some kk outside mind-1..mind+1 has sad <= thresh; count all sad <= thresh instead
+                const int thresh = minsad + (minsad * g.uniq / 100);
+                int cnt = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    cnt += ((int)(s[k] & 0xffffu) <= thresh && !padlo[k]) + ((int)(s[k] >> 16) <= thresh && !padhi[k]);
+#pragma unroll
+                for (int o = WD / 2; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+                if (cnt > 1 + (hasp && p <= thresh) + (hasn && n <= thresh)) ok = false;
+            }
+            // park the pixel in lane nrec of its group; 8 parked pixels are finished together (one division per lane)
+            if (ok) {
+                if (l == nrec) { rkey = key; rpn = (uint32_t)p | ((uint32_t)n << 16); roff = (uint32_t)(y * W + x); }
+                if (++nrec == WD) {
+                    bm2_finish(rkey, rpn, roff, D, g.minD, dimg, cimg);
+                    nrec = 0;
+                }
+            }
+        }
+    }
+    if (l < nrec) bm2_finish(rkey, rpn, roff, D, g.minD, dimg, cimg);
+}
+static int bm2g_launch(const BmGeo& g, const uint8_t* lp, const uint32_t* rdesc, const uint8_t* tex, int nb, int num_sms,
+                       int16_t* disp, int16_t* cost, cudaStream_t st)
+{
+    // output columns per strip: all of them, or a multiple of the group count when that wastes little
+    const int ocmax = BMG_PC - 2 * g.r, groups = 4 * BMG_WARPS, ocr = ocmax / groups * groups;
+    const int OC = ocr >= groups && ocmax - ocr <= groups / 8 ? ocr : ocmax;
+    const int bs = 2 * g.r + 1, nstrips = svb_ceil_div(g.width1, OC), rows = g.H - 2 * g.r;
+    int nsegs = 1;
+    while ((long long)nstrips * nb * nsegs < 4LL * num_sms && rows / (nsegs * 2) >= 4 * bs) nsegs *= 2;
+    const int rseg = svb_ceil_div(rows, nsegs);
+    nsegs = svb_ceil_div(rows, rseg);
+    const size_t smem = ((size_t)2 * BMG_PC + 4 * BMG_WARPS) * 32 * 4;
+    if (cost) {
+        SVB_CUDA(cudaFuncSetAttribute(k_bm2g<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_bm2g<true><<<dim3(nstrips * nsegs, 1, nb), BMG_WARPS * 32, smem, st>>>(lp, rdesc, tex, g, OC, nstrips, rseg, disp, cost);
+    } else {
+        SVB_CUDA(cudaFuncSetAttribute(k_bm2g<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_bm2g<false><<<dim3(nstrips * nsegs, 1, nb), BMG_WARPS * 32, smem, st>>>(lp, rdesc, tex, g, OC, nstrips, rseg, disp, cost);
+    }
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
 template <int NP>
 static int bm2_launch(const BmGeo& g, const uint8_t* lp, const uint32_t* rdesc, const uint8_t* tex, int nb, int num_sms,
                       int16_t* disp, int16_t* cost, cudaStream_t st)
@@ -576,7 +761,8 @@ extern "C" int svb_bm_compute_dev(svb_bm_t* h, const uint8_t* left, const uint8_
     SVB_LAUNCH_CHECK(); h->launches++;
     k_bm_tex_v<<<dim3(svb_ceil_div(W, 256), H, B), 256, 0, st>>>(th, g, validate ? 1 : 0, tex);
     SVB_LAUNCH_CHECK(); h->launches++;
-    switch (g.NP) {
+    if (BM_GROUPED && g.NP == 1) rc = bm2g_launch(g, lp, rdesc, tex, B, h->num_sms, disp, cost, st);
+    else switch (g.NP) {
 #define CASE(N) case N: rc = bm2_launch<N>(g, lp, rdesc, tex, B, h->num_sms, disp, cost, st); break;
         CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
 #undef CASE

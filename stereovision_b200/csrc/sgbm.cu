@@ -333,12 +333,38 @@ __device__ __forceinline__ void vec_st(uint32_t* p, int lane, const uint32_t (&v
 #ifndef CK_BUDGET_KB
 #define CK_BUDGET_KB 200       // shared memory per CTA (experiment knob: 109 = two CTAs per SM at numDisparities 256 / blockSize 5)
 #endif
+#ifndef CK_SHARE
+#define CK_SHARE 4             // k_cost: from this many words per lane on, a warp's two adjacent columns share one load of the right
+                               // descriptor planes (1080p/D256 13.87 -> 13.77 ms, 480p/D320 4.11 -> 3.80; slower at D128: 8.06 -> 8.76)
+#endif
+#ifndef CK_MAXSEG
+#define CK_MAXSEG 16           // most row segments per job (1 = never cut a job's rows)
+#endif
 #define CK_PC 32               // pixel-cost columns per strip (2 per warp)
 // staged entries per plane: the disparity window of the strip + 8 so that the window can start on a
 // 16-byte boundary (TMA needs the inner coordinate's byte offset 16-byte aligned -- measured, tools/tma_test.cu)
 __host__ __device__ constexpr int ck_se(int NP) { return 32 * NP + CK_PC + 8; }
 __host__ __device__ constexpr int ck_nblk(int NP) { return ck_se(NP) > 256 ? 2 : 1; }   // TMA boxes are <= 256 wide
 __host__ __device__ constexpr int ck_blkw(int NP) { return (6 * (ck_se(NP) / ck_nblk(NP)) + 31) & ~31; }   // words per staged box, 128-byte padded
+
+// Birchfield-Tomasi pixel cost of one packed word (two disparities) from the left record {u, -u, u0, 1 - u1} x 2 channels
+// and the six right planes {-v1, v0, -v} x 2 channels (A.1 step 4):
+// channel 0: c0 = max(0, u - v1, v0 - u); c1 = max(0, v - u1, u0 - v); channel 1 (raw intensity) the same, cost >> 2.
+// Operands are stored negated where that saves the subtraction (a packed negation would cost two more instructions).
+__device__ __forceinline__ uint32_t bt_pix(const uint4& l0, const uint4& l1, uint32_t v1a, uint32_t v0a, uint32_t nva,
+                                           uint32_t v1b, uint32_t v0b, uint32_t nvb)
+{
+    uint32_t a = __vadd2(l0.x, v1a);                         // u - v1
+    uint32_t c0 = __viaddmax_s16x2_relu(v0a, l0.y, a);
+    uint32_t bb = __vadd2(~nva, l0.w);                       // v - u1
+    uint32_t c1 = __viaddmax_s16x2_relu(l0.z, nva, bb);
+    uint32_t pix = __vminu2(c0, c1);
+    a = __vadd2(l1.x, v1b);
+    c0 = __viaddmax_s16x2_relu(v0b, l1.y, a);
+    bb = __vadd2(~nvb, l1.w);
+    c1 = __viaddmax_s16x2_relu(l1.z, nvb, bb);
+    return pix + ((__vminu2(c0, c1) >> 2) & 0x3fff3fffu);
+}
 
 struct CostArgs {
     int OC;                    // output columns per strip = CK_PC - 2r (or less when the ring is large)
@@ -427,6 +453,7 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
     }
     const int oc0 = 2 * warp;
     const bool two = oc0 + 1 < OC;
+    const bool pair = 2 * warp + 1 < PC && eoff[1] == eoff[0] + 1;   // not at a clamped image border
     int slot = 0;
 
     for (int v = v0; v <= v1; ++v) {
@@ -436,6 +463,33 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
         uint32_t* pb = pixbuf + buf * CK_PC * VW;
         mbar_wait(&mbar[buf], (it >> 1) & 1);
         // ---- pixel costs of this warp's two strip columns
+        if (CK_SHARE && NP >= CK_SHARE && pair) {
+            // entry(c + 1, w + 1) == entry(c, w): the lane that holds the planes of (c, 32k + lane) uses them again for
+            // word 32k + lane + 1 of the next column; only word 0 of that column (lane 31, last pass) needs its own load
+            const int c = 2 * warp;
+            const uint4 a0 = *reinterpret_cast<const uint4*>(ls + loff[0]);
+            const uint4 a1 = *reinterpret_cast<const uint4*>(ls + loff[0] + 4);
+            const uint4 b0 = *reinterpret_cast<const uint4*>(ls + loff[1]);
+            const uint4 b1 = *reinterpret_cast<const uint4*>(ls + loff[1] + 4);
+#pragma unroll
+            for (int k = 0; k < NP; ++k) {
+                int e = eoff[0] - 32 * k;
+                const uint32_t* sp = st;
+                if (NBLK > 1) { if (e >= BW) { e -= BW; sp += BLKW; } }
+                uint32_t v1a = sp[0 * BW + e], v0a = sp[1 * BW + e], nva = sp[2 * BW + e];
+                uint32_t v1b = sp[3 * BW + e], v0b = sp[4 * BW + e], nvb = sp[5 * BW + e];
+                pb[c * VW + 32 * k + lane] = bt_pix(a0, a1, v1a, v0a, nva, v1b, v0b, nvb);
+                if (k == NP - 1) {
+                    int e2 = lane == 31 ? eoff[0] + 32 : eoff[0] - 32 * k;
+                    sp = st;
+                    if (NBLK > 1) { if (e2 >= BW) { e2 -= BW; sp += BLKW; } }
+                    v1a = sp[0 * BW + e2]; v0a = sp[1 * BW + e2]; nva = sp[2 * BW + e2];
+                    v1b = sp[3 * BW + e2]; v0b = sp[4 * BW + e2]; nvb = sp[5 * BW + e2];
+                }
+                const int wb = 32 * k + lane + 1;
+                pb[(c + 1) * VW + (wb == VW ? 0 : wb)] = bt_pix(b0, b1, v1a, v0a, nva, v1b, v0b, nvb);
+            }
+        } else
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
             const int c = 2 * warp + cc;
@@ -449,21 +503,7 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
                     if (NBLK > 1) { if (e >= BW) { e -= BW; sp += BLKW; } }
                     const uint32_t v1a = sp[0 * BW + e], v0a = sp[1 * BW + e], nva = sp[2 * BW + e];
                     const uint32_t v1b = sp[3 * BW + e], v0b = sp[4 * BW + e], nvb = sp[5 * BW + e];
-                    // channel 0: c0 = max(0, u - v1, v0 - u); c1 = max(0, v - u1, u0 - v)
-                    // (operands are stored negated where that saves the subtraction: planes {-v1, v0, -v},
-                    //  records {u, -u, u0, 1 - u1}; a packed negation would cost two more instructions)
-                    uint32_t a = __vadd2(l0.x, v1a);                         // u - v1
-                    uint32_t c0 = __viaddmax_s16x2_relu(v0a, l0.y, a);
-                    uint32_t bb = __vadd2(~nva, l0.w);                       // v - u1
-                    uint32_t c1 = __viaddmax_s16x2_relu(l0.z, nva, bb);
-                    uint32_t pix = __vminu2(c0, c1);
-                    // channel 1 (raw intensity), cost >> 2
-                    a = __vadd2(l1.x, v1b);
-                    c0 = __viaddmax_s16x2_relu(v0b, l1.y, a);
-                    bb = __vadd2(~nvb, l1.w);
-                    c1 = __viaddmax_s16x2_relu(l1.z, nvb, bb);
-                    pix += (__vminu2(c0, c1) >> 2) & 0x3fff3fffu;
-                    pb[c * VW + 32 * k + lane] = pix;
+                    pb[c * VW + 32 * k + lane] = bt_pix(l0, l1, v1a, v0a, nva, v1b, v0b, nvb);
                 }
             }
         }
@@ -2199,11 +2239,21 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         }
         ca.OC = OC;
         ca.nstrips = svb_ceil_div(g.width1, OC);
-        // row segments: enough CTAs to balance the SMs, few enough to keep the bs-1 warm-up rows cheap
-        int nsegs = 1;
-        while ((long long)ca.nstrips * njobs * nsegs < 8LL * h->num_sms && g.rowsMax / (nsegs * 2) >= 16 * bs) nsegs *= 2;
-        ca.rseg = svb_ceil_div(g.rowsMax, nsegs);
-        ca.nsegs = svb_ceil_div(g.rowsMax, ca.rseg);
+        // Row segments: every CTA walks rseg rows (+ bs-1 warm-up rows, + a few rows' worth of start-up).  The CTAs of a launch
+        // run in waves of (resident CTAs per SM) x SMs; take the segment count that minimises waves x rows per CTA.  Measured:
+        // a host-pipe sub-range of 8 pairs at 1080p/D256 (480 strips on 296 slots) needs the cut (e2e 568 -> 601 pairs/s);
+        // 720p/D128, 32 pairs: k_cost 8.06 -> 7.81 ms; 32 pairs at 1080p/D256 (6.5 waves) gain nothing from it -- an SM left
+        // with one CTA in the last wave runs it at nearly twice the speed, the kernel is bound per SM, not per CTA.
+        auto plan_segs = [&](int per_sm) {
+            const long long slots = (long long)std::max(per_sm, 1) * h->num_sms, base = (long long)ca.nstrips * njobs;
+            const int maxseg = std::max(1, std::min(CK_MAXSEG, g.rowsMax / (16 * bs)));
+            long long best = 0;
+            for (int n = 1; n <= maxseg; ++n) {
+                const int rs = svb_ceil_div(g.rowsMax, n), nsg = svb_ceil_div(g.rowsMax, rs);
+                const long long cost = ((base * nsg + slots - 1) / slots) * (rs + bs - 1 + 6);
+                if (n == 1 || cost < best) { best = cost; ca.rseg = rs; ca.nsegs = nsg; }
+            }
+        };
         const size_t smem = fixed + (size_t)OC * bs * VW * 4;
         // TMA views: right planes [nb*H*6][Wp] u32 (box 6 x BW), left records [nb*H][W*8] u32 (box 1 x 256)
         CUtensorMap tmR, tmL;
@@ -2212,15 +2262,16 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         if (rc != SVB_OK) return rc;
         rc = svb_make_tmap_2d_u32(&tmL, ldesc, (uint64_t)g.W * 8, (uint64_t)nb * g.H, (uint64_t)g.W * 32, CK_PC * 8, 1);
         if (rc != SVB_OK) return rc;
-        dim3 grid(ca.nstrips * ca.nsegs, njobs);
         ProfScope ps(h, CAT_COST, st);
         const bool xtra = ca.accum || g.mode == SVB_MODE_HH4;
-#define LAUNCH_COST(F, X) do { \
-            SVB_CUDA(cudaFuncSetAttribute(k_cost<NP, F, X>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-            k_cost<NP, F, X><<<grid, CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv); } while (0)
-#define LAUNCH_COSTG(F, X) do { \
-            SVB_CUDA(cudaFuncSetAttribute(k_costg<NP, F, X>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-            k_costg<NP, F, X><<<grid, CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv); } while (0)
+        int per_sm = 0;
+#define LAUNCH_COST_K(K) do { \
+            SVB_CUDA(cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, K, CK_WARPS * 32, smem)); \
+            plan_segs(per_sm); \
+            K<<<dim3(ca.nstrips * ca.nsegs, njobs), CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv); } while (0)
+#define LAUNCH_COST(F, X) LAUNCH_COST_K((k_cost<NP, F, X>))
+#define LAUNCH_COSTG(F, X) LAUNCH_COST_K((k_costg<NP, F, X>))
         if constexpr (GROUPED) {
             if (g.D == g.Dp) { if (xtra) LAUNCH_COSTG(true, true); else LAUNCH_COSTG(true, false); }
             else             { if (xtra) LAUNCH_COSTG(false, true); else LAUNCH_COSTG(false, false); }
@@ -2230,6 +2281,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         }
 #undef LAUNCH_COSTG
 #undef LAUNCH_COST
+#undef LAUNCH_COST_K
         SVB_LAUNCH_CHECK(); h->launches++;
     }
     }

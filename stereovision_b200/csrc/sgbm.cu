@@ -312,6 +312,59 @@ __device__ __forceinline__ void vec_st(uint32_t* p, int lane, const uint32_t (&v
     }
 }
 
+// Shared-memory vector accesses by 32-bit shared-space address (no generic-address arithmetic in the rows' loop).
+// volatile: kept in order with the progress-flag accesses (also volatile asm); the immediate offset is folded.
+template <int NP, int OFS, int I = 0>
+__device__ __forceinline__ void lds_vec(uint32_t sa, uint32_t (&v)[NP])
+{
+    if constexpr (NP % 4 == 0) {
+        if constexpr (I < NP / 4) {
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4 + %5];"
+                         : "=r"(v[4 * I]), "=r"(v[4 * I + 1]), "=r"(v[4 * I + 2]), "=r"(v[4 * I + 3]) : "r"(sa), "n"(OFS + 16 * I));
+            lds_vec<NP, OFS, I + 1>(sa, v);
+        }
+    } else if constexpr (NP % 2 == 0) {
+        if constexpr (I < NP / 2) {
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2 + %3];" : "=r"(v[2 * I]), "=r"(v[2 * I + 1]) : "r"(sa), "n"(OFS + 8 * I));
+            lds_vec<NP, OFS, I + 1>(sa, v);
+        }
+    } else if constexpr (I < NP) {
+        asm volatile("ld.shared.u32 %0, [%1 + %2];" : "=r"(v[I]) : "r"(sa), "n"(OFS + 4 * I));
+        lds_vec<NP, OFS, I + 1>(sa, v);
+    }
+}
+template <int NP, int OFS, int I = 0>
+__device__ __forceinline__ void sts_vec(uint32_t sa, const uint32_t (&v)[NP])
+{
+    if constexpr (NP % 4 == 0) {
+        if constexpr (I < NP / 4) {
+            asm volatile("st.shared.v4.u32 [%0 + %1], {%2, %3, %4, %5};" ::"r"(sa), "n"(OFS + 16 * I), "r"(v[4 * I]),
+                         "r"(v[4 * I + 1]), "r"(v[4 * I + 2]), "r"(v[4 * I + 3]));
+            sts_vec<NP, OFS, I + 1>(sa, v);
+        }
+    } else if constexpr (NP % 2 == 0) {
+        if constexpr (I < NP / 2) {
+            asm volatile("st.shared.v2.u32 [%0 + %1], {%2, %3};" ::"r"(sa), "n"(OFS + 8 * I), "r"(v[2 * I]), "r"(v[2 * I + 1]));
+            sts_vec<NP, OFS, I + 1>(sa, v);
+        }
+    } else if constexpr (I < NP) {
+        asm volatile("st.shared.u32 [%0 + %1], %2;" ::"r"(sa), "n"(OFS + 4 * I), "r"(v[I]));
+        sts_vec<NP, OFS, I + 1>(sa, v);
+    }
+}
+template <int OFS>
+__device__ __forceinline__ uint32_t lds_u32(uint32_t sa)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1 + %2];" : "=r"(v) : "r"(sa), "n"(OFS));
+    return v;
+}
+template <int OFS>
+__device__ __forceinline__ void sts_u32(uint32_t sa, uint32_t v)
+{
+    asm volatile("st.shared.u32 [%0 + %1], %2;" ::"r"(sa), "n"(OFS), "r"(v));
+}
+
 // ------------------------------------------------------------------------------------------
 // k_cost: one CTA walks DOWN a strip of columns of one job (a row segment of it).  Per image
 // row one elected thread asks the TMA for two tiles (cp.async.bulk.tensor, one row ahead,
@@ -336,6 +389,12 @@ __device__ __forceinline__ void vec_st(uint32_t* p, int lane, const uint32_t (&v
 #ifndef CK_SHARE
 #define CK_SHARE 4             // k_cost: from this many words per lane on, a warp's two adjacent columns share one load of the right
                                // descriptor planes (1080p/D256 13.87 -> 13.77 ms, 480p/D320 4.11 -> 3.80; slower at D128: 8.06 -> 8.76)
+#endif
+#ifndef CK_UNROLL2_NP
+#define CK_UNROLL2_NP 4        // k_cost: row loop unrolled by two (constant staging buffer index) up to this many words per lane
+#endif
+#ifndef CK_BS5
+#define CK_BS5 1               // k_cost instances with blockSize 5 as a compile-time constant
 #endif
 #ifndef CK_MAXSEG
 #define CK_MAXSEG 16           // most row segments per job (1 = never cut a job's rows)
@@ -366,6 +425,8 @@ __device__ __forceinline__ uint32_t bt_pix(const uint4& l0, const uint4& l1, uin
     return pix + ((__vminu2(c0, c1) >> 2) & 0x3fff3fffu);
 }
 
+template <int V> struct CkInt { __device__ constexpr operator int() const { return V; } };   // a compile-time int as a lambda argument
+
 struct CostArgs {
     int OC;                    // output columns per strip = CK_PC - 2r (or less when the ring is large)
     int nstrips, rseg, nsegs;  // strips per row, rows per segment, segments per job
@@ -375,7 +436,9 @@ struct CostArgs {
 
 // XTRA: the rare variants (colour accumulation passes, MODE_HH4's zero rows) live in their own instance so that
 // the plain kernel keeps its code and register allocation (13.8 vs 14.5 ms per 32 pairs at 1080p/D256 otherwise)
-template <int NP, bool FULL, bool XTRA>
+// BS: blockSize as a compile-time constant (0 = read it from the geometry): the box loop unrolls, its loop control and
+// register copies go away (k_cost runs ~75 % issue-bound)
+template <int NP, bool FULL, bool XTRA, int BS>
 __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ CUtensorMap tmR,
                                                         const __grid_constant__ CUtensorMap tmL,
                                                         SgbmGeo g, CostArgs ca, uint32_t* __restrict__ vol)
@@ -384,7 +447,7 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
     extern __shared__ __align__(128) uint32_t smem[];
     __shared__ __align__(8) uint64_t mbar[2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int r = g.r, bs = 2 * r + 1, OC = ca.OC, PC = OC + 2 * r;
+    const int r = BS ? BS / 2 : g.r, bs = BS ? BS : 2 * r + 1, OC = ca.OC, PC = OC + 2 * r;
     uint32_t* stage = smem;                                  // [2][NBLK][6][BW] (each box padded to BLKW words)
     uint32_t* lstage = stage + 2 * NBLK * BLKW;                   // [2][CK_PC][8]
     uint32_t* pixbuf = lstage + 2 * CK_PC * 8;               // [2][CK_PC][VW]
@@ -455,9 +518,14 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
     const bool two = oc0 + 1 < OC;
     const bool pair = 2 * warp + 1 < PC && eoff[1] == eoff[0] + 1;   // not at a clamped image border
     int slot = 0;
+    // volume vector of this warp's first output column in the row being emitted (the first one is ya, at it == bs - 1)
+    uint32_t* drow = vol + (((size_t)job * g.rowsMax + (ya - ys)) * w1 + xs + oc0) * VW;
 
-    for (int v = v0; v <= v1; ++v) {
-        const int it = v - v0, buf = it & 1;
+    // one input row.  Up to 4 words per lane the row loop is unrolled by two and the staging buffer index is a constant
+    // in each copy (720p/D128 7.27 -> 6.75 ms); with more words the doubled loop body no longer pays (480p/D320 3.47 -> 3.77)
+    auto do_row = [&](const int v, auto bufc) {
+        const int buf = bufc;
+        const int it = v - v0;
         const uint32_t* st = stage + buf * NBLK * BLKW;
         const uint32_t* ls = lstage + buf * CK_PC * 8;
         uint32_t* pb = pixbuf + buf * CK_PC * VW;
@@ -517,7 +585,8 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
             uint32_t first[NP];
 #pragma unroll
             for (int k = 0; k < NP; ++k) first[k] = hs0[k];
-            for (int j = 1; j < bs; ++j) {
+#pragma unroll
+            for (int j = 1; j < (BS ? BS : bs); ++j) {
                 vec_ld<NP>(pcol + j * VW, lane, t, LdPlain());
 #pragma unroll
                 for (int k = 0; k < NP; ++k) hs0[k] += t[k];
@@ -551,7 +620,7 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
                     for (int k = 0; k < NP; ++k) acc[1][k] += hs1[k];
                 }
                 if (emit && xc < w1) {
-                    uint32_t* dst = vol + (((size_t)job * g.rowsMax + (y - ys)) * w1 + xc) * VW;
+                    uint32_t* dst = drow + cc * VW;
                     uint32_t o[NP];
                     if constexpr (XTRA) {
                         // MODE_HH4: cv2 leaves the rows whose window reaches below the image at cost 0 (oracle/sgbm_oracle.c)
@@ -570,7 +639,16 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
                 }
             }
         }
+        if (it >= bs - 1) drow += (size_t)w1 * VW;
         slot = slot + 1 == bs ? 0 : slot + 1;
+    };
+    if constexpr (NP <= CK_UNROLL2_NP) {
+        for (int v = v0; v <= v1; v += 2) {
+            do_row(v, CkInt<0>());
+            if (v + 1 <= v1) do_row(v + 1, CkInt<1>());
+        }
+    } else {
+        for (int v = v0; v <= v1; ++v) do_row(v, (v - v0) & 1);
     }
 }
 
@@ -585,7 +663,7 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_cost(const __grid_constant__ 
 __host__ __device__ constexpr int ckg_pc(int NP) { return CK_WARPS * (4 / NP); }             // pixel-cost columns per strip
 __host__ __device__ constexpr int ckg_se(int NP) { return 32 * NP + ckg_pc(NP) + 8; }        // staged entries per plane (<= 256)
 __host__ __device__ constexpr int ckg_blkw(int NP) { return (6 * ckg_se(NP) + 31) & ~31; }   // words per staged box, 128-byte padded
-template <int NP, bool FULL, bool XTRA>
+template <int NP, bool FULL, bool XTRA, int BS>
 __global__ void __launch_bounds__(CK_WARPS * 32) k_costg(const __grid_constant__ CUtensorMap tmR,
                                                          const __grid_constant__ CUtensorMap tmL,
                                                          SgbmGeo g, CostArgs ca, uint32_t* __restrict__ vol)
@@ -595,7 +673,7 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_costg(const __grid_constant__
     extern __shared__ __align__(128) uint32_t smem[];
     __shared__ __align__(8) uint64_t mbar[2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, grp = lane / WD, l = lane % WD;
-    const int r = g.r, bs = 2 * r + 1, OC = ca.OC, PC = OC + 2 * r;
+    const int r = BS ? BS / 2 : g.r, bs = BS ? BS : 2 * r + 1, OC = ca.OC, PC = OC + 2 * r;
     uint32_t* stage = smem;                                  // [2][6][SE] (each box padded to BLKW words)
     uint32_t* lstage = stage + 2 * BLKW;                     // [2][PCG][8]
     uint32_t* pixbuf = lstage + 2 * PCG * 8;                 // [2][PCG][VW]
@@ -650,9 +728,12 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_costg(const __grid_constant__
     const bool has_pix = c < PC, has_out = c < OC;
     const int xc = xs + c;                                   // output column in the cost domain
     int slot = 0;
+    // this lane's words of the volume vector being emitted (the first row is ya, at it == bs - 1)
+    uint32_t* drow = vol + (((size_t)job * g.rowsMax + (ya - ys)) * w1 + xc) * VW + 4 * l;
 
-    for (int v = v0; v <= v1; ++v) {
-        const int it = v - v0, buf = it & 1;
+    auto do_row = [&](const int v, auto bufc) {              // as in k_cost: row loop unrolled by two, constant buffer index
+        const int buf = bufc;
+        const int it = v - v0;
         const uint32_t* st = stage + buf * BLKW;
         const uint32_t* ls = lstage + buf * PCG * 8;
         uint32_t* pb = pixbuf + buf * PCG * VW;
@@ -691,7 +772,8 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_costg(const __grid_constant__
         if (has_out) {
             const uint32_t* pcol = pb + c * VW + 4 * l;
             uint4 hs = *reinterpret_cast<const uint4*>(pcol);
-            for (int j = 1; j < bs; ++j) {
+#pragma unroll
+            for (int j = 1; j < (BS ? BS : bs); ++j) {
                 const uint4 t = *reinterpret_cast<const uint4*>(pcol + j * VW);
                 hs.x += t.x; hs.y += t.y; hs.z += t.z; hs.w += t.w;
             }
@@ -704,7 +786,7 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_costg(const __grid_constant__
             acc[0] += hs.x; acc[1] += hs.y; acc[2] += hs.z; acc[3] += hs.w;
             const int y = v - r;                             // output row once the window is complete
             if (it >= bs - 1 && xc < w1) {
-                uint32_t* dst = vol + (((size_t)job * g.rowsMax + (y - ys)) * w1 + xc) * VW + 4 * l;
+                uint32_t* dst = drow;
                 uint32_t o[4];
                 if constexpr (XTRA) {
                     // MODE_HH4: cv2 leaves the rows whose window reaches below the image at cost 0 (oracle/sgbm_oracle.c)
@@ -724,7 +806,12 @@ __global__ void __launch_bounds__(CK_WARPS * 32) k_costg(const __grid_constant__
                 *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
             }
         }
+        if (it >= bs - 1) drow += (size_t)w1 * VW;
         slot = slot + 1 == bs ? 0 : slot + 1;
+    };
+    for (int v = v0; v <= v1; v += 2) {
+        do_row(v, CkInt<0>());
+        if (v + 1 <= v1) do_row(v + 1, CkInt<1>());
     }
 }
 
@@ -825,59 +912,6 @@ __device__ __forceinline__ void cp_async_vec_s(uint32_t sdst, const uint32_t* gs
         for (int i = 0; i < NP; ++i)
             asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst + 4 * i), "l"(gsrc + i));
     }
-}
-
-// Shared-memory vector accesses by 32-bit shared-space address (no generic-address arithmetic in the rows' loop).
-// volatile: kept in order with the progress-flag accesses (also volatile asm); the immediate offset is folded.
-template <int NP, int OFS, int I = 0>
-__device__ __forceinline__ void lds_vec(uint32_t sa, uint32_t (&v)[NP])
-{
-    if constexpr (NP % 4 == 0) {
-        if constexpr (I < NP / 4) {
-            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4 + %5];"
-                         : "=r"(v[4 * I]), "=r"(v[4 * I + 1]), "=r"(v[4 * I + 2]), "=r"(v[4 * I + 3]) : "r"(sa), "n"(OFS + 16 * I));
-            lds_vec<NP, OFS, I + 1>(sa, v);
-        }
-    } else if constexpr (NP % 2 == 0) {
-        if constexpr (I < NP / 2) {
-            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2 + %3];" : "=r"(v[2 * I]), "=r"(v[2 * I + 1]) : "r"(sa), "n"(OFS + 8 * I));
-            lds_vec<NP, OFS, I + 1>(sa, v);
-        }
-    } else if constexpr (I < NP) {
-        asm volatile("ld.shared.u32 %0, [%1 + %2];" : "=r"(v[I]) : "r"(sa), "n"(OFS + 4 * I));
-        lds_vec<NP, OFS, I + 1>(sa, v);
-    }
-}
-template <int NP, int OFS, int I = 0>
-__device__ __forceinline__ void sts_vec(uint32_t sa, const uint32_t (&v)[NP])
-{
-    if constexpr (NP % 4 == 0) {
-        if constexpr (I < NP / 4) {
-            asm volatile("st.shared.v4.u32 [%0 + %1], {%2, %3, %4, %5};" ::"r"(sa), "n"(OFS + 16 * I), "r"(v[4 * I]),
-                         "r"(v[4 * I + 1]), "r"(v[4 * I + 2]), "r"(v[4 * I + 3]));
-            sts_vec<NP, OFS, I + 1>(sa, v);
-        }
-    } else if constexpr (NP % 2 == 0) {
-        if constexpr (I < NP / 2) {
-            asm volatile("st.shared.v2.u32 [%0 + %1], {%2, %3};" ::"r"(sa), "n"(OFS + 8 * I), "r"(v[2 * I]), "r"(v[2 * I + 1]));
-            sts_vec<NP, OFS, I + 1>(sa, v);
-        }
-    } else if constexpr (I < NP) {
-        asm volatile("st.shared.u32 [%0 + %1], %2;" ::"r"(sa), "n"(OFS + 4 * I), "r"(v[I]));
-        sts_vec<NP, OFS, I + 1>(sa, v);
-    }
-}
-template <int OFS>
-__device__ __forceinline__ uint32_t lds_u32(uint32_t sa)
-{
-    uint32_t v;
-    asm volatile("ld.shared.u32 %0, [%1 + %2];" : "=r"(v) : "r"(sa), "n"(OFS));
-    return v;
-}
-template <int OFS>
-__device__ __forceinline__ void sts_u32(uint32_t sa, uint32_t v)
-{
-    asm volatile("st.shared.u32 [%0 + %1], %2;" ::"r"(sa), "n"(OFS), "r"(v));
 }
 
 // Uniqueness threshold of A.4: a disparity d counts against the winner iff S[d] < th.
@@ -2270,8 +2304,10 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
             SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, K, CK_WARPS * 32, smem)); \
             plan_segs(per_sm); \
             K<<<dim3(ca.nstrips * ca.nsegs, njobs), CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv); } while (0)
-#define LAUNCH_COST(F, X) LAUNCH_COST_K((k_cost<NP, F, X>))
-#define LAUNCH_COSTG(F, X) LAUNCH_COST_K((k_costg<NP, F, X>))
+#define LAUNCH_COST(F, X) do { if (CK_BS5 && !(X) && g.bs == 5) LAUNCH_COST_K((k_cost<NP, F, false, 5>)); \
+                               else LAUNCH_COST_K((k_cost<NP, F, X, 0>)); } while (0)
+#define LAUNCH_COSTG(F, X) do { if (CK_BS5 && !(X) && g.bs == 5) LAUNCH_COST_K((k_costg<NP, F, false, 5>)); \
+                                else LAUNCH_COST_K((k_costg<NP, F, X, 0>)); } while (0)
         if constexpr (GROUPED) {
             if (g.D == g.Dp) { if (xtra) LAUNCH_COSTG(true, true); else LAUNCH_COSTG(true, false); }
             else             { if (xtra) LAUNCH_COSTG(false, true); else LAUNCH_COSTG(false, false); }

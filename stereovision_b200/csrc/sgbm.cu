@@ -393,8 +393,8 @@ __device__ __forceinline__ void sts_u32(uint32_t sa, uint32_t v)
 #ifndef CK_UNROLL2_NP
 #define CK_UNROLL2_NP 4        // k_cost: row loop unrolled by two (constant staging buffer index) up to this many words per lane
 #endif
-#ifndef CK_BS5
-#define CK_BS5 1               // k_cost instances with blockSize 5 as a compile-time constant
+#ifndef CK_BSCONST
+#define CK_BSCONST 1           // k_cost / k_costg instances with blockSize 3 / 5 / 7 / 9 as a compile-time constant
 #endif
 #ifndef CK_MAXSEG
 #define CK_MAXSEG 16           // most row segments per job (1 = never cut a job's rows)
@@ -2304,10 +2304,16 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
             SVB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, K, CK_WARPS * 32, smem)); \
             plan_segs(per_sm); \
             K<<<dim3(ca.nstrips * ca.nsegs, njobs), CK_WARPS * 32, smem, st>>>(tmR, tmL, g, ca, Cv); } while (0)
-#define LAUNCH_COST(F, X) do { if (CK_BS5 && !(X) && g.bs == 5) LAUNCH_COST_K((k_cost<NP, F, false, 5>)); \
-                               else LAUNCH_COST_K((k_cost<NP, F, X, 0>)); } while (0)
-#define LAUNCH_COSTG(F, X) do { if (CK_BS5 && !(X) && g.bs == 5) LAUNCH_COST_K((k_costg<NP, F, false, 5>)); \
-                                else LAUNCH_COST_K((k_costg<NP, F, X, 0>)); } while (0)
+        // blockSize 3 / 5 / 7 / 9 (the reference's scripts use 7, and 5 at half scale) have instances with the size built in
+#define LAUNCH_COST_BS(KERN, F, X) do { \
+            const int cbs = (CK_BSCONST && !(X)) ? g.bs : 0; \
+            if (cbs == 5) LAUNCH_COST_K((KERN<NP, F, false, 5>)); \
+            else if (cbs == 7) LAUNCH_COST_K((KERN<NP, F, false, 7>)); \
+            else if (cbs == 3) LAUNCH_COST_K((KERN<NP, F, false, 3>)); \
+            else if (cbs == 9) LAUNCH_COST_K((KERN<NP, F, false, 9>)); \
+            else LAUNCH_COST_K((KERN<NP, F, X, 0>)); } while (0)
+#define LAUNCH_COST(F, X) LAUNCH_COST_BS(k_cost, F, X)
+#define LAUNCH_COSTG(F, X) LAUNCH_COST_BS(k_costg, F, X)
         if constexpr (GROUPED) {
             if (g.D == g.Dp) { if (xtra) LAUNCH_COSTG(true, true); else LAUNCH_COSTG(true, false); }
             else             { if (xtra) LAUNCH_COSTG(false, true); else LAUNCH_COSTG(false, false); }
@@ -2317,6 +2323,7 @@ static int run_chunk(svb_sgbm* h, const SgbmGeo& g, const SgbmLayout& L, const u
         }
 #undef LAUNCH_COSTG
 #undef LAUNCH_COST
+#undef LAUNCH_COST_BS
 #undef LAUNCH_COST_K
         SVB_LAUNCH_CHECK(); h->launches++;
     }

@@ -255,3 +255,18 @@ def test_sgbm_3way_ties_and_min_disparity_vs_oracle():
         got = svb.StereoSGBM_create(**prm).compute(l, r)
         ref = oracle.sgbm_compute(l, r, **prm)
         assert np.array_equal(got, ref), (H, W, prm, int((got != ref).sum()))
+
+
+@pytest.mark.parametrize("D,bs,mode", [(256, 3, 1), (256, 7, 0), (256, 9, 1), (320, 7, 2), (384, 3, 0), (512, 7, 1), (208, 9, 0),
+                                       (64, 7, 0), (48, 9, 2), (128, 7, 1), (256, 11, 0)])
+def test_sgbm_block_sizes_at_wide_vectors_vs_oracle(D, bs, mode):
+    """The cost kernels have instances with blockSize 3 / 5 / 7 / 9 built in (unrolled box sums) and a generic one
+    (blockSize 11 here): every vector width they are dispatched at, including a padded one (208)."""
+    _torch()
+    H, W = 40, D + 90
+    l, r, _ = make_pair(H, W, D, seed=40 + bs)
+    prm = dict(minDisparity=0, numDisparities=D, blockSize=bs, P1=8 * bs * bs, P2=32 * bs * bs, disp12MaxDiff=1,
+               preFilterCap=63, uniquenessRatio=10, speckleWindowSize=50, speckleRange=2, mode=mode)
+    got = svb.StereoSGBM_create(**prm).compute(np.stack([l, l]), np.stack([r, r]))
+    ref = oracle.sgbm_compute(l, r, **prm)
+    assert np.array_equal(got[0], ref) and np.array_equal(got[1], ref)

@@ -517,6 +517,12 @@ extern "C" int svb_bm_last_launches(const svb_bm_t* h) { return h ? h->launches 
 #define BMG_PC 128                         // window columns per strip: BMG_NP passes of 4 per warp
 #endif
 #define BMG_NP (BMG_PC / (4 * BMG_WARPS))
+#ifndef BMG_STAGE
+#define BMG_STAGE 1              // right descriptors of the strip staged in a shared-memory ring of blockSize + 2 rows
+#endif
+// words per staged plane: the strip's columns span <= (BMG_PC - 1) / 2 + 1 words, a vector 32 more; == 2 (mod 4) so that the
+// four columns of a warp pass (two parities x two adjacent words) fall on different banks
+#define BMG_NWP (((BMG_PC / 2 + 32 + 1) & ~3) + 2)
 template <bool COST>
 __global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restrict__ lp, const uint32_t* __restrict__ rdesc,
                                                          const uint8_t* __restrict__ okmap, BmGeo g, int OC, int nstrips,
@@ -526,6 +532,7 @@ __global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restri
     extern __shared__ __align__(16) uint32_t smem[];
     uint32_t* vbuf = smem;                                   // [2][BMG_PC][VW] vertical sums of the current row
     uint32_t* scr = smem + 2 * BMG_PC * VW;                  // [BMG_WARPS][4][VW] per-group scratch for the subpixel taps
+    uint32_t* rring = scr + 4 * BMG_WARPS * VW;              // [bs + 2][4][BMG_NWP] right descriptors of the last rows (BMG_STAGE)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, grp = lane / WD, l = lane % WD;
     const int strip = blockIdx.x % nstrips, seg = blockIdx.x / nstrips, b = blockIdx.z;
     const int r = g.r, bs = 2 * r + 1, D = g.D, W = g.W, H = g.H;
@@ -535,6 +542,8 @@ __global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restri
 
     // row-invariant addressing of this group's two window columns (A.6: left column and right start clamp separately)
     int lc[BMG_NP], pl[BMG_NP], m[BMG_NP][4];
+    // BMG_STAGE: first descriptor word the strip needs (its first column's last disparity); m[][] then index the staged row
+    const int wlo = max(((min(max(xs - r + g.rofs, 0), W - D) + D - 1) >> 1) - 31, 0);
 #pragma unroll
     for (int p = 0; p < BMG_NP; ++p) {
         const int j = xs - r + 4 * BMG_NP * warp + 4 * p + grp;
@@ -543,7 +552,10 @@ __global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restri
         const int xr0 = rs + D - 1;                          // right column of disparity index d' = 0
         pl[p] = (xr0 & 1) * g.Wh;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) m[p][k] = max((xr0 >> 1) - (4 * l + k), 0);
+        for (int k = 0; k < 4; ++k) {
+            m[p][k] = max((xr0 >> 1) - (4 * l + k), 0);
+            if (BMG_STAGE) m[p][k] += (xr0 & 1) * BMG_NWP - wlo;
+        }
     }
     uint32_t V[BMG_NP][4];
 #pragma unroll
@@ -570,10 +582,48 @@ __global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restri
     uint32_t* sv = scr + (size_t)(4 * warp + grp) * VW;
 
     const int v0 = ya - r, v1 = yb - 1 + r;                  // input rows: all inside the image
+    // BMG_STAGE: row v of the four descriptor planes, words wlo .. wlo + BMG_NWP - 1, into ring slot (v - v0) % (bs + 2); the
+    // row is staged one iteration ahead, and the slot it takes was last read (as row v - bs) two barriers ago
+    const int nslot = bs + 2;
+    auto stage_row = [&](int v, int slot) {
+        if (threadIdx.x < 4 * BMG_NWP) {
+            const int q = threadIdx.x / BMG_NWP, i = threadIdx.x - q * BMG_NWP;
+            rring[(slot * 4 + q) * BMG_NWP + i] = __ldg(rimg + ((size_t)v * 4 + q) * g.Wh + min(wlo + i, g.Wh - 1));
+        }
+    };
+    int snew = 0;
+    if (BMG_STAGE) {
+        stage_row(v0, 0);
+        __syncthreads();
+    }
     for (int v = v0; v <= v1; ++v) {
         const int it = v - v0, buf = it & 1;
         // ---- vertical phase: V += |L - R|(row v) - |L - R|(row v - bs), two passes of four columns
-        {
+        if (BMG_STAGE) {
+            const int sn = snew, so = sn + 2 >= nslot ? sn + 2 - nslot : sn + 2, sx = sn + 1 == nslot ? 0 : sn + 1;
+            snew = sx;
+            if (v + 1 <= v1) stage_row(v + 1, sx);
+            const uint8_t* lrow = limg + (size_t)v * W;
+            const uint32_t* rn = rring + sn * 4 * BMG_NWP;
+            const uint32_t* ro = rring + so * 4 * BMG_NWP;
+            uint32_t* vb = vbuf + ((size_t)buf * BMG_PC + 4 * BMG_NP * warp + grp) * VW + 4 * l;
+#pragma unroll
+            for (int p = 0; p < BMG_NP; ++p) {
+                {
+                    const int u = lrow[lc[p]];
+                    const uint32_t U2 = pk_dup((uint32_t)u), nU2 = pk_dup((uint32_t)(-u));
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) V[p][k] += bm_absdiff(U2, nU2, rn[m[p][k]], rn[m[p][k] + 2 * BMG_NWP]);
+                }
+                if (it >= bs) {
+                    const int u = (lrow - (size_t)bs * W)[lc[p]];
+                    const uint32_t U2 = pk_dup((uint32_t)u), nU2 = pk_dup((uint32_t)(-u));
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) V[p][k] -= bm_absdiff(U2, nU2, ro[m[p][k]], ro[m[p][k] + 2 * BMG_NWP]);
+                }
+                *reinterpret_cast<uint4*>(vb + 4 * p * VW) = make_uint4(V[p][0], V[p][1], V[p][2], V[p][3]);
+            }
+        } else {
             const uint8_t* lrow = limg + (size_t)v * W;
             const uint32_t* rrow = rimg + (size_t)v * 4 * g.Wh;
             uint32_t* vb = vbuf + ((size_t)buf * BMG_PC + 4 * BMG_NP * warp + grp) * VW + 4 * l;
@@ -674,7 +724,7 @@ static int bm2g_launch(const BmGeo& g, const uint8_t* lp, const uint32_t* rdesc,
     while ((long long)nstrips * nb * nsegs < 4LL * num_sms && rows / (nsegs * 2) >= 4 * bs) nsegs *= 2;
     const int rseg = svb_ceil_div(rows, nsegs);
     nsegs = svb_ceil_div(rows, rseg);
-    const size_t smem = ((size_t)2 * BMG_PC + 4 * BMG_WARPS) * 32 * 4;
+    const size_t smem = ((size_t)2 * BMG_PC + 4 * BMG_WARPS) * 32 * 4 + (BMG_STAGE ? (size_t)(bs + 2) * 4 * BMG_NWP * 4 : 0);
     if (cost) {
         SVB_CUDA(cudaFuncSetAttribute(k_bm2g<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_bm2g<true><<<dim3(nstrips * nsegs, 1, nb), BMG_WARPS * 32, smem, st>>>(lp, rdesc, tex, g, OC, nstrips, rseg, disp, cost);

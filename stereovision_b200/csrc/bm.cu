@@ -542,8 +542,11 @@ __global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restri
 
     // row-invariant addressing of this group's two window columns (A.6: left column and right start clamp separately)
     int lc[BMG_NP], pl[BMG_NP], m[BMG_NP][4];
-    // BMG_STAGE: first descriptor word the strip needs (its first column's last disparity); m[][] then index the staged row
-    const int wlo = max(((min(max(xs - r + g.rofs, 0), W - D) + D - 1) >> 1) - 31, 0);
+    // BMG_STAGE: first descriptor word the strip needs (its first column's last disparity; negative where numDisparities < 64
+    // leaves pad lanes -- the staged row holds word max(w, 0) there, what the clamp in m[][] reads).  Word k of a lane is then
+    // mb[p] - 4k bytes into the staged row with no clamp of its own: two registers instead of eight
+    const int wlo = ((min(max(xs - r + g.rofs, 0), W - D) + D - 1) >> 1) - 31;
+    int mb[BMG_NP];
 #pragma unroll
     for (int p = 0; p < BMG_NP; ++p) {
         const int j = xs - r + 4 * BMG_NP * warp + 4 * p + grp;
@@ -552,10 +555,8 @@ __global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restri
         const int xr0 = rs + D - 1;                          // right column of disparity index d' = 0
         pl[p] = (xr0 & 1) * g.Wh;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            m[p][k] = max((xr0 >> 1) - (4 * l + k), 0);
-            if (BMG_STAGE) m[p][k] += (xr0 & 1) * BMG_NWP - wlo;
-        }
+        for (int k = 0; k < 4; ++k) m[p][k] = max((xr0 >> 1) - (4 * l + k), 0);
+        mb[p] = ((xr0 & 1) * BMG_NWP + (xr0 >> 1) - 4 * l - wlo) * 4;
     }
     uint32_t V[BMG_NP][4];
 #pragma unroll
@@ -588,7 +589,7 @@ __global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restri
     auto stage_row = [&](int v, int slot) {
         if (threadIdx.x < 4 * BMG_NWP) {
             const int q = threadIdx.x / BMG_NWP, i = threadIdx.x - q * BMG_NWP;
-            rring[(slot * 4 + q) * BMG_NWP + i] = __ldg(rimg + ((size_t)v * 4 + q) * g.Wh + min(wlo + i, g.Wh - 1));
+            rring[(slot * 4 + q) * BMG_NWP + i] = __ldg(rimg + ((size_t)v * 4 + q) * g.Wh + min(max(wlo + i, 0), g.Wh - 1));
         }
     };
     int snew = 0;
@@ -604,8 +605,9 @@ __global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restri
             snew = sx;
             if (v + 1 <= v1) stage_row(v + 1, sx);
             const uint8_t* lrow = limg + (size_t)v * W;
-            const uint32_t* rn = rring + sn * 4 * BMG_NWP;
-            const uint32_t* ro = rring + so * 4 * BMG_NWP;
+            const char* rn = reinterpret_cast<const char*>(rring + sn * 4 * BMG_NWP);
+            const char* ro = reinterpret_cast<const char*>(rring + so * 4 * BMG_NWP);
+            auto rd = [](const char* row, int ofs) { return *reinterpret_cast<const uint32_t*>(row + ofs); };
             uint32_t* vb = vbuf + ((size_t)buf * BMG_PC + 4 * BMG_NP * warp + grp) * VW + 4 * l;
 #pragma unroll
             for (int p = 0; p < BMG_NP; ++p) {
@@ -613,13 +615,15 @@ __global__ void __launch_bounds__(BMG_WARPS * 32) k_bm2g(const uint8_t* __restri
                     const int u = lrow[lc[p]];
                     const uint32_t U2 = pk_dup((uint32_t)u), nU2 = pk_dup((uint32_t)(-u));
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) V[p][k] += bm_absdiff(U2, nU2, rn[m[p][k]], rn[m[p][k] + 2 * BMG_NWP]);
+                    for (int k = 0; k < 4; ++k)
+                        V[p][k] += bm_absdiff(U2, nU2, rd(rn, mb[p] - 4 * k), rd(rn, mb[p] - 4 * k + 2 * BMG_NWP * 4));
                 }
                 if (it >= bs) {
                     const int u = (lrow - (size_t)bs * W)[lc[p]];
                     const uint32_t U2 = pk_dup((uint32_t)u), nU2 = pk_dup((uint32_t)(-u));
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) V[p][k] -= bm_absdiff(U2, nU2, ro[m[p][k]], ro[m[p][k] + 2 * BMG_NWP]);
+                    for (int k = 0; k < 4; ++k)
+                        V[p][k] -= bm_absdiff(U2, nU2, rd(ro, mb[p] - 4 * k), rd(ro, mb[p] - 4 * k + 2 * BMG_NWP * 4));
                 }
                 *reinterpret_cast<uint4*>(vb + 4 * p * VW) = make_uint4(V[p][0], V[p][1], V[p][2], V[p][3]);
             }

@@ -544,6 +544,9 @@ __global__ void k_bilat_lut(FuseState* __restrict__ fs, float gc, float min_max 
 
 #define BT_X 32
 #define BT_Y 8
+// DD: the window diameter as a compile-time constant (0 = bt.d): both loops unroll, the circle test folds away and every tap is
+// one shared-memory load at an immediate offset and one constant-bank operand -- same taps in the same order
+template <int DD>
 __global__ void __launch_bounds__(BT_X * BT_Y) k_bilateral(const float* __restrict__ fused, int H, int W, BilatTaps bt,
                                                           const FuseState* __restrict__ fs, unsigned char* __restrict__ out8,
                                                           float* __restrict__ outf, int clip255)
@@ -552,7 +555,7 @@ __global__ void __launch_bounds__(BT_X * BT_Y) k_bilateral(const float* __restri
     __shared__ float lut[LUT_BINS + 2];
     const int b = blockIdx.z;
     const FuseState* s = fs + b;
-    const int r = bt.d / 2, tw = BT_X + 2 * r, th = BT_Y + 2 * r;
+    const int d = DD ? DD : bt.d, r = d / 2, tw = BT_X + 2 * r, th = BT_Y + 2 * r;
     const int x0 = blockIdx.x * BT_X, y0 = blockIdx.y * BT_Y;
     const int tid = threadIdx.y * BT_X + threadIdx.x;
     const bool filter = s->filter != 0;
@@ -572,10 +575,13 @@ __global__ void __launch_bounds__(BT_X * BT_Y) k_bilateral(const float* __restri
         const float c = tile[threadIdx.y + r][threadIdx.x + r];
         const float scale = s->scale;
         float sum = 0.f, wsum = 0.f;
-        for (int i = 0; i < bt.d; ++i)
-            for (int j = 0; j < bt.d; ++j) {
-                const float sw = bt.sw[i * bt.d + j];
-                if (sw < 0.f) continue;
+#pragma unroll
+        for (int i = 0; i < (DD ? DD : d); ++i)
+#pragma unroll
+            for (int j = 0; j < (DD ? DD : d); ++j) {
+                if (DD && (i - DD / 2) * (i - DD / 2) + (j - DD / 2) * (j - DD / 2) > (DD / 2) * (DD / 2)) continue;   // make_bilat_taps' circle
+                const float sw = bt.sw[i * d + j];
+                if (!DD && sw < 0.f) continue;
                 const float v = tile[threadIdx.y + i][threadIdx.x + j];
                 float al = __fmul_rn(fabsf(__fsub_rn(v, c)), scale);
                 const int idx = (int)al;
@@ -669,7 +675,8 @@ extern "C" int svb_fuse_depth_maps_dev(const float* stereo_dev, const float* con
     k_blend<<<grid, 128, 0, s>>>(a, H, W, g, fused, fs);
     k_bilat_lut<<<B, 256, 0, s>>>(fs, bt.gc, 10.0f);
     dim3 bgrid(svb_ceil_div(W, BT_X), svb_ceil_div(H, BT_Y), B);
-    k_bilateral<<<bgrid, dim3(BT_X, BT_Y), 0, s>>>(fused, H, W, bt, fs, out_u8_dev, out_f32_dev, 1);
+    if (bt.d == 9) k_bilateral<9><<<bgrid, dim3(BT_X, BT_Y), 0, s>>>(fused, H, W, bt, fs, out_u8_dev, out_f32_dev, 1);
+    else k_bilateral<0><<<bgrid, dim3(BT_X, BT_Y), 0, s>>>(fused, H, W, bt, fs, out_u8_dev, out_f32_dev, 1);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }
@@ -861,8 +868,9 @@ extern "C" int svb_bilateral_f32_dev(const float* src_dev, int B, int H, int W, 
     const int nb = (int)min((size_t)svb_ceil_div(148 * 8, B), (n + 1023) / 1024);
     k_minmax_f32<<<dim3(max(nb, 1), B), 256, 0, s>>>(src_dev, n, fs);
     k_bilat_lut<<<B, 256, 0, s>>>(fs, bt.gc, -FLT_MAX);
-    k_bilateral<<<dim3(svb_ceil_div(W, BT_X), svb_ceil_div(H, BT_Y), B), dim3(BT_X, BT_Y), 0, s>>>(
-        src_dev, H, W, bt, fs, nullptr, dst_dev, 0);
+    const dim3 bgrid(svb_ceil_div(W, BT_X), svb_ceil_div(H, BT_Y), B);
+    if (d == 9) k_bilateral<9><<<bgrid, dim3(BT_X, BT_Y), 0, s>>>(src_dev, H, W, bt, fs, nullptr, dst_dev, 0);
+    else k_bilateral<0><<<bgrid, dim3(BT_X, BT_Y), 0, s>>>(src_dev, H, W, bt, fs, nullptr, dst_dev, 0);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

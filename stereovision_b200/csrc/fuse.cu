@@ -452,18 +452,29 @@ __device__ __forceinline__ int reflect101(int i, int n)
     return i;
 }
 
-__global__ void k_fill_rows(const float* __restrict__ conf, int H, int W, float wm, GaussTaps g, float* __restrict__ tmp)
+// Horizontal pass of the confidence blur.  A block owns FR_T consecutive columns of one row: it stages v = (1 - conf) * wm for
+// them and their k - 1 neighbours (reflect-101 applied here, once per staged value) in shared memory; every thread then runs
+// its k taps from there in cv2's order.  K: the kernel size as a compile-time constant (0 = g.k): taps unrolled, weights as
+// constant-bank operands (instances for 15 -- the reference's midas_blend_radius is used as the kernel size -- and 31).
+#define FR_T 128
+template <int K>
+__global__ void __launch_bounds__(FR_T) k_fill_rows(const float* __restrict__ conf, int H, int W, float wm, GaussTaps g,
+                                                    float* __restrict__ tmp)
 {
-    const int b = blockIdx.z, y = blockIdx.y, x = blockIdx.x * blockDim.x + threadIdx.x;
-    if (x >= W) return;
+    __shared__ float sv[FR_T + FUSE_MAXK - 1];
+    const int k = K ? K : g.k, r = k / 2;
+    const int b = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * FR_T;
     const float* row = conf + ((size_t)b * H + y) * W;
-    const int r = g.k / 2;
-    float s = 0.f;
-    for (int i = 0; i < g.k; ++i) {
-        const float c = row[reflect101(x - r + i, W)];
-        const float v = __fmul_rn(__fsub_rn(1.0f, c), wm);
-        s = i == 0 ? __fmul_rn(g.w[0], v) : __fadd_rn(s, __fmul_rn(g.w[i], v));
+    for (int i = threadIdx.x; i < FR_T + 2 * r; i += FR_T) {
+        const int xx = min(x0 - r + i, W - 1 + r);           // (columns past the row's last tap are never used)
+        sv[i] = __fmul_rn(__fsub_rn(1.0f, row[reflect101(xx, W)]), wm);
     }
+    __syncthreads();
+    const int x = x0 + threadIdx.x;
+    if (x >= W) return;
+    float s = __fmul_rn(g.w[0], sv[threadIdx.x]);
+#pragma unroll
+    for (int i = 1; i < (K ? K : k); ++i) s = __fadd_rn(s, __fmul_rn(g.w[i], sv[threadIdx.x + i]));
     tmp[((size_t)b * H + y) * W + x] = s;
 }
 
@@ -474,6 +485,8 @@ struct BlendArgs {
     int midas_fill, flow_fill;
 };
 
+// K: as in k_fill_rows; rows whose window lies inside the image walk down the column without the reflection
+template <int K>
 __global__ void k_blend(BlendArgs a, int H, int W, GaussTaps g, float* __restrict__ fused, FuseState* __restrict__ fs)
 {
     const int b = blockIdx.z, y = blockIdx.y, x = blockIdx.x * blockDim.x + threadIdx.x;
@@ -486,11 +499,19 @@ __global__ void k_blend(BlendArgs a, int H, int W, GaussTaps g, float* __restric
             if (a.midas_fill) {
                 const float c = a.conf ? a.conf[i] : 1.0f;
                 if (c < a.thr_conf) {
-                    const int r = g.k / 2;
-                    float s = 0.f;
-                    for (int t = 0; t < g.k; ++t) {
-                        const float v = a.tmp[((size_t)b * H + reflect101(y - r + t, H)) * W + x];
-                        s = t == 0 ? __fmul_rn(g.w[0], v) : __fadd_rn(s, __fmul_rn(g.w[t], v));
+                    const int k = K ? K : g.k, r = k / 2;
+                    float s;
+                    if (y - r >= 0 && y + r < H) {
+                        const float* col = a.tmp + ((size_t)b * H + (y - r)) * W + x;
+                        s = __fmul_rn(g.w[0], col[0]);
+#pragma unroll
+                        for (int t = 1; t < (K ? K : k); ++t) s = __fadd_rn(s, __fmul_rn(g.w[t], col[(size_t)t * W]));
+                    } else {
+                        s = 0.f;
+                        for (int t = 0; t < k; ++t) {
+                            const float v = a.tmp[((size_t)b * H + reflect101(y - r + t, H)) * W + x];
+                            s = t == 0 ? __fmul_rn(g.w[0], v) : __fadd_rn(s, __fmul_rn(g.w[t], v));
+                        }
                     }
                     const float fw = fminf(fmaxf(s, 0.0f), 1.0f);
                     if (fw > 0.1f)
@@ -669,10 +690,14 @@ extern "C" int svb_fuse_depth_maps_dev(const float* stereo_dev, const float* con
     dim3 grid(svb_ceil_div(W, 128), H, B);
     if (a.midas_fill) {
         const float* c = conf_dev;
-        if (c) k_fill_rows<<<grid, 128, 0, s>>>(c, H, W, (float)p->midas_fill_weight, g, tmp);
+        if (c && g.k == 15) k_fill_rows<15><<<grid, FR_T, 0, s>>>(c, H, W, (float)p->midas_fill_weight, g, tmp);
+        else if (c && g.k == 31) k_fill_rows<31><<<grid, FR_T, 0, s>>>(c, H, W, (float)p->midas_fill_weight, g, tmp);
+        else if (c) k_fill_rows<0><<<grid, FR_T, 0, s>>>(c, H, W, (float)p->midas_fill_weight, g, tmp);
         else SVB_CUDA(cudaMemsetAsync(tmp, 0, n * sizeof(float), s));      // conf == 1 everywhere -> weight 0
     }
-    k_blend<<<grid, 128, 0, s>>>(a, H, W, g, fused, fs);
+    if (g.k == 15) k_blend<15><<<grid, 128, 0, s>>>(a, H, W, g, fused, fs);
+    else if (g.k == 31) k_blend<31><<<grid, 128, 0, s>>>(a, H, W, g, fused, fs);
+    else k_blend<0><<<grid, 128, 0, s>>>(a, H, W, g, fused, fs);
     k_bilat_lut<<<B, 256, 0, s>>>(fs, bt.gc, 10.0f);
     dim3 bgrid(svb_ceil_div(W, BT_X), svb_ceil_div(H, BT_Y), B);
     if (bt.d == 9) k_bilateral<9><<<bgrid, dim3(BT_X, BT_Y), 0, s>>>(fused, H, W, bt, fs, out_u8_dev, out_f32_dev, 1);

@@ -87,8 +87,13 @@ __global__ void k_count_gt(const float* __restrict__ m, size_t n, float thr, uns
     const int b = blockIdx.y;
     const float* p = m + (size_t)b * n;
     unsigned c = 0;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        c += p[i] > thr;
+    const size_t n4 = (reinterpret_cast<uintptr_t>(p) & 15) == 0 ? n / 4 : 0, stride = (size_t)gridDim.x * blockDim.x;
+    const size_t t0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (size_t i = t0; i < n4; i += stride) {
+        const float4 a = reinterpret_cast<const float4*>(p)[i];
+        c += (a.x > thr) + (a.y > thr) + (a.z > thr) + (a.w > thr);
+    }
+    for (size_t i = 4 * n4 + t0; i < n; i += stride) c += p[i] > thr;
     c = __reduce_add_sync(0xffffffffu, c);
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(&cnt[b], c);
 }
@@ -119,12 +124,11 @@ __global__ void __launch_bounds__(512) k_sel_hist(SelDesc d0, SelDesc d1, size_t
     __syncthreads();
     const float* v = d.vals + (size_t)b * n;
     const float* m = d.mask ? d.mask + (size_t)b * n : nullptr;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const float x = v[i];
+    auto count = [&](float x, float mv) {
         bool sel = true;
-        if (mode == MASK_GT) sel = m[i] > d.thr;
+        if (mode == MASK_GT) sel = mv > d.thr;
         else if (mode == MASK_SELF_POS) sel = x > 0.0f;
-        if (!sel) continue;
+        if (!sel) return;
         const unsigned k = f2key(x);
         if (PASS == 0) {
             atomicAdd(&sh[0][k >> 21], 1u);
@@ -135,7 +139,20 @@ __global__ void __launch_bounds__(512) k_sel_hist(SelDesc d0, SelDesc d1, size_t
             for (int r = 0; r < SEL_NR; ++r)
                 if (!dup[r] && hi == pre[r]) atomicAdd(&sh[r][dig], 1u);
         }
+    };
+    // 128-bit loads where the image starts on a 16-byte boundary (16 bytes in flight per thread instead of 4: the pass is a
+    // stream over the image and was latency-bound at a third of the HBM rate); the order of the counts does not matter
+    const bool use_m = mode == MASK_GT;
+    const bool al16 = ((reinterpret_cast<uintptr_t>(v) | (use_m ? reinterpret_cast<uintptr_t>(m) : 0)) & 15) == 0;
+    const size_t n4 = al16 ? n / 4 : 0, stride = (size_t)gridDim.x * blockDim.x, t0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    const float4* v4 = reinterpret_cast<const float4*>(v);
+    const float4* m4 = reinterpret_cast<const float4*>(m);
+    for (size_t i = t0; i < n4; i += stride) {
+        const float4 a = v4[i];
+        const float4 q = use_m ? m4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        count(a.x, q.x); count(a.y, q.y); count(a.z, q.z); count(a.w, q.w);
     }
+    for (size_t i = 4 * n4 + t0; i < n; i += stride) count(v[i], use_m ? m[i] : 0.f);
     __syncthreads();
     for (int i = threadIdx.x; i < NH * SEL_BINS; i += blockDim.x) {
         const unsigned c = (&sh[0][0])[i];

@@ -17,12 +17,23 @@
 __global__ void k_norm_conf(const float* __restrict__ disp, size_t n, float lo, float hi, float numD,
                             float c_lo, float c_hi, float* __restrict__ norm, float* __restrict__ conf)
 {
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const float d = disp[i];
+    auto nrm = [&](float d) {
         const float c = fminf(fmaxf(d, lo), hi);
         const float v = __fmul_rn(__fdiv_rn(__fsub_rn(c, lo), numD), 255.0f);
-        norm[i] = (float)(unsigned char)(int)v;
-        conf[i] = (d > c_lo && d < c_hi) ? 1.0f : 0.0f;
+        return (float)(unsigned char)(int)v;
+    };
+    auto cnf = [&](float d) { return (d > c_lo && d < c_hi) ? 1.0f : 0.0f; };
+    const bool al16 = ((reinterpret_cast<uintptr_t>(disp) | reinterpret_cast<uintptr_t>(norm) | reinterpret_cast<uintptr_t>(conf)) & 15) == 0;
+    const size_t n4 = al16 ? n / 4 : 0, stride = (size_t)gridDim.x * blockDim.x, t0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (size_t i = t0; i < n4; i += stride) {
+        const float4 a = reinterpret_cast<const float4*>(disp)[i];
+        reinterpret_cast<float4*>(norm)[i] = make_float4(nrm(a.x), nrm(a.y), nrm(a.z), nrm(a.w));
+        reinterpret_cast<float4*>(conf)[i] = make_float4(cnf(a.x), cnf(a.y), cnf(a.z), cnf(a.w));
+    }
+    for (size_t i = 4 * n4 + t0; i < n; i += stride) {
+        const float d = disp[i];
+        norm[i] = nrm(d);
+        conf[i] = cnf(d);
     }
 }
 
@@ -339,14 +350,18 @@ __global__ void k_range_apply(const float* __restrict__ src, size_t n, const Sel
             mode = 1;
         }
     }
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const float x = p[i];
-        float r;
-        if (mode == 2) r = (float)__dadd_rn(__dmul_rn((double)x, scale), offset);
-        else if (mode == 1) r = __fadd_rn(smin, __fmul_rn(__fdiv_rn(__fsub_rn(x, mmin), den), srng));
-        else r = cst;
-        o[i] = r;
+    auto map = [&](float x) {
+        if (mode == 2) return (float)__dadd_rn(__dmul_rn((double)x, scale), offset);
+        if (mode == 1) return __fadd_rn(smin, __fmul_rn(__fdiv_rn(__fsub_rn(x, mmin), den), srng));
+        return cst;
+    };
+    const bool al16 = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(o)) & 15) == 0;
+    const size_t n4 = al16 ? n / 4 : 0, stride = (size_t)gridDim.x * blockDim.x, t0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (size_t i = t0; i < n4; i += stride) {
+        const float4 a = reinterpret_cast<const float4*>(p)[i];
+        reinterpret_cast<float4*>(o)[i] = make_float4(map(a.x), map(a.y), map(a.z), map(a.w));
     }
+    for (size_t i = 4 * n4 + t0; i < n; i += stride) o[i] = map(p[i]);
 }
 
 extern "C" size_t svb_range_scratch_bytes(int B) { return (size_t)2 * B * sizeof(SelState) + (size_t)B * sizeof(unsigned) + 64; }
@@ -872,7 +887,15 @@ __global__ void k_minmax_f32(const float* __restrict__ src, size_t n, FuseState*
     const int b = blockIdx.y;
     const float* p = src + (size_t)b * n;
     unsigned kmin = 0xffffffffu, kmax = 0;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t n4 = (reinterpret_cast<uintptr_t>(p) & 15) == 0 ? n / 4 : 0, stride = (size_t)gridDim.x * blockDim.x;
+    const size_t t0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (size_t i = t0; i < n4; i += stride) {
+        const float4 a = reinterpret_cast<const float4*>(p)[i];
+        const unsigned k0 = f2key(a.x), k1 = f2key(a.y), k2 = f2key(a.z), k3 = f2key(a.w);
+        kmin = min(min(kmin, k0), min(k1, min(k2, k3)));
+        kmax = max(max(kmax, k0), max(k1, max(k2, k3)));
+    }
+    for (size_t i = 4 * n4 + t0; i < n; i += stride) {
         const unsigned k = f2key(p[i]);
         kmin = min(kmin, k);
         kmax = max(kmax, k);

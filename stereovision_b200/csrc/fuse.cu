@@ -1026,33 +1026,62 @@ extern "C" int svb_midas_upsample_normalize_dev(const float* pred_dev, int B, in
 
 // contrast confidence (fused_depth_map.py:1150-1156): cv2.GaussianBlur(u8, 5x5, sigma 0) is the fixed-point
 // binomial filter (sum w_i w_j p + 128) >> 8 with w = {1,4,6,4,1} and BORDER_REFLECT_101
-constexpr int CC_X = 64, CC_Y = 8;
-__global__ void __launch_bounds__(CC_X* CC_Y) k_contrast_u8(const unsigned char* __restrict__ gray, int H, int W,
-                                                             unsigned char* __restrict__ contrast, FuseState* __restrict__ fs)
+// Four pixels per thread: the tile starts four columns left of the block so that every thread reads its 12-byte window as three
+// aligned words; the horizontal taps of a row are two dp4a per pixel on byte windows cut out with PRMT, the contrast bytes leave
+// as one 32-bit store.  Interior blocks fill the tile with 32-bit loads, border blocks byte by byte through the reflection.
+constexpr int CC_X = 128, CC_Y = 8, CC_TW = CC_X / 4 + 2;     // tile: CC_Y + 4 rows of CC_TW words (pixels x0 - 4 .. x0 + CC_X + 3)
+__global__ void __launch_bounds__(CC_X / 4 * CC_Y) k_contrast_u8(const unsigned char* __restrict__ gray, int H, int W,
+                                                                 unsigned char* __restrict__ contrast, FuseState* __restrict__ fs)
 {
-    __shared__ unsigned char tile[CC_Y + 4][CC_X + 4];
+    __shared__ uint32_t tile[CC_Y + 4][CC_TW];
     const int b = blockIdx.z, x0 = blockIdx.x * CC_X, y0 = blockIdx.y * CC_Y;
     const unsigned char* img = gray + (size_t)b * H * W;
-    const int tid = threadIdx.y * CC_X + threadIdx.x;
-    for (int i = tid; i < (CC_Y + 4) * (CC_X + 4); i += CC_X * CC_Y) {
-        const int ty = i / (CC_X + 4), tx = i - ty * (CC_X + 4);
-        tile[ty][tx] = img[(size_t)reflect101(y0 + ty - 2, H) * W + reflect101(x0 + tx - 2, W)];
+    const int tid = threadIdx.y * (CC_X / 4) + threadIdx.x;
+    const bool words = (W & 3) == 0 && (reinterpret_cast<uintptr_t>(img) & 3) == 0 && x0 >= 4 && x0 + CC_X + 4 <= W &&
+                       y0 >= 2 && y0 + CC_Y + 2 <= H;
+    for (int i = tid; i < (CC_Y + 4) * CC_TW; i += CC_X / 4 * CC_Y) {
+        const int ty = i / CC_TW, tw = i - ty * CC_TW;
+        uint32_t v;
+        if (words) {
+            v = *reinterpret_cast<const uint32_t*>(img + (size_t)(y0 + ty - 2) * W + x0 - 4 + 4 * tw);
+        } else {
+            const unsigned char* row = img + (size_t)reflect101(y0 + ty - 2, H) * W;
+            v = 0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) v |= (uint32_t)row[reflect101(min(x0 - 4 + 4 * tw + q, W + 1), W)] << (8 * q);
+        }
+        tile[ty][tw] = v;
     }
     __syncthreads();
-    const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
-    unsigned c = 0, cmin = 255, cmax = 0;
+    const int x = x0 + 4 * threadIdx.x, y = y0 + threadIdx.y;
+    unsigned cmin = 255, cmax = 0;
     if (x < W && y < H) {
-        unsigned s = 0;
+        unsigned s[4] = {0u, 0u, 0u, 0u};
+        uint32_t centre = 0;
 #pragma unroll
         for (int i = 0; i < 5; ++i) {
-            const unsigned char* t = &tile[threadIdx.y + i][threadIdx.x];
-            const unsigned r = t[0] + 4u * t[1] + 6u * t[2] + 4u * t[3] + t[4];
-            s += r * (i == 0 || i == 4 ? 1u : i == 2 ? 6u : 4u);
+            const uint32_t a = tile[threadIdx.y + i][threadIdx.x], m = tile[threadIdx.y + i][threadIdx.x + 1],
+                           c = tile[threadIdx.y + i][threadIdx.x + 2];
+            // byte k of win[j] = pixel x + j - 2 + k
+            const uint32_t win[5] = {__byte_perm(a, m, 0x5432), __byte_perm(a, m, 0x6543), m, __byte_perm(m, c, 0x4321),
+                                     __byte_perm(m, c, 0x5432)};
+            const unsigned wv = i == 0 || i == 4 ? 1u : i == 2 ? 6u : 4u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) s[j] += wv * __dp4a(win[j + 1], 0x01000000u, __dp4a(win[j], 0x04060401u, 0u));
+            if (i == 2) centre = m;
         }
-        const int blur = (int)((s + 128u) >> 8), g = tile[threadIdx.y + 2][threadIdx.x + 2];
-        c = (unsigned)abs(g - blur);
-        contrast[((size_t)b * H + y) * W + x] = (unsigned char)c;
-        cmin = cmax = c;
+        uint32_t out = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int blur = (int)((s[j] + 128u) >> 8), g = (int)((centre >> (8 * j)) & 0xffu);
+            const unsigned c = (unsigned)abs(g - blur);
+            out |= c << (8 * j);
+            if (x + j < W) { cmin = min(cmin, c); cmax = max(cmax, c); }
+        }
+        unsigned char* dst = contrast + ((size_t)b * H + y) * W + x;
+        if (x + 3 < W && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) *reinterpret_cast<uint32_t*>(dst) = out;
+        else
+            for (int j = 0; j < 4 && x + j < W; ++j) dst[j] = (unsigned char)(out >> (8 * j));
     }
     cmin = __reduce_min_sync(0xffffffffu, cmin);
     cmax = __reduce_max_sync(0xffffffffu, cmax);
@@ -1075,7 +1104,18 @@ __global__ void k_contrast_norm(unsigned char* __restrict__ data, size_t n, cons
         lut[i] = (unsigned char)min(max(__float2int_rn(__fadd_rn(__fmul_rn((float)i, fsc), fsh)), 0), 255);
     __syncthreads();
     unsigned char* p = data + (size_t)b * n;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = lut[p[i]];
+    const size_t n16 = (reinterpret_cast<uintptr_t>(p) & 15) == 0 ? n / 16 : 0, stride = (size_t)gridDim.x * blockDim.x;
+    const size_t t0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (size_t i = t0; i < n16; i += stride) {             // 16 pixels per thread and access
+        uint4 v = reinterpret_cast<uint4*>(p)[i];
+        uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            w[q] = (uint32_t)lut[w[q] & 0xffu] | ((uint32_t)lut[(w[q] >> 8) & 0xffu] << 8) |
+                   ((uint32_t)lut[(w[q] >> 16) & 0xffu] << 16) | ((uint32_t)lut[w[q] >> 24] << 24);
+        reinterpret_cast<uint4*>(p)[i] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    for (size_t i = 16 * n16 + t0; i < n; i += stride) p[i] = lut[p[i]];
 }
 
 extern "C" int svb_contrast_confidence_u8_dev(const uint8_t* gray_dev, int B, int H, int W, uint8_t* conf_dev, void* scratch_dev,
@@ -1089,7 +1129,7 @@ extern "C" int svb_contrast_confidence_u8_dev(const uint8_t* gray_dev, int B, in
     cudaStream_t s = (cudaStream_t)stream;
     FuseState* fs = (FuseState*)(((uintptr_t)scratch_dev + 127) & ~(uintptr_t)127);
     k_fuse_init<<<svb_ceil_div(B, 128), 128, 0, s>>>(fs, B);
-    k_contrast_u8<<<dim3(svb_ceil_div(W, CC_X), svb_ceil_div(H, CC_Y), B), dim3(CC_X, CC_Y), 0, s>>>(gray_dev, H, W, conf_dev, fs);
+    k_contrast_u8<<<dim3(svb_ceil_div(W, CC_X), svb_ceil_div(H, CC_Y), B), dim3(CC_X / 4, CC_Y), 0, s>>>(gray_dev, H, W, conf_dev, fs);
     const size_t n = (size_t)H * W;
     const int nb = (int)min((size_t)svb_ceil_div(148 * 8, B), (n + 1023) / 1024);
     k_contrast_norm<<<dim3(max(nb, 1), B), 256, 0, s>>>(conf_dev, n, fs);

@@ -510,6 +510,29 @@ __global__ void __launch_bounds__(FR_T) k_fill_rows(const float* __restrict__ co
     tmp[((size_t)b * H + y) * W + x] = s;
 }
 
+// Per-image running min / max (ordered keys) from a whole block.  The target only moves one way, so a value that cannot
+// improve the current one (a plain L2 read, possibly stale -- safe for a monotone target) skips its atomic.  ONE thread per
+// block does that read: with one per warp, the half a million warps of a call all read the same two words of one L2 slice
+// and every block's last step queued behind them.  Call from all threads of the block.
+__device__ __forceinline__ void block_minmax_update(unsigned kmin, unsigned kmax, unsigned* gmin, unsigned* gmax)
+{
+    __shared__ unsigned s_mn[32], s_mx[32];
+    const int tid = (threadIdx.z * blockDim.y + threadIdx.y) * blockDim.x + threadIdx.x;
+    const int nw = (blockDim.x * blockDim.y * blockDim.z + 31) >> 5;
+    kmin = __reduce_min_sync(0xffffffffu, kmin);
+    kmax = __reduce_max_sync(0xffffffffu, kmax);
+    if ((tid & 31) == 0) { s_mn[tid >> 5] = kmin; s_mx[tid >> 5] = kmax; }
+    __syncthreads();
+    if (tid < 32) {
+        kmin = __reduce_min_sync(0xffffffffu, tid < nw ? s_mn[tid] : 0xffffffffu);
+        kmax = __reduce_max_sync(0xffffffffu, tid < nw ? s_mx[tid] : 0u);
+        if (tid == 0) {
+            if (kmin < __ldcg(gmin)) atomicMin(gmin, kmin);
+            if (kmax > __ldcg(gmax)) atomicMax(gmax, kmax);
+        }
+    }
+}
+
 struct BlendArgs {
     const float* stereo; const float* conf; const float* midas; const float* flow; const float* tmp;
     float ws, thr_conf, hole, wf, wf1;   // wf1 = (float)(1 - w_flow)
@@ -560,15 +583,8 @@ __global__ void k_blend(BlendArgs a, int H, int W, GaussTaps g, float* __restric
         fused[i] = f;
         kmin = kmax = f2key(f);
     }
-    kmin = __reduce_min_sync(0xffffffffu, kmin);
-    kmax = __reduce_max_sync(0xffffffffu, kmax);
-    if ((threadIdx.x & 31) == 0) {
-        // min / max only ever move one way: a warp whose value cannot improve the current one (a plain L2 read, possibly
-        // stale, which is safe for a monotone target) skips the atomic -- half a million same-address atomics per call
-        // had made this kernel latency-bound (ncu: 8.7 % issue-active at 410 GB/s)
-        if (kmin != 0xffffffffu && kmin < __ldcg(&fs[b].kmin)) atomicMin(&fs[b].kmin, kmin);
-        if (kmax && kmax > __ldcg(&fs[b].kmax)) atomicMax(&fs[b].kmax, kmax);
-    }
+    // (half a million same-address atomics per call had made this kernel latency-bound: ncu 8.7 % issue-active at 410 GB/s)
+    block_minmax_update(kmin, kmax, &fs[b].kmin, &fs[b].kmax);
 }
 
 __global__ void k_fuse_init(FuseState* fs, int B)
@@ -957,36 +973,59 @@ __device__ __forceinline__ void cubic_coeffs(float t, float (&w)[4])
 __global__ void __launch_bounds__(256) k_resize_bicubic(const float* __restrict__ src, int Hi, int Wi, float* __restrict__ dst,
                                                         int Ho, int Wo, float sy, float sx, FuseState* __restrict__ fs)
 {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+    // A block writes 256 columns of one output row: its taps come from four source rows and, when upsampling, a few dozen source
+    // columns -- staged (already clamped) in shared memory, so that the sixteen taps of a pixel are shared-memory loads instead
+    // of dependent gathers from L2.  Wider source ranges (downsampling) keep the direct path.
+    constexpr int TW = 320;
+    __shared__ float tile[4][TW];
+    const int x0 = blockIdx.x * blockDim.x, x = x0 + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+    const float* img = src + (size_t)b * Hi * Wi;
+    const float fy = __fsub_rn(__fmul_rn((float)y + 0.5f, sy), 0.5f);
+    const float fly = floorf(fy);
+    const int iy = (int)fly;
+    const int xl = min(x0 + (int)blockDim.x, Wo) - 1;            // last output column of the block
+    const int first = (int)floorf(__fsub_rn(__fmul_rn((float)x0 + 0.5f, sx), 0.5f)) - 1;
+    const int ncols = (int)floorf(__fsub_rn(__fmul_rn((float)xl + 0.5f, sx), 0.5f)) + 2 - first + 1;
+    const bool staged = ncols <= TW;
+    if (staged) {
+        for (int i = threadIdx.x; i < 4 * ncols; i += blockDim.x) {
+            const int a = i / ncols, j = i - a * ncols;
+            tile[a][j] = img[(size_t)min(max(iy - 1 + a, 0), Hi - 1) * Wi + min(max(first + j, 0), Wi - 1)];
+        }
+        __syncthreads();
+    }
     unsigned kmin = 0xffffffffu, kmax = 0;
     if (x < Wo) {
-        const float fy = __fsub_rn(__fmul_rn((float)y + 0.5f, sy), 0.5f), fx = __fsub_rn(__fmul_rn((float)x + 0.5f, sx), 0.5f);
-        const float fly = floorf(fy), flx = floorf(fx);
-        const int iy = (int)fly, ix = (int)flx;
+        const float fx = __fsub_rn(__fmul_rn((float)x + 0.5f, sx), 0.5f);
+        const float flx = floorf(fx);
+        const int ix = (int)flx;
         float wy[4], wx[4];
         cubic_coeffs(fy - fly, wy);
         cubic_coeffs(fx - flx, wx);
-        const float* img = src + (size_t)b * Hi * Wi;
         float acc = 0.f;
+        if (staged) {
+            const int j0 = ix - 1 - first;
 #pragma unroll
-        for (int a = 0; a < 4; ++a) {
-            const float* row = img + (size_t)min(max(iy - 1 + a, 0), Hi - 1) * Wi;
-            float r = 0.f;
+            for (int a = 0; a < 4; ++a) {
+                float r = 0.f;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) r += row[min(max(ix - 1 + c, 0), Wi - 1)] * wx[c];
-            acc += r * wy[a];
+                for (int c = 0; c < 4; ++c) r += tile[a][j0 + c] * wx[c];
+                acc += r * wy[a];
+            }
+        } else {
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const float* row = img + (size_t)min(max(iy - 1 + a, 0), Hi - 1) * Wi;
+                float r = 0.f;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) r += row[min(max(ix - 1 + c, 0), Wi - 1)] * wx[c];
+                acc += r * wy[a];
+            }
         }
         dst[((size_t)b * Ho + y) * Wo + x] = acc;
         kmin = kmax = f2key(acc);
     }
-    if (fs) {
-        kmin = __reduce_min_sync(0xffffffffu, kmin);
-        kmax = __reduce_max_sync(0xffffffffu, kmax);
-        if ((threadIdx.x & 31) == 0) {
-            if (kmin != 0xffffffffu && kmin < __ldcg(&fs[b].kmin)) atomicMin(&fs[b].kmin, kmin);
-            if (kmax && kmax > __ldcg(&fs[b].kmax)) atomicMax(&fs[b].kmax, kmax);
-        }
-    }
+    if (fs) block_minmax_update(kmin, kmax, &fs[b].kmin, &fs[b].kmax);
 }
 
 // (x - min) / (max - min + 1e-8) * 255 in float32, zeros when max - min < 1e-6 (fused_depth_map.py:1138-1145)
@@ -998,8 +1037,14 @@ __global__ void k_minmax_scale255(float* __restrict__ data, size_t n, const Fuse
     const bool flat = len < 1e-6f;
     const float den = __fadd_rn(len, 1e-8f);
     float* p = data + (size_t)b * n;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        p[i] = flat ? 0.0f : __fmul_rn(__fdiv_rn(__fsub_rn(p[i], mn), den), 255.0f);
+    auto sc = [&](float v) { return flat ? 0.0f : __fmul_rn(__fdiv_rn(__fsub_rn(v, mn), den), 255.0f); };
+    const size_t n4 = (reinterpret_cast<uintptr_t>(p) & 15) == 0 ? n / 4 : 0, stride = (size_t)gridDim.x * blockDim.x;
+    const size_t t0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (size_t i = t0; i < n4; i += stride) {
+        const float4 a = reinterpret_cast<float4*>(p)[i];
+        reinterpret_cast<float4*>(p)[i] = make_float4(sc(a.x), sc(a.y), sc(a.z), sc(a.w));
+    }
+    for (size_t i = 4 * n4 + t0; i < n; i += stride) p[i] = sc(p[i]);
 }
 
 extern "C" size_t svb_midas_scratch_bytes(int B) { return (size_t)B * sizeof(FuseState) + 256; }
@@ -1083,12 +1128,7 @@ __global__ void __launch_bounds__(CC_X / 4 * CC_Y) k_contrast_u8(const unsigned 
         else
             for (int j = 0; j < 4 && x + j < W; ++j) dst[j] = (unsigned char)(out >> (8 * j));
     }
-    cmin = __reduce_min_sync(0xffffffffu, cmin);
-    cmax = __reduce_max_sync(0xffffffffu, cmax);
-    if ((tid & 31) == 0) {
-        if (cmin < __ldcg(&fs[b].kmin)) atomicMin(&fs[b].kmin, cmin);
-        if (cmax > __ldcg(&fs[b].kmax)) atomicMax(&fs[b].kmax, cmax);
-    }
+    block_minmax_update(cmin, cmax, &fs[b].kmin, &fs[b].kmax);
 }
 
 // cv2.normalize(c, None, 0, 1, NORM_MINMAX) on CV_8U: scale = 1 / (max - min) (0 for a flat image),

@@ -790,15 +790,30 @@ __global__ void __launch_bounds__(256) k_occ_blocks(const unsigned char* __restr
 
 __global__ void __launch_bounds__(256) k_occ_hist(const unsigned char* __restrict__ gray, size_t n, unsigned* __restrict__ hist)
 {
-    __shared__ unsigned sh[256];
-    const int b = blockIdx.y;
-    sh[threadIdx.x] = 0;
+    __shared__ unsigned sh[8][256];                          // one histogram per warp: an eighth of the same-bin collisions
+    const int b = blockIdx.y, wp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 8 * 256; i += 256) (&sh[0][0])[i] = 0;
     __syncthreads();
     const unsigned char* p = gray + (size_t)b * n;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        atomicAdd(&sh[p[i]], 1u);
+    const size_t n16 = (reinterpret_cast<uintptr_t>(p) & 15) == 0 ? n / 16 : 0, stride = (size_t)gridDim.x * blockDim.x;
+    const size_t t0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (size_t i = t0; i < n16; i += stride) {              // 16 pixels per load
+        const uint4 v = reinterpret_cast<const uint4*>(p)[i];
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            atomicAdd(&sh[wp][w[q] & 0xffu], 1u);
+            atomicAdd(&sh[wp][(w[q] >> 8) & 0xffu], 1u);
+            atomicAdd(&sh[wp][(w[q] >> 16) & 0xffu], 1u);
+            atomicAdd(&sh[wp][w[q] >> 24], 1u);
+        }
+    }
+    for (size_t i = 16 * n16 + t0; i < n; i += stride) atomicAdd(&sh[wp][p[i]], 1u);
     __syncthreads();
-    if (sh[threadIdx.x]) atomicAdd(&hist[b * 256 + threadIdx.x], sh[threadIdx.x]);
+    unsigned c = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) c += sh[q][threadIdx.x];
+    if (c) atomicAdd(&hist[b * 256 + threadIdx.x], c);
 }
 
 __device__ double block_sum_256(double v, double* red)

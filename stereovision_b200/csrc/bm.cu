@@ -555,6 +555,9 @@ extern "C" int svb_bm_last_launches(const svb_bm_t* h) { return h ? h->launches 
 #define BMG_PC 128                         // window columns per strip: BMG_NP passes of 4 per warp
 #endif
 #define BMG_NP (BMG_PC / (4 * BMG_WARPS))
+#ifndef BMG_MAXSEG
+#define BMG_MAXSEG 16            // most row segments per image
+#endif
 #ifndef BMG_STAGE
 #define BMG_STAGE 1              // right descriptors of the strip staged in a shared-memory ring of blockSize + 2 rows
 #endif
@@ -762,10 +765,18 @@ static int bm2g_launch(const BmGeo& g, const uint8_t* lp, const uint32_t* rdesc,
     const int ocmax = BMG_PC - 2 * g.r, groups = 4 * BMG_WARPS, ocr = ocmax / groups * groups;
     const int OC = ocr >= groups && ocmax - ocr <= groups / 8 ? ocr : ocmax;
     const int bs = 2 * g.r + 1, nstrips = svb_ceil_div(g.width1, OC), rows = g.H - 2 * g.r;
-    int nsegs = 1;
-    while ((long long)nstrips * nb * nsegs < 4LL * num_sms && rows / (nsegs * 2) >= 4 * bs) nsegs *= 2;
-    const int rseg = svb_ceil_div(rows, nsegs);
-    nsegs = svb_ceil_div(rows, rseg);
+    // row segments by waves x rows per CTA (two CTAs of 512 threads per SM), as for the SGBM cost kernel
+    int nsegs = 1, rseg = rows;
+    {
+        const long long slots = 2LL * num_sms, base = (long long)nstrips * nb;
+        const int maxseg = std::max(1, std::min(BMG_MAXSEG, rows / (4 * bs)));
+        long long best = 0;
+        for (int n = 1; n <= maxseg; ++n) {
+            const int rs = svb_ceil_div(rows, n), nsg = svb_ceil_div(rows, rs);
+            const long long cost = ((base * nsg + slots - 1) / slots) * (rs + bs - 1 + 6);
+            if (n == 1 || cost < best) { best = cost; rseg = rs; nsegs = nsg; }
+        }
+    }
     const size_t smem = ((size_t)2 * BMG_PC + 4 * BMG_WARPS) * 32 * 4 + (BMG_STAGE ? (size_t)(bs + 2) * 4 * BMG_NWP * 4 : 0);
     if (cost) {
         SVB_CUDA(cudaFuncSetAttribute(k_bm2g<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
